@@ -1,0 +1,142 @@
+/*
+ * lazzaro_b200 — C-ABI of the B200-native memory hot path (liblazzaro_b200.so).
+ *
+ * The reference (thelaycon/lazzaro) is pure Python; the only native code on its hot path is the
+ * third-party `lancedb` engine reached through pyo3.  This header is what a binding for that path
+ * binds instead: plain C symbols, raw DEVICE pointers and sizes, an explicit CUDA stream, an `int`
+ * status (0 = ok, < 0 = error; text from lz_last_error()).  No exceptions cross the boundary and no
+ * call synchronises the device unless its comment says so.  Unless stated otherwise every pointer
+ * is a device pointer owned by the caller, `stream` is a `cudaStream_t` passed as `void*`, and work
+ * is enqueued on that stream.
+ *
+ * Citations are to /root/reference/src/lazzaro/ (the interface each entry point stands behind).
+ * INTEGRATION.md shows the ctypes binding and how the Python `Store` mirror calls these.
+ *
+ * Conventions
+ *   rows      float32 [n, ld] row-major, `dim` used floats per row, dim % 4 == 0, ld % 4 == 0, base 16-B aligned
+ *   norms     float64 [n]  Euclidean norm of each row (lz_row_norms)
+ *   tags      int32   [n]  owner tag of each row (the store's user index); tag < 0 = deleted row
+ *   metric    LZ_COSINE: score = x.q/(|x||q|), 0 when |x||q| == 0, best = largest
+ *             LZ_L2    : score = sum (x-q)^2, best = smallest
+ *   ordering  best score first, ties by ascending row index; NaN scores are never returned
+ */
+#ifndef LAZZARO_B200_H
+#define LAZZARO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LZ_OK            0
+#define LZ_ERR_ARG      -1   /* bad argument (size, alignment, unsupported k/dim) */
+#define LZ_ERR_CUDA     -2   /* a CUDA runtime call failed */
+#define LZ_ERR_SCRATCH  -3   /* scratch buffer too small */
+#define LZ_ERR_DEVICE   -4   /* not an sm_100 device */
+
+#define LZ_COSINE 0
+#define LZ_L2     1
+
+#define LZ_MAX_K          1024  /* largest top-k a search call accepts */
+#define LZ_MAX_GROUP      4     /* most queries that share one pass over the rows in lz_search_exact */
+
+/* Library version (major*10000 + minor*100 + patch). Host only. */
+int lz_version(void);
+
+/* Text of the calling thread's last error ("" if none). Host only; the pointer stays valid until
+ * the thread's next failing call. */
+const char* lz_last_error(void);
+
+/* Checks that the current device is sm_100 and returns its SM count in *sm_count. Host only.
+ * The kernels are built for sm_100a only: every compute entry point fails with LZ_ERR_DEVICE /
+ * LZ_ERR_CUDA on anything else — there is no CPU or generic-GPU fallback. */
+int lz_device_info(int* sm_count, int* cc_major, int* cc_minor);
+
+/* ---- row ingest (stands behind LanceDBStore.add_nodes, core/vector_store.py:89-112) ------------ */
+
+/* norms[i] = sqrt(sum_j double(rows[i][j])^2), float64.  Precomputed once per added row so that a
+ * search reads each row exactly once (memory_system.py:202 recomputes both norms per pair). */
+int lz_row_norms(const float* rows, int64_t n, int dim, int64_t ld, double* norms, void* stream);
+
+/* ---- exact flat search (stands behind LanceDBStore.search_nodes, core/vector_store.py:132-140,
+ *      and MemorySystem._cosine_similarity, core/memory_system.py:197-203) ----------------------- */
+
+/* Bytes of device scratch lz_search_exact needs for (n_queries, k, n_chunks). */
+size_t lz_search_exact_scratch_bytes(int n_queries, int k, int n_chunks);
+
+/* Suggested n_chunks (CTAs per query group) for a scan of `n_rows` rows by `n_groups` groups on
+ * the current device: a multiple of the SM count when the rows allow it. Host only. */
+int lz_search_exact_default_chunks(int64_t n_rows, int n_groups);
+
+/*
+ * Exhaustive top-k in float64 over float32 rows: one streaming pass over the rows per query group.
+ *
+ * Queries are taken in groups of `group_size` (1..LZ_MAX_GROUP) consecutive queries; a group scans
+ * rows [lo, hi) once for all its queries.  If group_lo/group_hi are NULL every group scans
+ * [row_lo, row_hi); otherwise group g scans [group_lo[g], group_hi[g]) (per-user or per-shard
+ * ranges).  If tags != NULL a row is eligible only when tags[row] >= 0 and, when group_tag != NULL
+ * and group_tag[g] >= 0, tags[row] == group_tag[g]  (the `.where(user_id = ...)` pre-filter of
+ * vector_store.py:137, applied BEFORE the top-k).
+ *
+ *   queries    float32 [n_queries, q_ld]
+ *   out_ids    int64   [n_queries, k]   row indices, -1 padded
+ *   out_scores float64 [n_queries, k]   cosine similarity or squared L2 distance, NaN padded
+ *   out_counts int32   [n_queries]      number of valid entries per query (<= k)
+ *   scratch    >= lz_search_exact_scratch_bytes(n_queries, k, n_chunks) bytes; contents are
+ *              overwritten; concurrent calls must not share it
+ *   norms      may be NULL for LZ_L2
+ */
+int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
+                    int64_t row_lo, int64_t row_hi,
+                    const int64_t* group_lo, const int64_t* group_hi, const int32_t* group_tag,
+                    const float* queries, int64_t q_ld, int n_queries, int group_size,
+                    int k, int metric, int n_chunks,
+                    void* scratch, size_t scratch_bytes,
+                    int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
+
+/* Merge `n_lists` per-partition top-k lists per query into one (the all-gather merge of the
+ * multi-GPU search; ids are global row ids).  in_ids int64 [n_lists, n_queries, k] (-1 = empty
+ * slot), in_scores float64 same shape; outputs as lz_search_exact.  Uses no scratch. */
+int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,
+                  int metric, int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
+
+/* Exact float64 scores of explicit (query, row) pairs — the rescoring step after a coarse pass and
+ * the pairwise cosine of memory_system.py:197-203.  pair_q int32 [n_pairs], pair_row int64
+ * [n_pairs] (row < 0 gives NaN); out float64 [n_pairs]. */
+int lz_score_pairs(const float* rows, int64_t ld, int dim, const double* norms,
+                   const float* queries, int64_t q_ld, const int32_t* pair_q, const int64_t* pair_row,
+                   int64_t n_pairs, int metric, double* out_scores, void* stream);
+
+/* ---- biological decay and pruning (stands behind MemoryShard.apply_temporal_decay and
+ *      MemoryShard.prune_weak_edges, core/memory_shard.py:64-84; fan-out core/buffer_graph.py:87-97) */
+
+/* Bytes of device scratch lz_edge_decay_prune needs for n edges. */
+size_t lz_edge_decay_prune_scratch_bytes(int64_t n);
+
+/*
+ * One fused sweep over the edge table (struct of arrays): w' = float32(double(w) * factor)
+ * (memory_shard.py:69-70 with factor = (1-decay_rate)^sweeps), drop edges with double(w)*factor <
+ * threshold (strict, memory_shard.py:81), and compact the survivors stably (their order is kept,
+ * as dict order is in the reference).  Outputs may alias the inputs (in-place compaction).
+ *   src,dst,cooc int32 [n]; weight float32 [n]; out_* same types, capacity >= n
+ *   out_kept     int64 [1] device: number of surviving edges (pruned = n - kept)
+ *   scratch      >= lz_edge_decay_prune_scratch_bytes(n); cleared by the call itself
+ */
+int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* weight, const int32_t* cooc,
+                        int64_t n, double factor, double threshold,
+                        int32_t* out_src, int32_t* out_dst, float* out_weight, int32_t* out_cooc,
+                        int64_t* out_kept, void* scratch, size_t scratch_bytes, void* stream);
+
+/* Decay only: weight[i] = float32(double(weight[i]) * factor) in place (memory_shard.py:69-70). */
+int lz_edge_decay(float* weight, int64_t n, double factor, void* stream);
+
+/* Node salience decay in place (memory_shard.py:72-77):
+ * s = s > floor ? floor + (s - floor) * (1 - rate) : floor, computed in float64, stored float32. */
+int lz_salience_decay(float* salience, int64_t n, double rate, double floor, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LAZZARO_B200_H */

@@ -1,0 +1,275 @@
+// K7: biological decay + threshold prune over the edge table (struct of arrays), one pass.
+//
+// Stands behind MemoryShard.apply_temporal_decay / prune_weak_edges (core/memory_shard.py:64-84).
+// HBM-bound integer/float streaming: 16 B read per edge (src, dst, weight, co_occurrence as four
+// 128-bit loads per 8 edges and thread) + 16 B written per surviving edge.  Survivors are compacted
+// stably in a single pass: per-thread flags -> warp ballot/shuffle scan -> block scan -> decoupled
+// look-back across tiles (tile order taken from an atomic ticket so a tile never waits on one that
+// has not started).  Survivors are staged in shared memory and written back coalesced.
+#include "lz_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kItems = 8;                       // edges per thread (two 128-bit loads per array)
+constexpr int kTile = kThreads * kItems;        // 2048 edges per tile
+
+constexpr u64 kFlagAgg = 1ull << 62;            // tile aggregate published
+constexpr u64 kFlagPrefix = 2ull << 62;         // inclusive prefix published
+constexpr u64 kValueMask = (1ull << 62) - 1;
+
+__device__ __forceinline__ u64 ld_state(const u64* p) {
+    u64 v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_state(u64* p, u64 v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Coherent (not .nc) streaming load: outputs may alias inputs, so the read-only path is off limits.
+__device__ __forceinline__ int4 ld_stream_i4(const void* p) {
+    int4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.s32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+
+struct PruneParams {
+    const int32_t* src; const int32_t* dst; const float* w; const int32_t* cooc;
+    int32_t* o_src; int32_t* o_dst; float* o_w; int32_t* o_cooc;
+    int64_t n; double factor; double thr;
+    u64* state;        // [n_tiles] look-back words, zeroed before launch
+    u32* ticket;       // zeroed before launch
+    int64_t* out_kept;
+    int n_tiles;
+};
+
+__global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
+    __shared__ int s_src[kTile];
+    __shared__ int s_dst[kTile];
+    __shared__ float s_w[kTile];
+    __shared__ int s_cooc[kTile];
+    __shared__ int s_warp[kThreads / 32];
+    __shared__ u32 s_tile;
+    __shared__ long long s_prefix;
+    __shared__ int s_total;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
+    __syncthreads();
+    const int tile = (int)s_tile;
+    const int64_t base = (int64_t)tile * kTile + (int64_t)tid * kItems;
+
+    int v_src[kItems], v_dst[kItems], v_cooc[kItems];
+    float v_w[kItems];
+    if (base + kItems <= p.n) {
+#pragma unroll
+        for (int h = 0; h < kItems / 4; ++h) {
+            int4 a = ld_stream_i4(p.src + base + 4 * h);
+            int4 b = ld_stream_i4(p.dst + base + 4 * h);
+            int4 c = ld_stream_i4(p.w + base + 4 * h);
+            int4 d = ld_stream_i4(p.cooc + base + 4 * h);
+            v_src[4 * h] = a.x; v_src[4 * h + 1] = a.y; v_src[4 * h + 2] = a.z; v_src[4 * h + 3] = a.w;
+            v_dst[4 * h] = b.x; v_dst[4 * h + 1] = b.y; v_dst[4 * h + 2] = b.z; v_dst[4 * h + 3] = b.w;
+            v_w[4 * h] = __int_as_float(c.x); v_w[4 * h + 1] = __int_as_float(c.y);
+            v_w[4 * h + 2] = __int_as_float(c.z); v_w[4 * h + 3] = __int_as_float(c.w);
+            v_cooc[4 * h] = d.x; v_cooc[4 * h + 1] = d.y; v_cooc[4 * h + 2] = d.z; v_cooc[4 * h + 3] = d.w;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            const bool in = base + j < p.n;
+            v_src[j] = in ? p.src[base + j] : 0;
+            v_dst[j] = in ? p.dst[base + j] : 0;
+            v_w[j] = in ? p.w[base + j] : 0.f;
+            v_cooc[j] = in ? p.cooc[base + j] : 0;
+        }
+    }
+    // decay in float64, strict '<' prune in float64, store the float32 rounding
+    unsigned keep = 0;
+    int cnt = 0;
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        const double w64 = (double)v_w[j] * p.factor;
+        const bool k = (base + j < p.n) && !(w64 < p.thr);
+        v_w[j] = (float)w64;
+        keep |= (unsigned)k << j;
+        cnt += k;
+    }
+    // block-wide exclusive scan of cnt
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int ws = lane < kThreads / 32 ? s_warp[lane] : 0;
+        int wi = ws;
+#pragma unroll
+        for (int o = 1; o < kThreads / 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        if (lane < kThreads / 32) s_warp[lane] = wi - ws;       // exclusive warp offsets
+        if (lane == kThreads / 32 - 1) s_total = wi;
+    }
+    __syncthreads();
+    // Tile-local compaction into shared memory.  This consumes every loaded value, so once the
+    // barrier below is passed all global loads of this tile have completed — which is what makes
+    // in-place operation safe: a later tile may overwrite this tile's input range only after it has
+    // seen this tile's published aggregate, and that is published after the barrier.
+    int off = s_warp[warp] + incl - cnt;
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        if (keep >> j & 1) {
+            s_src[off] = v_src[j]; s_dst[off] = v_dst[j]; s_w[off] = v_w[j]; s_cooc[off] = v_cooc[j];
+            ++off;
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        const int total = s_total;
+        // decoupled look-back: publish the aggregate, then walk predecessors 32 at a time
+        long long excl = 0;
+        if (tile == 0) {
+            if (lane == 0) st_state(p.state, kFlagPrefix | (u64)total);
+        } else {
+            if (lane == 0) st_state(p.state + tile, kFlagAgg | (u64)total);
+            int look = tile - 1;
+            while (true) {
+                const int idx = look - lane;
+                u64 st = idx >= 0 ? ld_state(p.state + idx) : kFlagPrefix;     // before tile 0: prefix 0
+                const unsigned empty = __ballot_sync(0xffffffffu, (st >> 62) == 0);
+                if (empty) continue;                                           // someone not published yet
+                const unsigned pref = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                const int first = pref ? __ffs(pref) - 1 : 32;                 // nearest tile with a full prefix
+                long long v = lane <= first ? (long long)(st & kValueMask) : 0;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                excl += v;
+                if (pref) break;
+                look -= 32;
+            }
+            if (lane == 0) st_state(p.state + tile, kFlagPrefix | (u64)(excl + total));
+        }
+        if (lane == 0) {
+            s_prefix = excl;
+            if (tile == p.n_tiles - 1) *p.out_kept = excl + total;
+        }
+    }
+    __syncthreads();
+    const int total = s_total;
+    const int64_t out0 = s_prefix;
+    for (int i = tid; i < total; i += kThreads) {
+        p.o_src[out0 + i] = s_src[i];
+        p.o_dst[out0 + i] = s_dst[i];
+        p.o_w[out0 + i] = s_w[i];
+        p.o_cooc[out0 + i] = s_cooc[i];
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) decay_kernel(float* __restrict__ w, int64_t n, double factor) {
+    const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
+    for (int64_t i = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4; i < n; i += stride) {
+        if (i + 4 <= n) {
+            float4 v = *reinterpret_cast<float4*>(w + i);
+            v.x = (float)((double)v.x * factor); v.y = (float)((double)v.y * factor);
+            v.z = (float)((double)v.z * factor); v.w = (float)((double)v.w * factor);
+            *reinterpret_cast<float4*>(w + i) = v;
+        } else {
+            for (int64_t j = i; j < n; ++j) w[j] = (float)((double)w[j] * factor);
+        }
+    }
+}
+
+__device__ __forceinline__ float salience_step(float s32, double keep, double floor) {
+    const double s = (double)s32;
+    return (float)(s > floor ? floor + (s - floor) * keep : floor);
+}
+
+__global__ void __launch_bounds__(kThreads) salience_kernel(float* __restrict__ s, int64_t n, double keep, double floor) {
+    const int64_t stride = (int64_t)gridDim.x * kThreads * 4;
+    for (int64_t i = ((int64_t)blockIdx.x * kThreads + threadIdx.x) * 4; i < n; i += stride) {
+        if (i + 4 <= n) {
+            float4 v = *reinterpret_cast<float4*>(s + i);
+            v.x = salience_step(v.x, keep, floor); v.y = salience_step(v.y, keep, floor);
+            v.z = salience_step(v.z, keep, floor); v.w = salience_step(v.w, keep, floor);
+            *reinterpret_cast<float4*>(s + i) = v;
+        } else {
+            for (int64_t j = i; j < n; ++j) s[j] = salience_step(s[j], keep, floor);
+        }
+    }
+}
+
+int elementwise_blocks(int64_t n) {
+    const int sms = lz_sm_count();
+    int64_t blocks = (n + kThreads * 4 - 1) / (kThreads * 4);
+    const int64_t cap = (int64_t)(sms > 0 ? sms : 148) * 8;
+    return (int)(blocks < cap ? (blocks < 1 ? 1 : blocks) : cap);
+}
+
+}  // namespace
+
+extern "C" size_t lz_edge_decay_prune_scratch_bytes(int64_t n) {
+    if (n <= 0) return 256;
+    const int64_t tiles = (n + kTile - 1) / kTile;
+    return (size_t)(((tiles + 1) * 8 + 255) & ~255ll);
+}
+
+extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* weight, const int32_t* cooc,
+                                   int64_t n, double factor, double threshold, int32_t* out_src, int32_t* out_dst,
+                                   float* out_weight, int32_t* out_cooc, int64_t* out_kept, void* scratch,
+                                   size_t scratch_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(out_kept != nullptr, "lz_edge_decay_prune: out_kept is NULL");
+    LZ_REQUIRE(n >= 0, "lz_edge_decay_prune: n=%lld", (long long)n);
+    if (n == 0) {
+        LZ_CUDA(cudaMemsetAsync(out_kept, 0, sizeof(int64_t), st));
+        return LZ_OK;
+    }
+    LZ_REQUIRE(src && dst && weight && cooc && out_src && out_dst && out_weight && out_cooc && scratch,
+               "lz_edge_decay_prune: NULL pointer");
+    LZ_REQUIRE((((uintptr_t)src | (uintptr_t)dst | (uintptr_t)weight | (uintptr_t)cooc) & 15) == 0,
+               "lz_edge_decay_prune: edge arrays must be 16-byte aligned");
+    LZ_REQUIRE(n < (1ll << 40), "lz_edge_decay_prune: n too large");
+    const size_t need = lz_edge_decay_prune_scratch_bytes(n);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_edge_decay_prune: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    const int64_t tiles = (n + kTile - 1) / kTile;
+    LZ_CUDA(cudaMemsetAsync(scratch, 0, need, st));
+    PruneParams p;
+    p.src = src; p.dst = dst; p.w = weight; p.cooc = cooc;
+    p.o_src = out_src; p.o_dst = out_dst; p.o_w = out_weight; p.o_cooc = out_cooc;
+    p.n = n; p.factor = factor; p.thr = threshold;
+    p.ticket = (u32*)scratch;
+    p.state = (u64*)scratch + 1;
+    p.out_kept = out_kept; p.n_tiles = (int)tiles;
+    decay_prune_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(p);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" int lz_edge_decay(float* weight, int64_t n, double factor, void* stream) {
+    if (n <= 0) return LZ_OK;
+    LZ_REQUIRE(weight && ((uintptr_t)weight & 15) == 0, "lz_edge_decay: weight must be non-NULL and 16-byte aligned");
+    decay_kernel<<<elementwise_blocks(n), kThreads, 0, (cudaStream_t)stream>>>(weight, n, factor);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" int lz_salience_decay(float* salience, int64_t n, double rate, double floor, void* stream) {
+    if (n <= 0) return LZ_OK;
+    LZ_REQUIRE(salience && ((uintptr_t)salience & 15) == 0,
+               "lz_salience_decay: salience must be non-NULL and 16-byte aligned");
+    salience_kernel<<<elementwise_blocks(n), kThreads, 0, (cudaStream_t)stream>>>(salience, n, 1.0 - rate, floor);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -1,0 +1,441 @@
+// K1: exact flat search — one streaming pass over float32 rows with float64 accumulation and a fused
+// per-CTA top-k, then a per-query merge of the per-CTA lists.  HBM-bound: every row is read once per
+// query group with 128-bit non-allocating loads; the arithmetic (24 cvt + 24*QB DFMA per lane and
+// row at D=768) stays well under B200's fp64 rate.
+//
+// Stands behind LanceDBStore.search_nodes (core/vector_store.py:132-140) and the cosine of
+// MemorySystem._cosine_similarity (core/memory_system.py:197-203).
+#include "lz_common.cuh"
+#include "lz_topk.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kR = 4;                       // rows per warp per iteration
+constexpr int kIters = 8;                   // iterations between two compaction checks
+constexpr int kChunkRows = kWarps * kR * kIters;   // 256 rows -> at most 256 pushes per selector
+
+// Sum over one vector of f(x_i) in the canonical order used by every kernel in this file: lane l
+// owns elements seg*128 + 4l .. 4l+3, accumulates them seg by seg with fma, then a butterfly sum.
+// Using one order everywhere makes bit-identical rows produce bit-identical norms and scores.
+__device__ __forceinline__ double warp_sumsq(const float* __restrict__ v, int dim, int lane) {
+    double acc = 0.0;
+    for (int e = lane * 4; e < dim; e += 128) {
+        float4 x = *reinterpret_cast<const float4*>(v + e);
+        acc = fma((double)x.x, (double)x.x, acc);
+        acc = fma((double)x.y, (double)x.y, acc);
+        acc = fma((double)x.z, (double)x.z, acc);
+        acc = fma((double)x.w, (double)x.w, acc);
+    }
+    return lz_warp_sum(acc);
+}
+
+__global__ void __launch_bounds__(kThreads) row_norms_kernel(const float* __restrict__ rows, int64_t n,
+                                                             int dim, int64_t ld, double* __restrict__ norms) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        double s = warp_sumsq(rows + r * ld, dim, lane);
+        if (lane == 0) norms[r] = sqrt(s);
+    }
+}
+
+struct ScanParams {
+    const float* rows; int64_t ld; int dim; const double* norms; const int32_t* tags;
+    int64_t row_lo, row_hi; const int64_t* group_lo; const int64_t* group_hi; const int32_t* group_tag;
+    const float* queries; int64_t q_ld; int n_queries;
+    int k; int n_chunks; int cap;
+    u64* part_key; u32* part_id; int32_t* part_cnt;
+};
+
+template <int QB, int METRIC>
+__global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nseg = (p.dim + 127) >> 7;
+    const int g = blockIdx.x / p.n_chunks;
+    const int c = blockIdx.x - g * p.n_chunks;
+    const int q0 = g * QB;
+    const int nq = min(QB, p.n_queries - q0);
+
+    // shared memory carve-up
+    double2* qs = reinterpret_cast<double2*>(smem);                 // [QB][nseg][2][32]
+    u64* keys = reinterpret_cast<u64*>(qs + (size_t)QB * nseg * 64); // [QB][cap]
+    u32* ids = reinterpret_cast<u32*>(keys + (size_t)QB * p.cap);    // [QB][cap]
+    __shared__ LzSelector sel[QB];
+    __shared__ double qnorm[QB];
+
+    // queries -> shared memory as float64, zero padded to nseg*128
+    for (int i = tid; i < QB * nseg * 128; i += kThreads) {
+        int b = i / (nseg * 128), e = i - b * nseg * 128;
+        double v = (b < nq && e < p.dim) ? (double)p.queries[(int64_t)(q0 + b) * p.q_ld + e] : 0.0;
+        int seg = e >> 7, l = (e & 127) >> 2, comp = e & 3;
+        double* dst = reinterpret_cast<double*>(&qs[((b * nseg + seg) * 2 + (comp >> 1)) * 32 + l]);
+        dst[comp & 1] = v;
+    }
+    if (warp < QB) {
+        double s = (warp < nq) ? warp_sumsq(p.queries + (int64_t)(q0 + warp) * p.q_ld, p.dim, lane) : 0.0;
+        if (lane == 0) {
+            qnorm[warp] = sqrt(s);
+            lz_sel_init(&sel[warp], keys + (size_t)warp * p.cap, ids + (size_t)warp * p.cap, p.cap, p.k);
+        }
+    }
+    __syncthreads();
+
+    int64_t lo = p.group_lo ? p.group_lo[g] : p.row_lo;
+    int64_t hi = p.group_hi ? p.group_hi[g] : p.row_hi;
+    if (hi < lo) hi = lo;
+    const int want_tag = p.group_tag ? p.group_tag[g] : -1;
+    const int64_t len = (hi - lo + p.n_chunks - 1) / p.n_chunks;
+    const int64_t cta_lo = lo + (int64_t)c * len;
+    const int64_t cta_hi = min(hi, cta_lo + len);
+
+    for (int64_t base = cta_lo; base < cta_hi; base += kChunkRows) {
+#pragma unroll 1
+        for (int it = 0; it < kIters; ++it) {
+            const int64_t row0 = base + (int64_t)(it * kWarps + warp) * kR;
+            if (row0 >= cta_hi) break;
+            const float* xp[kR];
+#pragma unroll
+            for (int r = 0; r < kR; ++r) xp[r] = p.rows + min(row0 + r, cta_hi - 1) * p.ld + lane * 4;
+            double my_norm = 0.0;
+            int my_tag = 0;
+            if (lane < kR) {
+                int64_t row = min(row0 + lane, cta_hi - 1);
+                if (METRIC == LZ_COSINE) my_norm = p.norms[row];
+                if (p.tags) my_tag = p.tags[row];
+            }
+            double acc[kR][QB];
+#pragma unroll
+            for (int r = 0; r < kR; ++r)
+#pragma unroll
+                for (int b = 0; b < QB; ++b) acc[r][b] = 0.0;
+
+#pragma unroll 2
+            for (int seg = 0; seg < nseg; ++seg) {
+                const bool act = seg * 128 + lane * 4 < p.dim;
+                float4 x[kR];
+#pragma unroll
+                for (int r = 0; r < kR; ++r)
+                    x[r] = act ? lz_ldg_stream(xp[r] + seg * 128) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int b = 0; b < QB; ++b) {
+                    const double2 qa = qs[((b * nseg + seg) * 2 + 0) * 32 + lane];
+                    const double2 qb = qs[((b * nseg + seg) * 2 + 1) * 32 + lane];
+#pragma unroll
+                    for (int r = 0; r < kR; ++r) {
+                        if (METRIC == LZ_COSINE) {
+                            acc[r][b] = fma((double)x[r].x, qa.x, acc[r][b]);
+                            acc[r][b] = fma((double)x[r].y, qa.y, acc[r][b]);
+                            acc[r][b] = fma((double)x[r].z, qb.x, acc[r][b]);
+                            acc[r][b] = fma((double)x[r].w, qb.y, acc[r][b]);
+                        } else {
+                            double d0 = (double)x[r].x - qa.x, d1 = (double)x[r].y - qa.y;
+                            double d2 = (double)x[r].z - qb.x, d3 = (double)x[r].w - qb.y;
+                            acc[r][b] = fma(d0, d0, acc[r][b]);
+                            acc[r][b] = fma(d1, d1, acc[r][b]);
+                            acc[r][b] = fma(d2, d2, acc[r][b]);
+                            acc[r][b] = fma(d3, d3, acc[r][b]);
+                        }
+                    }
+                }
+            }
+            // butterfly: every lane ends with every total; lane l then finishes pair (r,b) = (l/QB, l%QB)
+            double mine = 0.0;
+#pragma unroll
+            for (int r = 0; r < kR; ++r)
+#pragma unroll
+                for (int b = 0; b < QB; ++b) {
+                    double t = lz_warp_sum(acc[r][b]);
+                    if (lane == r * QB + b) mine = t;
+                }
+            const int r = lane / QB, b = lane - r * QB;
+            const double nx = __shfl_sync(0xffffffffu, my_norm, r & 31);
+            const int tg = __shfl_sync(0xffffffffu, my_tag, r & 31);
+            const int64_t row = row0 + r;
+            bool ok = lane < kR * QB && row < cta_hi && b < nq;
+            if (p.tags) ok = ok && tg >= 0 && (want_tag < 0 || tg == want_tag);
+            if (ok) {
+                double s;
+                if (METRIC == LZ_COSINE) {
+                    const double den = nx * qnorm[b];
+                    s = den > 0.0 ? mine / den : 0.0;
+                    s += 0.0;
+                } else {
+                    s = 0.0 - mine;
+                }
+                if (s == s) lz_sel_push(&sel[b], lz_ord(s), (u32)row);
+            }
+        }
+#pragma unroll
+        for (int b = 0; b < QB; ++b) lz_sel_maybe_compact<kThreads>(&sel[b], kChunkRows);
+    }
+    __syncthreads();
+    for (int b = 0; b < nq; ++b) {
+        lz_sel_compact<kThreads>(&sel[b]);
+        const int n = min(sel[b].count, p.k);
+        const size_t slot = (size_t)(q0 + b) * p.n_chunks + c;
+        for (int j = tid; j < n; j += kThreads) {
+            p.part_key[slot * p.k + j] = sel[b].key[j];
+            p.part_id[slot * p.k + j] = sel[b].id[j];
+        }
+        if (tid == 0) p.part_cnt[slot] = n;
+    }
+}
+
+// One CTA per query: stream the per-chunk lists through a selector.
+struct MergeParams {
+    const u64* part_key; const u32* part_id; const int32_t* part_cnt;   // form A: scan partials
+    const int64_t* in_ids; const double* in_scores; int n_queries;      // form B: (id, score) lists
+    int n_lists; int k; int cap; int metric;
+    int64_t* out_ids; double* out_scores; int32_t* out_counts;
+};
+
+__global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* keys = reinterpret_cast<u64*>(smem);
+    u32* ids = reinterpret_cast<u32*>(keys + p.cap);
+    __shared__ LzSelector sel;
+    const int tid = threadIdx.x, q = blockIdx.x;
+    if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
+    __syncthreads();
+    const int64_t total = (int64_t)p.n_lists * p.k;
+    for (int64_t base = 0; base < total; base += kThreads) {
+        const int64_t i = base + tid;
+        if (i < total) {
+            const int c = (int)(i / p.k), j = (int)(i - (int64_t)c * p.k);
+            if (p.part_key) {
+                const size_t slot = (size_t)q * p.n_lists + c;
+                if (j < p.part_cnt[slot]) lz_sel_push(&sel, p.part_key[slot * p.k + j], p.part_id[slot * p.k + j]);
+            } else {
+                const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
+                const int64_t id = p.in_ids[at];
+                const double s = p.in_scores[at];
+                if (id >= 0 && s == s) {
+                    const double v = (p.metric == LZ_COSINE) ? s + 0.0 : 0.0 - s;
+                    lz_sel_push(&sel, lz_ord(v), (u32)id);
+                }
+            }
+        }
+        lz_sel_maybe_compact<kThreads>(&sel, kThreads);
+    }
+    __syncthreads();
+    lz_sel_compact<kThreads>(&sel);
+    const int n = min(sel.count, p.k);
+    for (int j = tid; j < p.k; j += kThreads) {
+        if (j < n) {
+            const double v = lz_unord(sel.key[j]);
+            p.out_ids[(size_t)q * p.k + j] = (int64_t)sel.id[j];
+            p.out_scores[(size_t)q * p.k + j] = (p.metric == LZ_COSINE) ? v : 0.0 - v;
+        } else {
+            p.out_ids[(size_t)q * p.k + j] = -1;
+            p.out_scores[(size_t)q * p.k + j] = __longlong_as_double(0x7ff8000000000000ll);
+        }
+    }
+    if (tid == 0) p.out_counts[q] = n;
+}
+
+// One warp per (query, row) pair, same summation order as the scan.
+template <int METRIC>
+__global__ void __launch_bounds__(kThreads) score_pairs_kernel(const float* __restrict__ rows, int64_t ld, int dim,
+                                                               const double* __restrict__ norms,
+                                                               const float* __restrict__ queries, int64_t q_ld,
+                                                               const int32_t* __restrict__ pair_q,
+                                                               const int64_t* __restrict__ pair_row, int64_t n_pairs,
+                                                               double* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * kWarps + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+    for (int64_t i = warp; i < n_pairs; i += nwarps) {
+        const int64_t row = pair_row[i];
+        if (row < 0) {
+            if (lane == 0) out[i] = __longlong_as_double(0x7ff8000000000000ll);
+            continue;
+        }
+        const float* x = rows + row * ld;
+        const float* q = queries + (int64_t)pair_q[i] * q_ld;
+        double acc = 0.0;
+        for (int e = lane * 4; e < dim; e += 128) {
+            const float4 xv = lz_ldg_stream(x + e);
+            const float4 qv = *reinterpret_cast<const float4*>(q + e);
+            if (METRIC == LZ_COSINE) {
+                acc = fma((double)xv.x, (double)qv.x, acc);
+                acc = fma((double)xv.y, (double)qv.y, acc);
+                acc = fma((double)xv.z, (double)qv.z, acc);
+                acc = fma((double)xv.w, (double)qv.w, acc);
+            } else {
+                double d0 = (double)xv.x - (double)qv.x, d1 = (double)xv.y - (double)qv.y;
+                double d2 = (double)xv.z - (double)qv.z, d3 = (double)xv.w - (double)qv.w;
+                acc = fma(d0, d0, acc);
+                acc = fma(d1, d1, acc);
+                acc = fma(d2, d2, acc);
+                acc = fma(d3, d3, acc);
+            }
+        }
+        acc = lz_warp_sum(acc);
+        double s;
+        if (METRIC == LZ_COSINE) {
+            const double qn = sqrt(warp_sumsq(q, dim, lane));
+            const double den = norms[row] * qn;
+            s = den > 0.0 ? acc / den : 0.0;
+            s += 0.0;
+        } else {
+            s = acc;
+        }
+        if (lane == 0) out[i] = s;
+    }
+}
+
+size_t scan_smem_bytes(int qb, int dim, int cap) {
+    const int nseg = (dim + 127) / 128;
+    return (size_t)qb * nseg * 1024 + (size_t)qb * cap * 12;
+}
+
+template <int QB>
+int launch_scan(const ScanParams& p, int metric, int n_groups, cudaStream_t st) {
+    const size_t smem = scan_smem_bytes(QB, p.dim, p.cap);
+    auto kern = metric == LZ_COSINE ? scan_kernel<QB, LZ_COSINE> : scan_kernel<QB, LZ_L2>;
+    LZ_REQUIRE(smem <= 220 * 1024, "lz_search_exact: k=%d dim=%d needs %zu B of shared memory", p.k, p.dim, smem);
+    LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)((int64_t)n_groups * p.n_chunks), kThreads, smem, st>>>(p);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+int check_rows(const char* who, const float* rows, int64_t ld, int dim) {
+    LZ_REQUIRE(rows != nullptr, "%s: rows is NULL", who);
+    LZ_REQUIRE(dim > 0 && dim % 4 == 0, "%s: dim=%d must be a positive multiple of 4", who, dim);
+    LZ_REQUIRE(ld >= dim && ld % 4 == 0, "%s: ld=%lld must be >= dim and a multiple of 4", who, (long long)ld);
+    LZ_REQUIRE(((uintptr_t)rows & 15) == 0, "%s: rows must be 16-byte aligned", who);
+    return LZ_OK;
+}
+
+}  // namespace
+
+extern "C" int lz_row_norms(const float* rows, int64_t n, int dim, int64_t ld, double* norms, void* stream) {
+    if (n <= 0) return LZ_OK;
+    if (int rc = check_rows("lz_row_norms", rows, ld, dim)) return rc;
+    LZ_REQUIRE(norms != nullptr, "lz_row_norms: norms is NULL");
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    int64_t blocks = (n + kWarps - 1) / kWarps;
+    if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
+    row_norms_kernel<<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" size_t lz_search_exact_scratch_bytes(int n_queries, int k, int n_chunks) {
+    if (n_queries <= 0 || k <= 0 || n_chunks <= 0) return 0;
+    const size_t slots = (size_t)n_queries * n_chunks;
+    size_t b = slots * k * sizeof(u64);
+    b += slots * k * sizeof(u32);
+    b = (b + 15) & ~(size_t)15;
+    b += slots * sizeof(int32_t);
+    return (b + 255) & ~(size_t)255;
+}
+
+extern "C" int lz_search_exact_default_chunks(int64_t n_rows, int n_groups) {
+    const int sms = lz_sm_count();
+    if (sms <= 0) return 1;
+    if (n_groups < 1) n_groups = 1;
+    int64_t by_rows = (n_rows + kChunkRows - 1) / kChunkRows;
+    int64_t want = ((int64_t)2 * sms + n_groups - 1) / n_groups;
+    int64_t c = by_rows < want ? by_rows : want;
+    return (int)(c < 1 ? 1 : c);
+}
+
+extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
+                               int64_t row_lo, int64_t row_hi, const int64_t* group_lo, const int64_t* group_hi,
+                               const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
+                               int group_size, int k, int metric, int n_chunks, void* scratch, size_t scratch_bytes,
+                               int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    if (int rc = check_rows("lz_search_exact", rows, ld, dim)) return rc;
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_exact: unknown metric %d", metric);
+    LZ_REQUIRE(metric == LZ_L2 || norms != nullptr, "lz_search_exact: cosine needs norms");
+    LZ_REQUIRE(k >= 1 && k <= LZ_MAX_K, "lz_search_exact: k=%d outside 1..%d", k, LZ_MAX_K);
+    LZ_REQUIRE(group_size == 1 || group_size == 2 || group_size == 4,
+               "lz_search_exact: group_size=%d must be 1, 2 or 4", group_size);
+    LZ_REQUIRE(n_chunks >= 1, "lz_search_exact: n_chunks=%d", n_chunks);
+    LZ_REQUIRE(queries && q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
+               "lz_search_exact: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
+    LZ_REQUIRE((group_lo == nullptr) == (group_hi == nullptr), "lz_search_exact: group_lo/group_hi must come together");
+    LZ_REQUIRE(out_ids && out_scores && out_counts && scratch, "lz_search_exact: NULL output or scratch");
+    LZ_REQUIRE(row_hi <= 0xfffffffeLL, "lz_search_exact: row index %lld exceeds 32 bits", (long long)row_hi);
+    const size_t need = lz_search_exact_scratch_bytes(n_queries, k, n_chunks);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_search_exact: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    const int n_groups = (n_queries + group_size - 1) / group_size;
+    const size_t slots = (size_t)n_queries * n_chunks;
+    ScanParams p;
+    p.rows = rows; p.ld = ld; p.dim = dim; p.norms = norms; p.tags = tags;
+    p.row_lo = row_lo; p.row_hi = row_hi; p.group_lo = group_lo; p.group_hi = group_hi; p.group_tag = group_tag;
+    p.queries = queries; p.q_ld = q_ld; p.n_queries = n_queries;
+    p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows);
+    unsigned char* s = (unsigned char*)scratch;
+    p.part_key = (u64*)s;
+    p.part_id = (u32*)(s + slots * k * sizeof(u64));
+    p.part_cnt = (int32_t*)(s + (((slots * k * (sizeof(u64) + sizeof(u32))) + 15) & ~(size_t)15));
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc = group_size == 1 ? launch_scan<1>(p, metric, n_groups, st)
+           : group_size == 2 ? launch_scan<2>(p, metric, n_groups, st)
+                             : launch_scan<4>(p, metric, n_groups, st);
+    if (rc) return rc;
+    MergeParams m;
+    m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
+    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries;
+    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric;
+    m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
+    const size_t msmem = (size_t)m.cap * 12;
+    LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+    merge_kernel<<<n_queries, kThreads, msmem, st>>>(m);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,
+                             int metric, int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    LZ_REQUIRE(in_ids && in_scores && out_ids && out_scores && out_counts, "lz_merge_topk: NULL pointer");
+    LZ_REQUIRE(n_lists >= 1 && k >= 1 && k <= LZ_MAX_K, "lz_merge_topk: n_lists=%d k=%d", n_lists, k);
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_merge_topk: unknown metric %d", metric);
+    MergeParams m;
+    m.part_key = nullptr; m.part_id = nullptr; m.part_cnt = nullptr;
+    m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries;
+    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric;
+    m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
+    const size_t msmem = (size_t)m.cap * 12;
+    LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+    merge_kernel<<<n_queries, kThreads, msmem, (cudaStream_t)stream>>>(m);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" int lz_score_pairs(const float* rows, int64_t ld, int dim, const double* norms, const float* queries,
+                              int64_t q_ld, const int32_t* pair_q, const int64_t* pair_row, int64_t n_pairs,
+                              int metric, double* out_scores, void* stream) {
+    if (n_pairs <= 0) return LZ_OK;
+    if (int rc = check_rows("lz_score_pairs", rows, ld, dim)) return rc;
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_score_pairs: unknown metric %d", metric);
+    LZ_REQUIRE(metric == LZ_L2 || norms != nullptr, "lz_score_pairs: cosine needs norms");
+    LZ_REQUIRE(queries && q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
+               "lz_score_pairs: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
+    LZ_REQUIRE(pair_q && pair_row && out_scores, "lz_score_pairs: NULL pointer");
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    int64_t blocks = (n_pairs + kWarps - 1) / kWarps;
+    if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
+    if (metric == LZ_COSINE)
+        score_pairs_kernel<LZ_COSINE><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            rows, ld, dim, norms, queries, q_ld, pair_q, pair_row, n_pairs, out_scores);
+    else
+        score_pairs_kernel<LZ_L2><<<(unsigned)blocks, kThreads, 0, (cudaStream_t)stream>>>(
+            rows, ld, dim, norms, queries, q_ld, pair_q, pair_row, n_pairs, out_scores);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -1,0 +1,258 @@
+"""Device-resident graph containers: the decay / prune side of the hot path.
+
+Host-side mirror of /root/reference/src/lazzaro/core/memory_shard.py (`MemoryShard`) and
+core/buffer_graph.py (`BufferGraph.apply_temporal_decay / prune_weak_edges`, lines 87-97), with the
+same method names and return values, over a struct-of-arrays edge table in HBM:
+
+    src int32 | dst int32 | weight float32 | co_occurrence int32        (16 B per edge)
+
+Strings (node ids, contents) stay on the host; edges refer to nodes by a per-shard integer slot.
+`apply_temporal_decay` and `prune_weak_edges` are single kernel sweeps (lz_edge_decay,
+lz_salience_decay, lz_edge_decay_prune); the fused `decay_and_prune` does both in one pass, which is
+what `MemorySystem.end_conversation` does back to back (core/memory_system.py:624-630).
+State is float32 (the reference persists weight and salience as float32, vector_store.py:42,63);
+each sweep computes in float64 exactly as the reference's Python floats do and stores the rounding.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass, field
+from typing import Dict, Iterable, List, Optional, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib, kernels
+
+
+@dataclass
+class Node:
+    """Same fields as the reference's models/graph.py:39-50."""
+    id: str
+    content: str
+    embedding: List[float] = field(default_factory=list)
+    type: str = "semantic"
+    timestamp: float = field(default_factory=time.time)
+    access_count: int = 0
+    last_accessed: float = field(default_factory=time.time)
+    salience: float = 0.5
+    is_super_node: bool = False
+    child_ids: List[str] = field(default_factory=list)
+    parent_id: Optional[str] = None
+    shard_key: str = "default"
+
+
+@dataclass
+class Edge:
+    """Same fields as the reference's models/graph.py:90-95."""
+    source: str
+    target: str
+    weight: float = 1.0
+    edge_type: str = "relates_to"
+    co_occurrence: int = 1
+    last_updated: float = field(default_factory=time.time)
+
+
+class EdgeTable:
+    """Edge struct-of-arrays in HBM with append, decay, fused decay+prune."""
+
+    def __init__(self, device=None, capacity: int = 1024):
+        _lib.require_cuda()
+        _lib.load()
+        self.device = torch.device(device or f"cuda:{torch.cuda.current_device()}")
+        self.n = 0
+        self._alloc(max(16, capacity))
+        self._scratch: Optional[torch.Tensor] = None
+        self._kept = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self._kept_host = torch.zeros(1, dtype=torch.int64, pin_memory=True)
+
+    def _alloc(self, cap: int):
+        new = [torch.empty(cap, dtype=dt, device=self.device)
+               for dt in (torch.int32, torch.int32, torch.float32, torch.int32)]
+        if self.n:
+            for a, b in zip(new, (self.src, self.dst, self.weight, self.cooc)):
+                a[:self.n] = b[:self.n]
+        self.src, self.dst, self.weight, self.cooc = new
+
+    @classmethod
+    def from_arrays(cls, src, dst, weight, cooc, device=None) -> "EdgeTable":
+        t = cls(device, capacity=len(src))
+        t.append(src, dst, weight, cooc)
+        return t
+
+    def append(self, src, dst, weight, cooc):
+        k = len(src)
+        if self.n + k > self.src.shape[0]:
+            self._alloc(max(self.n + k, 2 * self.src.shape[0]))
+        for col, vals, dt in ((self.src, src, torch.int32), (self.dst, dst, torch.int32),
+                              (self.weight, weight, torch.float32), (self.cooc, cooc, torch.int32)):
+            col[self.n:self.n + k] = torch.as_tensor(vals, dtype=dt).to(self.device, non_blocking=True)
+        self.n += k
+
+    def decay(self, factor: float):
+        """weight *= factor (memory_shard.py:69-70), one elementwise sweep."""
+        kernels.edge_decay(self.weight, self.n, factor)
+
+    def decay_prune(self, factor: float, threshold: float, sync: bool = True) -> int:
+        """Fused sweep: decay by `factor`, drop weight < threshold (strict), compact in place keeping
+        order.  Returns the number pruned (memory_shard.py:79-84) — this reads one int64 back."""
+        n0 = self.n
+        if n0 == 0:
+            return 0
+        lib = _lib.load()
+        with torch.cuda.device(self.device):
+            need = int(lib.lz_edge_decay_prune_scratch_bytes(n0))
+            if self._scratch is None or self._scratch.numel() < need:
+                self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            kernels.edge_decay_prune(self.src, self.dst, self.weight, self.cooc, n0, factor, threshold,
+                                     scratch=self._scratch, kept=self._kept)
+            if not sync:
+                return -1
+            self._kept_host.copy_(self._kept, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        self.n = int(self._kept_host[0])
+        return n0 - self.n
+
+    def to_numpy(self):
+        n = self.n
+        return (self.src[:n].cpu().numpy(), self.dst[:n].cpu().numpy(),
+                self.weight[:n].cpu().numpy(), self.cooc[:n].cpu().numpy())
+
+
+class MemoryShard:
+    """Mirror of the reference's MemoryShard (core/memory_shard.py:7-88) over a device edge table."""
+
+    def __init__(self, shard_key: str, device=None):
+        self.shard_key = shard_key
+        self.nodes: Dict[str, Node] = {}
+        self.last_accessed = time.time()
+        self.access_count = 0
+        self._slot: Dict[str, int] = {}              # node id -> integer slot (also for edge-only ids)
+        self._names: List[str] = []
+        self._table = EdgeTable(device)
+        self._edge_meta: Dict[Tuple[int, int], Tuple[str, float]] = {}   # (edge_type, last_updated)
+        self._index: Optional[Dict[Tuple[int, int], int]] = None         # (src,dst) -> row, lazily rebuilt
+        self._pending: List[Tuple[int, int, float, int]] = []            # edges not yet uploaded
+
+    # -- nodes
+    def _slot_of(self, node_id: str) -> int:
+        s = self._slot.get(node_id)
+        if s is None:
+            s = self._slot[node_id] = len(self._names)
+            self._names.append(node_id)
+        return s
+
+    def add_node(self, node: Node) -> None:
+        node.shard_key = self.shard_key                   # memory_shard.py:39
+        self.nodes[node.id] = node
+        self._slot_of(node.id)
+
+    # -- edges
+    def _flush(self):
+        if self._pending:
+            s, d, w, c = zip(*self._pending)
+            self._table.append(np.int32(s), np.int32(d), np.float32(w), np.int32(c))
+            self._pending.clear()
+
+    def _edge_index(self) -> Dict[Tuple[int, int], int]:
+        if self._index is None:
+            self._flush()
+            s, d, _, _ = self._table.to_numpy()
+            self._index = {(int(a), int(b)): i for i, (a, b) in enumerate(zip(s, d))}
+        return self._index
+
+    def add_edge(self, edge: Edge) -> None:
+        """memory_shard.py:42-52: an existing (source, target) key is reinforced (+0.1 capped at 1,
+        co_occurrence += 1), otherwise the edge is appended."""
+        key = (self._slot_of(edge.source), self._slot_of(edge.target))
+        idx = self._edge_index()
+        row = idx.get(key)
+        if row is not None:
+            self._flush()
+            w = float(self._table.weight[row].item())
+            self._table.weight[row] = float(np.float32(min(1.0, w + 0.1)))
+            self._table.cooc[row] += 1
+        else:
+            idx[key] = self._table.n + len(self._pending)
+            self._pending.append((key[0], key[1], float(edge.weight), int(edge.co_occurrence)))
+            self._edge_meta[key] = (edge.edge_type, edge.last_updated)
+
+    @property
+    def edges(self) -> Dict[Tuple[str, str], Edge]:
+        """Materialises the edge dict from HBM (a device->host copy; not for hot loops)."""
+        self._flush()
+        s, d, w, c = self._table.to_numpy()
+        out = {}
+        for a, b, ww, cc in zip(s.tolist(), d.tolist(), w.tolist(), c.tolist()):
+            et, lu = self._edge_meta.get((a, b), ("relates_to", 0.0))
+            out[(self._names[a], self._names[b])] = Edge(self._names[a], self._names[b], ww, et, cc, lu)
+        return out
+
+    def get_neighbors(self, node_id: str, min_weight: float = 0.3) -> List[str]:
+        """memory_shard.py:54-62 (host loop over a device->host copy; the CSR kernel is SURVEY §8f)."""
+        out = []
+        for (src, tgt), e in self.edges.items():
+            if src == node_id and e.weight >= min_weight:
+                out.append(tgt)
+            elif tgt == node_id and e.weight >= min_weight:
+                out.append(src)
+        return out
+
+    # -- the hot path
+    def _salience_sweep(self, decay_rate: float):
+        if not self.nodes:
+            return
+        nodes = list(self.nodes.values())
+        s = torch.tensor([n.salience for n in nodes], dtype=torch.float32).to(self._table.device)
+        kernels.salience_decay(s, s.numel(), decay_rate, 0.2)
+        for n, v in zip(nodes, s.cpu().tolist()):
+            n.salience = v
+
+    def apply_temporal_decay(self, decay_rate: float = 0.01) -> None:
+        """memory_shard.py:64-77."""
+        self._flush()
+        self._table.decay(1.0 - decay_rate)
+        self._salience_sweep(decay_rate)
+
+    def prune_weak_edges(self, threshold: float = 0.5) -> int:
+        """memory_shard.py:79-84; returns the number of edges removed."""
+        self._flush()
+        pruned = self._table.decay_prune(1.0, threshold)
+        if pruned:
+            self._index = None
+        return pruned
+
+    def decay_and_prune(self, decay_rate: float = 0.01, threshold: float = 0.5) -> int:
+        """apply_temporal_decay followed by prune_weak_edges as ONE sweep over the edge table
+        (core/memory_system.py:624-630 calls them back to back)."""
+        self._flush()
+        pruned = self._table.decay_prune(1.0 - decay_rate, threshold)
+        self._salience_sweep(decay_rate)
+        if pruned:
+            self._index = None
+        return pruned
+
+    def size(self) -> Tuple[int, int]:
+        return len(self.nodes), self._table.n + len(self._pending)
+
+
+class BufferGraph:
+    """Decay / prune fan-out of the reference's BufferGraph (core/buffer_graph.py:87-97)."""
+
+    def __init__(self, shards: Dict[str, MemoryShard], super_nodes: Optional[Dict[str, Node]] = None):
+        self.shards = shards
+        self.super_nodes = super_nodes if super_nodes is not None else {}
+
+    def apply_temporal_decay(self, decay_rate: float = 0.01):
+        for shard in self.shards.values():
+            shard.apply_temporal_decay(decay_rate)
+
+    def prune_weak_edges(self, threshold: float = 0.5) -> int:
+        return sum(shard.prune_weak_edges(threshold) for shard in self.shards.values())
+
+    def decay_and_prune(self, decay_rate: float = 0.01, threshold: float = 0.5) -> int:
+        return sum(shard.decay_and_prune(decay_rate, threshold) for shard in self.shards.values())
+
+    def size(self) -> Tuple[int, int]:
+        n = sum(s.size()[0] for s in self.shards.values()) + len(self.super_nodes)
+        return n, sum(s.size()[1] for s in self.shards.values())

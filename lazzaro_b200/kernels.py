@@ -1,0 +1,139 @@
+"""Thin typed wrappers over the C-ABI (include/lazzaro_b200.h): torch tensors in, torch tensors out.
+
+torch is used here for device memory and streams only; every computation below is a call into
+liblazzaro_b200.so.  All calls are asynchronous on torch's current stream of the tensors' device.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream_ptr
+
+
+def _dev(t: torch.Tensor):
+    if not t.is_cuda:
+        raise _lib.LazzaroB200Error("lazzaro_b200 kernels take CUDA tensors only (no CPU fallback)")
+    return t.device
+
+
+def row_norms(rows: torch.Tensor, dim: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """float64 Euclidean norm of each float32 row (lz_row_norms)."""
+    dev = _dev(rows)
+    assert rows.dtype == torch.float32 and rows.dim() == 2 and rows.stride(1) == 1
+    n, dim = rows.shape[0], dim or rows.shape[1]
+    if out is None:
+        out = torch.empty(n, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_row_norms(ptr(rows), n, dim, rows.stride(0), ptr(out), stream_ptr(dev)), "lz_row_norms")
+    return out
+
+
+def default_chunks(n_rows: int, n_groups: int, device) -> int:
+    with torch.cuda.device(device):
+        return int(_lib.load().lz_search_exact_default_chunks(int(n_rows), int(n_groups)))
+
+
+def search_exact(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], tags: Optional[torch.Tensor],
+                 queries: torch.Tensor, k: int, metric: int = _lib.COSINE,
+                 row_range: Optional[Tuple[int, int]] = None,
+                 group_lo: Optional[torch.Tensor] = None, group_hi: Optional[torch.Tensor] = None,
+                 group_tag: Optional[torch.Tensor] = None, group_size: Optional[int] = None,
+                 n_chunks: Optional[int] = None, scratch: Optional[torch.Tensor] = None,
+                 out: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None):
+    """Exhaustive float64 top-k (lz_search_exact). Returns (ids int64 [B,k], scores float64 [B,k],
+    counts int32 [B]) on the device, unsynchronised."""
+    dev = _dev(rows)
+    assert rows.dtype == torch.float32 and queries.dtype == torch.float32 and queries.dim() == 2
+    assert queries.stride(1) == 1 and rows.stride(1) == 1 and queries.device == dev
+    B = queries.shape[0]
+    lo, hi = row_range if row_range is not None else (0, rows.shape[0])
+    if group_lo is not None:
+        group_size = 1 if group_size is None else group_size
+    if group_size is None:
+        group_size = 4 if B >= 4 else (2 if B >= 2 else 1)
+    n_groups = (B + group_size - 1) // group_size
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        if n_chunks is None:
+            span = (hi - lo) if group_lo is None else max(1, (hi - lo))
+            n_chunks = int(lib.lz_search_exact_default_chunks(int(span), n_groups))
+        need = int(lib.lz_search_exact_scratch_bytes(B, k, n_chunks))
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        if out is None:
+            out = (torch.empty((B, k), dtype=torch.int64, device=dev),
+                   torch.empty((B, k), dtype=torch.float64, device=dev),
+                   torch.empty((B,), dtype=torch.int32, device=dev))
+        ids, scores, counts = out
+        check(lib.lz_search_exact(ptr(rows), rows.stride(0), dim, ptr(norms), ptr(tags), lo, hi,
+                                  ptr(group_lo), ptr(group_hi), ptr(group_tag),
+                                  ptr(queries), queries.stride(0), B, group_size, k, metric, n_chunks,
+                                  ptr(scratch), scratch.numel(), ptr(ids), ptr(scores), ptr(counts),
+                                  stream_ptr(dev)), "lz_search_exact")
+    return ids, scores, counts
+
+
+def merge_topk(in_ids: torch.Tensor, in_scores: torch.Tensor, metric: int = _lib.COSINE):
+    """Merge [n_lists, B, k] per-partition lists into [B, k] (lz_merge_topk)."""
+    dev = _dev(in_ids)
+    assert in_ids.dtype == torch.int64 and in_scores.dtype == torch.float64
+    assert in_ids.is_contiguous() and in_scores.is_contiguous() and in_ids.shape == in_scores.shape
+    L, B, k = in_ids.shape
+    ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+    scores = torch.empty((B, k), dtype=torch.float64, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_merge_topk(ptr(in_ids), ptr(in_scores), L, B, k, metric, ptr(ids), ptr(scores),
+                                        ptr(counts), stream_ptr(dev)), "lz_merge_topk")
+    return ids, scores, counts
+
+
+def score_pairs(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], queries: torch.Tensor,
+                pair_q: torch.Tensor, pair_row: torch.Tensor, metric: int = _lib.COSINE) -> torch.Tensor:
+    """Exact float64 score of each (query, row) pair (lz_score_pairs)."""
+    dev = _dev(rows)
+    assert pair_q.dtype == torch.int32 and pair_row.dtype == torch.int64
+    n = pair_q.numel()
+    out = torch.empty(n, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_score_pairs(ptr(rows), rows.stride(0), dim, ptr(norms), ptr(queries), queries.stride(0),
+                                         ptr(pair_q), ptr(pair_row), n, metric, ptr(out), stream_ptr(dev)),
+              "lz_score_pairs")
+    return out
+
+
+def edge_decay_prune(src, dst, weight, cooc, n: int, factor: float, threshold: float,
+                     out=None, scratch: Optional[torch.Tensor] = None, kept: Optional[torch.Tensor] = None):
+    """Fused decay + strict-threshold prune + stable compaction (lz_edge_decay_prune).
+    `out` = (src, dst, weight, cooc) destination tensors; default is in place.
+    Returns (kept int64[1] on device, out tensors)."""
+    dev = _dev(weight)
+    lib = _lib.load()
+    if out is None:
+        out = (src, dst, weight, cooc)
+    with torch.cuda.device(dev):
+        need = int(lib.lz_edge_decay_prune_scratch_bytes(n))
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(need, dtype=torch.uint8, device=dev)
+        if kept is None:
+            kept = torch.empty(1, dtype=torch.int64, device=dev)
+        check(lib.lz_edge_decay_prune(ptr(src), ptr(dst), ptr(weight), ptr(cooc), n, float(factor), float(threshold),
+                                      ptr(out[0]), ptr(out[1]), ptr(out[2]), ptr(out[3]), ptr(kept),
+                                      ptr(scratch), scratch.numel(), stream_ptr(dev)), "lz_edge_decay_prune")
+    return kept, out
+
+
+def edge_decay(weight: torch.Tensor, n: int, factor: float):
+    dev = _dev(weight)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_edge_decay(ptr(weight), n, float(factor), stream_ptr(dev)), "lz_edge_decay")
+
+
+def salience_decay(salience: torch.Tensor, n: int, rate: float, floor: float = 0.2):
+    dev = _dev(salience)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_salience_decay(ptr(salience), n, float(rate), float(floor), stream_ptr(dev)),
+              "lz_salience_decay")

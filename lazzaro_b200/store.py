@@ -1,0 +1,442 @@
+"""B200Store — a device-resident drop-in for the reference's `LanceDBStore`.
+
+Mirrors /root/reference/src/lazzaro/core/vector_store.py (the `Store` protocol of
+core/interfaces.py:55-102, same method names, argument meaning and "return [] / None rather than
+raise" behaviour) plus the legacy `add/search/delete` surface the reference's tests still call
+(tests/test_vector_store.py:15,43,46,66).  It is injected the same way the reference allows:
+`MemorySystem(store=B200Store(...))` (core/memory_system.py:83,104-107).
+
+What lives where
+  HBM   rows float32 [capacity, dim_p] (insertion order, zero-padded to a multiple of 8 columns),
+        norms float64 [capacity], tags int32 [capacity] (user index, -1 = deleted row)
+  host  everything that is string-valued: ids, user ids, contents, JSON blobs, edges, profiles —
+        the reference keeps those in Arrow tables; they never touch the hot path.
+
+search_nodes = one call of the exact flat-scan kernel (lz_search_exact) over the user's row span
+with the tag pre-filter; there is no CPU path: without the CUDA library every search raises.
+"""
+from __future__ import annotations
+
+import json
+import threading
+import time
+from typing import Any, Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _lib, kernels
+
+
+def _round_up(v: int, m: int) -> int:
+    return (v + m - 1) // m * m
+
+
+class B200Store:
+    def __init__(self, db_dir: str = "db", dim: Optional[int] = None, metric: str = "cosine",
+                 device: Optional[str] = None, capacity: int = 4096, batched_search: str = "auto"):
+        _lib.require_cuda()
+        _lib.load()
+        if metric not in _lib.METRICS:
+            raise ValueError(f"metric must be 'cosine' or 'l2', got {metric!r}")
+        self.db_dir = db_dir
+        self.metric = metric
+        self._metric = _lib.METRICS[metric]
+        self.device = torch.device(device or f"cuda:{torch.cuda.current_device()}")
+        self.dim: Optional[int] = None
+        self._dim_p = 0
+        self._cap0 = max(16, int(capacity))
+        self._n = 0                                   # rows appended so far (live + deleted)
+        self._rows = self._norms = self._tags = None
+        self._lock = threading.RLock()
+        self._version = 1
+        # host-side string world
+        self._users: Dict[str, int] = {}
+        self._user_names: List[str] = []
+        self._span: List[List[int]] = []              # per user [lo, hi) over rows ever added
+        self._live: List[int] = []                    # per user live row count
+        self._row_id: Dict[int, str] = {}             # explicit ids
+        self._row_meta: Dict[int, Dict[str, Any]] = {}
+        self._row_user = np.empty(0, np.int32)        # host copy of tags (for get/delete bookkeeping)
+        self._id_rows: Dict[tuple, List[int]] = {}    # (user idx, id) -> rows
+        self._blocks: List[tuple] = []                # implicit-id blocks (lo, hi, prefix, first)
+        self._edges: List[Dict[str, Any]] = []
+        self._profiles: Dict[str, Dict[str, Any]] = {}
+        self._pin: Dict[str, torch.Tensor] = {}
+        self._scratch: Optional[torch.Tensor] = None
+        self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
+        if dim is not None:
+            self._set_dim(int(dim))
+
+    # ------------------------------------------------------------------ storage management
+    def _set_dim(self, dim: int):
+        self.dim = dim
+        self._dim_p = _round_up(dim, 8)
+        self._alloc(self._cap0)
+
+    def _alloc(self, cap: int):
+        rows = torch.zeros((cap, self._dim_p), dtype=torch.float32, device=self.device)
+        norms = torch.zeros(cap, dtype=torch.float64, device=self.device)
+        tags = torch.full((cap,), -1, dtype=torch.int32, device=self.device)
+        if self._rows is not None and self._n:
+            rows[:self._n] = self._rows[:self._n]
+            norms[:self._n] = self._norms[:self._n]
+            tags[:self._n] = self._tags[:self._n]
+        self._rows, self._norms, self._tags = rows, norms, tags
+
+    def _reserve(self, extra: int):
+        need = self._n + extra
+        if need > self._rows.shape[0]:
+            self._alloc(max(need, 2 * self._rows.shape[0]))
+        if need > self._row_user.shape[0]:
+            grown = np.full(max(need, 2 * self._row_user.shape[0], 16), -1, np.int32)
+            grown[:self._n] = self._row_user[:self._n]
+            self._row_user = grown
+
+    def _pinned(self, name: str, shape, dtype) -> torch.Tensor:
+        t = self._pin.get(name)
+        n = int(np.prod(shape))
+        if t is None or t.numel() < n or t.dtype != dtype:
+            t = torch.empty(max(n, 1), dtype=dtype, pin_memory=True)
+            self._pin[name] = t
+        return t[:n].view(*shape)
+
+    def _user(self, user_id: str, create: bool = False) -> int:
+        u = self._users.get(user_id, -1)
+        if u < 0 and create:
+            u = len(self._user_names)
+            self._users[user_id] = u
+            self._user_names.append(user_id)
+            self._span.append([1 << 62, 0])
+            self._live.append(0)
+        return u
+
+    def _id_of(self, row: int) -> str:
+        s = self._row_id.get(row)
+        if s is not None:
+            return s
+        for lo, hi, prefix, first in self._blocks:
+            if lo <= row < hi:
+                return f"{prefix}{first + row - lo}"
+        return str(row)
+
+    @property
+    def n_rows(self) -> int:
+        return self._n
+
+    # ------------------------------------------------------------------ nodes (vector_store.py:89-148)
+    def add_nodes(self, nodes: List[Dict[str, Any]], user_id: str = "default"):
+        if not nodes:                                               # vector_store.py:90-91
+            return
+        emb = np.asarray([n["embedding"] for n in nodes], dtype=np.float32)
+        if emb.ndim != 2:
+            raise ValueError("every node needs an 'embedding' of the same length")
+        with self._lock:
+            if self.dim is None:
+                self._set_dim(int(emb.shape[1]))
+            if emb.shape[1] != self.dim:
+                raise ValueError(f"embedding has {emb.shape[1]} dims, store has {self.dim}")
+            n0 = self._append_rows_host(emb, user_id)
+            u = self._users[user_id]
+            for i, node in enumerate(nodes):
+                row = n0 + i
+                self._row_id[row] = node["id"]
+                self._id_rows.setdefault((u, node["id"]), []).append(row)
+                self._row_meta[row] = {                             # vector_store.py:95-110
+                    "content": node["content"],
+                    "type": node.get("type", "semantic"),
+                    "timestamp": node.get("timestamp", 0.0),
+                    "access_count": node.get("access_count", 0),
+                    "last_accessed": node.get("last_accessed", 0.0),
+                    "salience": float(np.float32(node.get("salience", 0.5))),
+                    "is_super_node": node.get("is_super_node", False),
+                    "child_ids": json.dumps(node.get("child_ids", [])),
+                    "parent_id": node.get("parent_id") or "",
+                    "shard_key": node.get("shard_key", "default"),
+                    "metadata": json.dumps(node.get("metadata", {})),
+                }
+            self._version += 1
+
+    def _append_rows_host(self, emb: np.ndarray, user_id: str) -> int:
+        n = emb.shape[0]
+        self._reserve(n)
+        n0 = self._n
+        stage = self._pinned("rows", (n, self._dim_p), torch.float32)
+        stage.zero_()
+        stage[:, :self.dim] = torch.from_numpy(emb)
+        with torch.cuda.device(self.device):
+            self._rows[n0:n0 + n].copy_(stage, non_blocking=True)
+            torch.cuda.current_stream().synchronize()               # staging buffer is reused
+        self._finish_append(n0, n, user_id)
+        return n0
+
+    def _finish_append(self, n0: int, n: int, user_id: str):
+        u = self._user(user_id, create=True)
+        kernels.row_norms(self._rows[n0:n0 + n], self._dim_p, out=self._norms[n0:n0 + n])
+        self._tags[n0:n0 + n] = u
+        self._row_user[n0:n0 + n] = u
+        self._n = n0 + n
+        sp = self._span[u]
+        sp[0], sp[1] = min(sp[0], n0), max(sp[1], n0 + n)
+        self._live[u] += n
+
+    def add_rows(self, rows: torch.Tensor, user_id: str = "default", id_prefix: str = "row_",
+                 first_id: Optional[int] = None) -> int:
+        """Bulk ingest of float32 rows already in HBM (or a numpy array): no per-row Python objects;
+        ids are implicit, f"{id_prefix}{first_id + i}".  Returns the first row index.  This is the
+        ingest used at benchmark scale; `add_nodes` is the reference-shaped call."""
+        with self._lock:
+            if isinstance(rows, np.ndarray):
+                rows = torch.from_numpy(np.ascontiguousarray(rows, dtype=np.float32))
+            if self.dim is None:
+                self._set_dim(int(rows.shape[1]))
+            if rows.shape[1] != self.dim:
+                raise ValueError(f"rows have {rows.shape[1]} dims, store has {self.dim}")
+            n = rows.shape[0]
+            self._reserve(n)
+            n0 = self._n
+            self._rows[n0:n0 + n, :self.dim].copy_(rows.to(torch.float32), non_blocking=True)
+            if self._dim_p != self.dim:
+                self._rows[n0:n0 + n, self.dim:].zero_()
+            self._finish_append(n0, n, user_id)
+            self._blocks.append((n0, n0 + n, id_prefix, n0 if first_id is None else first_id))
+            self._version += 1
+            return n0
+
+    def adopt_rows(self, rows: torch.Tensor, user_id: str = "default", id_prefix: str = "row_"):
+        """Take ownership of a [n, dim] float32 CUDA tensor as the store's row matrix without copying
+        (dim % 8 == 0, store must be empty).  For benchmark-size tables that should exist once in HBM."""
+        with self._lock:
+            assert self._n == 0 and rows.is_cuda and rows.dtype == torch.float32 and rows.is_contiguous()
+            assert rows.shape[1] % 8 == 0, "adopt_rows needs dim % 8 == 0"
+            self.dim = self._dim_p = int(rows.shape[1])
+            self.device = rows.device
+            n = rows.shape[0]
+            self._rows = rows
+            self._norms = torch.empty(n, dtype=torch.float64, device=self.device)
+            self._tags = torch.empty(n, dtype=torch.int32, device=self.device)
+            self._row_user = np.full(n, -1, np.int32)
+            self._finish_append(0, n, user_id)
+            self._blocks.append((0, n, id_prefix, 0))
+            self._version += 1
+
+    def get_nodes(self, user_id: str = "default") -> List[Dict[str, Any]]:
+        with self._lock:
+            u = self._user(user_id)
+            if u < 0 or self._n == 0:                                # vector_store.py:116-117
+                return []
+            rows = np.nonzero(self._row_user[:self._n] == u)[0]
+            if rows.size == 0:
+                return []
+            idx = torch.from_numpy(rows).to(self.device)
+            vecs = self._rows.index_select(0, idx)[:, :self.dim].cpu().numpy()
+            out = []
+            for r, v in zip(rows.tolist(), vecs):
+                m = self._row_meta.get(r, {})
+                d = {"id": self._id_of(r), "user_id": user_id, "content": m.get("content", ""),
+                     "vector": v.tolist(), "type": m.get("type", "semantic"),
+                     "timestamp": m.get("timestamp", 0.0), "access_count": m.get("access_count", 0),
+                     "last_accessed": m.get("last_accessed", 0.0), "salience": m.get("salience", 0.5),
+                     "is_super_node": m.get("is_super_node", False),
+                     "child_ids": json.loads(m.get("child_ids", "[]")),          # vector_store.py:119-129
+                     "parent_id": m.get("parent_id", ""), "shard_key": m.get("shard_key", "default"),
+                     "metadata": json.loads(m.get("metadata", "{}"))}
+                out.append(d)
+            return out
+
+    def search_nodes(self, query_emb: Sequence[float], user_id: str = "default", limit: int = 5) -> List[str]:
+        """vector_store.py:132-140: ids of the `limit` best rows of `user_id`, best first."""
+        with self._lock:
+            u = self._user(user_id)
+            if self._n == 0 or u < 0 or self._live[u] == 0 or limit <= 0:   # vector_store.py:133-134
+                return []
+            q = np.asarray(query_emb, dtype=np.float32).reshape(1, -1)
+            ids, _, counts = self._search_host(q, u, limit)
+            return [self._id_of(r) for r in ids[0, :counts[0]].tolist()]
+
+    def search_batch(self, queries, user_id: str = "default", limit: int = 5, return_scores: bool = False):
+        """Batched form of `search_nodes` (our addition): queries float32 [B, dim] on the host.
+        Returns a list of id lists (and the float64 score lists if asked)."""
+        with self._lock:
+            q = np.ascontiguousarray(queries, dtype=np.float32)
+            u = self._user(user_id)
+            if self._n == 0 or u < 0 or self._live[u] == 0 or limit <= 0:
+                empty = [[] for _ in range(q.shape[0])]
+                return (empty, empty) if return_scores else empty
+            ids, scores, counts = self._search_host(q, u, limit)
+            out = [[self._id_of(r) for r in ids[b, :counts[b]].tolist()] for b in range(q.shape[0])]
+            if return_scores:
+                return out, [scores[b, :counts[b]].tolist() for b in range(q.shape[0])]
+            return out
+
+    def _check_limit(self, limit: int, u: int) -> int:
+        k = min(int(limit), self._live[u])
+        if k > _lib.MAX_K:
+            raise ValueError(f"limit={limit} exceeds the kernel's top-k bound of {_lib.MAX_K}")
+        return max(k, 1)
+
+    def _search_host(self, q: np.ndarray, u: int, limit: int):
+        """host queries [B, dim] -> (row ids int64 [B,k], scores float64 [B,k], counts int32 [B]) as
+        numpy, via pinned staging; one stream synchronisation at the end."""
+        if q.shape[1] != self.dim:
+            raise ValueError(f"query has {q.shape[1]} dims, store has {self.dim}")
+        k = self._check_limit(limit, u)
+        B = q.shape[0]
+        with torch.cuda.device(self.device):
+            stage = self._pinned("q", (B, self._dim_p), torch.float32)
+            if self._dim_p != self.dim:
+                stage.zero_()
+            stage[:, :self.dim] = torch.from_numpy(q)
+            qd = torch.empty((B, self._dim_p), dtype=torch.float32, device=self.device)
+            qd.copy_(stage, non_blocking=True)
+            ids, scores, counts = self.search_device(qd, u, k)
+            h_ids = self._pinned("ids", (B, k), torch.int64)
+            h_sc = self._pinned("sc", (B, k), torch.float64)
+            h_cnt = self._pinned("cnt", (B,), torch.int32)
+            h_ids.copy_(ids, non_blocking=True)
+            h_sc.copy_(scores, non_blocking=True)
+            h_cnt.copy_(counts, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()
+
+    def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10):
+        """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
+        tensors, nothing synchronised.  The exact fp64 scan over the user's row span."""
+        u = self._user(user) if isinstance(user, str) else user
+        lo, hi = self._span[u]
+        single_user = len(self._user_names) == 1 and self._live[u] == self._n
+        tags = None if single_user else self._tags
+        B = queries.shape[0]
+        gs = 4 if B >= 4 else (2 if B >= 2 else 1)
+        n_groups = (B + gs - 1) // gs
+        gtag = None if tags is None else torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
+        n_chunks = kernels.default_chunks(hi - lo, n_groups, self.device)
+        need = int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks))
+        if self._scratch is None or self._scratch.numel() < need:
+            self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, self._metric,
+                                    row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
+                                    scratch=self._scratch)
+
+    def delete_nodes(self, node_ids: List[str], user_id: str = "default"):
+        with self._lock:
+            u = self._user(user_id)
+            if u < 0:
+                return
+            if node_ids is None or len(node_ids) == 0:               # vector_store.py:143-145
+                rows = np.nonzero(self._row_user[:self._n] == u)[0]
+            else:
+                found: List[int] = []
+                for nid in node_ids:
+                    found.extend(self._id_rows.pop((u, nid), []))
+                    found.extend(self._implicit_rows(nid, u))
+                rows = np.asarray(sorted(set(found)), dtype=np.int64)
+                rows = rows[self._row_user[rows] == u] if rows.size else rows
+            if rows.size:
+                self._tags.index_fill_(0, torch.from_numpy(rows.astype(np.int64)).to(self.device), -1)
+                self._row_user[rows] = -1
+                self._live[u] -= int(rows.size)
+                for r in rows.tolist():
+                    rid = self._row_id.pop(r, None)
+                    self._row_meta.pop(r, None)
+                    if rid is not None:
+                        lst = self._id_rows.get((u, rid))
+                        if lst and r in lst:
+                            lst.remove(r)
+                            if not lst:
+                                del self._id_rows[(u, rid)]
+            self._version += 1
+
+    def _implicit_rows(self, nid: str, u: int) -> List[int]:
+        out = []
+        for lo, hi, prefix, first in self._blocks:
+            if nid.startswith(prefix) and nid[len(prefix):].isdigit():
+                r = lo + int(nid[len(prefix):]) - first
+                if lo <= r < hi and r not in self._row_id:
+                    out.append(r)
+        return out
+
+    def get_latest_version(self) -> int:                             # vector_store.py:150-156
+        return self._version
+
+    # ------------------------------------------------------------------ edges (vector_store.py:159-212)
+    def add_edges(self, edges: List[Dict[str, Any]], user_id: str = "default"):
+        if not edges:
+            return
+        with self._lock:
+            for edge in edges:
+                src = edge.get("source") or edge.get("source_id")
+                tgt = edge.get("target") or edge.get("target_id")
+                self._edges.append({
+                    "id": edge.get("id", f"{src}_{tgt}"), "user_id": user_id,
+                    "source_id": src, "target_id": tgt,
+                    "weight": float(np.float32(edge.get("weight", 1.0))),      # float32 column
+                    "edge_type": edge.get("edge_type") or edge.get("type", "relates_to"),
+                    "co_occurrence": edge.get("co_occurrence", 1),
+                    "last_updated": edge.get("last_updated", 0.0),
+                    "metadata": json.dumps(edge.get("metadata", {})),
+                })
+
+    def delete_edges(self, source_id: Optional[str] = None, user_id: str = "default"):
+        with self._lock:
+            self._edges = [e for e in self._edges
+                           if not (e["user_id"] == user_id and (not source_id or e["source_id"] == source_id))]
+
+    def get_edges(self, source_id: Optional[str] = None, user_id: str = "default") -> List[Dict[str, Any]]:
+        with self._lock:
+            out = []
+            for e in self._edges:
+                if e["user_id"] != user_id or (source_id and e["source_id"] != source_id):
+                    continue
+                d = dict(e)
+                d["type"] = d["edge_type"]                            # vector_store.py:204-205
+                d["metadata"] = json.loads(d["metadata"])
+                out.append(d)
+            return out
+
+    # ------------------------------------------------------------------ profiles (vector_store.py:216-233)
+    def save_profile(self, profile_data: Dict[str, Any], user_id: str = "default"):
+        with self._lock:
+            self._profiles[user_id] = {"data": json.dumps(profile_data), "updated_at": time.time()}
+
+    def load_profile(self, user_id: str = "default") -> Optional[Dict[str, Any]]:
+        with self._lock:
+            p = self._profiles.get(user_id)
+            return json.loads(p["data"]) if p else None
+
+    def close(self):                                                  # vector_store.py:235-244
+        with self._lock:
+            self._rows = self._norms = self._tags = self._scratch = None
+            self._pin.clear()
+            self._n = 0
+
+    # ------------------------------------------------------------------ legacy surface
+    # tests/test_vector_store.py:15,43,46,66 and tests/test_lancedb_integration.py:67,79,84
+    def add(self, nodes):
+        return self.add_nodes(nodes)
+
+    def search(self, query_emb=None, limit: int = 5):
+        if query_emb is None:                                         # table-style use, memory_system.py:1438
+            return _UserScan(self)
+        return self.search_nodes(query_emb, limit=limit)
+
+    def delete(self, ids):
+        return self.delete_nodes(ids)
+
+
+class _UserScan:
+    """`store._nodes_table.search().select(["user_id"]).to_list()` (memory_system.py:1434-1439)."""
+
+    def __init__(self, store: B200Store):
+        self._s = store
+
+    def select(self, cols):
+        return self
+
+    def to_list(self):
+        s = self._s
+        return [{"user_id": s._user_names[u]} for u in s._row_user[:s._n].tolist() if u >= 0]
+
+
+# The reference's older name for the same thing (tests/test_vector_store.py:8).
+LanceDBVectorStore = B200Store

@@ -1,0 +1,115 @@
+"""GPU parity: decay / prune / salience sweeps (through the C-ABI) against the numpy oracle and
+against outputs of the reference's own MemoryShard code (tests/golden). Bit-exact."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import graph_ops
+
+pytestmark = pytest.mark.gpu
+
+
+def table(src, dst, w, cooc):
+    from lazzaro_b200.graph import EdgeTable
+    return EdgeTable.from_arrays(src, dst, w, cooc, device="cuda")
+
+
+def test_decay_prune_matches_reference_shard(golden):
+    g = golden
+    t = table(g["dp_src"], g["dp_dst"], g["dp_w"], g["dp_cooc"])
+    pruned = t.decay_prune(graph_ops.decay_factor(0.01), 0.5)          # memory_shard.py:64-84 fused
+    s, d, w, c = t.to_numpy()
+    assert pruned == int(g["dp_pruned"])
+    np.testing.assert_array_equal(np.stack([s, d], 1), g["dp_kept"])   # same survivors, same order
+    np.testing.assert_array_equal(w, g["dp_kept_w"].astype(np.float32))
+    assert (c == 1).all()
+
+
+def test_separate_decay_then_prune_equals_reference(golden):
+    g = golden
+    t = table(g["dp_src"], g["dp_dst"], g["dp_w"], g["dp_cooc"])
+    t.decay(0.99)
+    np.testing.assert_array_equal(t.to_numpy()[2], g["dp_w_after"].astype(np.float32))
+    # pruning the float32-rounded weights may differ from the float64 reference only inside the
+    # documented tie band |w - thr| <= 2^-24 * thr
+    pruned = t.decay_prune(1.0, 0.5)
+    w64 = g["dp_w_after"]
+    band = np.abs(w64 - 0.5) <= 2.0 ** -24 * 0.5
+    assert abs(pruned - int(g["dp_pruned"])) <= int(band.sum())
+
+
+def test_salience_matches_reference(golden):
+    from lazzaro_b200 import kernels
+    s = torch.tensor(golden["dp_sal"], device="cuda")
+    kernels.salience_decay(s, s.numel(), 0.01, 0.2)
+    np.testing.assert_array_equal(s.cpu().numpy(), golden["dp_sal_after"].astype(np.float32))
+
+
+@pytest.mark.parametrize("n", [0, 1, 7, 2047, 2048, 2049, 100_003, 1_000_000])
+@pytest.mark.parametrize("thr", [0.5, 0.0, 2.0])
+def test_decay_prune_sizes_and_extremes(n, thr):
+    from lazzaro_b200 import synth
+    src, dst, w, cooc = synth.edge_table(n, 1000, seed=n + 1)
+    cooc = np.arange(n, dtype=np.int32)
+    t = table(src, dst, w, cooc)
+    pruned = t.decay_prune(0.99, thr)
+    es, ed, ew, ec, ep = graph_ops.decay_prune_edges(src, dst, w, cooc, 0.99, thr)
+    s, d, ww, c = t.to_numpy()
+    assert pruned == ep and t.n == n - ep
+    np.testing.assert_array_equal(s, es); np.testing.assert_array_equal(d, ed)
+    np.testing.assert_array_equal(ww, ew); np.testing.assert_array_equal(c, ec)
+
+
+def test_out_of_place_and_idempotence():
+    from lazzaro_b200 import kernels, synth
+    n = 300_000
+    src, dst, w, cooc = synth.edge_table(n, 5000, seed=4)
+    ins = [torch.as_tensor(a).cuda() for a in (src, dst, w, cooc)]
+    outs = [torch.empty_like(a) for a in ins]
+    kept, _ = kernels.edge_decay_prune(*ins, n, 0.99, 0.5, out=tuple(outs))
+    k = int(kept.item())
+    es, ed, ew, ec, ep = graph_ops.decay_prune_edges(src, dst, w, cooc, 0.99, 0.5)
+    assert k == n - ep
+    np.testing.assert_array_equal(outs[2][:k].cpu().numpy(), ew)
+    np.testing.assert_array_equal(ins[2].cpu().numpy(), w)             # inputs untouched
+    # pruning the survivors again with factor 1 removes nothing (idempotence)
+    kept2, _ = kernels.edge_decay_prune(*[o[:k] for o in outs], k, 1.0, 0.5)
+    assert int(kept2.item()) == k
+    np.testing.assert_array_equal(outs[0][:k].cpu().numpy(), es)
+
+
+def test_full_size_50m_edges_properties():
+    """cfg5 size: 50M edges — sizes the oracle still handles in seconds with numpy."""
+    from lazzaro_b200 import synth
+    n = 50_000_000
+    src, dst, w, cooc = synth.edge_table(n, 100_000_000 // 1000)
+    t = table(src, dst, w, cooc)
+    pruned = t.decay_prune(0.99, 0.5)
+    es, ed, ew, ec, ep = graph_ops.decay_prune_edges(src, dst, w, cooc, 0.99, 0.5)
+    assert pruned == ep
+    s, d, ww, c = t.to_numpy()
+    assert np.array_equal(s, es) and np.array_equal(d, ed) and np.array_equal(ww, ew)
+    assert (ww >= np.float32(0.5) - 1e-7).all()
+
+
+def test_memory_shard_mirror_runs_reference_scenario():
+    """tests/test_profile_update.py:32-78 through our MemoryShard mirror: edges 0.8 survive a decay
+    and a prune at 0.5; a fresh chain edge of 0.5 decays to 0.495 and is pruned."""
+    from lazzaro_b200.graph import BufferGraph, Edge, MemoryShard, Node
+    shard = MemoryShard("default", device="cuda")
+    for i in range(4):
+        shard.add_node(Node(id=f"seed_{i}", content=f"m{i}", salience=0.9))
+    for i in range(3):
+        shard.add_edge(Edge(source=f"seed_{i}", target=f"seed_{i+1}", weight=0.8))
+    shard.add_edge(Edge(source="seed_0", target="seed_3", weight=0.5))
+    shard.add_edge(Edge(source="seed_0", target="seed_1", weight=0.8))        # reinforce: 0.9, cooc 2
+    bg = BufferGraph({"default": shard})
+    bg.apply_temporal_decay(0.01)
+    assert bg.prune_weak_edges(0.5) == 1
+    edges = shard.edges
+    assert set(edges) == {("seed_0", "seed_1"), ("seed_1", "seed_2"), ("seed_2", "seed_3")}
+    assert edges[("seed_0", "seed_1")].co_occurrence == 2
+    assert edges[("seed_0", "seed_1")].weight == pytest.approx(np.float32(np.float32(0.9) * 0.99), rel=1e-7)
+    assert shard.nodes["seed_0"].salience == pytest.approx(0.893, abs=1e-6)   # 0.2 + 0.7*0.99
+    assert shard.get_neighbors("seed_1") == ["seed_0", "seed_2"]
+    assert shard.size() == (4, 3)

@@ -1,0 +1,102 @@
+"""GPU: B200Store behind the reference's Store protocol — the reference's own store tests,
+retargeted (tests/test_vector_store.py, tests/test_lancedb_integration.py), and call-for-call
+equivalence with the oracle FlatStore."""
+import numpy as np
+import pytest
+
+from oracle.flat_store import FlatStore
+
+pytestmark = pytest.mark.gpu
+
+
+def legacy_nodes():
+    return [
+        {"id": "node_1", "content": "I like apples", "embedding": [0.1] * 1536, "type": "semantic",
+         "salience": 0.8, "shard_key": "food", "timestamp": 1234.5},
+        {"id": "node_2", "content": "I hate oranges", "embedding": [-0.1] * 1536, "type": "semantic",
+         "salience": 0.5, "shard_key": "food", "timestamp": 1235.0},
+    ]
+
+
+@pytest.mark.parametrize("metric", ["cosine", "l2"])
+def test_reference_vector_store_tests(metric):
+    # tests/test_vector_store.py:22-68
+    from lazzaro_b200.store import LanceDBVectorStore
+    vs = LanceDBVectorStore(db_dir="test_vector_db", metric=metric)
+    vs.add(legacy_nodes())
+    results = vs.search([0.1] * 1536, limit=1)
+    assert len(results) == 1 and results[0] == "node_1"
+    vs.delete(["node_1"])
+    assert vs.search([0.1] * 1536, limit=1) == ["node_2"]
+    vs.delete(["node_2"])
+    assert vs.search([0.1] * 1536, limit=1) == []
+    vs.close()
+
+
+def test_store_matches_flat_store_call_for_call():
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    rows, shard = synth.clustered_rows(3000, 96, 6, seed=14)
+    qs = synth.queries_near_rows(rows, 12, seed=15)
+    ours, ref = B200Store(capacity=64), FlatStore()
+    users = ["alice", "bob", "carol"]
+    v0 = ours.get_latest_version()
+    for st in (ours, ref):
+        assert st.search_nodes(qs[0].tolist()) == [] and st.get_nodes("alice") == []
+        for lo in range(0, 3000, 500):
+            u = users[(lo // 500) % 3]
+            st.add_nodes([{"id": f"n{i}", "content": f"c{i}", "embedding": rows[i].tolist(),
+                           "shard_key": f"s{shard[i]}", "salience": 0.25 + (i % 3) / 4,
+                           "child_ids": [f"n{i+1}"], "metadata": {"i": i}} for i in range(lo, lo + 500)], user_id=u)
+    assert ours.get_latest_version() > v0
+    for u in users + ["nobody"]:
+        for q in qs:
+            for limit in (1, 5, 40):
+                assert ours.search_nodes(q.tolist(), user_id=u, limit=limit) == ref.search_nodes(q.tolist(), user_id=u, limit=limit)
+    assert ours.search_batch(qs, "bob", 7) == [ref.search_nodes(q.tolist(), "bob", 7) for q in qs]
+    for st in (ours, ref):
+        st.delete_nodes([f"n{i}" for i in range(0, 3000, 7)], user_id="alice")
+        st.delete_nodes([], user_id="carol")                      # empty list = all of the user
+    for u in users:
+        for q in qs[:4]:
+            assert ours.search_nodes(q.tolist(), user_id=u, limit=10) == ref.search_nodes(q.tolist(), user_id=u, limit=10)
+    a, b = ours.get_nodes("alice"), ref.get_nodes("alice")
+    assert [x["id"] for x in a] == [x["id"] for x in b]
+    for x, y in zip(a[:20], b[:20]):
+        assert x["vector"] == y["vector"] and x["child_ids"] == y["child_ids"] and x["metadata"] == y["metadata"]
+        assert x["salience"] == y["salience"] and x["shard_key"] == y["shard_key"]
+    # edges / profiles round trip (vector_store.py:159-233)
+    for st in (ours, ref):
+        st.add_edges([{"source": "n1", "target": "n2", "weight": 0.9}, {"source_id": "n2", "target_id": "n3", "type": "x"}], "alice")
+        st.save_profile({"a": 1}, "alice")
+    assert ours.get_edges(user_id="alice") == ref.get_edges(user_id="alice")
+    assert ours.get_edges("n2", "alice")[0]["type"] == "x" and ours.load_profile("alice") == {"a": 1}
+    assert ours.load_profile("bob") is None
+    ours.delete_edges("n1", "alice")
+    assert [e["source_id"] for e in ours.get_edges(user_id="alice")] == ["n2"]
+
+
+def test_search_memories_golden_through_b200_store(golden):
+    """memory_system.py:1460-1472 recorded from the reference over the oracle store: our store
+    returns the same id lists for the same rows and queries."""
+    import json
+    from lazzaro_b200.store import B200Store
+    g = golden
+    st = B200Store()
+    st.add_nodes([{"id": f"node_{i}", "content": f"memory {i}", "embedding": r.tolist()} for i, r in enumerate(g["sm_rows"])])
+    missing = {f"node_{i}" for i in g["sm_missing"].tolist()}
+    want = json.loads(str(g["sm_ids"]))
+    for q, w in zip(g["sm_queries"], want):
+        got = [i for i in st.search_nodes(q.tolist(), limit=10) if i not in missing]
+        assert got == w
+
+
+def test_limit_bound_is_loud():
+    from lazzaro_b200.store import B200Store
+    st = B200Store()
+    st.add_rows(np.random.default_rng(0).standard_normal((3000, 16)).astype(np.float32))
+    assert len(st.search_nodes([0.1] * 16, limit=1024)) == 1024
+    with pytest.raises(ValueError):
+        st.search_nodes([0.1] * 16, limit=2000)
+    with pytest.raises(ValueError):
+        st.search_nodes([0.1] * 17, limit=1)
