@@ -87,12 +87,14 @@ int lz_search_exact_default_chunks(int64_t n_rows, int n_groups);
  *   scratch    >= lz_search_exact_scratch_bytes(n_queries, k, n_chunks) bytes; contents are
  *              overwritten; concurrent calls must not share it
  *   norms      may be NULL for LZ_L2
+ *   id_base    added to every returned row index (a partition's first global row id, so that
+ *              per-GPU results can be merged by lz_merge_topk without another pass)
  */
 int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
                     int64_t row_lo, int64_t row_hi,
                     const int64_t* group_lo, const int64_t* group_hi, const int32_t* group_tag,
                     const float* queries, int64_t q_ld, int n_queries, int group_size,
-                    int k, int metric, int n_chunks,
+                    int k, int metric, int n_chunks, int64_t id_base,
                     void* scratch, size_t scratch_bytes,
                     int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
 

@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
 struct MergeParams {
     const u64* part_key; const u32* part_id; const int32_t* part_cnt;   // form A: scan partials
     const int64_t* in_ids; const double* in_scores; int n_queries;      // form B: (id, score) lists
-    int n_lists; int k; int cap; int metric;
+    int n_lists; int k; int cap; int metric; int64_t id_base;
     int64_t* out_ids; double* out_scores; int32_t* out_counts;
 };
 
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
     for (int j = tid; j < p.k; j += kThreads) {
         if (j < n) {
             const double v = lz_unord(sel.key[j]);
-            p.out_ids[(size_t)q * p.k + j] = (int64_t)sel.id[j];
+            p.out_ids[(size_t)q * p.k + j] = (int64_t)sel.id[j] + p.id_base;
             p.out_scores[(size_t)q * p.k + j] = (p.metric == LZ_COSINE) ? v : 0.0 - v;
         } else {
             p.out_ids[(size_t)q * p.k + j] = -1;
@@ -350,7 +350,8 @@ extern "C" int lz_search_exact_default_chunks(int64_t n_rows, int n_groups) {
 extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
                                int64_t row_lo, int64_t row_hi, const int64_t* group_lo, const int64_t* group_hi,
                                const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
-                               int group_size, int k, int metric, int n_chunks, void* scratch, size_t scratch_bytes,
+                               int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
+                               size_t scratch_bytes,
                                int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream) {
     if (n_queries <= 0) return LZ_OK;
     if (int rc = check_rows("lz_search_exact", rows, ld, dim)) return rc;
@@ -389,7 +390,7 @@ extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const dou
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
     m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries;
-    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric;
+    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = id_base;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
     const size_t msmem = (size_t)m.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
@@ -407,7 +408,7 @@ extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int
     MergeParams m;
     m.part_key = nullptr; m.part_id = nullptr; m.part_cnt = nullptr;
     m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries;
-    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric;
+    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = 0;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
     const size_t msmem = (size_t)m.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));

@@ -1,0 +1,98 @@
+"""Multi-GPU search: rows partitioned across the GPUs of one box, per-GPU top-k merged after an
+all-gather.
+
+One process per GPU (torchrun); rank r holds whole semantic shards — a contiguous slab of global row
+ids [row_offset, row_offset + n_local).  A search broadcasts nothing (every rank is handed the same
+query batch), runs the local exact scan with `id_base = row_offset` so the ids it emits are already
+global, all-gathers the (ids int64, scores float64) lists — B*k*16 bytes per rank over NVLink — and
+merges them on every rank with lz_merge_topk under the same (score desc, id asc) order, which makes
+the merge associative and the result identical to a single-GPU search.  Decay, prune and shard
+assignment are shard-local and need no collective.
+
+The reference has no distributed code at all; this module is the data-parallel layout
+north_star asks for.  `local_search` / `merge` are injectable so the gather/merge bookkeeping can be
+tested on CPU with gloo (tests/test_dist_gloo.py) — the product path always uses the CUDA kernels.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def partition_shards(shard_rows: Sequence[int], world: int) -> List[List[int]]:
+    """Greedy bin-packing of semantic shards onto GPUs by row count (largest first); returns the
+    shard indices owned by each rank.  Each shard lives wholly on one GPU."""
+    order = sorted(range(len(shard_rows)), key=lambda s: (-shard_rows[s], s))
+    load = [0] * world
+    owned: List[List[int]] = [[] for _ in range(world)]
+    for s in order:
+        r = min(range(world), key=lambda i: (load[i], i))
+        owned[r].append(s)
+        load[r] += shard_rows[s]
+    return [sorted(o) for o in owned]
+
+
+def even_slabs(n_rows: int, world: int) -> List[Tuple[int, int]]:
+    """[lo, hi) global row ranges of equal size (the last rank takes the remainder)."""
+    per = n_rows // world
+    return [(r * per, (r + 1) * per if r < world - 1 else n_rows) for r in range(world)]
+
+
+class ShardedSearch:
+    def __init__(self, store, row_offset: int = 0, world: Optional[int] = None, group=None,
+                 local_search: Optional[Callable] = None, merge: Optional[Callable] = None):
+        self.store = store
+        self.row_offset = int(row_offset)
+        self.group = group
+        self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
+        self._local = local_search or self._local_cuda
+        self._merge = merge or self._merge_cuda
+        self._gather_ids = self._gather_sc = None
+
+    # -- the product path
+    def _local_cuda(self, queries: torch.Tensor, k: int):
+        ids, sc, cnt = self.store.search_device(queries, 0, k, id_base=self.row_offset)
+        return ids, sc, cnt
+
+    def _merge_cuda(self, ids: torch.Tensor, scores: torch.Tensor):
+        from . import kernels
+        return kernels.merge_topk(ids, scores, self.store._metric)
+
+    def search_device(self, queries: torch.Tensor, k: int):
+        """queries float32 [B, dim_p] on this rank's GPU (same batch on every rank) -> global
+        (ids int64 [B,k], scores float64 [B,k], counts int32 [B]) on every rank."""
+        ids, sc, cnt = self._local(queries, k)
+        if self.world == 1:
+            return ids, sc, cnt
+        B = ids.shape[0]
+        if self._gather_ids is None or self._gather_ids.shape[1:] != (B, k):
+            self._gather_ids = torch.empty((self.world, B, k), dtype=torch.int64, device=ids.device)
+            self._gather_sc = torch.empty((self.world, B, k), dtype=torch.float64, device=ids.device)
+        dist.all_gather_into_tensor(self._gather_ids, ids, group=self.group)
+        dist.all_gather_into_tensor(self._gather_sc, sc, group=self.group)
+        return self._merge(self._gather_ids, self._gather_sc)
+
+    def search_host(self, queries: np.ndarray, k: int):
+        """Host queries in, host (ids, scores, counts) out: pinned H2D, search, D2H, one sync."""
+        st = self.store
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        B = q.shape[0]
+        with torch.cuda.device(st.device):
+            stage = st._pinned("q", (B, st._dim_p), torch.float32)
+            if st._dim_p != st.dim:
+                stage.zero_()
+            stage[:, :st.dim] = torch.from_numpy(q)
+            qd = torch.empty((B, st._dim_p), dtype=torch.float32, device=st.device)
+            qd.copy_(stage, non_blocking=True)
+            ids, sc, cnt = self.search_device(qd, k)
+            h_ids = st._pinned("ids", (B, k), torch.int64)
+            h_sc = st._pinned("sc", (B, k), torch.float64)
+            h_cnt = st._pinned("cnt", (B,), torch.int32)
+            h_ids.copy_(ids, non_blocking=True)
+            h_sc.copy_(sc, non_blocking=True)
+            h_cnt.copy_(cnt, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()

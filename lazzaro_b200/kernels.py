@@ -41,7 +41,7 @@ def search_exact(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], ta
                  row_range: Optional[Tuple[int, int]] = None,
                  group_lo: Optional[torch.Tensor] = None, group_hi: Optional[torch.Tensor] = None,
                  group_tag: Optional[torch.Tensor] = None, group_size: Optional[int] = None,
-                 n_chunks: Optional[int] = None, scratch: Optional[torch.Tensor] = None,
+                 n_chunks: Optional[int] = None, scratch: Optional[torch.Tensor] = None, id_base: int = 0,
                  out: Optional[Tuple[torch.Tensor, torch.Tensor, torch.Tensor]] = None):
     """Exhaustive float64 top-k (lz_search_exact). Returns (ids int64 [B,k], scores float64 [B,k],
     counts int32 [B]) on the device, unsynchronised."""
@@ -70,7 +70,7 @@ def search_exact(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], ta
         ids, scores, counts = out
         check(lib.lz_search_exact(ptr(rows), rows.stride(0), dim, ptr(norms), ptr(tags), lo, hi,
                                   ptr(group_lo), ptr(group_hi), ptr(group_tag),
-                                  ptr(queries), queries.stride(0), B, group_size, k, metric, n_chunks,
+                                  ptr(queries), queries.stride(0), B, group_size, k, metric, n_chunks, int(id_base),
                                   ptr(scratch), scratch.numel(), ptr(ids), ptr(scores), ptr(counts),
                                   stream_ptr(dev)), "lz_search_exact")
     return ids, scores, counts

@@ -299,7 +299,7 @@ class B200Store:
             torch.cuda.current_stream().synchronize()
         return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()
 
-    def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10):
+    def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
         tensors, nothing synchronised.  The exact fp64 scan over the user's row span."""
         u = self._user(user) if isinstance(user, str) else user
@@ -316,7 +316,7 @@ class B200Store:
             self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
         return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, self._metric,
                                     row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
-                                    scratch=self._scratch)
+                                    scratch=self._scratch, id_base=id_base)
 
     def delete_nodes(self, node_ids: List[str], user_id: str = "default"):
         with self._lock:
