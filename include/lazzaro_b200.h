@@ -131,6 +131,33 @@ int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* wei
                         int32_t* out_src, int32_t* out_dst, float* out_weight, int32_t* out_cooc,
                         int64_t* out_kept, void* scratch, size_t scratch_bytes, void* stream);
 
+/*
+ * The same sweep for callers that cannot allocate device memory where it runs.  (No counterpart in
+ * the reference: it exists because of how this library is deployed, not because of the algorithm.)
+ * Such callers are, for example, a service that filled HBM with the row store at start-up, where a
+ * late cudaMalloc may fail and would in any case synchronise the device under the searches in
+ * flight, or a plain-C / cgo / JNI binding that owns the edge columns but has no device allocator
+ * to ask for scratch.  The look-back words live in an array inside the library image instead
+ * (256 KiB + 8 B of global memory on every GPU that loads the library, kept until the process exits),
+ * so this call takes inputs and outputs only and never calls cudaMalloc, cudaFree or any allocating
+ * routine.
+ *   limit      n <= LZ_NOALLOC_MAX_EDGES (2^26 = 67,108,864 edges); a larger n is rejected with
+ *              LZ_ERR_ARG and a message — use lz_edge_decay_prune with your own scratch for those.
+ *   first call the first call on each device looks the array's address up (with that device
+ *              current) and caches it; make that first call outside of any stream capture.
+ *   sharing    every call on a device uses the same array and finds the previous call's contents
+ *              in it; the call zeroes the words it needs on `stream` before the kernel, so calls
+ *              issued one after another on one stream are fine, but two calls that can overlap on
+ *              the GPU (different streams, different host threads) race on it and corrupt each
+ *              other — serialise them, or use lz_edge_decay_prune with separate scratch buffers.
+ * Arguments, results and aliasing rules are otherwise those of lz_edge_decay_prune.
+ */
+#define LZ_NOALLOC_MAX_EDGES 67108864
+int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* dst, const float* weight, const int32_t* cooc,
+                                int64_t n, double factor, double threshold,
+                                int32_t* out_src, int32_t* out_dst, float* out_weight, int32_t* out_cooc,
+                                int64_t* out_kept, void* stream);
+
 /* Decay only: weight[i] = float32(double(weight[i]) * factor) in place (memory_shard.py:69-70). */
 int lz_edge_decay(float* weight, int64_t n, double factor, void* stream);
 

@@ -8,6 +8,8 @@
 // has not started).  Survivors are staged in shared memory and written back coalesced.
 #include "lz_common.cuh"
 
+#include <mutex>
+
 namespace {
 
 constexpr int kThreads = 256;
@@ -270,6 +272,85 @@ extern "C" int lz_salience_decay(float* salience, int64_t n, double rate, double
     LZ_REQUIRE(salience && ((uintptr_t)salience & 15) == 0,
                "lz_salience_decay: salience must be non-NULL and 16-byte aligned");
     salience_kernel<<<elementwise_blocks(n), kThreads, 0, (cudaStream_t)stream>>>(salience, n, 1.0 - rate, floor);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+// ---- allocation-free variant of the decay + prune sweep --------------------------------------------
+//
+// lz_edge_decay_prune needs a small device buffer (one ticket word + one look-back word per tile of
+// 2048 edges) that its caller must allocate.  Some callers of this library cannot do that at the
+// point where the sweep runs:
+//   * a service that sized the row store to fill HBM and pre-allocated everything at start-up — a
+//     late cudaMalloc can fail there, and cudaMalloc/cudaFree also synchronise the device, which
+//     would stall the searches running on other streams while a conversation is being closed;
+//   * a binding written against the bare C-ABI (C, Go/cgo, a JNI shim) that has device pointers for
+//     its edge columns but no device allocator of its own to ask for scratch.
+// For them the buffer below lives in the library image itself: a file-scope __device__ array, one
+// copy per GPU that loads the library, held until the process exits.  Its size fixes the largest
+// table the entry point accepts (kNoAllocMaxEdges); larger tables must use lz_edge_decay_prune.
+namespace {
+constexpr int64_t kNoAllocMaxEdges = LZ_NOALLOC_MAX_EDGES;                 // 2^26 edges
+constexpr int64_t kNoAllocMaxTiles = kNoAllocMaxEdges / kTile;             // 32768 tiles
+}  // namespace
+
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + 1];   // 256 KiB + 8 B
+
+namespace {
+std::mutex g_noalloc_mu;
+void* g_noalloc_addr[64] = {nullptr};      // device address of g_noalloc_scratch, per device ordinal
+
+// In host code `g_noalloc_scratch` is only a handle for the symbol, not a device address, so it must
+// never be handed to a kernel as is.  The real address is looked up once per device (with that
+// device current) and cached.
+int noalloc_scratch(void** out) {
+    int dev = 0;
+    LZ_CUDA(cudaGetDevice(&dev));
+    LZ_REQUIRE(dev >= 0 && dev < 64, "lz_edge_decay_prune_noalloc: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (g_noalloc_addr[dev] == nullptr) {
+        void* addr = nullptr;
+        LZ_CUDA(cudaGetSymbolAddress(&addr, g_noalloc_scratch));
+        LZ_REQUIRE(addr != nullptr, "lz_edge_decay_prune_noalloc: cudaGetSymbolAddress returned NULL");
+        g_noalloc_addr[dev] = addr;
+    }
+    *out = g_noalloc_addr[dev];
+    return LZ_OK;
+}
+}  // namespace
+
+extern "C" int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* dst, const float* weight,
+                                           const int32_t* cooc, int64_t n, double factor, double threshold,
+                                           int32_t* out_src, int32_t* out_dst, float* out_weight,
+                                           int32_t* out_cooc, int64_t* out_kept, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(out_kept != nullptr, "lz_edge_decay_prune_noalloc: out_kept is NULL");
+    LZ_REQUIRE(n >= 0, "lz_edge_decay_prune_noalloc: n=%lld", (long long)n);
+    LZ_REQUIRE(n <= kNoAllocMaxEdges,
+               "lz_edge_decay_prune_noalloc: n=%lld exceeds the built-in scratch limit of %lld edges; "
+               "use lz_edge_decay_prune with caller-provided scratch",
+               (long long)n, (long long)kNoAllocMaxEdges);
+    if (n == 0) {
+        LZ_CUDA(cudaMemsetAsync(out_kept, 0, sizeof(int64_t), st));
+        return LZ_OK;
+    }
+    LZ_REQUIRE(src && dst && weight && cooc && out_src && out_dst && out_weight && out_cooc,
+               "lz_edge_decay_prune_noalloc: NULL pointer");
+    LZ_REQUIRE((((uintptr_t)src | (uintptr_t)dst | (uintptr_t)weight | (uintptr_t)cooc) & 15) == 0,
+               "lz_edge_decay_prune_noalloc: edge arrays must be 16-byte aligned");
+    void* scratch = nullptr;
+    if (int rc = noalloc_scratch(&scratch)) return rc;
+    const int64_t tiles = (n + kTile - 1) / kTile;
+    // the array still holds the previous call's ticket and look-back words: start them from zero
+    LZ_CUDA(cudaMemsetAsync(scratch, 0, (size_t)(tiles + 1) * sizeof(u64), st));
+    PruneParams p;
+    p.src = src; p.dst = dst; p.w = weight; p.cooc = cooc;
+    p.o_src = out_src; p.o_dst = out_dst; p.o_w = out_weight; p.o_cooc = out_cooc;
+    p.n = n; p.factor = factor; p.thr = threshold;
+    p.ticket = (u32*)scratch;
+    p.state = (u64*)scratch + 1;
+    p.out_kept = out_kept; p.n_tiles = (int)tiles;
+    decay_prune_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
