@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(_HERE, "liblazzaro_b200.so")
 
 OK, ERR_ARG, ERR_CUDA, ERR_SCRATCH, ERR_DEVICE = 0, -1, -2, -3, -4
 COSINE, L2 = 0, 1
-MAX_K, MAX_GROUP = 1024, 4
+MAX_K, MAX_GROUP, BATCHED_MAX_K = 1024, 4, 128
 METRICS = {"cosine": COSINE, "l2": L2}
 
 _p, _i32, _i64, _f64, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_double, C.c_size_t
@@ -28,6 +28,10 @@ SIGNATURES = {
     "lz_search_exact_default_chunks": (_i32, [_i64, _i32]),
     "lz_search_exact": (_i32, [_p, _i64, _i32, _p, _p, _i64, _i64, _p, _p, _p, _p, _i64, _i32, _i32,
                                _i32, _i32, _i32, _i64, _p, _sz, _p, _p, _p, _p]),
+    "lz_rows_to_bf16": (_i32, [_p, _i64, _i32, _i64, _p, _p, _p]),
+    "lz_search_batched_scratch_bytes": (_sz, [_i64, _i32, _i32, _i32]),
+    "lz_search_batched": (_i32, [_p, _p, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _i32, _i32, _f64,
+                                 _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),
     "lz_edge_decay_prune_scratch_bytes": (_sz, [_i64]),

@@ -31,7 +31,16 @@ void lz_set_error(const char* fmt, ...);
         }                                                                                     \
     } while (0)
 
-int lz_sm_count();   // SM count of the current device (cached per device), <= 0 on failure
+int lz_sm_count();
+
+// lz_search_exact with an optional per-query skip mask (device int32 [n_queries], non-zero = leave the
+// query's outputs untouched).  Used by the batched search to re-run only the uncertified queries.
+int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
+                         int64_t row_lo, int64_t row_hi, const int64_t* group_lo, const int64_t* group_hi,
+                         const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
+                         int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
+                         size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
+                         const int32_t* query_skip, void* stream);   // SM count of the current device (cached per device), <= 0 on failure
 
 // ---- device helpers ----------------------------------------------------------------------------
 

@@ -1,0 +1,560 @@
+// K2: batched cosine search as a tensor-core contraction with a fused candidate epilogue.
+//
+//   coarse pass   scores[q, row] = bf16(q/|q|) . bf16(x/|x|), fp32 accumulate in TMEM: a persistent,
+//                 warp-specialised tcgen05 GEMM (TMA 128B-swizzled tiles -> shared memory ring ->
+//                 tcgen05.mma 128x256x16 -> double-buffered TMEM accumulators).  The B x N score matrix
+//                 is never written: four epilogue warps read each accumulator tile with tcgen05.ld
+//                 (one query per thread, i.e. per TMEM lane) and keep, per query, the best KP coarse
+//                 candidates of the CTA's slice of the rows (threshold compare, append, warp-cooperative
+//                 bitonic compaction).
+//   exact pass    per query: merge the slices' candidates by coarse score, rescore the best KP in
+//                 float64 from the float32 rows (same summation order as the exact scan, so certified
+//                 results are bit-identical to it), select the top-k with the id tie-break, and CERTIFY:
+//                 every row dropped anywhere had coarse score <= T, hence exact score <= T + eps; if the
+//                 k-th exact score exceeds T + eps the top-k is complete.
+//   fallback      queries that fail certification are re-run by the exact float64 scan (still on the
+//                 GPU), so the call always returns the exact answer.
+//
+// Stands behind LanceDBStore.search_nodes (core/vector_store.py:132-140) for query batches, and behind
+// the dedup / linking scans of core/memory_system.py:719-742, 838-891 (same contraction, small k).
+#include <cuda_bf16.h>
+
+#include "lz_common.cuh"
+#include "lz_sm100.cuh"
+#include "lz_topk.cuh"
+
+namespace {
+
+using namespace sm100;
+
+constexpr int BM = 128;                 // queries per tile  (MMA M, one TMEM lane per query)
+constexpr int BN = 256;                 // rows per tile     (MMA N, one TMEM column per row)
+constexpr int BK = 64;                  // bf16 elements per pipeline stage = one 128-byte swizzle row
+constexpr int kStages = 4;
+constexpr int A_BYTES = BM * BK * 2;    // 16 KiB
+constexpr int B_BYTES = BN * BK * 2;    // 32 KiB
+constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int kGemmThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
+constexpr int kTmemCols = 512;          // two 128x256 fp32 accumulators
+constexpr int kSelThreads = 256;
+
+__device__ __forceinline__ u32 ord32(float v) {
+    u32 b = __float_as_uint(v);
+    return (b >> 31) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float unord32(u32 k) {
+    u32 b = (k >> 31) ? (k & 0x7fffffffu) : ~k;
+    return __uint_as_float(b);
+}
+
+// ---- preparation: normalised bf16 copies ------------------------------------------------------------
+__global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restrict__ rows, int64_t n, int dim, int64_t ld,
+                                                           const double* __restrict__ norms,
+                                                           __nv_bfloat16* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int64_t nwarps = (int64_t)gridDim.x * 8;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const double nr = norms[r];
+        const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
+        const float* x = rows + r * ld;
+        __nv_bfloat16* o = out + r * dim;
+        for (int e = lane * 4; e < dim; e += 128) {
+            const float4 v = lz_ldg_stream(x + e);
+            __nv_bfloat162 a = __floats2bfloat162_rn(v.x * inv, v.y * inv);
+            __nv_bfloat162 b = __floats2bfloat162_rn(v.z * inv, v.w * inv);
+            uint2 pk;
+            pk.x = *reinterpret_cast<u32*>(&a);
+            pk.y = *reinterpret_cast<u32*>(&b);
+            *reinterpret_cast<uint2*>(o + e) = pk;
+        }
+    }
+}
+
+// one warp per query: normalised bf16 copy + the certification margin eps[q]
+__global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
+                                                              __nv_bfloat16* __restrict__ out, double* __restrict__ eps,
+                                                              int32_t* __restrict__ gtag, int want_tag, double sigmas) {
+    const int lane = threadIdx.x & 31;
+    const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (w >= n) return;
+    const float* v = q + (int64_t)w * q_ld;
+    double ss = 0.0;
+    float mx = 0.f;
+    for (int e = lane; e < dim; e += 32) {
+        const float x = v[e];
+        ss = fma((double)x, (double)x, ss);
+        mx = fmaxf(mx, fabsf(x));
+    }
+    ss = lz_warp_sum(ss);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    const double nr = sqrt(ss);
+    const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
+    for (int e = lane; e < dim; e += 32) out[(int64_t)w * dim + e] = __float2bfloat16_rn(v[e] * inv);
+    if (lane == 0) {
+        // bf16 rounding: each operand carries an independent relative error uniform in +-2^-9, so the
+        // coarse dot of unit vectors errs with std <= 2^-9*sqrt(2/3)*max|q_i| (sum x_i^2 q_i^2 <=
+        // max q_i^2); fp32 accumulation adds a few 1e-7.  eps = sigmas * that + 8e-6.
+        eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)(mx * inv) + 8e-6;
+        gtag[w] = want_tag;
+    }
+}
+
+// ---- the coarse pass ----------------------------------------------------------------------------------
+struct GemmParams {
+    int n_queries, n_qtiles, n_slices, tiles_per_slice, n_tiles, kblocks;
+    int64_t row_lo, row_hi;
+    int kp, cap;
+    const int32_t* tags;
+    int want_tag;
+    u64* cand;          // [n_items][BM][cap]  key = ord32(coarse) << 32 | (0xffffffff - row)
+    int32_t* cand_cnt;  // [n_items][BM]
+    float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
+};
+
+// Warp-cooperative compaction of the candidate buffers of the lanes in `need`: sort descending in the
+// warp's shared scratch, keep the best kp, raise that lane's threshold to the kp-th coarse score.
+__device__ __forceinline__ void warp_compact(unsigned need, u64* my_buf, int& count, float& thr, u64* scratch,
+                                             int cap, int kp, int lane) {
+    __syncwarp();
+    while (need) {
+        const int L = __ffs(need) - 1;
+        need &= need - 1;
+        u64* src = reinterpret_cast<u64*>(__shfl_sync(0xffffffffu, (unsigned long long)my_buf, L));
+        const int n = __shfl_sync(0xffffffffu, count, L);
+        for (int j = lane; j < cap; j += 32) scratch[j] = j < n ? src[j] : 0ull;
+        __syncwarp();
+        for (int size = 2; size <= cap; size <<= 1) {
+            for (int stride = size >> 1; stride > 0; stride >>= 1) {
+                for (int t = lane; t < (cap >> 1); t += 32) {
+                    const int lo = 2 * t - (t & (stride - 1));
+                    const int hi = lo + stride;
+                    const bool desc = (lo & size) == 0;
+                    const u64 a = scratch[lo], b = scratch[hi];
+                    if ((a > b) != desc && a != b) { scratch[lo] = b; scratch[hi] = a; }
+                }
+                __syncwarp();
+            }
+        }
+        const int m = n < kp ? n : kp;
+        for (int j = lane; j < m; j += 32) src[j] = scratch[j];
+        if (lane == L) {
+            count = m;
+            if (n >= kp) thr = unord32((u32)(scratch[kp - 1] >> 32));
+        }
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, GemmParams p) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* tiles = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    u64* sort_scratch = reinterpret_cast<u64*>(tiles + kStages * STAGE_BYTES);          // [4 warps][cap]
+    uint64_t* full = reinterpret_cast<uint64_t*>(sort_scratch + 4 * p.cap);
+    uint64_t* empty = full + kStages;
+    uint64_t* tfull = empty + kStages;
+    uint64_t* tempty = tfull + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_items = p.n_qtiles * p.n_slices;
+
+    if (threadIdx.x == 0) {
+        prefetch_tmap(&tmap_q);
+        prefetch_tmap(&tmap_x);
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int qt = item % p.n_qtiles, sl = item / p.n_qtiles;
+                const int t0 = sl * p.tiles_per_slice;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
+                for (int t = t0; t < t1; ++t) {
+                    const int row0 = (int)(p.row_lo + (int64_t)t * BN);
+                    for (int kb = 0; kb < p.kblocks; ++kb) {
+                        mbar_wait(&empty[stage], phase ^ 1);
+                        mbar_expect_tx(&full[stage], STAGE_BYTES);
+                        unsigned char* st = tiles + stage * STAGE_BYTES;
+                        tma_load_2d(st, &tmap_q, &full[stage], kb * BK, qt * BM);
+                        tma_load_2d(st + A_BYTES, &tmap_x, &full[stage], kb * BK, row0);
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16_f32(BM, BN);
+            uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+                const int sl = item / p.n_qtiles;
+                const int t0 = sl * p.tiles_per_slice;
+                const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
+                for (int t = t0; t < t1; ++t) {
+                    mbar_wait(&tempty[acc], acc_phase ^ 1);          // epilogue has drained this accumulator
+                    tc_fence_after();
+                    const uint32_t d = tmem_base + acc * BN;
+                    for (int kb = 0; kb < p.kblocks; ++kb) {
+                        mbar_wait(&full[stage], phase);
+                        tc_fence_after();
+                        const uint64_t da = smem_desc_sw128(tiles + stage * STAGE_BYTES);
+                        const uint64_t db = smem_desc_sw128(tiles + stage * STAGE_BYTES + A_BYTES);
+#pragma unroll
+                        for (int k = 0; k < BK / 16; ++k)       // 32 bytes along K per MMA: +2 in 16-byte units
+                            mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                        mma_commit(&empty[stage]);               // frees the smem stage when these MMAs retire
+                        if (++stage == kStages) { stage = 0; phase ^= 1; }
+                    }
+                    mma_commit(&tfull[acc]);                     // accumulator complete
+                    acc ^= 1;
+                    if (acc == 0) acc_phase ^= 1;
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: one query per thread =====
+        const int quarter = warp & 3;                            // the TMEM lane quarter this warp may read
+        const int qlane = quarter * 32 + lane;
+        u64* scratch = sort_scratch + (warp - 2) * p.cap;
+        uint32_t acc = 0, acc_phase = 0;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int qt = item % p.n_qtiles, sl = item / p.n_qtiles;
+            const int t0 = sl * p.tiles_per_slice;
+            const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
+            u64* buf = p.cand + ((size_t)item * BM + qlane) * p.cap;
+            int count = 0;
+            float thr = (qt * BM + qlane < p.n_queries) ? -INFINITY : INFINITY;
+            for (int t = t0; t < t1; ++t) {
+                const int64_t row0 = p.row_lo + (int64_t)t * BN;
+                mbar_wait(&tfull[acc], acc_phase);
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < BN / 32; ++c) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const float s = __uint_as_float(v[i]);
+                        if (s > thr) {
+                            const int64_t row = row0 + c * 32 + i;
+                            bool ok = row < p.row_hi;
+                            if (ok && p.tags) {
+                                const int tg = p.tags[row];
+                                ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                            }
+                            if (ok) buf[count++] = ((u64)ord32(s) << 32) | (u64)(0xffffffffu - (u32)row);
+                        }
+                    }
+                    const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32);
+                    if (need) warp_compact(need, buf, count, thr, scratch, p.cap, p.kp, lane);
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty[acc]);
+                acc ^= 1;
+                if (acc == 0) acc_phase ^= 1;
+            }
+            const unsigned need = __ballot_sync(0xffffffffu, count > 0);
+            if (need) warp_compact(need, buf, count, thr, scratch, p.cap, p.kp, lane);
+            p.cand_cnt[(size_t)item * BM + qlane] = count;
+            p.cand_thr[(size_t)item * BM + qlane] = thr;
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, kTmemCols);
+    }
+}
+
+// ---- the exact pass: one CTA per query ---------------------------------------------------------------
+struct SelectParams {
+    const float* rows; int64_t ld; int dim; const double* norms;
+    const float* queries; int64_t q_ld; const double* eps;
+    const u64* cand; const int32_t* cand_cnt; const float* cand_thr;
+    int n_qtiles, n_slices, kp, cap, k, cap_a, cap_b;
+    int64_t id_base;
+    int64_t* out_ids; double* out_scores; int32_t* out_counts; int32_t* certified;
+};
+
+__global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* key_a = reinterpret_cast<u64*>(smem);
+    u64* key_b = key_a + p.cap_a;
+    u32* id_a = reinterpret_cast<u32*>(key_b + p.cap_b);
+    u32* id_b = id_a + p.cap_a;
+    __shared__ LzSelector sa, sb;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q = blockIdx.x, qt = q / BM, ql = q % BM;
+    if (tid == 0) {
+        lz_sel_init(&sa, key_a, id_a, p.cap_a, p.kp);
+        lz_sel_init(&sb, key_b, id_b, p.cap_b, p.k);
+    }
+    __syncthreads();
+    // 1. merge the slices' candidates by coarse score
+    float T = -INFINITY;
+    int total = 0;
+    for (int sl = 0; sl < p.n_slices; ++sl) {
+        const size_t slot = (size_t)(sl * p.n_qtiles + qt) * BM + ql;
+        const int cnt = p.cand_cnt[slot];
+        T = fmaxf(T, p.cand_thr[slot]);
+        total += cnt;
+        const u64* src = p.cand + slot * p.cap;
+        for (int j = tid; j < cnt; j += kSelThreads) {
+            const u64 kk = src[j];
+            lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
+        }
+        lz_sel_maybe_compact<kSelThreads>(&sa, 2 * kSelThreads);
+    }
+    __syncthreads();
+    lz_sel_compact<kSelThreads>(&sa);
+    const int m = min(sa.count, p.kp);
+    if (total > p.kp) T = fmaxf(T, unord32((u32)key_a[p.kp - 1]));
+    // 2. exact float64 rescoring of the survivors, canonical summation order
+    const float* qv = p.queries + (int64_t)q * p.q_ld;
+    double qs = 0.0;
+    for (int e = lane * 4; e < p.dim; e += 128) {
+        const float4 x = *reinterpret_cast<const float4*>(qv + e);
+        qs = fma((double)x.x, (double)x.x, qs);
+        qs = fma((double)x.y, (double)x.y, qs);
+        qs = fma((double)x.z, (double)x.z, qs);
+        qs = fma((double)x.w, (double)x.w, qs);
+    }
+    const double qn = sqrt(lz_warp_sum(qs));
+    for (int j = warp; j < m; j += kSelThreads / 32) {
+        const u32 row = id_a[j];
+        const float* x = p.rows + (int64_t)row * p.ld;
+        double acc = 0.0;
+        for (int e = lane * 4; e < p.dim; e += 128) {
+            const float4 xv = lz_ldg_stream(x + e);
+            const float4 qq = *reinterpret_cast<const float4*>(qv + e);
+            acc = fma((double)xv.x, (double)qq.x, acc);
+            acc = fma((double)xv.y, (double)qq.y, acc);
+            acc = fma((double)xv.z, (double)qq.z, acc);
+            acc = fma((double)xv.w, (double)qq.w, acc);
+        }
+        acc = lz_warp_sum(acc);
+        if (lane == 0) {
+            const double den = p.norms[row] * qn;
+            double s = den > 0.0 ? acc / den : 0.0;
+            s += 0.0;
+            if (s == s) lz_sel_push(&sb, lz_ord(s), row);
+        }
+    }
+    __syncthreads();
+    lz_sel_compact<kSelThreads>(&sb);
+    const int n = min(sb.count, p.k);
+    for (int j = tid; j < p.k; j += kSelThreads) {
+        if (j < n) {
+            p.out_ids[(size_t)q * p.k + j] = (int64_t)id_b[j] + p.id_base;
+            p.out_scores[(size_t)q * p.k + j] = lz_unord(key_b[j]);
+        } else {
+            p.out_ids[(size_t)q * p.k + j] = -1;
+            p.out_scores[(size_t)q * p.k + j] = __longlong_as_double(0x7ff8000000000000ll);
+        }
+    }
+    if (tid == 0) {
+        p.out_counts[q] = n;
+        // 3. certify: rows dropped anywhere had coarse <= T, i.e. exact <= T + eps
+        bool cert = T == -INFINITY;
+        if (!cert && n >= p.k) cert = lz_unord(key_b[p.k - 1]) > (double)T + p.eps[q];
+        p.certified[q] = cert ? 1 : 0;
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void* sym = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(sym);
+    }
+    return fn;
+}
+
+// bf16 [n_rows, dim] row-major, box = 64 elements x box_rows rows, 128-byte swizzle, zero fill out of bounds
+int make_tmap(CUtensorMap* m, const void* base, int64_t n_rows, int dim, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) { lz_set_error("cuTensorMapEncodeTiled is not available from the driver"); return LZ_ERR_CUDA; }
+    cuuint64_t gdim[2] = {(cuuint64_t)dim, (cuuint64_t)n_rows};
+    cuuint64_t gstride[1] = {(cuuint64_t)dim * 2};
+    cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { lz_set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return LZ_ERR_CUDA; }
+    return LZ_OK;
+}
+
+struct Plan {
+    int n_qtiles, n_tiles, n_slices, tiles_per_slice, kp, cap, fb_chunks, grid;
+};
+
+int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    pl->n_qtiles = (n_queries + BM - 1) / BM;
+    pl->n_tiles = (int)((n_rows + BN - 1) / BN);
+    int want = (2 * sms) / pl->n_qtiles;
+    if (want < 1) want = 1;
+    if (want > pl->n_tiles) want = pl->n_tiles;
+    if (want < 1) want = 1;
+    pl->tiles_per_slice = (pl->n_tiles + want - 1) / want;
+    if (pl->tiles_per_slice < 1) pl->tiles_per_slice = 1;
+    pl->n_slices = (pl->n_tiles + pl->tiles_per_slice - 1) / pl->tiles_per_slice;
+    if (pl->n_slices < 1) pl->n_slices = 1;
+    pl->kp = k <= 16 ? 128 : (k <= 48 ? 256 : 512);
+    pl->cap = 2 * pl->kp;
+    int64_t fb = (n_rows + 255) / 256;
+    pl->fb_chunks = (int)(fb < sms ? (fb < 1 ? 1 : fb) : sms);
+    const int items = pl->n_qtiles * pl->n_slices;
+    pl->grid = items < sms ? items : sms;
+    return LZ_OK;
+}
+
+struct ScratchLayout {
+    size_t q_bf16, eps, gtag, cand, cand_cnt, cand_thr, certified, fallback, total;
+};
+
+ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
+    ScratchLayout L;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
+    const size_t items = (size_t)pl.n_qtiles * pl.n_slices;
+    L.q_bf16 = take((size_t)n_queries * dim * 2);
+    L.eps = take((size_t)n_queries * 8);
+    L.gtag = take((size_t)n_queries * 4);
+    L.cand = take(items * BM * pl.cap * 8);
+    L.cand_cnt = take(items * BM * 4);
+    L.cand_thr = take(items * BM * 4);
+    L.certified = take((size_t)n_queries * 4);
+    L.fallback = take(lz_search_exact_scratch_bytes(n_queries, k, pl.fb_chunks));
+    L.total = off;
+    return L;
+}
+
+}  // namespace
+
+extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, void* out_bf16,
+                               void* stream) {
+    if (n <= 0) return LZ_OK;
+    LZ_REQUIRE(rows && norms && out_bf16, "lz_rows_to_bf16: NULL pointer");
+    LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_rows_to_bf16: dim=%d must be a multiple of 8", dim);
+    LZ_REQUIRE((((uintptr_t)rows | (uintptr_t)out_bf16) & 15) == 0, "lz_rows_to_bf16: pointers must be 16-byte aligned");
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    int64_t blocks = (n + 7) / 8;
+    if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
+    rows_to_bf16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms,
+                                                                            (__nv_bfloat16*)out_bf16);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int dim) {
+    if (n_rows <= 0 || n_queries <= 0 || k <= 0) return 0;
+    Plan pl;
+    if (make_plan(n_rows, n_queries, k, &pl)) return 0;
+    return layout(pl, n_queries, k, dim).total;
+}
+
+extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, int dim, const double* norms,
+                                 const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
+                                 int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
+                                 double margin_sigmas, int64_t id_base, void* scratch, size_t scratch_bytes,
+                                 int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
+                                 void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(shadow_bf16 && rows && norms && queries && scratch && out_ids && out_scores && out_counts,
+               "lz_search_batched: NULL pointer");
+    LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_search_batched: dim=%d must be a multiple of 8", dim);
+    LZ_REQUIRE(q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
+               "lz_search_batched: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
+    LZ_REQUIRE((((uintptr_t)shadow_bf16 | (uintptr_t)rows | (uintptr_t)scratch) & 15) == 0,
+               "lz_search_batched: pointers must be 16-byte aligned");
+    LZ_REQUIRE(k >= 1 && k <= LZ_BATCHED_MAX_K, "lz_search_batched: k=%d outside 1..%d", k, LZ_BATCHED_MAX_K);
+    LZ_REQUIRE(0 <= row_lo && row_lo <= row_hi && row_hi <= n_rows_total && n_rows_total <= 0x7fffff00LL,
+               "lz_search_batched: bad row range [%lld, %lld) of %lld", (long long)row_lo, (long long)row_hi,
+               (long long)n_rows_total);
+    LZ_REQUIRE(margin_sigmas > 0.0, "lz_search_batched: margin_sigmas must be positive");
+    Plan pl;
+    if (int rc = make_plan(row_hi - row_lo, n_queries, k, &pl)) return rc;
+    const ScratchLayout L = layout(pl, n_queries, k, dim);
+    if (scratch_bytes < L.total) {
+        lz_set_error("lz_search_batched: scratch has %zu bytes, needs %zu", scratch_bytes, L.total);
+        return LZ_ERR_SCRATCH;
+    }
+    unsigned char* s = (unsigned char*)scratch;
+    __nv_bfloat16* q16 = (__nv_bfloat16*)(s + L.q_bf16);
+    double* eps = (double*)(s + L.eps);
+    int32_t* cert = out_certified ? out_certified : (int32_t*)(s + L.certified);
+
+    int32_t* gtag = (int32_t*)(s + L.gtag);
+    queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, want_tag,
+                                                                margin_sigmas);
+    LZ_CUDA(cudaGetLastError());
+
+    if (row_hi > row_lo) {
+        CUtensorMap tq, tx;
+        if (int rc = make_tmap(&tq, q16, n_queries, dim, BM)) return rc;
+        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim, BN)) return rc;
+        GemmParams g;
+        g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
+        g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
+        g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
+        g.tags = tags; g.want_tag = want_tag;
+        g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
+        const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (size_t)4 * pl.cap * 8 + (2 * kStages + 4) * 8 + 16;
+        LZ_CUDA(cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gemm_topk_kernel<<<pl.grid, kGemmThreads, smem, st>>>(tq, tx, g);
+        LZ_CUDA(cudaGetLastError());
+    } else {
+        const size_t items = (size_t)pl.n_qtiles * pl.n_slices;
+        LZ_CUDA(cudaMemsetAsync(s + L.cand_cnt, 0, items * BM * 4, st));
+        LZ_CUDA(cudaMemsetAsync(s + L.cand_thr, 0xff, items * BM * 4, st));     // 0xff800000-ish: written below
+    }
+
+    SelectParams sp;
+    sp.rows = rows; sp.ld = ld; sp.dim = dim; sp.norms = norms; sp.queries = queries; sp.q_ld = q_ld; sp.eps = eps;
+    sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
+    sp.cand_thr = (const float*)(s + L.cand_thr);
+    sp.n_qtiles = pl.n_qtiles; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
+    sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
+    sp.id_base = id_base;
+    sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
+    const size_t ssmem = (size_t)(sp.cap_a + sp.cap_b) * 12;
+    LZ_CUDA(cudaFuncSetAttribute(select_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
+    select_rescore_kernel<<<n_queries, kSelThreads, ssmem, st>>>(sp);
+    LZ_CUDA(cudaGetLastError());
+
+    // exact float64 scan for the queries that could not be certified (a no-op launch when all were)
+    return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, nullptr, nullptr, tags ? gtag : nullptr, queries, q_ld,
+                                n_queries, 1, k, LZ_COSINE, pl.fb_chunks, id_base, s + L.fallback,
+                                L.total - L.fallback, out_ids, out_scores, out_counts, cert, stream);
+}

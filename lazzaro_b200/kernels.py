@@ -137,3 +137,44 @@ def salience_decay(salience: torch.Tensor, n: int, rate: float, floor: float = 0
     with torch.cuda.device(dev):
         check(_lib.load().lz_salience_decay(ptr(salience), n, float(rate), float(floor), stream_ptr(dev)),
               "lz_salience_decay")
+
+
+def rows_to_bf16(rows: torch.Tensor, dim: int, norms: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Normalised bf16 shadow of float32 rows (lz_rows_to_bf16): out[i] = bf16(rows[i] / norms[i])."""
+    dev = _dev(rows)
+    n = rows.shape[0]
+    if out is None:
+        out = torch.empty((n, dim), dtype=torch.bfloat16, device=dev)
+    assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.shape[1] == dim
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_rows_to_bf16(ptr(rows), n, dim, rows.stride(0), ptr(norms), ptr(out), stream_ptr(dev)),
+              "lz_rows_to_bf16")
+    return out
+
+
+def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: torch.Tensor,
+                   tags: Optional[torch.Tensor], want_tag: int, queries: torch.Tensor, k: int,
+                   row_range: Optional[Tuple[int, int]] = None, margin_sigmas: float = 4.0, id_base: int = 0,
+                   scratch: Optional[torch.Tensor] = None, n_rows_total: Optional[int] = None):
+    """Batched exact cosine top-k on the tensor cores (lz_search_batched).
+    Returns (ids int64 [B,k], scores float64 [B,k], counts int32 [B], certified int32 [B])."""
+    dev = _dev(rows)
+    assert shadow.dtype == torch.bfloat16 and shadow.is_contiguous() and shadow.shape[1] == dim
+    assert queries.dtype == torch.float32 and queries.stride(1) == 1 and rows.stride(1) == 1
+    B = queries.shape[0]
+    n_total = n_rows_total if n_rows_total is not None else min(rows.shape[0], shadow.shape[0])
+    lo, hi = row_range if row_range is not None else (0, n_total)
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        need = int(lib.lz_search_batched_scratch_bytes(hi - lo, B, k, dim))
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+        scores = torch.empty((B, k), dtype=torch.float64, device=dev)
+        counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        cert = torch.empty((B,), dtype=torch.int32, device=dev)
+        check(lib.lz_search_batched(ptr(shadow), ptr(rows), rows.stride(0), dim, ptr(norms), ptr(tags), int(want_tag),
+                                    int(n_total), int(lo), int(hi), ptr(queries), queries.stride(0), B, k,
+                                    float(margin_sigmas), int(id_base), ptr(scratch), scratch.numel(),
+                                    ptr(ids), ptr(scores), ptr(counts), ptr(cert), stream_ptr(dev)), "lz_search_batched")
+    return ids, scores, counts, cert

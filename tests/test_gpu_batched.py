@@ -1,0 +1,87 @@
+"""GPU parity: the tensor-core batched search (lz_search_batched) against the exact scan and the
+numpy oracle. ids bit-exact; scores bit-identical to the exact scan (same float64 summation order)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import flat_search
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(rows_np):
+    from lazzaro_b200 import kernels as K
+    rows = torch.as_tensor(np.ascontiguousarray(rows_np, np.float32)).cuda()
+    norms = K.row_norms(rows)
+    shadow = K.rows_to_bf16(rows, rows.shape[1], norms)
+    return K, rows, norms, shadow
+
+
+def test_shadow_is_normalised_bf16():
+    from lazzaro_b200 import synth
+    rows_np, _ = synth.clustered_rows(1000, 64, 4, seed=1)
+    rows_np *= np.linspace(0.5, 3.0, 1000, dtype=np.float32)[:, None]
+    rows_np[7] = 0
+    K, rows, norms, shadow = setup(rows_np)
+    want = torch.as_tensor(rows_np / np.maximum(np.linalg.norm(rows_np, axis=1, keepdims=True), 1e-30)).to(torch.bfloat16)
+    got = shadow.cpu()
+    assert (got[7] == 0).all()
+    assert torch.allclose(got.float(), want.float(), atol=2 ** -8, rtol=2 ** -7)
+
+
+@pytest.mark.parametrize("n,dim,B,k", [(5000, 64, 3, 5), (20000, 384, 130, 10), (33333, 768, 256, 10),
+                                       (4096, 128, 128, 100), (70000, 200, 64, 20), (300, 72, 9, 10)])
+def test_batched_matches_exact_scan_and_oracle(n, dim, B, k):
+    from lazzaro_b200 import synth, _lib
+    rows_np, _ = synth.clustered_rows(n, dim, 8, seed=n)
+    qs_np = synth.queries_near_rows(rows_np, B, seed=B)
+    K, rows, norms, shadow = setup(rows_np)
+    qs = torch.as_tensor(qs_np).cuda()
+    ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+    eids, esc, ecnt = K.search_exact(rows, dim, norms, None, qs, k, _lib.COSINE)
+    torch.cuda.synchronize()
+    assert torch.equal(ids, eids) and torch.equal(cnt, ecnt)
+    assert torch.equal(sc[ids >= 0], esc[eids >= 0])                    # bit-identical float64 scores
+    sub = slice(0, min(B, 16))
+    want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np[sub], k)
+    np.testing.assert_array_equal(ids[sub].cpu().numpy(), want_ids)
+    kk = min(k, n)
+    np.testing.assert_allclose(sc[sub, :kk].cpu().numpy(), want_sc[:, :kk], rtol=1e-12)
+    assert cert.float().mean().item() > 0.5, "the tensor-core pass should certify most queries on this data"
+
+
+def test_batched_with_filter_range_and_uncertifiable_queries():
+    from lazzaro_b200 import synth, _lib
+    rows_np, _ = synth.clustered_rows(30000, 128, 8, seed=77)
+    rows_np[100:400] = rows_np[50]                      # 300 exact duplicates: coarse ties, cannot be certified
+    qs_np = synth.queries_near_rows(rows_np, 40, seed=78)
+    qs_np[0] = rows_np[50]
+    qs_np[1] = 0                                        # zero query
+    tags_np = (np.arange(30000) % 3).astype(np.int32)
+    tags_np[::11] = -1
+    K, rows, norms, shadow = setup(rows_np)
+    qs, tags = torch.as_tensor(qs_np).cuda(), torch.as_tensor(tags_np).cuda()
+    for want, rng in [(-1, (0, 30000)), (1, (0, 30000)), (2, (777, 25001)), (0, (5000, 5003))]:
+        ids, sc, cnt, cert = K.search_batched(shadow, rows, 128, norms, tags, want, qs, 10, row_range=rng)
+        torch.cuda.synchronize()
+        mask = (tags_np >= 0) if want < 0 else (tags_np == want)
+        mask = mask & (np.arange(30000) >= rng[0]) & (np.arange(30000) < rng[1])
+        want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np, 10, mask=mask)
+        np.testing.assert_array_equal(ids.cpu().numpy(), want_ids)
+        np.testing.assert_array_equal(cnt.cpu().numpy(), (want_ids >= 0).sum(1))
+    assert cert[0].item() == 0 or rng != (0, 30000)      # the duplicate-heavy query went through the fallback
+
+
+def test_batched_cfg2_size_against_exact_scan():
+    """BASELINE configs[1]: 1M x 768, 64 shards, batch 256, top-10 — tensor-core path vs exact scan."""
+    from lazzaro_b200 import synth, kernels as K, _lib
+    n, dim, B, k = 1_000_000, 768, 256, 10
+    rows, _ = synth.clustered_rows_device(n, dim, 64, "cuda")
+    qs = synth.queries_near_rows_device(rows, B)
+    norms = K.row_norms(rows)
+    shadow = K.rows_to_bf16(rows, dim, norms)
+    ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+    eids, esc, ecnt = K.search_exact(rows, dim, norms, None, qs, k, _lib.COSINE)
+    torch.cuda.synchronize()
+    assert torch.equal(ids, eids) and torch.equal(sc, esc) and torch.equal(cnt, ecnt)
+    assert cert.float().mean().item() > 0.9
