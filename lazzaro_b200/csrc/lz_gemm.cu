@@ -113,46 +113,66 @@ struct GemmParams {
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
 };
 
-// Warp-cooperative compaction of the candidate buffers of the lanes in `need`: sort descending in the
-// warp's shared scratch, keep the best kp, raise that lane's threshold to the kp-th coarse score.
-__device__ __forceinline__ void warp_compact(unsigned need, u64* my_buf, int& count, float& thr, u64* scratch,
-                                             int cap, int kp, int lane) {
+// Warp-cooperative compaction of the candidate buffers of the lanes in `need` (each over kp entries):
+// the warp loads one lane's buffer into registers (EPL keys per lane), finds the kp-th largest coarse
+// score by a 32-step bisection on the order-preserving key (compare + warp reduce-add per step), and
+// writes back the entries above it plus enough of the ties to make kp.  No sort: the buffer stays
+// unordered, which is all the later merge needs.  Which of several rows tied AT the threshold survive
+// is immaterial — the threshold itself is what the certification accounts for.
+template <int EPL>
+__device__ __forceinline__ void warp_select(unsigned need, u64* my_buf, int& count, float& thr, int kp, int lane) {
+    const unsigned lt = (1u << lane) - 1u;
     __syncwarp();
     while (need) {
         const int L = __ffs(need) - 1;
         need &= need - 1;
         u64* src = reinterpret_cast<u64*>(__shfl_sync(0xffffffffu, (unsigned long long)my_buf, L));
         const int n = __shfl_sync(0xffffffffu, count, L);
-        for (int j = lane; j < cap; j += 32) scratch[j] = j < n ? src[j] : 0ull;
-        __syncwarp();
-        for (int size = 2; size <= cap; size <<= 1) {
-            for (int stride = size >> 1; stride > 0; stride >>= 1) {
-                for (int t = lane; t < (cap >> 1); t += 32) {
-                    const int lo = 2 * t - (t & (stride - 1));
-                    const int hi = lo + stride;
-                    const bool desc = (lo & size) == 0;
-                    const u64 a = scratch[lo], b = scratch[hi];
-                    if ((a > b) != desc && a != b) { scratch[lo] = b; scratch[hi] = a; }
-                }
-                __syncwarp();
-            }
+        u64 key[EPL];
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) key[i] = (lane + 32 * i) < n ? src[lane + 32 * i] : 0ull;
+        u32 prefix = 0;
+#pragma unroll 1
+        for (int bit = 31; bit >= 0; --bit) {
+            const u32 cand = prefix | (1u << bit);
+            int c = 0;
+#pragma unroll
+            for (int i = 0; i < EPL; ++i) c += (u32)(key[i] >> 32) >= cand;
+            c = __reduce_add_sync(0xffffffffu, c);
+            if (c >= kp) prefix = cand;
         }
-        const int m = n < kp ? n : kp;
-        for (int j = lane; j < m; j += 32) src[j] = scratch[j];
+        int gt = 0;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) gt += (u32)(key[i] >> 32) > prefix;
+        gt = __reduce_add_sync(0xffffffffu, gt);
+        const int room = kp - gt;
+        __syncwarp();
+        int out = 0, eq_seen = 0;
+#pragma unroll
+        for (int i = 0; i < EPL; ++i) {
+            const u32 hi = (u32)(key[i] >> 32);
+            const bool e = hi == prefix && prefix != 0;
+            const unsigned me = __ballot_sync(0xffffffffu, e);
+            const bool keep = hi > prefix || (e && eq_seen + __popc(me & lt) < room);
+            const unsigned mk = __ballot_sync(0xffffffffu, keep);
+            if (keep) src[out + __popc(mk & lt)] = key[i];
+            out += __popc(mk);
+            eq_seen += __popc(me);
+        }
         if (lane == L) {
-            count = m;
-            if (n >= kp) thr = unord32((u32)(scratch[kp - 1] >> 32));
+            count = out;
+            thr = unord32(prefix);
         }
         __syncwarp();
     }
 }
 
+template <int EPL>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, GemmParams p) {
     extern __shared__ unsigned char smem_raw[];
-    unsigned char* tiles = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    u64* sort_scratch = reinterpret_cast<u64*>(tiles + kStages * STAGE_BYTES);          // [4 warps][cap]
-    uint64_t* full = reinterpret_cast<uint64_t*>(sort_scratch + 4 * p.cap);
+    unsigned char* tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned
+    uint64_t* full = reinterpret_cast<uint64_t*>(tiles + kStages * STAGE_BYTES);
     uint64_t* empty = full + kStages;
     uint64_t* tfull = empty + kStages;
     uint64_t* tempty = tfull + 2;
@@ -231,7 +251,6 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         // ===== epilogue: one query per thread =====
         const int quarter = warp & 3;                            // the TMEM lane quarter this warp may read
         const int qlane = quarter * 32 + lane;
-        u64* scratch = sort_scratch + (warp - 2) * p.cap;
         uint32_t acc = 0, acc_phase = 0;
         for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
             const int qt = item % p.n_qtiles, sl = item / p.n_qtiles;
@@ -263,7 +282,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                         }
                     }
                     const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32);
-                    if (need) warp_compact(need, buf, count, thr, scratch, p.cap, p.kp, lane);
+                    if (need) warp_select<EPL>(need, buf, count, thr, p.kp, lane);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -271,8 +290,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
-            const unsigned need = __ballot_sync(0xffffffffu, count > 0);
-            if (need) warp_compact(need, buf, count, thr, scratch, p.cap, p.kp, lane);
+            const unsigned need = __ballot_sync(0xffffffffu, count > p.kp);
+            if (need) warp_select<EPL>(need, buf, count, thr, p.kp, lane);
             p.cand_cnt[(size_t)item * BM + qlane] = count;
             p.cand_thr[(size_t)item * BM + qlane] = thr;
         }
@@ -530,9 +549,10 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
-        const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (size_t)4 * pl.cap * 8 + (2 * kStages + 4) * 8 + 16;
-        LZ_CUDA(cudaFuncSetAttribute(gemm_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        gemm_topk_kernel<<<pl.grid, kGemmThreads, smem, st>>>(tq, tx, g);
+        const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (2 * kStages + 4) * 8 + 16;
+        auto kern = pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
+        LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<pl.grid, kGemmThreads, smem, st>>>(tq, tx, g);
         LZ_CUDA(cudaGetLastError());
     } else {
         const size_t items = (size_t)pl.n_qtiles * pl.n_slices;

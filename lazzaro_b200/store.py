@@ -64,6 +64,15 @@ class B200Store:
         self._profiles: Dict[str, Dict[str, Any]] = {}
         self._pin: Dict[str, torch.Tensor] = {}
         self._scratch: Optional[torch.Tensor] = None
+        if batched_search not in ("auto", "never", "always"):
+            raise ValueError("batched_search must be 'auto', 'never' or 'always'")
+        self.batched_search = batched_search
+        self.min_batch = 8                    # 'auto': query batches this large go to the tensor-core path
+        self.margin_sigmas = 4.0
+        self._shadow: Optional[torch.Tensor] = None   # bf16 [capacity, dim_p] normalised copy of the rows
+        self._shadow_n = 0                            # rows of the shadow that are up to date
+        self._bscratch: Optional[torch.Tensor] = None
+        self.last_certified: Optional[torch.Tensor] = None
         self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
         if dim is not None:
             self._set_dim(int(dim))
@@ -83,6 +92,20 @@ class B200Store:
             norms[:self._n] = self._norms[:self._n]
             tags[:self._n] = self._tags[:self._n]
         self._rows, self._norms, self._tags = rows, norms, tags
+        if self._shadow is not None:
+            shadow = torch.empty((cap, self._dim_p), dtype=torch.bfloat16, device=self.device)
+            shadow[:self._shadow_n] = self._shadow[:self._shadow_n]
+            self._shadow = shadow
+
+    def _ensure_shadow(self):
+        """Brings the normalised bf16 copy of the rows (read by the tensor-core pass) up to date."""
+        if self._shadow is None:
+            self._shadow = torch.empty((self._rows.shape[0], self._dim_p), dtype=torch.bfloat16, device=self.device)
+            self._shadow_n = 0
+        if self._shadow_n < self._n:
+            a, b = self._shadow_n, self._n
+            kernels.rows_to_bf16(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b])
+            self._shadow_n = b
 
     def _reserve(self, extra: int):
         need = self._n + extra
@@ -307,6 +330,19 @@ class B200Store:
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
         tags = None if single_user else self._tags
         B = queries.shape[0]
+        batched = (self._metric == _lib.COSINE and k <= _lib.BATCHED_MAX_K and
+                   (self.batched_search == "always" or (self.batched_search == "auto" and B >= self.min_batch)))
+        if batched:
+            self._ensure_shadow()
+            need = int(_lib.load().lz_search_batched_scratch_bytes(hi - lo, B, k, self._dim_p))
+            if self._bscratch is None or self._bscratch.numel() < need:
+                self._bscratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            ids, sc, cnt, cert = kernels.search_batched(self._shadow, self._rows, self._dim_p, self._norms, tags,
+                                                        -1 if tags is None else u, queries, k, row_range=(lo, hi),
+                                                        margin_sigmas=self.margin_sigmas, id_base=id_base,
+                                                        scratch=self._bscratch, n_rows_total=self._n)
+            self.last_certified = cert
+            return ids, sc, cnt
         gs = 4 if B >= 4 else (2 if B >= 2 else 1)
         n_groups = (B + gs - 1) // gs
         gtag = None if tags is None else torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
@@ -406,7 +442,7 @@ class B200Store:
 
     def close(self):                                                  # vector_store.py:235-244
         with self._lock:
-            self._rows = self._norms = self._tags = self._scratch = None
+            self._rows = self._norms = self._tags = self._scratch = self._shadow = self._bscratch = None
             self._pin.clear()
             self._n = 0
 

@@ -1,0 +1,25 @@
+"""Small driver for profiling the batched search: python scripts/run_batched.py [rows] [batch] [k] [iters]"""
+import os, sys, time
+sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..")))
+import torch
+from lazzaro_b200 import synth, kernels as K
+
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_000_000
+B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
+k = int(sys.argv[3]) if len(sys.argv) > 3 else 10
+iters = int(sys.argv[4]) if len(sys.argv) > 4 else 3
+dim = 768
+rows, _ = synth.clustered_rows_device(n, dim, max(1, n // 9766), "cuda")
+qs = synth.queries_near_rows_device(rows, B)
+norms = K.row_norms(rows)
+shadow = K.rows_to_bf16(rows, dim, norms)
+out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+torch.cuda.synchronize()
+e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+e0.record()
+for _ in range(iters):
+    out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+e1.record()
+torch.cuda.synchronize()
+ms = e0.elapsed_time(e1) / iters
+print(f"rows={n} B={B} k={k}: {ms:.3f} ms/batch, {2.0*B*n*dim/ms/1e9:.1f} TFLOP/s, certified={out[3].float().mean().item():.3f}")
