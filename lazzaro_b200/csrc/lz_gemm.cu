@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restri
 // one warp per query: normalised bf16 copy + the certification margin eps[q]
 __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
                                                               __nv_bfloat16* __restrict__ out, double* __restrict__ eps,
-                                                              int32_t* __restrict__ gtag, int want_tag, double sigmas) {
+                                                              int32_t* __restrict__ gtag, u32* __restrict__ gthr, int want_tag, double sigmas) {
     const int lane = threadIdx.x & 31;
     const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (w >= n) return;
@@ -98,6 +98,7 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
         // max q_i^2); fp32 accumulation adds a few 1e-7.  eps = sigmas * that + 8e-6.
         eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)(mx * inv) + 8e-6;
         gtag[w] = want_tag;
+        gthr[w] = 0u;
     }
 }
 
@@ -111,6 +112,7 @@ struct GemmParams {
     u64* cand;          // [n_items][BM][cap]  key = ord32(coarse) << 32 | (0xffffffff - row)
     int32_t* cand_cnt;  // [n_items][BM]
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
+    u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
 };
 
 // Warp-cooperative compaction of the candidate buffers of the lanes in `need` (each over kp entries):
@@ -257,10 +259,19 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const int t0 = sl * p.tiles_per_slice;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
             u64* buf = p.cand + ((size_t)item * BM + qlane) * p.cap;
+            const int q = qt * BM + qlane;
+            const bool valid = q < p.n_queries;
             int count = 0;
-            float thr = (qt * BM + qlane < p.n_queries) ? -INFINITY : INFINITY;
+            float thr = valid ? -INFINITY : INFINITY;
             for (int t = t0; t < t1; ++t) {
                 const int64_t row0 = p.row_lo + (int64_t)t * BN;
+                if (valid) {
+                    // adopt the best threshold any CTA working on this query has reached: a row below some
+                    // CTA's kp-th best coarse score cannot be among the kp best overall
+                    u32 g;
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(g) : "l"(p.gthr + q) : "memory");
+                    if (g != 0u) thr = fmaxf(thr, unord32(g));
+                }
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
 #pragma unroll 1
@@ -268,21 +279,29 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     uint32_t v[32];
                     tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c * 32, v);
                     tmem_ld_wait();
+                    float m = __uint_as_float(v[0]);
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const float s = __uint_as_float(v[i]);
-                        if (s > thr) {
-                            const int64_t row = row0 + c * 32 + i;
-                            bool ok = row < p.row_hi;
-                            if (ok && p.tags) {
-                                const int tg = p.tags[row];
-                                ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                    for (int i = 1; i < 32; ++i) m = fmaxf(m, __uint_as_float(v[i]));
+                    if (m > thr) {                                // uncommon once the thresholds have risen
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const float s = __uint_as_float(v[i]);
+                            if (s > thr) {
+                                const int64_t row = row0 + c * 32 + i;
+                                bool ok = row < p.row_hi;
+                                if (ok && p.tags) {
+                                    const int tg = p.tags[row];
+                                    ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                                }
+                                if (ok) buf[count++] = ((u64)ord32(s) << 32) | (u64)(0xffffffffu - (u32)row);
                             }
-                            if (ok) buf[count++] = ((u64)ord32(s) << 32) | (u64)(0xffffffffu - (u32)row);
                         }
                     }
                     const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32);
-                    if (need) warp_select<EPL>(need, buf, count, thr, p.kp, lane);
+                    if (need) {
+                        warp_select<EPL>(need, buf, count, thr, p.kp, lane);
+                        if ((need >> lane) & 1u) atomicMax(p.gthr + q, ord32(thr));
+                    }
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -457,7 +476,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
 }
 
 struct ScratchLayout {
-    size_t q_bf16, eps, gtag, cand, cand_cnt, cand_thr, certified, fallback, total;
+    size_t q_bf16, eps, gtag, gthr, cand, cand_cnt, cand_thr, certified, fallback, total;
 };
 
 ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
@@ -468,6 +487,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     L.q_bf16 = take((size_t)n_queries * dim * 2);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
+    L.gthr = take((size_t)n_queries * 4);
     L.cand = take(items * BM * pl.cap * 8);
     L.cand_cnt = take(items * BM * 4);
     L.cand_thr = take(items * BM * 4);
@@ -535,8 +555,9 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     int32_t* cert = out_certified ? out_certified : (int32_t*)(s + L.certified);
 
     int32_t* gtag = (int32_t*)(s + L.gtag);
-    queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, want_tag,
-                                                                margin_sigmas);
+    u32* gthr = (u32*)(s + L.gthr);
+    queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
+                                                                want_tag, margin_sigmas);
     LZ_CUDA(cudaGetLastError());
 
     if (row_hi > row_lo) {
@@ -547,7 +568,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
-        g.tags = tags; g.want_tag = want_tag;
+        g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (2 * kStages + 4) * 8 + 16;
         auto kern = pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
