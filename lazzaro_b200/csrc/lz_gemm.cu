@@ -18,6 +18,7 @@
 // Stands behind LanceDBStore.search_nodes (core/vector_store.py:132-140) for query batches, and behind
 // the dedup / linking scans of core/memory_system.py:719-742, 838-891 (same contraction, small k).
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "lz_common.cuh"
 #include "lz_sm100.cuh"
@@ -105,6 +106,7 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
 // ---- the coarse pass ----------------------------------------------------------------------------------
 struct GemmParams {
     int n_queries, n_qtiles, n_slices, tiles_per_slice, n_tiles, kblocks;
+    int cs, n_qgroups;  // cluster size (CTAs that share one rows tile by TMA multicast) and q-tile groups of that size
     int64_t row_lo, row_hi;
     int kp, cap;
     const int32_t* tags;
@@ -181,18 +183,25 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_items = p.n_qtiles * p.n_slices;
+    // A cluster of cs CTAs walks the same (slice, tile) sequence; CTA `rank` owns q-tile qg*cs + rank and
+    // loads 1/cs of every rows tile, multicast into all cs CTAs.
+    const int cs = p.cs;
+    const int rank = cs > 1 ? (int)cluster_rank() : 0;
+    const uint16_t mc_mask = (uint16_t)((1u << cs) - 1u);
+    const int n_items = p.n_qgroups * p.n_slices;
+    const int cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
 
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_q);
         prefetch_tmap(&tmap_x);
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], cs); }
         for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
     tc_fence_before();
     __syncthreads();
+    if (cs > 1) cluster_sync();          // every CTA's barriers exist before anyone multicasts into them
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -200,18 +209,23 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         // ===== TMA producer =====
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int qt = item % p.n_qtiles, sl = item / p.n_qtiles;
+            const int slice_rows = BN / cs;
+            for (int item = cluster_id; item < n_items; item += n_clusters) {
+                const int qt = (item % p.n_qgroups) * cs + rank, sl = item / p.n_qgroups;
                 const int t0 = sl * p.tiles_per_slice;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
                 for (int t = t0; t < t1; ++t) {
                     const int row0 = (int)(p.row_lo + (int64_t)t * BN);
                     for (int kb = 0; kb < p.kblocks; ++kb) {
-                        mbar_wait(&empty[stage], phase ^ 1);
+                        mbar_wait(&empty[stage], phase ^ 1);          // all cs consumers have released the stage
                         mbar_expect_tx(&full[stage], STAGE_BYTES);
                         unsigned char* st = tiles + stage * STAGE_BYTES;
                         tma_load_2d(st, &tmap_q, &full[stage], kb * BK, qt * BM);
-                        tma_load_2d(st + A_BYTES, &tmap_x, &full[stage], kb * BK, row0);
+                        if (cs > 1)
+                            tma_load_2d_mc(st + A_BYTES + rank * slice_rows * BK * 2, &tmap_x, &full[stage], kb * BK,
+                                           row0 + rank * slice_rows, mc_mask);
+                        else
+                            tma_load_2d(st + A_BYTES, &tmap_x, &full[stage], kb * BK, row0);
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -223,8 +237,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (lane == 0) {
             constexpr uint32_t idesc = idesc_bf16_f32(BM, BN);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
-            for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-                const int sl = item / p.n_qtiles;
+            for (int item = cluster_id; item < n_items; item += n_clusters) {
+                const int sl = item / p.n_qgroups;
                 const int t0 = sl * p.tiles_per_slice;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
                 for (int t = t0; t < t1; ++t) {
@@ -239,7 +253,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 #pragma unroll
                         for (int k = 0; k < BK / 16; ++k)       // 32 bytes along K per MMA: +2 in 16-byte units
                             mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-                        mma_commit(&empty[stage]);               // frees the smem stage when these MMAs retire
+                        if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
+                        else mma_commit(&empty[stage]);          // frees the smem stage when these MMAs retire
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
                     mma_commit(&tfull[acc]);                     // accumulator complete
@@ -254,11 +269,12 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int quarter = warp & 3;                            // the TMEM lane quarter this warp may read
         const int qlane = quarter * 32 + lane;
         uint32_t acc = 0, acc_phase = 0;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int qt = item % p.n_qtiles, sl = item / p.n_qtiles;
+        for (int item = cluster_id; item < n_items; item += n_clusters) {
+            const int qt = (item % p.n_qgroups) * cs + rank, sl = item / p.n_qgroups;
             const int t0 = sl * p.tiles_per_slice;
             const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
-            u64* buf = p.cand + ((size_t)item * BM + qlane) * p.cap;
+            const size_t slot0 = ((size_t)sl * p.n_qgroups * cs + qt) * BM + qlane;   // [slice][q-tile][query lane]
+            u64* buf = p.cand + slot0 * p.cap;
             const int q = qt * BM + qlane;
             const bool valid = q < p.n_queries;
             int count = 0;
@@ -311,12 +327,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             }
             const unsigned need = __ballot_sync(0xffffffffu, count > p.kp);
             if (need) warp_select<EPL>(need, buf, count, thr, p.kp, lane);
-            p.cand_cnt[(size_t)item * BM + qlane] = count;
-            p.cand_thr[(size_t)item * BM + qlane] = thr;
+            p.cand_cnt[slot0] = count;
+            p.cand_thr[slot0] = thr;
         }
     }
     tc_fence_before();
     __syncthreads();
+    if (cs > 1) cluster_sync();          // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, kTmemCols);
@@ -328,7 +345,7 @@ struct SelectParams {
     const float* rows; int64_t ld; int dim; const double* norms;
     const float* queries; int64_t q_ld; const double* eps;
     const u64* cand; const int32_t* cand_cnt; const float* cand_thr;
-    int n_qtiles, n_slices, kp, cap, k, cap_a, cap_b;
+    int n_qtiles_pad, n_slices, kp, cap, k, cap_a, cap_b;   // n_qtiles_pad = n_qgroups * cs
     int64_t id_base;
     int64_t* out_ids; double* out_scores; int32_t* out_counts; int32_t* certified;
 };
@@ -351,7 +368,7 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
     float T = -INFINITY;
     int total = 0;
     for (int sl = 0; sl < p.n_slices; ++sl) {
-        const size_t slot = (size_t)(sl * p.n_qtiles + qt) * BM + ql;
+        const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
         const int cnt = p.cand_cnt[slot];
         T = fmaxf(T, p.cand_thr[slot]);
         total += cnt;
@@ -450,15 +467,29 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t n_rows, int dim, int box
 }
 
 struct Plan {
-    int n_qtiles, n_tiles, n_slices, tiles_per_slice, kp, cap, fb_chunks, grid;
+    int n_qtiles, cs, n_qgroups, n_tiles, n_slices, tiles_per_slice, kp, cap, fb_chunks, grid;
 };
 
+int env_int(const char* name, int dflt) {
+    const char* v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+// cs = CTAs per cluster sharing each rows tile by TMA multicast (one q-tile each).  Measured at 10M x 768,
+// batch 1024 on B200: cs=1 20.9 ms, cs=2 18.4 ms, cs=4 31.8 ms, cs=8 38.0 ms — larger clusters couple
+// more epilogues to one pipeline (and leave SMs idle), so the default is 2; LZ_CLUSTER overrides.
 int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     const int sms = lz_sm_count();
     if (sms <= 0) return LZ_ERR_DEVICE;
     pl->n_qtiles = (n_queries + BM - 1) / BM;
+    int cs = env_int("LZ_CLUSTER", 2);
+    if (cs != 1 && cs != 2 && cs != 4 && cs != 8) cs = 2;
+    while (cs > 1 && cs / 2 >= pl->n_qtiles) cs /= 2;             // no larger than the q-tiles there are
+    pl->cs = cs;
+    pl->n_qgroups = (pl->n_qtiles + cs - 1) / cs;
     pl->n_tiles = (int)((n_rows + BN - 1) / BN);
-    int want = (2 * sms) / pl->n_qtiles;
+    const int n_clusters = sms / cs > 0 ? sms / cs : 1;
+    int want = (2 * n_clusters) / pl->n_qgroups;
     if (want < 1) want = 1;
     if (want > pl->n_tiles) want = pl->n_tiles;
     if (want < 1) want = 1;
@@ -470,8 +501,8 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     pl->cap = 2 * pl->kp;
     int64_t fb = (n_rows + 255) / 256;
     pl->fb_chunks = (int)(fb < sms ? (fb < 1 ? 1 : fb) : sms);
-    const int items = pl->n_qtiles * pl->n_slices;
-    pl->grid = items < sms ? items : sms;
+    const int items = pl->n_qgroups * pl->n_slices;
+    pl->grid = (items < n_clusters ? items : n_clusters) * cs;
     return LZ_OK;
 }
 
@@ -483,7 +514,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     ScratchLayout L;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
-    const size_t items = (size_t)pl.n_qtiles * pl.n_slices;
+    const size_t items = (size_t)pl.n_qgroups * pl.cs * pl.n_slices;
     L.q_bf16 = take((size_t)n_queries * dim * 2);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
@@ -563,29 +594,42 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim, BM)) return rc;
-        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim, BN)) return rc;
+        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim, BN / pl.cs)) return rc;
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
+        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (2 * kStages + 4) * 8 + 16;
         auto kern = pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
         LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<pl.grid, kGemmThreads, smem, st>>>(tq, tx, g);
-        LZ_CUDA(cudaGetLastError());
+        if (pl.cs > 4) LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)pl.grid);
+        cfg.blockDim = dim3(kGemmThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)pl.cs;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, g));
     } else {
-        const size_t items = (size_t)pl.n_qtiles * pl.n_slices;
+        const size_t items = (size_t)pl.n_qgroups * pl.cs * pl.n_slices;
         LZ_CUDA(cudaMemsetAsync(s + L.cand_cnt, 0, items * BM * 4, st));
-        LZ_CUDA(cudaMemsetAsync(s + L.cand_thr, 0xff, items * BM * 4, st));     // 0xff800000-ish: written below
+        LZ_CUDA(cudaMemsetAsync(s + L.cand_thr, 0xff, items * BM * 4, st));     // NaN: ignored by fmaxf
     }
 
     SelectParams sp;
     sp.rows = rows; sp.ld = ld; sp.dim = dim; sp.norms = norms; sp.queries = queries; sp.q_ld = q_ld; sp.eps = eps;
     sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
     sp.cand_thr = (const float*)(s + L.cand_thr);
-    sp.n_qtiles = pl.n_qtiles; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
+    sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
     sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
