@@ -38,6 +38,10 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int kGemmThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
 constexpr int kTmemCols = 512;          // two 128x256 fp32 accumulators
 constexpr int kSelThreads = 256;
+#ifndef LZ_SUB
+#define LZ_SUB 8
+#endif
+constexpr int kSub = LZ_SUB;            // rows per candidate group in the coarse pass (8, 16 or 32)
 
 __device__ __forceinline__ u32 ord32(float v) {
     u32 b = __float_as_uint(v);
@@ -103,15 +107,25 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
     }
 }
 
+#ifdef LZ_STATS
+__device__ unsigned long long g_stats[8];   // 0 epi busy, 1 epi max, 2 mma wait tempty, 3 mma wait full, 4 prod wait empty, 5 tiles
+#define LZ_T0 long long t0_ = clock64();
+#define LZ_ACC(i) atomicAdd(&g_stats[i], (unsigned long long)(clock64() - t0_));
+#else
+#define LZ_T0
+#define LZ_ACC(i)
+#endif
+
 // ---- the coarse pass ----------------------------------------------------------------------------------
 struct GemmParams {
     int n_queries, n_qtiles, n_slices, tiles_per_slice, n_tiles, kblocks;
+    int debug;          // experiments only: bit 0 = epilogue skips the scan
     int cs, n_qgroups;  // cluster size (CTAs that share one rows tile by TMA multicast) and q-tile groups of that size
     int64_t row_lo, row_hi;
     int kp, cap;
     const int32_t* tags;
     int want_tag;
-    u64* cand;          // [n_items][BM][cap]  key = ord32(coarse) << 32 | (0xffffffff - row)
+    u64* cand;          // [n_items][BM][cap]  key = ord32(best coarse of the group) << 32 | (0xffffffff - first row)
     int32_t* cand_cnt;  // [n_items][BM]
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
     u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
@@ -171,6 +185,36 @@ __device__ __forceinline__ void warp_select(unsigned need, u64* my_buf, int& cou
     }
 }
 
+// One TMEM chunk (32 consecutive rows of this thread's query): reduce each group of kSub rows to its best
+// coarse score and append the groups that beat the query's threshold.
+template <int EPL>
+__device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_first, const GemmParams& p, u64* buf,
+                                           int& count, float& thr, int q, int lane) {
+    float g[32 / kSub];
+#pragma unroll
+    for (int j = 0; j < 32 / kSub; ++j) {
+        float m = __uint_as_float(v[j * kSub]);
+#pragma unroll
+        for (int i = 1; i < kSub; ++i) m = fmaxf(m, __uint_as_float(v[j * kSub + i]));
+        g[j] = m;
+    }
+    float m = g[0];
+#pragma unroll
+    for (int j = 1; j < 32 / kSub; ++j) m = fmaxf(m, g[j]);
+    if (m > thr) {
+#pragma unroll
+        for (int j = 0; j < 32 / kSub; ++j) {
+            const int64_t r0 = row_first + j * kSub;
+            if (g[j] > thr && r0 < p.row_hi) buf[count++] = ((u64)ord32(g[j]) << 32) | (u64)(0xffffffffu - (u32)r0);
+        }
+    }
+    const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32 / kSub);
+    if (need) {
+        warp_select<EPL>(need, buf, count, thr, p.kp, lane);
+        if ((need >> lane) & 1u) atomicMax(p.gthr + q, ord32(thr));
+    }
+}
+
 template <int EPL>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, GemmParams p) {
@@ -217,7 +261,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int t = t0; t < t1; ++t) {
                     const int row0 = (int)(p.row_lo + (int64_t)t * BN);
                     for (int kb = 0; kb < p.kblocks; ++kb) {
-                        mbar_wait(&empty[stage], phase ^ 1);          // all cs consumers have released the stage
+                        { LZ_T0 mbar_wait(&empty[stage], phase ^ 1); LZ_ACC(4) }   // all cs consumers have released the stage
                         mbar_expect_tx(&full[stage], STAGE_BYTES);
                         unsigned char* st = tiles + stage * STAGE_BYTES;
                         tma_load_2d(st, &tmap_q, &full[stage], kb * BK, qt * BM);
@@ -242,11 +286,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const int t0 = sl * p.tiles_per_slice;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
                 for (int t = t0; t < t1; ++t) {
-                    mbar_wait(&tempty[acc], acc_phase ^ 1);          // epilogue has drained this accumulator
+                    { LZ_T0 mbar_wait(&tempty[acc], acc_phase ^ 1); LZ_ACC(2) }   // epilogue has drained this accumulator
                     tc_fence_after();
                     const uint32_t d = tmem_base + acc * BN;
                     for (int kb = 0; kb < p.kblocks; ++kb) {
-                        mbar_wait(&full[stage], phase);
+                        { LZ_T0 mbar_wait(&full[stage], phase); LZ_ACC(3) }
                         tc_fence_after();
                         const uint64_t da = smem_desc_sw128(tiles + stage * STAGE_BYTES);
                         const uint64_t db = smem_desc_sw128(tiles + stage * STAGE_BYTES + A_BYTES);
@@ -290,37 +334,34 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 }
                 mbar_wait(&tfull[acc], acc_phase);
                 tc_fence_after();
+#ifdef LZ_STATS
+                long long te0 = clock64();
+#endif
+                // Candidates are GROUPS of kSub consecutive rows keyed by the group's best coarse score: one
+                // compare per group, no per-row branch, so a tile costs the same whether or not it holds a
+                // query's neighbours.  TMEM loads are double-buffered in registers (load chunk c+1, scan c).
+                const uint32_t tacc = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
+                uint32_t va[32], vb[32];
+                tmem_ld32(tacc, va);
 #pragma unroll 1
-                for (int c = 0; c < BN / 32; ++c) {
-                    uint32_t v[32];
-                    tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN + c * 32, v);
+                for (int c = 0; c < BN / 32; c += 2) {
                     tmem_ld_wait();
-                    float m = __uint_as_float(v[0]);
-#pragma unroll
-                    for (int i = 1; i < 32; ++i) m = fmaxf(m, __uint_as_float(v[i]));
-                    if (m > thr) {                                // uncommon once the thresholds have risen
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            const float s = __uint_as_float(v[i]);
-                            if (s > thr) {
-                                const int64_t row = row0 + c * 32 + i;
-                                bool ok = row < p.row_hi;
-                                if (ok && p.tags) {
-                                    const int tg = p.tags[row];
-                                    ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
-                                }
-                                if (ok) buf[count++] = ((u64)ord32(s) << 32) | (u64)(0xffffffffu - (u32)row);
-                            }
-                        }
-                    }
-                    const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32);
-                    if (need) {
-                        warp_select<EPL>(need, buf, count, thr, p.kp, lane);
-                        if ((need >> lane) & 1u) atomicMax(p.gthr + q, ord32(thr));
-                    }
+                    tmem_ld32(tacc + (c + 1) * 32, vb);
+                    scan_chunk<EPL>(va, row0 + c * 32, p, buf, count, thr, q, lane);
+                    tmem_ld_wait();
+                    if (c + 2 < BN / 32) tmem_ld32(tacc + (c + 2) * 32, va);
+                    scan_chunk<EPL>(vb, row0 + (c + 1) * 32, p, buf, count, thr, q, lane);
                 }
                 tc_fence_before();
                 __syncwarp();
+#ifdef LZ_STATS
+                if (lane == 0) {
+                    unsigned long long d = (unsigned long long)(clock64() - te0);
+                    atomicAdd(&g_stats[0], d); atomicMax(&g_stats[1], d); atomicAdd(&g_stats[5], 1ull);
+                    if (d > 6000) atomicAdd(&g_stats[6], 1ull);
+                    if (d > 6000) atomicAdd(&g_stats[7], d - 6000);
+                }
+#endif
                 if (lane == 0) mbar_arrive(&tempty[acc]);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
@@ -344,6 +385,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
 struct SelectParams {
     const float* rows; int64_t ld; int dim; const double* norms;
     const float* queries; int64_t q_ld; const double* eps;
+    const int32_t* tags; int want_tag; int64_t row_lo, row_hi;
     const u64* cand; const int32_t* cand_cnt; const float* cand_thr;
     int n_qtiles_pad, n_slices, kp, cap, k, cap_a, cap_b;   // n_qtiles_pad = n_qgroups * cs
     int64_t id_base;
@@ -394,25 +436,35 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         qs = fma((double)x.w, (double)x.w, qs);
     }
     const double qn = sqrt(lz_warp_sum(qs));
-    for (int j = warp; j < m; j += kSelThreads / 32) {
-        const u32 row = id_a[j];
-        const float* x = p.rows + (int64_t)row * p.ld;
-        double acc = 0.0;
-        for (int e = lane * 4; e < p.dim; e += 128) {
-            const float4 xv = lz_ldg_stream(x + e);
-            const float4 qq = *reinterpret_cast<const float4*>(qv + e);
-            acc = fma((double)xv.x, (double)qq.x, acc);
-            acc = fma((double)xv.y, (double)qq.y, acc);
-            acc = fma((double)xv.z, (double)qq.z, acc);
-            acc = fma((double)xv.w, (double)qq.w, acc);
+    for (int j = 0; j < m; ++j) {
+        // every row of candidate group j that passes the range / tag filter
+        for (int r = warp; r < kSub; r += kSelThreads / 32) {
+            const int64_t row = (int64_t)id_a[j] + r;
+            bool ok = row < p.row_hi;
+            if (ok && p.tags) {
+                const int tg = p.tags[row];
+                ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+            }
+            if (!ok) continue;                                      // warp-uniform
+            const float* x = p.rows + row * p.ld;
+            double acc = 0.0;
+            for (int e = lane * 4; e < p.dim; e += 128) {
+                const float4 xv = lz_ldg_stream(x + e);
+                const float4 qq = *reinterpret_cast<const float4*>(qv + e);
+                acc = fma((double)xv.x, (double)qq.x, acc);
+                acc = fma((double)xv.y, (double)qq.y, acc);
+                acc = fma((double)xv.z, (double)qq.z, acc);
+                acc = fma((double)xv.w, (double)qq.w, acc);
+            }
+            acc = lz_warp_sum(acc);
+            if (lane == 0) {
+                const double den = p.norms[row] * qn;
+                double s = den > 0.0 ? acc / den : 0.0;
+                s += 0.0;
+                if (s == s) lz_sel_push(&sb, lz_ord(s), (u32)row);
+            }
         }
-        acc = lz_warp_sum(acc);
-        if (lane == 0) {
-            const double den = p.norms[row] * qn;
-            double s = den > 0.0 ? acc / den : 0.0;
-            s += 0.0;
-            if (s == s) lz_sel_push(&sb, lz_ord(s), row);
-        }
+        if ((j & 7) == 7) lz_sel_maybe_compact<kSelThreads>(&sb, 8 * kSub);
     }
     __syncthreads();
     lz_sel_compact<kSelThreads>(&sb);
@@ -530,6 +582,15 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
 
 }  // namespace
 
+#ifdef LZ_STATS
+extern "C" int lz_debug_stats(unsigned long long* host_out, int reset) {
+    LZ_CUDA(cudaDeviceSynchronize());
+    LZ_CUDA(cudaMemcpyFromSymbol(host_out, g_stats, sizeof(unsigned long long) * 8));
+    if (reset) { unsigned long long z[8] = {0}; LZ_CUDA(cudaMemcpyToSymbol(g_stats, z, sizeof(z))); }
+    return LZ_OK;
+}
+#endif
+
 extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, void* out_bf16,
                                void* stream) {
     if (n <= 0) return LZ_OK;
@@ -598,7 +659,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
-        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups;
+        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.debug = env_int("LZ_DEBUG", 0);
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
@@ -627,6 +688,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
 
     SelectParams sp;
     sp.rows = rows; sp.ld = ld; sp.dim = dim; sp.norms = norms; sp.queries = queries; sp.q_ld = q_ld; sp.eps = eps;
+    sp.tags = tags; sp.want_tag = want_tag; sp.row_lo = row_lo; sp.row_hi = row_hi;
     sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;

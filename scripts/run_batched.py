@@ -1,6 +1,8 @@
 """Small driver for profiling the batched search: python scripts/run_batched.py [rows] [batch] [k] [iters]"""
 import os, sys, time
 sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..")))
+from lazzaro_b200 import _lib
+_lib.LIB_PATH = os.environ.get('LZ_LIB', _lib.LIB_PATH)
 import torch
 from lazzaro_b200 import synth, kernels as K
 
