@@ -12,8 +12,10 @@ the N ranks, so total work is fixed: "scaling": "strong").  Prints ONE JSON line
             on the launching stream, max over ranks)
   e2e       the same metric through the public Store call with HOST query buffers and host results
             (pinned H2D of the queries and D2H of ids/scores inside the timed region)
-  roofline  the scan kernel against the measured HBM peak (MEASURED_PEAKS.json), algorithmic bytes =
-            rows_scanned * dim * 4 per pass over the rows
+  roofline  batch >= 8: the tensor-core search against the measured bf16 peak, algorithmic flops =
+            2 * batch * rows * dim; batch < 8: the exact scan against the measured HBM peak, algorithmic
+            bytes = rows * dim * 4 per pass.  The default run reports batch 1024 as `value`
+            and adds the batch-1 search (north_star's second target) under "batch1"
   cpu_baseline  the CPU port (oracle.flat_search.fast_topk_f32: float32 BLAS GEMM on all host cores
             + argpartition) on a bounded row sample, scaled linearly to the full row count
 
@@ -48,7 +50,8 @@ def parse():
     ap.add_argument("--rows", type=int, default=10_000_000)
     ap.add_argument("--dim", type=int, default=768)
     ap.add_argument("--shards", type=int, default=1024)
-    ap.add_argument("--batch", type=int, default=1)
+    ap.add_argument("--batch", type=int, default=1024)
+    ap.add_argument("--no-batch1", action="store_true", help="skip the secondary batch-1 (HBM-bound) measurement")
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--cpu-sample-rows", type=int, default=400_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -240,12 +243,16 @@ def main():
     assert bool((scores[:, 1:] <= scores[:, :-1]).all()), "results not sorted"
 
     hbm_peak, tc_peak, peak_src = peaks()
+    traffic = {}
+    tp = os.path.join(ROOT, "profiles", "traffic.json")           # dram bytes per launch from ncu --set full captures
+    if os.path.exists(tp) and args.rows == 10_000_000 and args.dim == 768 and world == 1:
+        traffic = json.load(open(tp))
     batched = args.batch >= store.min_batch and store.batched_search != "never"
     if batched:
         algo_flops = 2.0 * args.batch * n_local * args.dim           # 2*B*rows*D per batch
         achieved = algo_flops / (ms_kernel / args.steps * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": achieved, "peak": tc_peak, "unit": "TFLOP/s", "frac": achieved / tc_peak,
-                "traffic": None, "kernel": "gemm_topk_kernel (lz_search_batched)", "peak_source": peak_src,
+                "traffic": traffic.get("gemm_topk_kernel_10M_b%d" % args.batch), "kernel": "gemm_topk_kernel (lz_search_batched)", "peak_source": peak_src,
                 "algorithmic_flops_per_launch": algo_flops,
                 "certified_fraction": float(store.last_certified.float().mean().item()),
                 "note": "achieved uses the device time of the whole local batched search (query prep + GEMM/top-k + "
@@ -255,7 +262,7 @@ def main():
         algo_bytes = n_local * args.dim * 4 * n_groups               # one pass over the rows per query group
         achieved = algo_bytes / (ms_kernel / args.steps * 1e-3) / 1e9
         roof = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "kernel": "scan_kernel (lz_search_exact)", "peak_source": peak_src,
+                "traffic": traffic.get("scan_kernel_10M_b1") if args.batch == 1 else None, "kernel": "scan_kernel (lz_search_exact)", "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": algo_bytes,
                 "note": "achieved uses the device time of the local scan+merge launches (no collective)"}
     line = {
@@ -270,6 +277,27 @@ def main():
         "roofline": roof,
         "clocks": clocks.summary(),
     }
+    if not args.no_batch1 and args.batch != 1:
+        q1 = queries[:1].contiguous()
+        q1_host = q_host[:1]
+        f_dev = lambda: sharded.search_device(q1, args.k)
+        f_loc = lambda: store.search_device(q1, 0, args.k)
+        f_e2e = (lambda: store.search_nodes(q1_host[0].tolist(), limit=args.k)) if world == 1 else (lambda: sharded.search_host(q1_host, args.k))
+        for _ in range(3):
+            f_dev(); f_e2e()
+        n1 = max(args.steps, 10)
+        ms1, _ = timed(f_dev, n1)
+        ms1k, _ = timed(f_loc, n1)
+        ms1e, _ = timed(f_e2e, n1)
+        bytes1 = n_local * args.dim * 4
+        ach1 = bytes1 / (ms1k / n1 * 1e-3) / 1e9
+        line["batch1"] = {"value": 1e3 / (ms1 / n1), "unit": UNIT, "ms_per_step": ms1 / n1, "steps": n1,
+                          "e2e": {"value": 1e3 / (ms1e / n1), "unit": UNIT, "h2d_bytes_per_step": int(store._dim_p * 4),
+                                  "d2h_bytes_per_step": int(args.k * 16 + 4)},
+                          "roofline": {"bound": "hbm", "achieved": ach1, "peak": hbm_peak, "unit": "GB/s",
+                                       "frac": ach1 / hbm_peak, "traffic": traffic.get("scan_kernel_10M_b1"),
+                                       "kernel": "scan_kernel (lz_search_exact)", "algorithmic_bytes_per_launch": bytes1},
+                          "gpu_launches": int(n1 * (2 + (1 if world > 1 else 0)))}
     if rank == 0 and not args.no_cpu_baseline:
         qps, desc, cores, _ = cpu_search_qps(args, 3, 1)
         line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}

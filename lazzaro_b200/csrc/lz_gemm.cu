@@ -119,7 +119,6 @@ __device__ unsigned long long g_stats[8];   // 0 epi busy, 1 epi max, 2 mma wait
 // ---- the coarse pass ----------------------------------------------------------------------------------
 struct GemmParams {
     int n_queries, n_qtiles, n_slices, tiles_per_slice, n_tiles, kblocks;
-    int debug;          // experiments only: bit 0 = epilogue skips the scan
     int cs, n_qgroups;  // cluster size (CTAs that share one rows tile by TMA multicast) and q-tile groups of that size
     int64_t row_lo, row_hi;
     int kp, cap;
@@ -659,7 +658,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
-        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.debug = env_int("LZ_DEBUG", 0);
+        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
