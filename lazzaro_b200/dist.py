@@ -71,9 +71,15 @@ class ShardedSearch:
         if self._gather_ids is None or self._gather_ids.shape[1:] != (B, k):
             self._gather_ids = torch.empty((self.world, B, k), dtype=torch.int64, device=ids.device)
             self._gather_sc = torch.empty((self.world, B, k), dtype=torch.float64, device=ids.device)
-        dist.all_gather_into_tensor(self._gather_ids, ids, group=self.group)
-        dist.all_gather_into_tensor(self._gather_sc, sc, group=self.group)
+        self._all_gather(self._gather_ids, ids)
+        self._all_gather(self._gather_sc, sc)
         return self._merge(self._gather_ids, self._gather_sc)
+
+    def _all_gather(self, out: torch.Tensor, part: torch.Tensor):
+        if dist.get_backend(self.group) == "gloo":           # CPU tests of the bookkeeping
+            dist.all_gather(list(out.unbind(0)), part.contiguous(), group=self.group)
+        else:
+            dist.all_gather_into_tensor(out, part.contiguous(), group=self.group)
 
     def search_host(self, queries: np.ndarray, k: int):
         """Host queries in, host (ids, scores, counts) out: pinned H2D, search, D2H, one sync."""
