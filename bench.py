@@ -298,7 +298,7 @@ def main():
                                        "frac": ach1 / hbm_peak, "traffic": traffic.get("scan_kernel_10M_b1"),
                                        "kernel": "scan_kernel (lz_search_exact)", "algorithmic_bytes_per_launch": bytes1},
                           "gpu_launches": int(n1 * (2 + (1 if world > 1 else 0)))}
-    if rank == 0 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
         qps, desc, cores, _ = cpu_search_qps(args, 3, 1)
         line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
     if rank == 0:
