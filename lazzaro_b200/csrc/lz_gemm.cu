@@ -422,8 +422,30 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
     }
     __syncthreads();
     lz_sel_compact<kSelThreads>(&sa);
-    const int m = min(sa.count, p.kp);
+    int m = min(sa.count, p.kp);
     if (total > p.kp) T = fmaxf(T, unord32((u32)key_a[p.kp - 1]));
+    // Prune before rescoring: the k best groups lying wholly inside the range each hold an eligible row with
+    // coarse >= c_k (the k-th such group's key), i.e. k rows with exact >= c_k - eps; a group whose best
+    // coarse is below c_k - 2 eps holds only rows with exact < c_k - eps and cannot reach the top-k.
+    // (Not applicable under a tag filter, where a group's best row may be ineligible.)
+    __shared__ int m_eff;
+    if (tid == 0) {
+        int keep = m;
+        if (p.tags == nullptr) {
+            int full = 0;
+            for (int j = 0; j < m; ++j) {
+                if ((int64_t)id_a[j] + kSub <= p.row_hi && ++full == p.k) {
+                    const float cutoff = unord32((u32)key_a[j]) - 2.0f * (float)p.eps[q];
+                    keep = j + 1;
+                    while (keep < m && unord32((u32)key_a[keep]) >= cutoff) ++keep;
+                    break;
+                }
+            }
+        }
+        m_eff = keep;
+    }
+    __syncthreads();
+    m = m_eff;
     // 2. exact float64 rescoring of the survivors, canonical summation order
     const float* qv = p.queries + (int64_t)q * p.q_ld;
     double qs = 0.0;
@@ -548,7 +570,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     if (pl->tiles_per_slice < 1) pl->tiles_per_slice = 1;
     pl->n_slices = (pl->n_tiles + pl->tiles_per_slice - 1) / pl->tiles_per_slice;
     if (pl->n_slices < 1) pl->n_slices = 1;
-    pl->kp = k <= 16 ? 128 : (k <= 48 ? 256 : 512);
+    pl->kp = k <= 3 ? 32 : (k <= 16 ? 128 : (k <= 48 ? 256 : 512));
     pl->cap = 2 * pl->kp;
     int64_t fb = (n_rows + 255) / 256;
     pl->fb_chunks = (int)(fb < sms ? (fb < 1 ? 1 : fb) : sms);
@@ -663,7 +685,8 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (2 * kStages + 4) * 8 + 16;
-        auto kern = pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
+        auto kern = pl.kp == 32 ? gemm_topk_kernel<2>
+                  : pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
         LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (pl.cs > 4) LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cudaLaunchConfig_t cfg = {};
