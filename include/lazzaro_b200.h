@@ -144,6 +144,17 @@ int lz_score_pairs(const float* rows, int64_t ld, int dim, const double* norms,
                    const float* queries, int64_t q_ld, const int32_t* pair_q, const int64_t* pair_row,
                    int64_t n_pairs, int metric, double* out_scores, void* stream);
 
+/* ---- centroids (stands behind MemorySystem._create_super_nodes_for_shard, core/memory_system.py:916-917,
+ *      and the centroid update of shard reassignment) ----------------------------------------------- */
+
+/* out_means[s][j] = mean over i in [seg_offsets[s], seg_offsets[s+1]) of rows[order ? order[i] : i][j],
+ * accumulated in float64 in a fixed order (deterministic); an empty segment gives zeros.
+ *   order        optional int64 [seg_offsets[n_segments]] row indices (members grouped by segment);
+ *                NULL = segments are contiguous row ranges (rows stored shard by shard)
+ *   seg_offsets  int64 [n_segments + 1];  out_means float64 [n_segments, dim] */
+int lz_segment_mean(const float* rows, int64_t ld, int dim, const int64_t* order, const int64_t* seg_offsets,
+                    int n_segments, double* out_means, void* stream);
+
 /* ---- biological decay and pruning (stands behind MemoryShard.apply_temporal_decay and
  *      MemoryShard.prune_weak_edges, core/memory_shard.py:64-84; fan-out core/buffer_graph.py:87-97) */
 

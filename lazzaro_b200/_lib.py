@@ -34,6 +34,7 @@ SIGNATURES = {
                                  _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),
+    "lz_segment_mean": (_i32, [_p, _i64, _i32, _p, _p, _i32, _p, _p]),
     "lz_edge_decay_prune_scratch_bytes": (_sz, [_i64]),
     "lz_edge_decay_prune": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "lz_edge_decay_prune_noalloc": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p]),

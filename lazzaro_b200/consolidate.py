@@ -1,0 +1,120 @@
+"""Episodic-buffer consolidation on the device: dedup, linking, shard (re)assignment, centroids.
+
+Host-side mirror of the arithmetic inside the reference's consolidation path
+(/root/reference/src/lazzaro/core/memory_system.py):
+
+  dedup_against_store   lines 719-742  per new memory: top-1 of the store, merge if cosine > 0.95
+  link_candidates       lines 838-891 / 816-836  per new memory: top-3 existing rows with cosine > 0.5,
+                        edge weight 0.8 * cosine
+  assign_to_centroids   no reference code: argmax_c cosine(x, centroid_c), ties to the
+                        lowest centroid index — the k-means style shard reassignment north_star names
+  centroid_means        lines 916-917  centroid = arithmetic mean of the member embeddings
+
+The reference issues one search per new memory, sequentially, and new memories of one batch never see
+each other (they are added to the store after the loop, memory_system.py:768-769), so a single batched
+search per step is semantically identical.  All of it is the same tensor-core contraction as the
+batched search (`lz_search_batched`, k = 1 or 3) followed by exact float64 rescoring, so the decisions
+(which rows, which side of the 0.95 / 0.5 gates) are those of the exact float64 cosine; the host only
+applies the reference's rules to the results.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib, kernels
+
+DEDUP_GATE = 0.95       # memory_system.py:731
+LINK_GATE = 0.5         # memory_system.py:829, 867
+LINK_TOP = 3            # memory_system.py:828, 866
+LINK_SCALE = 0.8        # memory_system.py:833, 881
+
+
+def _queries_on_device(store, emb) -> torch.Tensor:
+    q = np.ascontiguousarray(emb, dtype=np.float32)
+    if q.shape[1] != store.dim:
+        raise ValueError(f"embeddings have {q.shape[1]} dims, store has {store.dim}")
+    out = torch.zeros((q.shape[0], store._dim_p), dtype=torch.float32, device=store.device)
+    out[:, :store.dim] = torch.from_numpy(q).to(store.device, non_blocking=True)
+    return out
+
+
+def dedup_against_store(store, new_emb, user_id: str = "default", gate: float = DEDUP_GATE):
+    """For each new embedding: the store's best row for `user_id` and whether it is a semantic duplicate.
+    Returns (ids: list of str or None, cosine float64 [n], is_duplicate bool [n])."""
+    n = len(new_emb)
+    u = store._user(user_id)
+    if n == 0 or store.n_rows == 0 or u < 0 or store._live[u] == 0:
+        return [None] * n, np.zeros(n), np.zeros(n, bool)
+    with store._lock:
+        ids, sc, cnt = store.search_device(_queries_on_device(store, new_emb), u, 1)
+        torch.cuda.current_stream(store.device).synchronize()
+        ids, sc, cnt = ids.cpu().numpy()[:, 0], sc.cpu().numpy()[:, 0], cnt.cpu().numpy()
+        if store.metric != "cosine":                    # the gate is a cosine whatever the search metric
+            q = _queries_on_device(store, new_emb)
+            pq = torch.arange(n, dtype=torch.int32, device=store.device)
+            sc = kernels.score_pairs(store._rows, store._dim_p, store._norms, q, pq,
+                                     torch.from_numpy(ids).to(store.device), _lib.COSINE).cpu().numpy()
+        names = [store._id_of(int(r)) if c else None for r, c in zip(ids, cnt)]
+        sims = np.where(cnt > 0, sc, 0.0)
+        return names, sims, (cnt > 0) & (sims > gate)
+
+
+def link_candidates(store, new_emb, user_id: str = "default", m: int = LINK_TOP, threshold: float = LINK_GATE,
+                    scale: float = LINK_SCALE, row_range: Optional[Tuple[int, int]] = None):
+    """For each new embedding the up-to-m best existing rows with cosine > threshold, best first, as
+    (id, cosine, edge_weight = scale * cosine).  `row_range` restricts the scan to one shard's rows
+    (_link_within_shards); the default scans every row of the user (_link_to_existing_memories)."""
+    n = len(new_emb)
+    u = store._user(user_id)
+    if n == 0 or store.n_rows == 0 or u < 0 or store._live[u] == 0:
+        return [[] for _ in range(n)]
+    with store._lock:
+        q = _queries_on_device(store, new_emb)
+        if row_range is None:
+            ids, sc, cnt = store.search_device(q, u, m)
+        else:
+            ids, sc, cnt = store.search_device(q, u, m, row_range=row_range)
+        torch.cuda.current_stream(store.device).synchronize()
+        ids, sc, cnt = ids.cpu().numpy(), sc.cpu().numpy(), cnt.cpu().numpy()
+        out = []
+        for i in range(n):
+            out.append([(store._id_of(int(r)), float(s), float(s) * scale)
+                        for r, s in zip(ids[i, :cnt[i]], sc[i, :cnt[i]]) if s > threshold])
+        return out
+
+
+def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigmas: float = 4.0):
+    """argmax_c cosine(row, centroid_c) for float32 CUDA tensors rows [n, dim], centroids [K, dim]
+    (dim % 8 == 0).  Returns (index int64 [n], cosine float64 [n]) on the device; ties go to the lowest
+    centroid index.  Rows are the query side of the contraction, centroids the scanned side."""
+    assert rows.is_cuda and centroids.is_cuda and rows.dtype == torch.float32 and centroids.dtype == torch.float32
+    dim = rows.shape[1]
+    cen = centroids.contiguous()
+    norms = kernels.row_norms(cen)
+    n = rows.shape[0]
+    if n >= 8 and dim % 8 == 0:
+        shadow = kernels.rows_to_bf16(cen, dim, norms)
+        ids, sc, cnt, _ = kernels.search_batched(shadow, cen, dim, norms, None, -1, rows, 1, margin_sigmas=margin_sigmas)
+    else:
+        ids, sc, cnt = kernels.search_exact(cen, dim, norms, None, rows, 1, _lib.COSINE)
+    return ids[:, 0], sc[:, 0]
+
+
+def centroid_means(rows: torch.Tensor, assign: Optional[torch.Tensor] = None, n_centroids: Optional[int] = None,
+                   seg_offsets: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """float64 [K, dim] arithmetic means (memory_system.py:916-917).  Either `seg_offsets` (int64 [K+1],
+    members of centroid c are the contiguous rows seg_offsets[c]:seg_offsets[c+1] — rows stored shard by
+    shard) or `assign` (int64 [n] centroid of each row).  With `assign`, member lists are formed by a
+    stable sort of the assignment (torch, index plumbing only); the summation is lz_segment_mean."""
+    dim = rows.shape[1]
+    if seg_offsets is not None:
+        return kernels.segment_mean(rows, dim, seg_offsets.to(torch.int64))
+    assert assign is not None and n_centroids is not None
+    order = torch.argsort(assign, stable=True)
+    counts = torch.bincount(assign, minlength=n_centroids)
+    seg = torch.zeros(n_centroids + 1, dtype=torch.int64, device=rows.device)
+    seg[1:] = torch.cumsum(counts, 0)
+    return kernels.segment_mean(rows, dim, seg, order)

@@ -456,3 +456,49 @@ extern "C" int lz_score_pairs(const float* rows, int64_t ld, int dim, const doub
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
+
+// ---- K6: segmented mean (centroids) ----------------------------------------------------------------------
+// Stands behind _create_super_nodes_for_shard (core/memory_system.py:916-917: centroid = np.mean of the
+// member embeddings) and the centroid update of shard reassignment.  One CTA per (segment, 128-column
+// chunk); warp w adds rows w, w+8, ... in float64 in a fixed order and the eight partial sums are combined
+// in warp order, so the result is deterministic.  HBM-bound: dim*4 bytes per member row.
+namespace {
+__global__ void __launch_bounds__(kThreads) segment_mean_kernel(const float* __restrict__ rows, int64_t ld, int dim,
+                                                                const int64_t* __restrict__ order,
+                                                                const int64_t* __restrict__ seg, double* __restrict__ out) {
+    __shared__ double part[kWarps][128];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int s = blockIdx.x, col = blockIdx.y * 128 + lane * 4;
+    const int64_t lo = seg[s], hi = seg[s + 1];
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    if (col < dim) {
+        for (int64_t i = lo + warp; i < hi; i += kWarps) {
+            const int64_t r = order ? order[i] : i;
+            const float4 v = lz_ldg_stream(rows + r * ld + col);
+            a0 += (double)v.x; a1 += (double)v.y; a2 += (double)v.z; a3 += (double)v.w;
+        }
+    }
+    part[warp][lane * 4 + 0] = a0; part[warp][lane * 4 + 1] = a1;
+    part[warp][lane * 4 + 2] = a2; part[warp][lane * 4 + 3] = a3;
+    __syncthreads();
+    if (threadIdx.x < 128 && blockIdx.y * 128 + threadIdx.x < dim) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < kWarps; ++w) t += part[w][threadIdx.x];
+        const int64_t n = hi - lo;
+        out[(int64_t)s * dim + blockIdx.y * 128 + threadIdx.x] = n > 0 ? t / (double)n : 0.0;
+    }
+}
+}  // namespace
+
+extern "C" int lz_segment_mean(const float* rows, int64_t ld, int dim, const int64_t* order, const int64_t* seg_offsets,
+                               int n_segments, double* out_means, void* stream) {
+    if (n_segments <= 0) return LZ_OK;
+    if (int rc = check_rows("lz_segment_mean", rows, ld, dim)) return rc;
+    LZ_REQUIRE(seg_offsets && out_means, "lz_segment_mean: NULL pointer");
+    dim3 grid((unsigned)n_segments, (unsigned)((dim + 127) / 128));
+    LZ_REQUIRE(grid.y <= 65535, "lz_segment_mean: dim too large");
+    segment_mean_kernel<<<grid, kThreads, 0, (cudaStream_t)stream>>>(rows, ld, dim, order, seg_offsets, out_means);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

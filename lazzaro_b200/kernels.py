@@ -178,3 +178,15 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
                                     float(margin_sigmas), int(id_base), ptr(scratch), scratch.numel(),
                                     ptr(ids), ptr(scores), ptr(counts), ptr(cert), stream_ptr(dev)), "lz_search_batched")
     return ids, scores, counts, cert
+
+
+def segment_mean(rows: torch.Tensor, dim: int, seg_offsets: torch.Tensor, order: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """float64 [n_segments, dim] means of row groups (lz_segment_mean)."""
+    dev = _dev(rows)
+    assert seg_offsets.dtype == torch.int64 and (order is None or order.dtype == torch.int64)
+    n_seg = seg_offsets.numel() - 1
+    out = torch.empty((n_seg, dim), dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_segment_mean(ptr(rows), rows.stride(0), dim, ptr(order), ptr(seg_offsets), n_seg, ptr(out),
+                                          stream_ptr(dev)), "lz_segment_mean")
+    return out

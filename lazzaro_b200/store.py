@@ -322,11 +322,15 @@ class B200Store:
             torch.cuda.current_stream().synchronize()
         return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()
 
-    def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0):
+    def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0,
+                      row_range=None):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
         tensors, nothing synchronised.  The exact fp64 scan over the user's row span."""
         u = self._user(user) if isinstance(user, str) else user
         lo, hi = self._span[u]
+        if row_range is not None:                      # e.g. one semantic shard's contiguous rows
+            lo, hi = max(lo, int(row_range[0])), min(hi, int(row_range[1]))
+            hi = max(hi, lo)
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
         tags = None if single_user else self._tags
         B = queries.shape[0]
