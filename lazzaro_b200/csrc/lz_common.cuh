@@ -33,14 +33,15 @@ void lz_set_error(const char* fmt, ...);
 
 int lz_sm_count();
 
-// lz_search_exact with an optional per-query skip mask (device int32 [n_queries], non-zero = leave the
-// query's outputs untouched).  Used by the batched search to re-run only the uncertified queries.
+// lz_search_exact with an optional device-side work list: int32 indices of the queries to answer (the
+// others' outputs are left untouched) and their count.  Used by the batched search to re-run only the
+// queries that failed certification; an empty list costs one small launch.
 int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
                          int64_t row_lo, int64_t row_hi, const int64_t* group_lo, const int64_t* group_hi,
                          const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
                          int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
                          size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
-                         const int32_t* query_skip, void* stream);   // SM count of the current device (cached per device), <= 0 on failure
+                         const int32_t* work_list, const int32_t* work_count, void* stream);   // SM count of the current device (cached per device), <= 0 on failure
 
 // ---- device helpers ----------------------------------------------------------------------------
 

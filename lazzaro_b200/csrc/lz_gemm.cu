@@ -79,9 +79,11 @@ __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restri
 // one warp per query: normalised bf16 copy + the certification margin eps[q]
 __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
                                                               __nv_bfloat16* __restrict__ out, double* __restrict__ eps,
-                                                              int32_t* __restrict__ gtag, u32* __restrict__ gthr, int want_tag, double sigmas) {
+                                                              int32_t* __restrict__ gtag, u32* __restrict__ gthr, int32_t* __restrict__ fb_count,
+                                                              int want_tag, double sigmas) {
     const int lane = threadIdx.x & 31;
     const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count = 0;
     if (w >= n) return;
     const float* v = q + (int64_t)w * q_ld;
     double ss = 0.0;
@@ -389,6 +391,7 @@ struct SelectParams {
     int n_qtiles_pad, n_slices, kp, cap, k, cap_a, cap_b;   // n_qtiles_pad = n_qgroups * cs
     int64_t id_base;
     int64_t* out_ids; double* out_scores; int32_t* out_counts; int32_t* certified;
+    int32_t* fb_list; int32_t* fb_count;     // queries that failed certification, for the exact fallback
 };
 
 __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParams p) {
@@ -505,6 +508,123 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         bool cert = T == -INFINITY;
         if (!cert && n >= p.k) cert = lz_unord(key_b[p.k - 1]) > (double)T + p.eps[q];
         p.certified[q] = cert ? 1 : 0;
+        if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
+    }
+}
+
+
+// Small-k variant of the exact pass (k <= 3: dedup, linking, centroid assignment — often millions of
+// "queries"): one WARP per query, no shared memory.  Same rule as above: find c_k among the candidate
+// groups, rescore every group within 2 eps of it, keep the best k rows in lane 0, certify against the
+// largest threshold any slice dropped under.  Nothing is discarded here, so T is just that maximum.
+constexpr int kSmallK = 3;
+
+__global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(SelectParams p, int n_queries) {
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * (kSelThreads / 32) + (threadIdx.x >> 5);
+    if (q >= n_queries) return;
+    const int qt = q / BM, ql = q % BM;
+    const float eps = (float)p.eps[q];
+    // pass 1: c_k = k-th largest group key among groups wholly inside the range (k rounds of warp max)
+    float T = -INFINITY;
+    u64 below = ~0ull;                     // keys must be < below to be picked in this round
+    float ck = -INFINITY;
+    bool have_k = true;
+    for (int round = 0; round < p.k; ++round) {
+        u64 best = 0ull;
+        for (int sl = 0; sl < p.n_slices; ++sl) {
+            const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+            const int cnt = p.cand_cnt[slot];
+            if (round == 0) T = fmaxf(T, p.cand_thr[slot]);
+            const u64* src = p.cand + slot * p.cap;
+            for (int j = lane; j < cnt; j += 32) {
+                const u64 kk = src[j];
+                const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
+                if (kk < below && kk > best && (p.tags != nullptr || r0 + kSub <= p.row_hi)) best = kk;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const u64 other = __shfl_xor_sync(0xffffffffu, best, o);
+            best = other > best ? other : best;
+        }
+        if (best == 0ull) { have_k = false; break; }
+        below = best;
+        ck = unord32((u32)(best >> 32));
+    }
+    const float cutoff = (have_k && p.tags == nullptr) ? ck - 2.0f * eps : -INFINITY;
+    // pass 2: rescore the rows of every group at or above the cutoff; lane 0 keeps the best k
+    const float* qv = p.queries + (int64_t)q * p.q_ld;
+    double qs = 0.0;
+    for (int e = lane * 4; e < p.dim; e += 128) {
+        const float4 x = *reinterpret_cast<const float4*>(qv + e);
+        qs = fma((double)x.x, (double)x.x, qs);
+        qs = fma((double)x.y, (double)x.y, qs);
+        qs = fma((double)x.z, (double)x.z, qs);
+        qs = fma((double)x.w, (double)x.w, qs);
+    }
+    const double qn = sqrt(lz_warp_sum(qs));
+    u64 bk[kSmallK];
+    u32 bi[kSmallK];
+#pragma unroll
+    for (int i = 0; i < kSmallK; ++i) { bk[i] = 0ull; bi[i] = 0xffffffffu; }
+    int found = 0;
+    for (int sl = 0; sl < p.n_slices; ++sl) {
+        const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+        const int cnt = p.cand_cnt[slot];
+        const u64* src = p.cand + slot * p.cap;
+        for (int j = 0; j < cnt; ++j) {
+            const u64 kk = src[j];                                          // warp-uniform
+            if (unord32((u32)(kk >> 32)) < cutoff) continue;
+            const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
+            for (int r = 0; r < kSub; ++r) {
+                const int64_t row = r0 + r;
+                bool ok = row < p.row_hi;
+                if (ok && p.tags) {
+                    const int tg = p.tags[row];
+                    ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                }
+                if (!ok) continue;
+                const float* x = p.rows + row * p.ld;
+                double acc = 0.0;
+                for (int e = lane * 4; e < p.dim; e += 128) {
+                    const float4 xv = lz_ldg_stream(x + e);
+                    const float4 qq = *reinterpret_cast<const float4*>(qv + e);
+                    acc = fma((double)xv.x, (double)qq.x, acc);
+                    acc = fma((double)xv.y, (double)qq.y, acc);
+                    acc = fma((double)xv.z, (double)qq.z, acc);
+                    acc = fma((double)xv.w, (double)qq.w, acc);
+                }
+                acc = lz_warp_sum(acc);
+                const double den = p.norms[row] * qn;
+                double s = den > 0.0 ? acc / den : 0.0;
+                s += 0.0;
+                if (s != s) continue;
+                u64 key = lz_ord(s);
+                u32 id = (u32)row;
+                ++found;
+#pragma unroll
+                for (int i = 0; i < kSmallK; ++i) {                         // insertion into the sorted best-k
+                    if (i < p.k && lz_better(key, id, bk[i], bi[i])) {
+                        const u64 tk = bk[i]; const u32 ti = bi[i];
+                        bk[i] = key; bi[i] = id; key = tk; id = ti;
+                    }
+                }
+            }
+        }
+    }
+    if (lane == 0) {
+        const int n = found < p.k ? found : p.k;
+        for (int j = 0; j < p.k; ++j) {
+            const bool has = j < n;
+            p.out_ids[(size_t)q * p.k + j] = has ? (int64_t)bi[j] + p.id_base : -1;
+            p.out_scores[(size_t)q * p.k + j] = has ? lz_unord(bk[j]) : __longlong_as_double(0x7ff8000000000000ll);
+        }
+        p.out_counts[q] = n;
+        bool cert = T == -INFINITY;
+        if (!cert && n >= p.k) cert = lz_unord(bk[p.k - 1]) > (double)T + (double)eps;
+        p.certified[q] = cert ? 1 : 0;
+        if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
     }
 }
 
@@ -580,7 +700,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
 }
 
 struct ScratchLayout {
-    size_t q_bf16, eps, gtag, gthr, cand, cand_cnt, cand_thr, certified, fallback, total;
+    size_t q_bf16, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
 };
 
 ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
@@ -592,6 +712,8 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
     L.gthr = take((size_t)n_queries * 4);
+    L.fb_list = take((size_t)n_queries * 4);
+    L.fb_count = take(4);
     L.cand = take(items * BM * pl.cap * 8);
     L.cand_cnt = take(items * BM * 4);
     L.cand_thr = take(items * BM * 4);
@@ -669,8 +791,10 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
 
     int32_t* gtag = (int32_t*)(s + L.gtag);
     u32* gthr = (u32*)(s + L.gthr);
+    int32_t* fb_list = (int32_t*)(s + L.fb_list);
+    int32_t* fb_count = (int32_t*)(s + L.fb_count);
     queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
-                                                                want_tag, margin_sigmas);
+                                                                fb_count, want_tag, margin_sigmas);
     LZ_CUDA(cudaGetLastError());
 
     if (row_hi > row_lo) {
@@ -717,13 +841,18 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
-    const size_t ssmem = (size_t)(sp.cap_a + sp.cap_b) * 12;
-    LZ_CUDA(cudaFuncSetAttribute(select_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
-    select_rescore_kernel<<<n_queries, kSelThreads, ssmem, st>>>(sp);
+    sp.fb_list = fb_list; sp.fb_count = fb_count;
+    if (k <= kSmallK) {
+        select_rescore_small_kernel<<<(n_queries + kSelThreads / 32 - 1) / (kSelThreads / 32), kSelThreads, 0, st>>>(sp, n_queries);
+    } else {
+        const size_t ssmem = (size_t)(sp.cap_a + sp.cap_b) * 12;
+        LZ_CUDA(cudaFuncSetAttribute(select_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
+        select_rescore_kernel<<<n_queries, kSelThreads, ssmem, st>>>(sp);
+    }
     LZ_CUDA(cudaGetLastError());
 
     // exact float64 scan for the queries that could not be certified (a no-op launch when all were)
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, nullptr, nullptr, tags ? gtag : nullptr, queries, q_ld,
                                 n_queries, 1, k, LZ_COSINE, pl.fb_chunks, id_base, s + L.fallback,
-                                L.total - L.fallback, out_ids, out_scores, out_counts, cert, stream);
+                                L.total - L.fallback, out_ids, out_scores, out_counts, fb_list, fb_count, stream);
 }

@@ -48,7 +48,8 @@ struct ScanParams {
     const float* queries; int64_t q_ld; int n_queries;
     int k; int n_chunks; int cap;
     u64* part_key; u32* part_id; int32_t* part_cnt;
-    const int32_t* skip;     // optional [n_queries]: non-zero = leave this query alone (group_size 1 only)
+    const int32_t* work_list;   // optional: indices of the queries to answer (group_size 1); others untouched
+    const int32_t* work_count;  // device count of work_list entries
 };
 
 template <int QB, int METRIC>
@@ -56,11 +57,14 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nseg = (p.dim + 127) >> 7;
-    const int g = blockIdx.x / p.n_chunks;
-    const int c = blockIdx.x - g * p.n_chunks;
+    // Normally one (group, chunk) item per CTA.  With a work list (the batched search's fallback) a fixed
+    // grid loops over (listed query, chunk) items, so an empty list costs one tiny launch.
+    const int total = p.work_list ? (*p.work_count) * p.n_chunks : (int)gridDim.x;
+    for (int item = blockIdx.x; item < total; item += gridDim.x) {
+    const int g = p.work_list ? p.work_list[item / p.n_chunks] : item / p.n_chunks;
+    const int c = item % p.n_chunks;
     const int q0 = g * QB;
     const int nq = min(QB, p.n_queries - q0);
-    if (p.skip != nullptr && p.skip[q0] != 0) return;      // CTA-uniform: group_size is 1 when skip is set
 
     // shared memory carve-up
     double2* qs = reinterpret_cast<double2*>(smem);                 // [QB][nseg][2][32]
@@ -185,6 +189,8 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
         }
         if (tid == 0) p.part_cnt[slot] = n;
     }
+    __syncthreads();            // shared state is re-initialised by the next item
+    }
 }
 
 // One CTA per query: stream the per-chunk lists through a selector.
@@ -192,7 +198,7 @@ struct MergeParams {
     const u64* part_key; const u32* part_id; const int32_t* part_cnt;   // form A: scan partials
     const int64_t* in_ids; const double* in_scores; int n_queries;      // form B: (id, score) lists
     int n_lists; int k; int cap; int metric; int64_t id_base;
-    const int32_t* skip;
+    const int32_t* work_list; const int32_t* work_count;
     int64_t* out_ids; double* out_scores; int32_t* out_counts;
 };
 
@@ -201,8 +207,10 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
     u64* keys = reinterpret_cast<u64*>(smem);
     u32* ids = reinterpret_cast<u32*>(keys + p.cap);
     __shared__ LzSelector sel;
-    const int tid = threadIdx.x, q = blockIdx.x;
-    if (p.skip != nullptr && p.skip[q] != 0) return;
+    const int tid = threadIdx.x;
+    const int n_items = p.work_list ? *p.work_count : (int)gridDim.x;
+    for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+    const int q = p.work_list ? p.work_list[item] : item;
     if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
     __syncthreads();
     const int64_t total = (int64_t)p.n_lists * p.k;
@@ -239,6 +247,8 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
         }
     }
     if (tid == 0) p.out_counts[q] = n;
+    __syncthreads();
+    }
 }
 
 // One warp per (query, row) pair, same summation order as the scan.
@@ -303,7 +313,12 @@ int launch_scan(const ScanParams& p, int metric, int n_groups, cudaStream_t st) 
     auto kern = metric == LZ_COSINE ? scan_kernel<QB, LZ_COSINE> : scan_kernel<QB, LZ_L2>;
     LZ_REQUIRE(smem <= 220 * 1024, "lz_search_exact: k=%d dim=%d needs %zu B of shared memory", p.k, p.dim, smem);
     LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)((int64_t)n_groups * p.n_chunks), kThreads, smem, st>>>(p);
+    int64_t grid = (int64_t)n_groups * p.n_chunks;
+    if (p.work_list) {                       // fallback mode: a fixed grid walks the device-side work list
+        const int64_t cap = (int64_t)lz_sm_count() * 4;
+        if (grid > cap) grid = cap;
+    }
+    kern<<<(unsigned)grid, kThreads, smem, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
@@ -356,7 +371,7 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
                          const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
                          int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
                          size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
-                         const int32_t* query_skip, void* stream) {
+                         const int32_t* work_list, const int32_t* work_count, void* stream) {
     if (n_queries <= 0) return LZ_OK;
     if (int rc = check_rows("lz_search_exact", rows, ld, dim)) return rc;
     LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_exact: unknown metric %d", metric);
@@ -365,7 +380,8 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     LZ_REQUIRE(group_size == 1 || group_size == 2 || group_size == 4,
                "lz_search_exact: group_size=%d must be 1, 2 or 4", group_size);
     LZ_REQUIRE(n_chunks >= 1, "lz_search_exact: n_chunks=%d", n_chunks);
-    LZ_REQUIRE(query_skip == nullptr || group_size == 1, "lz_search_exact: a skip mask needs group_size 1");
+    LZ_REQUIRE(work_list == nullptr || (group_size == 1 && work_count != nullptr),
+               "lz_search_exact: a work list needs group_size 1 and a count");
     LZ_REQUIRE(queries && q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
                "lz_search_exact: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
     LZ_REQUIRE((group_lo == nullptr) == (group_hi == nullptr), "lz_search_exact: group_lo/group_hi must come together");
@@ -382,7 +398,8 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     p.rows = rows; p.ld = ld; p.dim = dim; p.norms = norms; p.tags = tags;
     p.row_lo = row_lo; p.row_hi = row_hi; p.group_lo = group_lo; p.group_hi = group_hi; p.group_tag = group_tag;
     p.queries = queries; p.q_ld = q_ld; p.n_queries = n_queries;
-    p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows); p.skip = query_skip;
+    p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows);
+    p.work_list = work_list; p.work_count = work_count;
     unsigned char* s = (unsigned char*)scratch;
     p.part_key = (u64*)s;
     p.part_id = (u32*)(s + slots * k * sizeof(u64));
@@ -395,11 +412,14 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
     m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries;
-    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = id_base; m.skip = query_skip;
+    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = id_base;
+    m.work_list = work_list; m.work_count = work_count;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
     const size_t msmem = (size_t)m.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
-    merge_kernel<<<n_queries, kThreads, msmem, st>>>(m);
+    int mgrid = n_queries;
+    if (work_list && mgrid > lz_sm_count() * 8) mgrid = lz_sm_count() * 8;
+    merge_kernel<<<mgrid, kThreads, msmem, st>>>(m);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
@@ -412,7 +432,7 @@ extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const dou
                                void* stream) {
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, group_lo, group_hi, group_tag, queries,
                                 q_ld, n_queries, group_size, k, metric, n_chunks, id_base, scratch, scratch_bytes,
-                                out_ids, out_scores, out_counts, nullptr, stream);
+                                out_ids, out_scores, out_counts, nullptr, nullptr, stream);
 }
 
 extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,
@@ -424,7 +444,8 @@ extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int
     MergeParams m;
     m.part_key = nullptr; m.part_id = nullptr; m.part_cnt = nullptr;
     m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries;
-    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = 0; m.skip = nullptr;
+    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = 0;
+    m.work_list = nullptr; m.work_count = nullptr;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
     const size_t msmem = (size_t)m.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));

@@ -358,6 +358,88 @@ class B200Store:
                                     row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
                                     scratch=self._scratch, id_base=id_base)
 
+    # ------------------------------------------------------------------ multi-tenant and two-level search
+    def search_users(self, queries, user_ids: Sequence[str], limit: int = 5):
+        """One query per (possibly different) user in a single launch: query i is answered from the rows
+        of user_ids[i] only (the per-user pre-filter of vector_store.py:137, batched).  Each query scans
+        just its user's row span, so 100k small tenants cost what their rows cost, not the table.
+        Returns a list of id lists."""
+        with self._lock:
+            q = np.ascontiguousarray(queries, dtype=np.float32)
+            B = q.shape[0]
+            assert len(user_ids) == B
+            us = np.array([self._user(u) for u in user_ids], dtype=np.int64)
+            known = us >= 0
+            lo = np.array([self._span[u][0] if u >= 0 else 0 for u in us], dtype=np.int64)
+            hi = np.array([self._span[u][1] if u >= 0 else 0 for u in us], dtype=np.int64)
+            hi = np.maximum(hi, lo)
+            live = np.array([self._live[u] if u >= 0 else 0 for u in us])
+            if self._n == 0 or not known.any() or limit <= 0:
+                return [[] for _ in range(B)]
+            k = int(min(limit, max(1, live.max())))
+            if k > _lib.MAX_K:
+                raise ValueError(f"limit={limit} exceeds the kernel's top-k bound of {_lib.MAX_K}")
+            ids, sc, cnt = self.search_ranges_device(self._to_device(q), lo, hi, us.astype(np.int32), k)
+            torch.cuda.current_stream(self.device).synchronize()
+            ids, cnt = ids.cpu().numpy(), cnt.cpu().numpy()
+            return [[self._id_of(int(r)) for r in ids[b, :cnt[b]]] if known[b] else [] for b in range(B)]
+
+    def _to_device(self, q: np.ndarray) -> torch.Tensor:
+        if q.shape[1] != self.dim:
+            raise ValueError(f"query has {q.shape[1]} dims, store has {self.dim}")
+        out = torch.zeros((q.shape[0], self._dim_p), dtype=torch.float32, device=self.device)
+        out[:, :self.dim] = torch.from_numpy(q).to(self.device, non_blocking=True)
+        return out
+
+    def search_ranges_device(self, queries: torch.Tensor, lo, hi, tag, k: int):
+        """Exact search of query i over rows [lo[i], hi[i]) restricted to tag[i] (< 0: any live row)."""
+        dev = self.device
+        as_dev = lambda a, dt: torch.as_tensor(np.asarray(a), dtype=dt).to(dev, non_blocking=True)
+        span = int(np.max(np.asarray(hi) - np.asarray(lo))) if len(lo) else 0
+        n_chunks = kernels.default_chunks(max(span, 1), queries.shape[0], dev)
+        return kernels.search_exact(self._rows, self._dim_p, self._norms, self._tags, queries, k, self._metric,
+                                    row_range=(0, self._n), group_lo=as_dev(lo, torch.int64),
+                                    group_hi=as_dev(hi, torch.int64), group_tag=as_dev(tag, torch.int32),
+                                    group_size=1, n_chunks=n_chunks)
+
+    def set_shards(self, shard_offsets: Sequence[int]):
+        """Declare the semantic-shard layout of the rows: shard s is the contiguous row range
+        shard_offsets[s]:shard_offsets[s+1] (rows are stored shard by shard).  Computes one centroid per
+        shard = mean of its member rows (memory_system.py:916-917) for the two-level search."""
+        with self._lock:
+            off = torch.as_tensor(np.asarray(shard_offsets, dtype=np.int64)).to(self.device)
+            assert int(off[-1]) <= self._n and int(off[0]) >= 0
+            cen = kernels.segment_mean(self._rows, self._dim_p, off).to(torch.float32).contiguous()
+            self._shard_off, self._shard_off_host = off, np.asarray(shard_offsets, dtype=np.int64)
+            self._centroids, self._centroid_norms = cen, kernels.row_norms(cen)
+
+    def search_two_level(self, queries, limit: int = 5, nprobe: Optional[int] = None, return_rows: bool = False):
+        """Two-level cosine search (north_star (1); the reference's level 1 is memory_system.py:464-470):
+        score the queries against the shard centroids, then search only the `nprobe` best shards' member
+        rows and merge.  nprobe = None or >= the number of shards visits every shard and equals the flat
+        search (the parity mode); smaller nprobe is approximate — callers report recall."""
+        with self._lock:
+            q = np.ascontiguousarray(queries, dtype=np.float32)
+            qd = self._to_device(q)
+            B, S = q.shape[0], self._centroids.shape[0]
+            p = S if nprobe is None else max(1, min(int(nprobe), S))
+            k = self._check_limit(limit, 0)
+            probe, _, _ = kernels.search_exact(self._centroids, self._dim_p, self._centroid_norms, None, qd, p, _lib.COSINE)
+            lo = self._shard_off[:-1][probe.clamp(min=0)].T.contiguous().reshape(-1)       # [p*B] list-major
+            hi = self._shard_off[1:][probe.clamp(min=0)].T.contiguous().reshape(-1)
+            vq = qd.repeat(p, 1)
+            n_chunks = kernels.default_chunks(int((self._shard_off_host[1:] - self._shard_off_host[:-1]).max()), p * B, self.device)
+            tag = torch.full((p * B,), -1, dtype=torch.int32, device=self.device)
+            ids, sc, cnt = kernels.search_exact(self._rows, self._dim_p, self._norms, self._tags, vq, k, self._metric,
+                                                row_range=(0, self._n), group_lo=lo, group_hi=hi, group_tag=tag,
+                                                group_size=1, n_chunks=n_chunks)
+            ids, sc, cnt = kernels.merge_topk(ids.view(p, B, k), sc.view(p, B, k), self._metric)
+            torch.cuda.current_stream(self.device).synchronize()
+            if return_rows:
+                return ids, sc, cnt
+            ids, cnt = ids.cpu().numpy(), cnt.cpu().numpy()
+            return [[self._id_of(int(r)) for r in ids[b, :cnt[b]]] for b in range(B)]
+
     def delete_nodes(self, node_ids: List[str], user_id: str = "default"):
         with self._lock:
             u = self._user(user_id)

@@ -100,3 +100,52 @@ def test_limit_bound_is_loud():
         st.search_nodes([0.1] * 16, limit=2000)
     with pytest.raises(ValueError):
         st.search_nodes([0.1] * 17, limit=1)
+
+
+def test_per_user_batched_search_matches_oracle():
+    """BASELINE configs[4] shape in miniature: many tenants, one query each, one launch."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    from oracle import flat_search
+    n_users, per, dim = 60, 50, 64
+    rows, _ = synth.clustered_rows(n_users * per, dim, 12, seed=33)
+    st = B200Store()
+    for u in range(n_users):
+        st.add_rows(rows[u * per:(u + 1) * per], user_id=f"u{u}", id_prefix=f"u{u}_", first_id=0)
+    st.delete_nodes([f"u3_{i}" for i in range(0, per, 2)], user_id="u3")
+    qs = synth.queries_near_rows(rows, 40, seed=34)
+    users = [f"u{(7 * i) % n_users}" for i in range(38)] + ["u3", "ghost"]
+    got = st.search_users(qs, users, limit=8)
+    for b, name in enumerate(users):
+        if name == "ghost":
+            assert got[b] == []
+            continue
+        u = int(name[1:])
+        mask = np.zeros(n_users * per, bool); mask[u * per:(u + 1) * per] = True
+        if u == 3:
+            mask[u * per:(u + 1) * per:2] = False
+        idx, _ = flat_search.flat_topk(rows, qs[b], 8, mask=mask)
+        assert got[b] == [f"u{u}_{i - u * per}" for i in idx]
+        assert got[b] == st.search_nodes(qs[b].tolist(), user_id=name, limit=8)
+
+
+def test_two_level_search_parity_and_recall():
+    """north_star (1): centroid routing then member scan. nprobe = all shards is the flat search."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    from oracle import flat_search
+    n, dim, S = 40000, 128, 32
+    rows, shard = synth.clustered_rows(n, dim, S, seed=44)
+    st = B200Store()
+    st.add_rows(rows, id_prefix="node_")
+    off = np.searchsorted(shard, np.arange(S + 1))
+    st.set_shards(off)
+    np.testing.assert_allclose(st._centroids[3].cpu().numpy(), rows[off[3]:off[4]].astype(np.float64).mean(0), rtol=1e-6)
+    qs = synth.queries_near_rows(rows, 24, seed=45)
+    want, _ = flat_search.flat_topk_batch(rows, qs, 10)
+    want = [[f"node_{i}" for i in w] for w in want.tolist()]
+    assert st.search_two_level(qs, limit=10) == want                       # every shard visited: exact
+    assert st.search_two_level(qs, limit=10, nprobe=S) == want
+    approx = st.search_two_level(qs, limit=10, nprobe=2)
+    recall = np.mean([len(set(a) & set(w)) / 10 for a, w in zip(approx, want)])
+    assert recall > 0.95                                                     # neighbours live in the query's shard
