@@ -177,6 +177,25 @@ class MemoryShard:
             self._pending.append((key[0], key[1], float(edge.weight), int(edge.co_occurrence)))
             self._edge_meta[key] = (edge.edge_type, edge.last_updated)
 
+    def has_edge(self, source: str, target: str) -> bool:
+        a, b = self._slot.get(source), self._slot.get(target)
+        return a is not None and b is not None and (a, b) in self._edge_index()
+
+    def remove_node(self, node_id: str) -> None:
+        """Drops a node and every edge touching it (memory_system.py:559-571).  Host-side rebuild of the
+        edge table: eviction is off the hot path."""
+        self.nodes.pop(node_id, None)
+        slot = self._slot.get(node_id)
+        if slot is None:
+            return
+        self._flush()
+        s, d, w, c = self._table.to_numpy()
+        keep = (s != slot) & (d != slot)
+        if not keep.all():
+            self._table = EdgeTable.from_arrays(s[keep], d[keep], w[keep], c[keep], device=self._table.device) \
+                if keep.any() else EdgeTable(self._table.device)
+            self._index = None
+
     @property
     def edges(self) -> Dict[Tuple[str, str], Edge]:
         """Materialises the edge dict from HBM (a device->host copy; not for hot loops)."""
@@ -242,6 +261,7 @@ class BufferGraph:
     def __init__(self, shards: Dict[str, MemoryShard], super_nodes: Optional[Dict[str, Node]] = None):
         self.shards = shards
         self.super_nodes = super_nodes if super_nodes is not None else {}
+        self._device = None
 
     def apply_temporal_decay(self, decay_rate: float = 0.01):
         for shard in self.shards.values():

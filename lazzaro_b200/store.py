@@ -468,6 +468,43 @@ class B200Store:
                             if not lst:
                                 del self._id_rows[(u, rid)]
             self._version += 1
+            dead = self._n - sum(self._live)
+            if dead > max(4096, sum(self._live)):
+                self._compact()
+
+    def _compact(self):
+        """Drops tombstoned rows (the reference rewrites a user's whole graph on every save,
+        memory_system.py:1283-1287, so deleted rows pile up).  Live rows keep their relative order, so
+        the insertion-order tie-break is unchanged.  Device side is a gather (torch indexing = plumbing)."""
+        live = np.nonzero(self._row_user[:self._n] >= 0)[0]
+        idx = torch.from_numpy(live).to(self.device)
+        m = int(live.size)
+        for name in ("_rows", "_norms", "_tags"):
+            t = getattr(self, name)
+            t[:m] = t.index_select(0, idx)
+        if self._shadow is not None:
+            self._shadow_n = 0                         # rebuilt lazily by the next batched search
+        remap = {int(old): new for new, old in enumerate(live.tolist())}
+        self._row_id = {remap[r]: v for r, v in self._row_id.items() if r in remap}
+        self._row_meta = {remap[r]: v for r, v in self._row_meta.items() if r in remap}
+        self._id_rows = {k: [remap[r] for r in v if r in remap] for k, v in self._id_rows.items()}
+        blocks = []
+        for lo, hi, prefix, first in self._blocks:      # implicit-id blocks survive only if wholly live
+            seg = live[(live >= lo) & (live < hi)]
+            if seg.size == hi - lo:
+                blocks.append((remap[lo], remap[lo] + (hi - lo), prefix, first))
+            else:
+                for r in seg.tolist():
+                    self._row_id[remap[r]] = f"{prefix}{first + r - lo}"
+                    self._id_rows.setdefault((int(self._row_user[r]), f"{prefix}{first + r - lo}"), []).append(remap[r])
+        self._blocks = blocks
+        self._row_user[:m] = self._row_user[live]
+        self._row_user[m:self._n] = -1
+        self._tags[m:self._n] = -1
+        self._n = m
+        for u in range(len(self._span)):
+            rows = np.nonzero(self._row_user[:m] == u)[0]
+            self._span[u] = [int(rows[0]), int(rows[-1]) + 1] if rows.size else [1 << 62, 0]
 
     def _implicit_rows(self, nid: str, u: int) -> List[int]:
         out = []

@@ -12,6 +12,7 @@ What is recorded (inputs AND reference outputs, so tests need nothing but numpy)
   centroid      memory_system.py:893-933 (_create_super_nodes_for_shard)
   search_mem    memory_system.py:1460-1472 over an injected flat store, cfg1-like (2k x 64)
   pins          the expectations of the reference's own tests, reproduced by running its code
+  msys          memory_system.py:580-785 end to end: three conversations (dedup, linking, super-nodes, decay, prune)
 """
 from __future__ import annotations
 
@@ -222,12 +223,55 @@ def gold_pins(lz):
                 pin_pruned=np.int64(pruned), pin_merge_noop=np.int64(merged))
 
 
+def gold_memory_system(lz):
+    """Three conversations through the reference's own MemorySystem (end_conversation -> consolidation,
+    dedup, linking, super-nodes, decay, prune) with scripted facts and table embeddings; the state after
+    each conversation and a few retrievals are recorded for the device mirror to reproduce."""
+    dim, per = 32, 9
+    topics = ["work", "health", "learning"]
+    rows, shard = synth.clustered_rows(3 * 3 * per, dim, 3, seed=61, sigma=0.6)
+    order = np.random.default_rng(62).permutation(rows.shape[0])
+    facts = [(f"fact number {i} about {topics[shard[i]]}", topics[shard[i]], rows[i]) for i in order]
+    dups, src = synth.near_duplicates(rows[order[:per * 3]], 5, seed=63, noise=0.15)       # re-told facts, conv 3
+    table = {c: v.astype(np.float64).tolist() for c, _, v in facts}
+    for j, v in enumerate(dups):
+        table[f"retold fact {j}"] = v.astype(np.float64).tolist()
+    queries = synth.queries_near_rows(rows, 6, seed=64)
+    for j, v in enumerate(queries):
+        table[f"query {j}"] = v.astype(np.float64).tolist()
+    store, llm, emb = FlatStore(metric="cosine"), ref_harness.ScriptedLLM(), ref_harness.TableEmbedder(table, dim)
+    ms = quiet(ref_harness.make_memory_system, store, llm, emb, max_buffer_size=10**6, super_node_threshold=12,
+               auto_consolidate=True, consolidate_every=3, prune_threshold=0.45)
+    convs = [facts[:per * 3], facts[per * 3:per * 6], facts[per * 6:]]
+    script, states = [], []
+    for ci, conv in enumerate(convs):
+        mems = [{"content": c, "type": "semantic", "salience": round(0.3 + 0.05 * (k % 9), 2), "topic": t}
+                for k, (c, t, _) in enumerate(conv)]
+        if ci == 2:
+            mems += [{"content": f"retold fact {j}", "type": "semantic", "salience": 0.95, "topic": facts[int(src[j])][1]}
+                     for j in range(len(dups))]
+        script.append(mems)
+        llm.push_memories(mems)
+        quiet(ms.start_conversation); ms.add_to_short_term(f"conversation {ci}"); quiet(ms.end_conversation)
+        states.append({
+            "nodes": {nid: [n.content, n.salience, n.access_count, n.shard_key, n.parent_id]
+                      for sh in ms.shards.values() for nid, n in sh.nodes.items()},
+            "edges": {f"{a}|{b}": [e.weight, e.co_occurrence] for sh in ms.shards.values() for (a, b), e in sh.edges.items()},
+            "super": {sid: [n.shard_key, n.child_ids, n.embedding] for sid, n in ms.super_nodes.items()},
+        })
+    sm = [[n.id for n in ms.search_memories(f"query {j}", limit=5)] for j in range(len(queries))]
+    orr = [ms._optimized_retrieval(table[f"query {j}"], f"query {j}") for j in range(len(queries))]
+    comps = sorted(sorted(c) for c in ms.buffer.get_connected_components() if len(c) >= 3)
+    return dict(msys=np.array(json.dumps({"table": table, "script": script, "states": states, "search": sm,
+                                          "retrieval": orr, "components": comps, "dim": dim})))
+
+
 def main():
     lz = ref_harness.import_reference()
     ms = quiet(ref_harness.make_memory_system, FlatStore())
     out = {}
     for fn, arg in [(gold_cosine, ms), (gold_decay_prune, lz), (gold_linking, lz), (gold_dedup, lz),
-                    (gold_centroid, lz), (gold_search_memories, lz), (gold_pins, lz)]:
+                    (gold_centroid, lz), (gold_search_memories, lz), (gold_pins, lz), (gold_memory_system, lz)]:
         out.update(fn(arg))
         print("ok", fn.__name__)
     path = os.path.join(OUT, "ref_python_path.npz")

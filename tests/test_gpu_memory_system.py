@@ -1,0 +1,110 @@
+"""GPU: the MemorySystem mirror against the reference's own MemorySystem (tests/golden 'msys': three
+conversations through end_conversation -> consolidation, dedup, linking, super-nodes, decay, prune) and
+against the scenarios of the reference's own tests."""
+import json
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+class ScriptedLLM:
+    def __init__(self):
+        self.queue = []
+
+    def push_memories(self, memories):
+        self.queue.append(json.dumps({"memories": memories}))
+
+    def completion(self, messages, response_format=None):
+        return self.queue.pop(0) if self.queue else "{}"
+
+
+class TableEmbedder:
+    def __init__(self, table, dim):
+        self.table, self.dim = dict(table), dim
+
+    def embed(self, text):
+        return list(self.table.get(text, [0.0] * self.dim))
+
+    def batch_embed(self, texts):
+        return [self.embed(t) for t in texts]
+
+
+def _norm_super(name):            # super-node ids carry a wall-clock suffix: compare them by shard
+    return "_".join(name.split("_")[:2]) if name.startswith("super_") else name
+
+
+def test_three_conversations_match_the_reference(golden):
+    from lazzaro_b200.memory_system import MemorySystem
+    g = json.loads(str(golden["msys"]))
+    llm, emb = ScriptedLLM(), TableEmbedder(g["table"], g["dim"])
+    ms = MemorySystem(llm_provider=llm, embedding_provider=emb, max_buffer_size=10 ** 6, super_node_threshold=12,
+                      auto_consolidate=True, consolidate_every=3, prune_threshold=0.45)
+    for ci, (mems, want) in enumerate(zip(g["script"], g["states"])):
+        llm.push_memories(mems)
+        ms.start_conversation(); ms.add_to_short_term(f"conversation {ci}"); ms.end_conversation()
+        nodes = {nid: n for sh in ms.shards.values() for nid, n in sh.nodes.items()}
+        assert list(nodes) == list(want["nodes"])                        # same ids, same order
+        for nid, (content, sal, acc, key, parent) in want["nodes"].items():
+            n = nodes[nid]
+            assert (n.content, n.access_count, n.shard_key) == (content, acc, key)
+            assert n.salience == pytest.approx(sal, rel=2e-7, abs=1e-7)  # float32 state vs float64 Python
+            assert (n.parent_id is None) == (parent is None)
+        edges = {f"{a}|{b}": e for sh in ms.shards.values() for (a, b), e in sh.edges.items()}
+        assert set(edges) == set(want["edges"]), f"conversation {ci}: edge sets differ"
+        for key, (w, cooc) in want["edges"].items():
+            assert edges[key].weight == pytest.approx(w, rel=3e-7) and edges[key].co_occurrence == cooc
+        sup = {n.shard_key: n for n in ms.super_nodes.values()}
+        assert set(sup) == {v[0] for v in want["super"].values()}
+        for sid, (key, children, centroid) in want["super"].items():
+            assert sup[key].child_ids == children
+            np.testing.assert_allclose(sup[key].embedding, centroid, rtol=1e-6, atol=1e-9)   # members are float32 here
+    got = [[_norm_super(n.id) for n in ms.search_memories(f"query {j}", limit=5)] for j in range(len(g["search"]))]
+    assert got == [[_norm_super(x) for x in lst] for lst in g["search"]]
+    got = [ms._optimized_retrieval(g["table"][f"query {j}"], f"query {j}") for j in range(len(g["retrieval"]))]
+    assert got == g["retrieval"]
+    comps = sorted(sorted(c) for c in ms.buffer.get_connected_components() if len(c) >= 3)
+    assert [[_norm_super(x) for x in c] for c in comps] == [[_norm_super(x) for x in c] for c in g["components"]]
+
+
+def test_reference_semantic_merging_scenario():
+    """tests/test_consolidation_semantic.py:27-71 against the mirror: the second, near-identical fact merges
+    into the first node; salience 0.9 decayed once = 0.893; access_count 1."""
+    from lazzaro_b200.memory_system import MemorySystem
+    f1 = "User prefers Python for data science"
+    f2 = "The user has a preference for the Python programming language in data science tasks"
+    llm, emb = ScriptedLLM(), TableEmbedder({f1: [0.1] * 1536, f2: [0.1001] * 1536}, 1536)
+    ms = MemorySystem(llm_provider=llm, embedding_provider=emb)
+    llm.push_memories([{"content": f1, "type": "semantic", "salience": 0.8, "topic": "work"}])
+    ms.start_conversation(); ms.add_to_short_term("I like Python for DS"); ms.end_conversation()
+    assert ms.buffer.size()[0] == 1
+    node_id = list(ms.buffer.nodes.keys())[0]
+    assert ms.buffer.nodes[node_id].content == f1
+    llm.push_memories([{"content": f2, "type": "semantic", "salience": 0.9, "topic": "work"}])
+    ms.start_conversation(); ms.add_to_short_term("Python is my go-to for data work"); ms.end_conversation()
+    assert ms.buffer.size()[0] == 1, "Should have merged semantically similar facts"
+    node = ms.buffer.get_node(node_id)
+    assert node.salience == pytest.approx(0.893, abs=5e-4) and node.access_count == 1
+    assert ms._merge_similar_nodes(0.95) == 0                              # a no-op in the reference too
+
+
+def test_buffer_limit_evicts_least_important_and_syncs_store():
+    """memory_system.py:535-578."""
+    import time
+    from lazzaro_b200.graph import Edge, Node
+    from lazzaro_b200.memory_system import MemorySystem
+    ms = MemorySystem(llm_provider=ScriptedLLM(), embedding_provider=TableEmbedder({}, 8), max_buffer_size=3)
+    now = time.time()
+    rng = np.random.default_rng(0)
+    sal = [0.9, 0.1, 0.5, 0.2, 0.8]
+    for i, s in enumerate(sal):
+        n = Node(id=f"n{i}", content=f"c{i}", embedding=rng.standard_normal(8).tolist(), salience=s, last_accessed=now)
+        ms.buffer.add_node(n)
+        ms.store.add_nodes([{"id": n.id, "content": n.content, "embedding": n.embedding}])
+    ms.buffer.add_edge(Edge(source="n0", target="n1", weight=0.9))
+    ms.buffer.add_edge(Edge(source="n0", target="n2", weight=0.9))
+    ms._enforce_buffer_limit()
+    assert sorted(ms.buffer.nodes) == ["n0", "n2", "n4"]                     # n1 (0.1) and n3 (0.2) evicted
+    assert set(ms.buffer.edges) == {("n0", "n2")}
+    assert sorted(ms.store.search_nodes([0.1] * 8, limit=10)) == ["n0", "n2", "n4"]
