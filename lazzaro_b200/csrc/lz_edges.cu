@@ -47,8 +47,12 @@ struct PruneParams {
     u32* ticket;       // zeroed before launch
     int64_t* out_kept;
     int n_tiles;
+    const int64_t* offsets;   // two-pass mode: exclusive prefix of the per-tile survivor counts
 };
 
+// CHAINED = true: single pass, tile order from an atomic ticket, offsets by decoupled look-back (safe in
+// place).  CHAINED = false: second pass of the two-pass form, offsets precomputed (no inter-CTA waiting).
+template <bool CHAINED>
 __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
     __shared__ int s_src[kTile];
     __shared__ int s_dst[kTile];
@@ -60,9 +64,11 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
     __shared__ int s_total;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
-    __syncthreads();
-    const int tile = (int)s_tile;
+    if (CHAINED) {
+        if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+    }
+    const int tile = CHAINED ? (int)s_tile : (int)blockIdx.x;
     const int64_t base = (int64_t)tile * kTile + (int64_t)tid * kItems;
 
     int v_src[kItems], v_dst[kItems], v_cooc[kItems];
@@ -135,7 +141,9 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
         }
     }
     __syncthreads();
-    if (warp == 0) {
+    if (!CHAINED) {
+        if (tid == 0) s_prefix = p.offsets[tile];
+    } else if (warp == 0) {
         const int total = s_total;
         // decoupled look-back: publish the aggregate, then walk predecessors 32 at a time
         long long excl = 0;
@@ -174,6 +182,60 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
         p.o_w[out0 + i] = s_w[i];
         p.o_cooc[out0 + i] = s_cooc[i];
     }
+}
+
+// First pass of the two-pass form: survivors per tile (reads the weights only, 4 B per edge).
+__global__ void __launch_bounds__(kThreads) count_kernel(const float* __restrict__ w, int64_t n, double factor, double thr,
+                                                         int32_t* __restrict__ counts) {
+    __shared__ int s_warp[kThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * kTile + (int64_t)tid * kItems;
+    int cnt = 0;
+    if (base + kItems <= n) {
+#pragma unroll
+        for (int h = 0; h < kItems / 4; ++h) {
+            const float4 v = lz_ldg_stream(w + base + 4 * h);
+            cnt += !((double)v.x * factor < thr);
+            cnt += !((double)v.y * factor < thr);
+            cnt += !((double)v.z * factor < thr);
+            cnt += !((double)v.w * factor < thr);
+        }
+    } else {
+        for (int j = 0; j < kItems; ++j)
+            if (base + j < n) cnt += !((double)w[base + j] * factor < thr);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) s_warp[warp] = cnt;
+    __syncthreads();
+    if (tid == 0) {
+        int t = 0;
+#pragma unroll
+        for (int i = 0; i < kThreads / 32; ++i) t += s_warp[i];
+        counts[blockIdx.x] = t;
+    }
+}
+
+// Exclusive scan of the tile counts by one CTA (tens of thousands of tiles at most).
+__global__ void __launch_bounds__(1024) tile_scan_kernel(const int32_t* __restrict__ counts, int n_tiles,
+                                                         int64_t* __restrict__ offsets, int64_t* __restrict__ total) {
+    __shared__ long long s_part[1024];
+    const int tid = threadIdx.x;
+    const int per = (n_tiles + 1023) / 1024;
+    const int lo = tid * per, hi = min(n_tiles, lo + per);
+    long long sum = 0;
+    for (int i = lo; i < hi; ++i) sum += counts[i];
+    s_part[tid] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {                 // Hillis-Steele inclusive scan
+        long long v = tid >= o ? s_part[tid - o] : 0;
+        __syncthreads();
+        s_part[tid] += v;
+        __syncthreads();
+    }
+    long long run = s_part[tid] - sum;
+    for (int i = lo; i < hi; ++i) { offsets[i] = run; run += counts[i]; }
+    if (tid == 1023) *total = s_part[1023];
 }
 
 __global__ void __launch_bounds__(kThreads) decay_kernel(float* __restrict__ w, int64_t n, double factor) {
@@ -221,7 +283,8 @@ int elementwise_blocks(int64_t n) {
 extern "C" size_t lz_edge_decay_prune_scratch_bytes(int64_t n) {
     if (n <= 0) return 256;
     const int64_t tiles = (n + kTile - 1) / kTile;
-    return (size_t)(((tiles + 1) * 8 + 255) & ~255ll);
+    // chained form: ticket + one look-back word per tile; two-pass form: int64 offsets + int32 counts
+    return (size_t)(((tiles + 1) * 8 + tiles * 4 + 255) & ~255ll);
 }
 
 extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* weight, const int32_t* cooc,
@@ -246,15 +309,33 @@ extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const
         return LZ_ERR_SCRATCH;
     }
     const int64_t tiles = (n + kTile - 1) / kTile;
-    LZ_CUDA(cudaMemsetAsync(scratch, 0, need, st));
     PruneParams p;
     p.src = src; p.dst = dst; p.w = weight; p.cooc = cooc;
     p.o_src = out_src; p.o_dst = out_dst; p.o_w = out_weight; p.o_cooc = out_cooc;
     p.n = n; p.factor = factor; p.thr = threshold;
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
-    p.out_kept = out_kept; p.n_tiles = (int)tiles;
-    decay_prune_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(p);
+    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr;
+    // Do any outputs overlap any inputs?  In place, a tile may only be overwritten after it has been read,
+    // which the single-pass chained kernel guarantees; out of place the tiles are independent and the
+    // two-pass form (count, scan, scatter) runs without any CTA waiting on another.
+    const uintptr_t in[4] = {(uintptr_t)src, (uintptr_t)dst, (uintptr_t)weight, (uintptr_t)cooc};
+    const uintptr_t out[4] = {(uintptr_t)out_src, (uintptr_t)out_dst, (uintptr_t)out_weight, (uintptr_t)out_cooc};
+    bool aliased = false;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+            aliased = aliased || (out[j] < in[i] + (uintptr_t)n * 4 && in[i] < out[j] + (uintptr_t)n * 4);
+    if (aliased) {
+        LZ_CUDA(cudaMemsetAsync(scratch, 0, (size_t)(tiles + 1) * 8, st));
+        decay_prune_kernel<true><<<(unsigned)tiles, kThreads, 0, st>>>(p);
+    } else {
+        int64_t* offsets = (int64_t*)scratch;
+        int32_t* counts = (int32_t*)((unsigned char*)scratch + (size_t)(tiles + 1) * 8);
+        count_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(weight, n, factor, threshold, counts);
+        tile_scan_kernel<<<1, 1024, 0, st>>>(counts, (int)tiles, offsets, out_kept);
+        p.offsets = offsets;
+        decay_prune_kernel<false><<<(unsigned)tiles, kThreads, 0, st>>>(p);
+    }
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
@@ -349,8 +430,8 @@ extern "C" int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* ds
     p.n = n; p.factor = factor; p.thr = threshold;
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
-    p.out_kept = out_kept; p.n_tiles = (int)tiles;
-    decay_prune_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(p);
+    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr;
+    decay_prune_kernel<true><<<(unsigned)tiles, kThreads, 0, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }

@@ -56,9 +56,11 @@ class Edge:
 class EdgeTable:
     """Edge struct-of-arrays in HBM with append, decay, fused decay+prune."""
 
-    def __init__(self, device=None, capacity: int = 1024):
+    def __init__(self, device=None, capacity: int = 1024, in_place: bool = False):
         _lib.require_cuda()
         _lib.load()
+        self._in_place = in_place
+        self._alt = None
         self.device = torch.device(device or f"cuda:{torch.cuda.current_device()}")
         self.n = 0
         self._alloc(max(16, capacity))
@@ -73,6 +75,7 @@ class EdgeTable:
             for a, b in zip(new, (self.src, self.dst, self.weight, self.cooc)):
                 a[:self.n] = b[:self.n]
         self.src, self.dst, self.weight, self.cooc = new
+        self._alt = None
 
     @classmethod
     def from_arrays(cls, src, dst, weight, cooc, device=None) -> "EdgeTable":
@@ -104,8 +107,19 @@ class EdgeTable:
             need = int(lib.lz_edge_decay_prune_scratch_bytes(n0))
             if self._scratch is None or self._scratch.numel() < need:
                 self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            # out of place into a second set of columns (then swap): the kernels then run the two-pass form
+            # with no CTA waiting on another; `in_place=True` at construction keeps one copy of the table
+            if self._in_place:
+                out = None
+            else:
+                if self._alt is None or self._alt[0].shape[0] < self.src.shape[0]:
+                    self._alt = [torch.empty_like(c) for c in (self.src, self.dst, self.weight, self.cooc)]
+                out = tuple(self._alt)
             kernels.edge_decay_prune(self.src, self.dst, self.weight, self.cooc, n0, factor, threshold,
-                                     scratch=self._scratch, kept=self._kept)
+                                     out=out, scratch=self._scratch, kept=self._kept)
+            if out is not None:
+                self._alt = [self.src, self.dst, self.weight, self.cooc]
+                self.src, self.dst, self.weight, self.cooc = out
             if not sync:
                 return -1
             self._kept_host.copy_(self._kept, non_blocking=True)

@@ -60,6 +60,20 @@ def test_decay_prune_sizes_and_extremes(n, thr):
     np.testing.assert_array_equal(ww, ew); np.testing.assert_array_equal(c, ec)
 
 
+def test_in_place_and_out_of_place_tables_agree():
+    from lazzaro_b200 import synth
+    from lazzaro_b200.graph import EdgeTable
+    n = 777_777
+    cols = synth.edge_table(n, 9000, seed=8)
+    a = EdgeTable.from_arrays(*cols, device="cuda")                  # two-pass, ping-pong columns
+    b = EdgeTable(device="cuda", capacity=n, in_place=True)          # single-pass chained scan, in place
+    b.append(*cols)
+    for factor, thr in ((0.99, 0.3), (0.97, 0.3), (1.0, 0.5)):
+        assert a.decay_prune(factor, thr) == b.decay_prune(factor, thr)
+        for x, y in zip(a.to_numpy(), b.to_numpy()):
+            np.testing.assert_array_equal(x, y)
+
+
 def test_out_of_place_and_idempotence():
     from lazzaro_b200 import kernels, synth
     n = 300_000
