@@ -216,26 +216,37 @@ __global__ void __launch_bounds__(kThreads) count_kernel(const float* __restrict
     }
 }
 
-// Exclusive scan of the tile counts by one CTA (tens of thousands of tiles at most).
+// Exclusive scan of the tile counts by one CTA (tens of thousands of tiles at most): per-thread serial
+// sums, warp shuffle scans, one shared-memory hop for the 32 warp totals.
 __global__ void __launch_bounds__(1024) tile_scan_kernel(const int32_t* __restrict__ counts, int n_tiles,
                                                          int64_t* __restrict__ offsets, int64_t* __restrict__ total) {
-    __shared__ long long s_part[1024];
-    const int tid = threadIdx.x;
+    __shared__ long long s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int per = (n_tiles + 1023) / 1024;
     const int lo = tid * per, hi = min(n_tiles, lo + per);
     long long sum = 0;
     for (int i = lo; i < hi; ++i) sum += counts[i];
-    s_part[tid] = sum;
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {                 // Hillis-Steele inclusive scan
-        long long v = tid >= o ? s_part[tid - o] : 0;
-        __syncthreads();
-        s_part[tid] += v;
-        __syncthreads();
+    long long incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
     }
-    long long run = s_part[tid] - sum;
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        long long w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        s_warp[lane] = wi - w;                           // exclusive warp offsets
+        if (lane == 31) *total = wi;
+    }
+    __syncthreads();
+    long long run = s_warp[warp] + incl - sum;
     for (int i = lo; i < hi; ++i) { offsets[i] = run; run += counts[i]; }
-    if (tid == 1023) *total = s_part[1023];
 }
 
 __global__ void __launch_bounds__(kThreads) decay_kernel(float* __restrict__ w, int64_t n, double factor) {
