@@ -209,6 +209,15 @@ int lz_edge_decay(float* weight, int64_t n, double factor, void* stream);
  * s = s > floor ? floor + (s - floor) * (1 - rate) : floor, computed in float64, stored float32. */
 int lz_salience_decay(float* salience, int64_t n, double rate, double floor, void* stream);
 
+/* ---- connected components (stands behind BufferGraph.get_connected_components,
+ *      core/buffer_graph.py:99-120; the reference's recursive DFS rescans a shard's edges per node) ------- */
+
+/* labels[v] = smallest node index in v's connected component of the undirected graph with edges
+ * (src[i], dst[i]), nodes 0..n_nodes-1 (edges with an endpoint outside that range are ignored).
+ * Union-find with min-root hooking; deterministic.  src, dst int32 [n_edges]; labels int32 [n_nodes]. */
+int lz_connected_components(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes,
+                            int32_t* labels, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

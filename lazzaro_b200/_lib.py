@@ -39,6 +39,7 @@ SIGNATURES = {
     "lz_edge_decay_prune": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "lz_edge_decay_prune_noalloc": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p]),
     "lz_edge_decay": (_i32, [_p, _i64, _f64, _p]),
+    "lz_connected_components": (_i32, [_p, _p, _i64, _i32, _p, _p]),
     "lz_salience_decay": (_i32, [_p, _i64, _f64, _f64, _p]),
 }
 

@@ -446,3 +446,65 @@ extern "C" int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* ds
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
+
+// ---- connected components over the edge table --------------------------------------
+// Stands behind BufferGraph.get_connected_components (core/buffer_graph.py:99-120), which walks the graph
+// with a recursive DFS that rescans every edge of a shard per visited node.  Here: union-find over the edge
+// struct-of-arrays — hook every edge with a compare-and-swap that always attaches the larger root under the
+// smaller one, then flatten — so labels[v] is the smallest node index of v's component whatever order the
+// edges were processed in (deterministic).  Edges are treated as undirected.
+namespace {
+__device__ __forceinline__ int cc_find(int* parent, int v) {
+    int p = parent[v];
+    while (p != v) {                    // path halving
+        const int gp = parent[p];
+        if (gp != p) parent[v] = gp;
+        v = p;
+        p = gp;
+    }
+    return v;
+}
+
+__global__ void __launch_bounds__(kThreads) cc_init_kernel(int* parent, int n) {
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) parent[i] = i;
+}
+
+__global__ void __launch_bounds__(kThreads) cc_hook_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                           int64_t n_edges, int n_nodes, int* parent) {
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < n_edges; e += (int64_t)gridDim.x * kThreads) {
+        int u = src[e], v = dst[e];
+        if (u < 0 || v < 0 || u >= n_nodes || v >= n_nodes || u == v) continue;
+        while (true) {
+            u = cc_find(parent, u);
+            v = cc_find(parent, v);
+            if (u == v) break;
+            const int hi = u > v ? u : v, lo = u > v ? v : u;
+            if (atomicCAS(&parent[hi], hi, lo) == hi) break;      // hi was still a root: attached
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) cc_flatten_kernel(int* parent, int n) {
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) {
+        int r = i;
+        while (parent[r] != r) r = parent[r];
+        parent[i] = r;
+    }
+}
+}  // namespace
+
+extern "C" int lz_connected_components(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes,
+                                       int32_t* labels, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_nodes <= 0) return LZ_OK;
+    LZ_REQUIRE(labels != nullptr && (n_edges == 0 || (src && dst)), "lz_connected_components: NULL pointer");
+    LZ_REQUIRE(n_edges >= 0, "lz_connected_components: n_edges=%lld", (long long)n_edges);
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    auto blocks = [&](int64_t n) { int64_t b = (n + kThreads - 1) / kThreads; return (unsigned)(b < 1 ? 1 : (b > sms * 16 ? sms * 16 : b)); };
+    cc_init_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(labels, n_nodes);
+    if (n_edges > 0) cc_hook_kernel<<<blocks(n_edges), kThreads, 0, st>>>(src, dst, n_edges, n_nodes, labels);
+    cc_flatten_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(labels, n_nodes);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -31,10 +31,7 @@ using namespace sm100;
 constexpr int BM = 128;                 // queries per tile  (MMA M, one TMEM lane per query)
 constexpr int BN = 256;                 // rows per tile     (MMA N, one TMEM column per row)
 constexpr int BK = 64;                  // bf16 elements per pipeline stage = one 128-byte swizzle row
-constexpr int kStages = 4;
-constexpr int A_BYTES = BM * BK * 2;    // 16 KiB
-constexpr int B_BYTES = BN * BK * 2;    // 32 KiB
-constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int A_BYTES = BM * BK * 2;    // 16 KiB per stage; the rows tile adds 32 KiB (16 KiB per CTA in pair mode)
 constexpr int kGemmThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
 constexpr int kTmemCols = 512;          // two 128x256 fp32 accumulators
 constexpr int kSelThreads = 256;
@@ -216,9 +213,17 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     }
 }
 
-template <int EPL>
+// PAIR = true: the 2-CTA cluster runs as one tcgen05 cta_group::2 unit — M = 256 (each CTA's 128 queries),
+// the 256-row rows tile split across the two CTAs' shared memories (128 rows each, read by the MMA from
+// both), one MMA issuer in the leader CTA.  Per CTA and K step that is 8 KB of operand reads and 8 KB of
+// TMA writes instead of 12 + 12 with multicast copies, which is what the 128 B/clk shared-memory port
+// can sustain; the ring is 6 stages of 32 KB.  PAIR = false: the cta_group::1 form (any cluster size).
+template <int EPL, bool PAIR>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, GemmParams p) {
+    constexpr int kStages = PAIR ? 6 : 4;
+    constexpr int B_BYTES = PAIR ? BN * BK : BN * BK * 2;            // half the rows tile per CTA in pair mode
+    constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     extern __shared__ unsigned char smem_raw[];
     unsigned char* tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned
     uint64_t* full = reinterpret_cast<uint64_t*>(tiles + kStages * STAGE_BYTES);
@@ -239,11 +244,16 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_q);
         prefetch_tmap(&tmap_x);
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], cs); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+        // pair mode: one multicast commit from the leader releases a stage in both CTAs; the leader's
+        // tempty collects the four epilogue warps of both CTAs
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], PAIR ? 1 : cs); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], PAIR ? 8 : 4); }
         fence_mbar_init();
     }
-    if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+    if (warp == 1) {
+        if (PAIR) tmem_alloc_pair(tmem_slot, kTmemCols);
+        else tmem_alloc(tmem_slot, kTmemCols);
+    }
     tc_fence_before();
     __syncthreads();
     if (cs > 1) cluster_sync();          // every CTA's barriers exist before anyone multicasts into them
@@ -263,8 +273,16 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     const int row0 = (int)(p.row_lo + (int64_t)t * BN);
                     for (int kb = 0; kb < p.kblocks; ++kb) {
                         { LZ_T0 mbar_wait(&empty[stage], phase ^ 1); LZ_ACC(4) }   // all cs consumers have released the stage
-                        mbar_expect_tx(&full[stage], STAGE_BYTES);
                         unsigned char* st = tiles + stage * STAGE_BYTES;
+                        if (PAIR) {
+                            // both CTAs' bytes are counted on the leader's barrier, which its MMA thread waits on
+                            if (rank == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);
+                            tma_load_2d_pair(st, &tmap_q, &full[stage], kb * BK, qt * BM);
+                            tma_load_2d_pair(st + A_BYTES, &tmap_x, &full[stage], kb * BK, row0 + rank * (BN / 2));
+                            if (++stage == kStages) { stage = 0; phase ^= 1; }
+                            continue;
+                        }
+                        mbar_expect_tx(&full[stage], STAGE_BYTES);
                         tma_load_2d(st, &tmap_q, &full[stage], kb * BK, qt * BM);
                         if (cs > 1)
                             tma_load_2d_mc(st + A_BYTES + rank * slice_rows * BK * 2, &tmap_x, &full[stage], kb * BK,
@@ -278,9 +296,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
-        if (lane == 0) {
-            constexpr uint32_t idesc = idesc_bf16_f32(BM, BN);
+        // ===== MMA issuer (one thread; in pair mode only the leader CTA issues) =====
+        if (lane == 0 && (!PAIR || rank == 0)) {
+            constexpr uint32_t idesc = idesc_bf16_f32(PAIR ? 2 * BM : BM, BN);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (int item = cluster_id; item < n_items; item += n_clusters) {
                 const int sl = item / p.n_qgroups;
@@ -296,13 +314,17 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                         const uint64_t da = smem_desc_sw128(tiles + stage * STAGE_BYTES);
                         const uint64_t db = smem_desc_sw128(tiles + stage * STAGE_BYTES + A_BYTES);
 #pragma unroll
-                        for (int k = 0; k < BK / 16; ++k)       // 32 bytes along K per MMA: +2 in 16-byte units
-                            mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-                        if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
+                        for (int k = 0; k < BK / 16; ++k) {     // 32 bytes along K per MMA: +2 in 16-byte units
+                            if (PAIR) mma_bf16_ss_pair(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                            else mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                        }
+                        if (PAIR) mma_commit_pair(&empty[stage], 3);         // frees the stage in both CTAs
+                        else if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
                         else mma_commit(&empty[stage]);          // frees the smem stage when these MMAs retire
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
-                    mma_commit(&tfull[acc]);                     // accumulator complete
+                    if (PAIR) mma_commit_pair(&tfull[acc], 3);   // accumulator complete, in both CTAs
+                    else mma_commit(&tfull[acc]);
                     acc ^= 1;
                     if (acc == 0) acc_phase ^= 1;
                 }
@@ -363,7 +385,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     if (d > 6000) atomicAdd(&g_stats[7], d - 6000);
                 }
 #endif
-                if (lane == 0) mbar_arrive(&tempty[acc]);
+                if (lane == 0) {
+                    if (PAIR) mbar_arrive_remote(&tempty[acc], 0);   // the leader's MMA thread owns the pair's accumulators
+                    else mbar_arrive(&tempty[acc]);
+                }
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
@@ -378,7 +403,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (cs > 1) cluster_sync();          // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, kTmemCols);
+        if (PAIR) tmem_dealloc_pair(tmem_base, kTmemCols);
+        else tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 
@@ -691,6 +717,9 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     pl->n_slices = (pl->n_tiles + pl->tiles_per_slice - 1) / pl->tiles_per_slice;
     if (pl->n_slices < 1) pl->n_slices = 1;
     pl->kp = k <= 3 ? 32 : (k <= 16 ? 128 : (k <= 48 ? 256 : 512));
+    // a table this small (centroids) has at most 2*128 candidate groups per query: keep them all and never
+    // compact — compaction per item would otherwise dominate when the query side is the large one
+    if (n_rows <= 2 * 128 * kSub && pl->kp < 128) pl->kp = 128;
     pl->cap = 2 * pl->kp;
     int64_t fb = (n_rows + 255) / 256;
     pl->fb_chunks = (int)(fb < sms ? (fb < 1 ? 1 : fb) : sms);
@@ -800,6 +829,10 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim, BM)) return rc;
+        // cta_group::2 (LZ_PAIR=1) measured no faster than two cta_group::1 CTAs with a multicast rows tile:
+        // 12.50 vs 12.27 ms in bursts, 14.83 vs 14.10 ms under the power cap (10M x 768, batch 1024), so the
+        // multicast form stays the default
+        const bool pair = pl.cs == 2 && env_int("LZ_PAIR", 0) != 0;
         if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim, BN / pl.cs)) return rc;
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
@@ -808,9 +841,11 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
-        const size_t smem = 1024 + (size_t)kStages * STAGE_BYTES + (2 * kStages + 4) * 8 + 16;
-        auto kern = pl.kp == 32 ? gemm_topk_kernel<2>
-                  : pl.kp == 128 ? gemm_topk_kernel<8> : (pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>);
+        const size_t smem = 1024 + (size_t)196608 + (2 * 6 + 4) * 8 + 16;   // 4 x 48 KiB or 6 x 32 KiB of stages
+        auto kern = pair ? (pl.kp == 32 ? gemm_topk_kernel<2, true> : pl.kp == 128 ? gemm_topk_kernel<8, true>
+                            : pl.kp == 256 ? gemm_topk_kernel<16, true> : gemm_topk_kernel<32, true>)
+                         : (pl.kp == 32 ? gemm_topk_kernel<2, false> : pl.kp == 128 ? gemm_topk_kernel<8, false>
+                            : pl.kp == 256 ? gemm_topk_kernel<16, false> : gemm_topk_kernel<32, false>);
         LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (pl.cs > 4) LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cudaLaunchConfig_t cfg = {};

@@ -268,6 +268,20 @@ class MemoryShard:
     def size(self) -> Tuple[int, int]:
         return len(self.nodes), self._table.n + len(self._pending)
 
+    def connected_components(self) -> List[set]:
+        """Components of this shard's graph (edges undirected, any weight), on the device
+        (lz_connected_components).  For a shard whose edges stay inside the shard this is what
+        BufferGraph.get_connected_components (core/buffer_graph.py:99-120) finds for its nodes."""
+        self._flush()
+        n = len(self._names)
+        if n == 0:
+            return []
+        labels = kernels.connected_components(self._table.src, self._table.dst, self._table.n, n).cpu().numpy()
+        groups: Dict[int, set] = {}
+        for slot, lab in enumerate(labels.tolist()):
+            groups.setdefault(lab, set()).add(self._names[slot])
+        return [groups[k] for k in sorted(groups)]
+
 
 class BufferGraph:
     """Decay / prune fan-out of the reference's BufferGraph (core/buffer_graph.py:87-97)."""

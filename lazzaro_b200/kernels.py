@@ -190,3 +190,13 @@ def segment_mean(rows: torch.Tensor, dim: int, seg_offsets: torch.Tensor, order:
         check(_lib.load().lz_segment_mean(ptr(rows), rows.stride(0), dim, ptr(order), ptr(seg_offsets), n_seg, ptr(out),
                                           stream_ptr(dev)), "lz_segment_mean")
     return out
+
+
+def connected_components(src: torch.Tensor, dst: torch.Tensor, n_edges: int, n_nodes: int) -> torch.Tensor:
+    """int32 [n_nodes] labels = smallest node index of each node's component (lz_connected_components)."""
+    dev = _dev(src)
+    labels = torch.empty(n_nodes, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_connected_components(ptr(src), ptr(dst), int(n_edges), int(n_nodes), ptr(labels),
+                                                  stream_ptr(dev)), "lz_connected_components")
+    return labels

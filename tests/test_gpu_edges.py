@@ -127,3 +127,44 @@ def test_memory_shard_mirror_runs_reference_scenario():
     assert shard.nodes["seed_0"].salience == pytest.approx(0.893, abs=1e-6)   # 0.2 + 0.7*0.99
     assert shard.get_neighbors("seed_1") == ["seed_0", "seed_2"]
     assert shard.size() == (4, 3)
+
+
+def _components_oracle(src, dst, n):
+    parent = list(range(n))
+
+    def find(v):
+        while parent[v] != v:
+            parent[v] = parent[parent[v]]
+            v = parent[v]
+        return v
+    for u, v in zip(src.tolist(), dst.tolist()):
+        ru, rv = find(u), find(v)
+        if ru != rv:
+            parent[max(ru, rv)] = min(ru, rv)
+    return np.array([find(v) for v in range(n)], dtype=np.int32)
+
+
+@pytest.mark.parametrize("n_nodes,n_edges", [(1, 0), (10, 3), (1000, 700), (50_000, 40_000), (200_000, 1_000_000)])
+def test_connected_components_match_union_find(n_nodes, n_edges):
+    from lazzaro_b200 import kernels
+    rng = np.random.default_rng(n_nodes + n_edges)
+    src = rng.integers(0, n_nodes, n_edges, dtype=np.int32)
+    dst = rng.integers(0, n_nodes, n_edges, dtype=np.int32)
+    if n_edges == 0:
+        s = d = torch.zeros(1, dtype=torch.int32, device="cuda")
+    else:
+        s, d = torch.as_tensor(src).cuda(), torch.as_tensor(dst).cuda()
+    got = kernels.connected_components(s, d, n_edges, n_nodes).cpu().numpy()
+    np.testing.assert_array_equal(got, _components_oracle(src, dst, n_nodes))       # label = min index: deterministic
+
+
+def test_shard_components_reference_scenario():
+    # tests/test_profile_update.py:32-78: a chain of four memories is one component of size >= 3
+    from lazzaro_b200.graph import Edge, MemoryShard, Node
+    shard = MemoryShard("default", device="cuda")
+    for i in range(6):
+        shard.add_node(Node(id=f"seed_{i}", content=f"m{i}"))
+    for i in range(3):
+        shard.add_edge(Edge(source=f"seed_{i}", target=f"seed_{i+1}", weight=0.8))
+    comps = shard.connected_components()
+    assert sorted(sorted(c) for c in comps) == [["seed_0", "seed_1", "seed_2", "seed_3"], ["seed_4"], ["seed_5"]]
