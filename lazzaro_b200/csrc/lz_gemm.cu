@@ -453,18 +453,44 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         if (g != 0u) { sa.thr_key = (u64)g; sa.thr_id = 0xffffffffu; }
     }
     __syncthreads();
-    // 1. merge the slices' candidates by coarse score
+    // 1. merge the slices' candidates by coarse score.  The per-slice counts and thresholds are fetched by all
+    // threads at once, then the (slice, entry) pairs are walked flat, 512 per round, so the global loads of a
+    // round are independent (a slice-by-slice loop is one dependent round trip per slice).
+    __shared__ float s_tw[kSelThreads / 32];
+    __shared__ int s_nw[kSelThreads / 32];
+    {
+        float t_loc = -INFINITY;
+        int n_loc = 0;
+        for (int sl = tid; sl < p.n_slices; sl += kSelThreads) {
+            const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+            t_loc = fmaxf(t_loc, p.cand_thr[slot]);
+            n_loc += p.cand_cnt[slot];
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            t_loc = fmaxf(t_loc, __shfl_xor_sync(0xffffffffu, t_loc, o));
+            n_loc += __shfl_xor_sync(0xffffffffu, n_loc, o);
+        }
+        if (lane == 0) { s_tw[warp] = t_loc; s_nw[warp] = n_loc; }
+    }
+    __syncthreads();
     float T = -INFINITY;
     int total = 0;
-    for (int sl = 0; sl < p.n_slices; ++sl) {
-        const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
-        const int cnt = p.cand_cnt[slot];
-        T = fmaxf(T, p.cand_thr[slot]);
-        total += cnt;
-        const u64* src = p.cand + slot * p.cap;
-        for (int j = tid; j < cnt; j += kSelThreads) {
-            const u64 kk = src[j];
-            lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
+#pragma unroll
+    for (int w = 0; w < kSelThreads / 32; ++w) { T = fmaxf(T, s_tw[w]); total += s_nw[w]; }
+    const int64_t flat = (int64_t)p.n_slices * p.kp;                          // each slice left at most kp entries
+    for (int64_t base = 0; base < flat; base += 2 * kSelThreads) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t i = base + h * kSelThreads + tid;
+            if (i < flat) {
+                const int sl = (int)(i / p.kp), j = (int)(i - (int64_t)sl * p.kp);
+                const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+                if (j < p.cand_cnt[slot]) {
+                    const u64 kk = p.cand[slot * p.cap + j];
+                    lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
+                }
+            }
         }
         lz_sel_maybe_compact<kSelThreads>(&sa, 2 * kSelThreads);
     }
@@ -505,35 +531,51 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         qs = fma((double)x.w, (double)x.w, qs);
     }
     const double qn = sqrt(lz_warp_sum(qs));
-    for (int j = 0; j < m; ++j) {
-        // every row of candidate group j that passes the range / tag filter
-        for (int r = warp; r < kSub; r += kSelThreads / 32) {
-            const int64_t row = (int64_t)id_a[j] + r;
-            bool ok = row < p.row_hi;
-            if (ok && p.tags) {
-                const int tg = p.tags[row];
-                ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+    // (group, row) pairs are walked flat, two per warp and step, so each warp keeps two rows' loads in flight
+    const int n_pairs = m * kSub;
+    for (int base = 0; base < n_pairs; base += 2 * (kSelThreads / 32) * 8) {
+        for (int it = 0; it < 8; ++it) {
+            const int pa = base + (it * 2 + 0) * (kSelThreads / 32) + warp;
+            const int pb = base + (it * 2 + 1) * (kSelThreads / 32) + warp;
+            int64_t row[2] = {-1, -1};
+            if (pa < n_pairs) row[0] = (int64_t)id_a[pa / kSub] + pa % kSub;
+            if (pb < n_pairs) row[1] = (int64_t)id_a[pb / kSub] + pb % kSub;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                bool ok = row[h] >= 0 && row[h] < p.row_hi;
+                if (ok && p.tags) {
+                    const int tg = p.tags[row[h]];
+                    ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                }
+                if (!ok) row[h] = -1;
             }
-            if (!ok) continue;                                      // warp-uniform
-            const float* x = p.rows + row * p.ld;
-            double acc = 0.0;
+            double acc[2] = {0.0, 0.0};
             for (int e = lane * 4; e < p.dim; e += 128) {
-                const float4 xv = lz_ldg_stream(x + e);
                 const float4 qq = *reinterpret_cast<const float4*>(qv + e);
-                acc = fma((double)xv.x, (double)qq.x, acc);
-                acc = fma((double)xv.y, (double)qq.y, acc);
-                acc = fma((double)xv.z, (double)qq.z, acc);
-                acc = fma((double)xv.w, (double)qq.w, acc);
+                float4 xv[2];
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    xv[h] = row[h] >= 0 ? lz_ldg_stream(p.rows + row[h] * p.ld + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    acc[h] = fma((double)xv[h].x, (double)qq.x, acc[h]);
+                    acc[h] = fma((double)xv[h].y, (double)qq.y, acc[h]);
+                    acc[h] = fma((double)xv[h].z, (double)qq.z, acc[h]);
+                    acc[h] = fma((double)xv[h].w, (double)qq.w, acc[h]);
+                }
             }
-            acc = lz_warp_sum(acc);
-            if (lane == 0) {
-                const double den = p.norms[row] * qn;
-                double s = den > 0.0 ? acc / den : 0.0;
-                s += 0.0;
-                if (s == s) lz_sel_push(&sb, lz_ord(s), (u32)row);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const double dot = lz_warp_sum(acc[h]);
+                if (lane == 0 && row[h] >= 0) {
+                    const double den = p.norms[row[h]] * qn;
+                    double s = den > 0.0 ? dot / den : 0.0;
+                    s += 0.0;
+                    if (s == s) lz_sel_push(&sb, lz_ord(s), (u32)row[h]);
+                }
             }
         }
-        if ((j & 7) == 7) lz_sel_maybe_compact<kSelThreads>(&sb, 8 * kSub);
+        lz_sel_maybe_compact<kSelThreads>(&sb, 2 * (kSelThreads / 32) * 8);
     }
     __syncthreads();
     lz_sel_compact<kSelThreads>(&sb);
