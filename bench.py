@@ -55,6 +55,7 @@ def parse():
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--cpu-sample-rows", type=int, default=400_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--edges", type=int, default=50_000_000, help="edge-table size for the decay+prune sub-result (0 = skip)")
     return ap.parse_args()
 
 
@@ -303,9 +304,46 @@ def main():
                                        "frac": ach1 / hbm_peak, "traffic": traffic.get("scan_kernel_10M_b1"),
                                        "kernel": "scan_kernel (lz_search_exact)", "algorithmic_bytes_per_launch": bytes1},
                           "gpu_launches": int(n1 * (2 + (1 if world > 1 else 0)))}
+    if args.edges > 0:
+        # north_star (3): decay + prune sweep over the edge table; edges are partitioned with their shards, so the
+        # ranks sweep disjoint slices with no collective (total edges fixed: strong scaling like the search)
+        del out, out_e2e
+        ne = args.edges // world
+        g = torch.Generator(device=dev); g.manual_seed(synth.SEED_EDGES + rank)
+        cols = [torch.randint(0, max(1, n_local), (ne,), generator=g, device=dev, dtype=torch.int32),
+                torch.randint(0, max(1, n_local), (ne,), generator=g, device=dev, dtype=torch.int32),
+                torch.rand(ne, generator=g, device=dev, dtype=torch.float32),
+                torch.ones(ne, device=dev, dtype=torch.int32)]
+        outs = [torch.empty_like(c) for c in cols]
+        kept = torch.zeros(1, dtype=torch.int64, device=dev)
+        scratch = torch.empty(int(_lib.load().lz_edge_decay_prune_scratch_bytes(ne)), dtype=torch.uint8, device=dev)
+        f_edges = lambda: kernels.edge_decay_prune(*cols, ne, 0.99, 0.5, out=tuple(outs), scratch=scratch, kept=kept)
+        for _ in range(3):
+            f_edges()
+        n_e = max(args.steps, 10)
+        ms_e, _ = timed(f_edges, n_e)
+        kf = float(kept.item()) / ne
+        ebytes = (16 + 16 * kf) * ne
+        ach_e = ebytes / (ms_e / n_e * 1e-3) / 1e9
+        line["decay_prune"] = {"metric": "decay+prune edges/s over %d edges (factor 0.99, threshold 0.5)" % args.edges,
+                               "value": ne * world / (ms_e / n_e * 1e-3), "unit": "edges/s", "ms_per_step": ms_e / n_e,
+                               "kept_fraction": kf, "gpu_launches": int(n_e * 3),
+                               "roofline": {"bound": "hbm", "achieved": ach_e, "peak": hbm_peak, "unit": "GB/s",
+                                            "frac": ach_e / hbm_peak, "traffic": None,
+                                            "kernel": "count_kernel + tile_scan_kernel + decay_prune_kernel (lz_edge_decay_prune)",
+                                            "algorithmic_bytes_per_launch": ebytes}}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         qps, desc, cores, _ = cpu_search_qps(args, 3, 1)
         line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+        if "decay_prune" in line:
+            from oracle import graph_ops
+            es, ed, ew, ec = synth.edge_table(2_000_000, 1_000_000)
+            t0 = time.perf_counter()
+            for _ in range(3):
+                graph_ops.decay_prune_edges(es, ed, ew, ec, 0.99, 0.5)
+            line["decay_prune"]["cpu_baseline"] = {"value": 2_000_000 * 3 / (time.perf_counter() - t0), "unit": "edges/s",
+                                                   "cores": 1, "kind": "port",
+                                                   "sample": "numpy vectorised decay+mask+compress on 2M edges (the reference's per-object Python loop, memory_shard.py:64-84, measured ~2.7M edges/s in SURVEY §6)"}
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
