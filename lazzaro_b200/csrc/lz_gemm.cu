@@ -118,6 +118,7 @@ __device__ unsigned long long g_stats[8];   // 0 epi busy, 1 epi max, 2 mma wait
 // ---- the coarse pass ----------------------------------------------------------------------------------
 struct GemmParams {
     int n_queries, n_qtiles, n_slices, tiles_per_slice, n_tiles, kblocks;
+    int tile_mul;       // rows tile t starts at row_lo + t * tile_mul * BN (1 normally; a stride in the sampling pass)
     int cs, n_qgroups;  // cluster size (CTAs that share one rows tile by TMA multicast) and q-tile groups of that size
     int64_t row_lo, row_hi;
     int kp, cap;
@@ -284,7 +285,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 const int t0 = sl * p.tiles_per_slice;
                 const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
                 for (int t = t0; t < t1; ++t) {
-                    const int row0 = (int)(p.row_lo + (int64_t)t * BN);
+                    const int row0 = (int)(p.row_lo + (int64_t)t * p.tile_mul * BN);
                     for (int kb = 0; kb < p.kblocks; ++kb) {
                         { LZ_T0 mbar_wait(&empty[stage], phase ^ 1); LZ_ACC(4) }   // all cs consumers have released the stage
                         unsigned char* st = tiles + stage * STAGE_BYTES;
@@ -361,7 +362,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             int count = 0;
             float thr = valid ? -INFINITY : INFINITY;
             for (int t = t0; t < t1; ++t) {
-                const int64_t row0 = p.row_lo + (int64_t)t * BN;
+                const int64_t row0 = p.row_lo + (int64_t)t * p.tile_mul * BN;
                 if (valid) {
                     // adopt the best threshold any CTA working on this query has reached: a row below some
                     // CTA's kp-th best coarse score cannot be among the kp best overall
@@ -715,6 +716,41 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
     }
 }
 
+// Threshold seeding: the coarse pass is first run over a strided sample of the rows tiles (64 tiles, one per
+// item, so nothing is compacted); here each query's kp-th best sampled group key becomes its starting
+// threshold.  The kp-th best of a subset can only be lower than the kp-th best of all groups, so the seed is
+// a valid lower bound; it lets the real pass reject ~94 % of the groups from its first tile on instead of
+// accepting everything until every lane's buffer has filled and been compacted a few times.
+__global__ void __launch_bounds__(kSelThreads) seed_threshold_kernel(SelectParams p, u32* gthr) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* key_a = reinterpret_cast<u64*>(smem);
+    u32* id_a = reinterpret_cast<u32*>(key_a + p.cap_a);
+    __shared__ LzSelector sa;
+    const int tid = threadIdx.x;
+    const int q = blockIdx.x, qt = q / BM, ql = q % BM;
+    if (tid == 0) lz_sel_init(&sa, key_a, id_a, p.cap_a, p.kp);
+    __syncthreads();
+    const int64_t flat = (int64_t)p.n_slices * (BN / kSub);                   // one tile = BN / kSub groups per slice
+    for (int64_t base = 0; base < flat; base += 2 * kSelThreads) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int64_t i = base + h * kSelThreads + tid;
+            if (i < flat) {
+                const int sl = (int)(i / (BN / kSub)), j = (int)(i % (BN / kSub));
+                const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+                if (j < p.cand_cnt[slot]) {
+                    const u64 kk = p.cand[slot * p.cap + j];
+                    lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
+                }
+            }
+        }
+        lz_sel_maybe_compact<kSelThreads>(&sa, 2 * kSelThreads);
+    }
+    __syncthreads();
+    lz_sel_compact<kSelThreads>(&sa);
+    if (tid == 0 && sa.count >= p.kp) gthr[q] = (u32)key_a[p.kp - 1];
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -797,7 +833,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     ScratchLayout L;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
-    const size_t items = (size_t)pl.n_qgroups * pl.cs * pl.n_slices;
+    const size_t items = (size_t)pl.n_qgroups * pl.cs * (pl.n_slices > 64 ? pl.n_slices : 64);
     L.q_bf16 = take((size_t)n_queries * dim * 2);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
@@ -898,7 +934,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
-        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups;
+        g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
@@ -910,7 +946,6 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         if (pl.cs > 4) LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)pl.grid);
         cfg.blockDim = dim3(kGemmThreads);
         cfg.dynamicSmemBytes = smem;
         cfg.stream = st;
@@ -921,6 +956,27 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         attr[0].val.clusterDim.z = 1;
         cfg.attrs = attr;
         cfg.numAttrs = 1;
+        // sampling pass: kSampleTiles tiles spread evenly over the range seed every query's threshold
+        // (skipped when the table is small, or when kp exceeds what the sample can rank)
+        constexpr int kSampleTiles = 64;
+        if (pl.n_tiles >= 8 * kSampleTiles && kSampleTiles * (BN / kSub) >= 4 * pl.kp && env_int("LZ_SEED", 1) != 0) {
+            GemmParams gs = g;
+            gs.n_tiles = kSampleTiles; gs.n_slices = kSampleTiles; gs.tiles_per_slice = 1;
+            gs.tile_mul = pl.n_tiles / kSampleTiles;
+            const int n_clusters = pl.grid / pl.cs;
+            const int items = pl.n_qgroups * kSampleTiles;
+            cfg.gridDim = dim3((unsigned)((items < n_clusters ? items : n_clusters) * pl.cs));
+            LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, gs));
+            SelectParams ss = {};
+            ss.cand = (const u64*)(s + L.cand); ss.cand_cnt = (const int32_t*)(s + L.cand_cnt);
+            ss.n_qtiles_pad = pl.n_qgroups * pl.cs; ss.n_slices = kSampleTiles; ss.kp = pl.kp; ss.cap = pl.cap;
+            ss.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads);
+            const size_t ssm = (size_t)ss.cap_a * 12;
+            LZ_CUDA(cudaFuncSetAttribute(seed_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm));
+            seed_threshold_kernel<<<n_queries, kSelThreads, ssm, st>>>(ss, gthr);
+            LZ_CUDA(cudaGetLastError());
+        }
+        cfg.gridDim = dim3((unsigned)pl.grid);
         LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, g));
     } else {
         const size_t items = (size_t)pl.n_qgroups * pl.cs * pl.n_slices;
