@@ -103,23 +103,26 @@ int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms,
 
 #define LZ_BATCHED_MAX_K 128   /* largest k lz_search_batched accepts (larger k: lz_search_exact) */
 
-/* shadow[i][j] = bf16(rows[i][j] / norms[i]) (zeros for a zero row), bf16 [n, dim] dense, dim % 8 == 0.
- * The normalised bf16 copy the coarse pass reads; refresh the rows you add. */
-int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, void* shadow_bf16,
-                    void* stream);
+/* The bf16 copy of the rows that the coarse pass reads; refresh the rows you add.  dim % 8 == 0.
+ *   LZ_COSINE: shadow[i][j] = bf16(rows[i][j] / norms[i]) (zeros for a zero row), bf16 [n, dim] dense
+ *   LZ_L2    : shadow[i] = [bf16(rows[i]), h, m, l, 0, 0, 0, 0], bf16 [n, dim + 8] dense, h + m + l = a three-way
+ *              bf16 split of -|row|^2 / 2, so that one contraction yields x.q - |x|^2/2 (L2 ranking) */
+int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
+                    void* shadow_bf16, void* stream);
 
 /* Bytes of device scratch lz_search_batched needs for a scan of n_rows = row_hi - row_lo rows. */
 size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int dim);
 
 /*
- * Exact cosine top-k for a batch of queries, computed as: bf16 tcgen05 GEMM (queries x rows, never
+ * Exact top-k (LZ_COSINE or LZ_L2) for a batch of queries, computed as: bf16 tcgen05 GEMM (queries x rows, never
  * materialised) with a fused per-query candidate selection -> float64 rescoring of the candidates from
  * the float32 rows -> top-k with the id tie-break -> certification (k-th exact score must exceed the
  * best dropped coarse score by the bf16 error margin) -> exact float64 scan of the queries that fail
- * it.  Results are those of lz_search_exact (LZ_COSINE) whenever the margin holds; the margin is
+ * it.  Results are those of lz_search_exact with the same metric whenever the margin holds; the margin is
  * statistical: margin_sigmas standard deviations of the bf16 rounding error (4 is the default used
  * by the Python layer).
- *   shadow_bf16   bf16 [n_rows_total, dim] from lz_rows_to_bf16 (row i of the shadow = row i of rows)
+ *   shadow_bf16   bf16 [n_rows_total, dim (+ 8 for LZ_L2)] from lz_rows_to_bf16 with the same metric
+ *   max_row_norm  LZ_L2 only: an upper bound of the row norms (scales the error margin)
  *   tags/want_tag as lz_search_exact with one tag for the whole batch (want_tag < 0: any live row)
  *   row_lo,row_hi the row range every query scans
  *   out_certified optional int32 [n_queries]: 1 = answered by the tensor-core pass, 0 = by the fallback
@@ -127,7 +130,7 @@ size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int
 int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, int dim, const double* norms,
                       const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo, int64_t row_hi,
                       const float* queries, int64_t q_ld, int n_queries, int k, double margin_sigmas,
-                      int64_t id_base, void* scratch, size_t scratch_bytes,
+                      int metric, double max_row_norm, int64_t id_base, void* scratch, size_t scratch_bytes,
                       int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                       void* stream);
 

@@ -50,17 +50,22 @@ __device__ __forceinline__ float unord32(u32 k) {
 }
 
 // ---- preparation: normalised bf16 copies ------------------------------------------------------------
+// LZ_COSINE: out[r] = bf16(x / |x|), dim columns.  LZ_L2: out[r] = [bf16(x), h, m, l, 0, 0, 0, 0], dim + 8 columns,
+// where h + m + l is a three-way bf16 split of -|x|^2 / 2 (24 significant bits): against the query
+// [bf16(q), 1, 1, 1, 0, ...] the contraction gives x.q - |x|^2/2 = -(|x - q|^2 - |q|^2) / 2, i.e. the L2
+// ranking comes out of the same GEMM, largest = nearest.
 __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restrict__ rows, int64_t n, int dim, int64_t ld,
-                                                           const double* __restrict__ norms,
+                                                           const double* __restrict__ norms, int metric,
                                                            __nv_bfloat16* __restrict__ out) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * 8;
+    const int odim = metric == LZ_L2 ? dim + 8 : dim;
     for (int64_t r = warp; r < n; r += nwarps) {
         const double nr = norms[r];
-        const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
+        const float inv = metric == LZ_L2 ? 1.f : (nr > 0.0 ? (float)(1.0 / nr) : 0.f);
         const float* x = rows + r * ld;
-        __nv_bfloat16* o = out + r * dim;
+        __nv_bfloat16* o = out + r * odim;
         for (int e = lane * 4; e < dim; e += 128) {
             const float4 v = lz_ldg_stream(x + e);
             __nv_bfloat162 a = __floats2bfloat162_rn(v.x * inv, v.y * inv);
@@ -70,6 +75,13 @@ __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restri
             pk.y = *reinterpret_cast<u32*>(&b);
             *reinterpret_cast<uint2*>(o + e) = pk;
         }
+        if (metric == LZ_L2 && lane < 8) {
+            const double v = -0.5 * nr * nr;
+            const __nv_bfloat16 h = __double2bfloat16(v);
+            const __nv_bfloat16 m = __double2bfloat16(v - (double)__bfloat162float(h));
+            const __nv_bfloat16 l = __double2bfloat16(v - (double)__bfloat162float(h) - (double)__bfloat162float(m));
+            o[dim + lane] = lane == 0 ? h : lane == 1 ? m : lane == 2 ? l : __float2bfloat16_rn(0.f);
+        }
     }
 }
 
@@ -77,7 +89,7 @@ __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restri
 __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
                                                               __nv_bfloat16* __restrict__ out, double* __restrict__ eps,
                                                               int32_t* __restrict__ gtag, u32* __restrict__ gthr, int32_t* __restrict__ fb_count,
-                                                              int want_tag, double sigmas) {
+                                                              int want_tag, double sigmas, int metric, double max_norm) {
     const int lane = threadIdx.x & 31;
     const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count = 0;
@@ -94,13 +106,24 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     const double nr = sqrt(ss);
-    const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
-    for (int e = lane; e < dim; e += 32) out[(int64_t)w * dim + e] = __float2bfloat16_rn(v[e] * inv);
+    if (metric == LZ_L2) {
+        __nv_bfloat16* o = out + (int64_t)w * (dim + 8);
+        for (int e = lane; e < dim; e += 32) o[e] = __float2bfloat16_rn(v[e]);
+        if (lane < 8) o[dim + lane] = __float2bfloat16_rn(lane < 3 ? 1.f : 0.f);
+        if (lane == 0)   // error of bf16(x).bf16(q) with |x| <= max_norm, plus the split's and the fp32 accumulator's residue
+            eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)mx * max_norm +
+                     2e-6 * (max_norm * nr + max_norm * max_norm) + 1e-30;
+    } else {
+        const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
+        for (int e = lane; e < dim; e += 32) out[(int64_t)w * dim + e] = __float2bfloat16_rn(v[e] * inv);
+        if (lane == 0) {
+            // bf16 rounding: each operand carries an independent relative error uniform in +-2^-9, so the
+            // coarse dot of unit vectors errs with std <= 2^-9*sqrt(2/3)*max|q_i| (sum x_i^2 q_i^2 <=
+            // max q_i^2); fp32 accumulation adds a few 1e-7.  eps = sigmas * that + 8e-6.
+            eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)(mx * inv) + 8e-6;
+        }
+    }
     if (lane == 0) {
-        // bf16 rounding: each operand carries an independent relative error uniform in +-2^-9, so the
-        // coarse dot of unit vectors errs with std <= 2^-9*sqrt(2/3)*max|q_i| (sum x_i^2 q_i^2 <=
-        // max q_i^2); fp32 accumulation adds a few 1e-7.  eps = sigmas * that + 8e-6.
-        eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)(mx * inv) + 8e-6;
         gtag[w] = want_tag;
         gthr[w] = 0u;
     }
@@ -434,6 +457,7 @@ struct SelectParams {
     int64_t* out_ids; double* out_scores; int32_t* out_counts; int32_t* certified;
     int32_t* fb_list; int32_t* fb_count;     // queries that failed certification, for the exact fallback
     const u32* gthr;                         // [n_queries] best threshold any CTA reached (lower bound of the kp-th best)
+    int metric;                              // LZ_COSINE, or LZ_L2 (coarse key = x.q - |x|^2/2 = -(d - |q|^2)/2)
 };
 
 __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParams p) {
@@ -559,19 +583,33 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
                     xv[h] = row[h] >= 0 ? lz_ldg_stream(p.rows + row[h] * p.ld + e) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
-                    acc[h] = fma((double)xv[h].x, (double)qq.x, acc[h]);
-                    acc[h] = fma((double)xv[h].y, (double)qq.y, acc[h]);
-                    acc[h] = fma((double)xv[h].z, (double)qq.z, acc[h]);
-                    acc[h] = fma((double)xv[h].w, (double)qq.w, acc[h]);
+                    if (p.metric == LZ_COSINE) {
+                        acc[h] = fma((double)xv[h].x, (double)qq.x, acc[h]);
+                        acc[h] = fma((double)xv[h].y, (double)qq.y, acc[h]);
+                        acc[h] = fma((double)xv[h].z, (double)qq.z, acc[h]);
+                        acc[h] = fma((double)xv[h].w, (double)qq.w, acc[h]);
+                    } else {
+                        const double d0 = (double)xv[h].x - (double)qq.x, d1 = (double)xv[h].y - (double)qq.y;
+                        const double d2 = (double)xv[h].z - (double)qq.z, d3 = (double)xv[h].w - (double)qq.w;
+                        acc[h] = fma(d0, d0, acc[h]);
+                        acc[h] = fma(d1, d1, acc[h]);
+                        acc[h] = fma(d2, d2, acc[h]);
+                        acc[h] = fma(d3, d3, acc[h]);
+                    }
                 }
             }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const double dot = lz_warp_sum(acc[h]);
                 if (lane == 0 && row[h] >= 0) {
-                    const double den = p.norms[row[h]] * qn;
-                    double s = den > 0.0 ? dot / den : 0.0;
-                    s += 0.0;
+                    double s;
+                    if (p.metric == LZ_COSINE) {
+                        const double den = p.norms[row[h]] * qn;
+                        s = den > 0.0 ? dot / den : 0.0;
+                        s += 0.0;
+                    } else {
+                        s = 0.0 - dot;                     // key order: larger = nearer
+                    }
                     if (s == s) lz_sel_push(&sb, lz_ord(s), (u32)row[h]);
                 }
             }
@@ -583,8 +621,9 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
     const int n = min(sb.count, p.k);
     for (int j = tid; j < p.k; j += kSelThreads) {
         if (j < n) {
+            const double v = lz_unord(key_b[j]);
             p.out_ids[(size_t)q * p.k + j] = (int64_t)id_b[j] + p.id_base;
-            p.out_scores[(size_t)q * p.k + j] = lz_unord(key_b[j]);
+            p.out_scores[(size_t)q * p.k + j] = p.metric == LZ_COSINE ? v : 0.0 - v;
         } else {
             p.out_ids[(size_t)q * p.k + j] = -1;
             p.out_scores[(size_t)q * p.k + j] = __longlong_as_double(0x7ff8000000000000ll);
@@ -594,7 +633,11 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         p.out_counts[q] = n;
         // 3. certify: rows dropped anywhere had coarse <= T, i.e. exact <= T + eps
         bool cert = T == -INFINITY;
-        if (!cert && n >= p.k) cert = lz_unord(key_b[p.k - 1]) > (double)T + p.eps[q];
+        if (!cert && n >= p.k) {
+            const double ek = lz_unord(key_b[p.k - 1]);                       // cosine, or -distance
+            const double e_coarse = p.metric == LZ_COSINE ? ek : 0.5 * (ek + qn * qn);   // -(d - |q|^2)/2
+            cert = e_coarse > (double)T + p.eps[q];
+        }
         p.certified[q] = cert ? 1 : 0;
         if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
     }
@@ -678,15 +721,29 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
                 for (int e = lane * 4; e < p.dim; e += 128) {
                     const float4 xv = lz_ldg_stream(x + e);
                     const float4 qq = *reinterpret_cast<const float4*>(qv + e);
-                    acc = fma((double)xv.x, (double)qq.x, acc);
-                    acc = fma((double)xv.y, (double)qq.y, acc);
-                    acc = fma((double)xv.z, (double)qq.z, acc);
-                    acc = fma((double)xv.w, (double)qq.w, acc);
+                    if (p.metric == LZ_COSINE) {
+                        acc = fma((double)xv.x, (double)qq.x, acc);
+                        acc = fma((double)xv.y, (double)qq.y, acc);
+                        acc = fma((double)xv.z, (double)qq.z, acc);
+                        acc = fma((double)xv.w, (double)qq.w, acc);
+                    } else {
+                        const double d0 = (double)xv.x - (double)qq.x, d1 = (double)xv.y - (double)qq.y;
+                        const double d2 = (double)xv.z - (double)qq.z, d3 = (double)xv.w - (double)qq.w;
+                        acc = fma(d0, d0, acc);
+                        acc = fma(d1, d1, acc);
+                        acc = fma(d2, d2, acc);
+                        acc = fma(d3, d3, acc);
+                    }
                 }
                 acc = lz_warp_sum(acc);
-                const double den = p.norms[row] * qn;
-                double s = den > 0.0 ? acc / den : 0.0;
-                s += 0.0;
+                double s;
+                if (p.metric == LZ_COSINE) {
+                    const double den = p.norms[row] * qn;
+                    s = den > 0.0 ? acc / den : 0.0;
+                    s += 0.0;
+                } else {
+                    s = 0.0 - acc;
+                }
                 if (s != s) continue;
                 u64 key = lz_ord(s);
                 u32 id = (u32)row;
@@ -705,12 +762,18 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
         const int n = found < p.k ? found : p.k;
         for (int j = 0; j < p.k; ++j) {
             const bool has = j < n;
+            const double v = has ? lz_unord(bk[j]) : 0.0;
             p.out_ids[(size_t)q * p.k + j] = has ? (int64_t)bi[j] + p.id_base : -1;
-            p.out_scores[(size_t)q * p.k + j] = has ? lz_unord(bk[j]) : __longlong_as_double(0x7ff8000000000000ll);
+            p.out_scores[(size_t)q * p.k + j] = has ? (p.metric == LZ_COSINE ? v : 0.0 - v)
+                                                    : __longlong_as_double(0x7ff8000000000000ll);
         }
         p.out_counts[q] = n;
         bool cert = T == -INFINITY;
-        if (!cert && n >= p.k) cert = lz_unord(bk[p.k - 1]) > (double)T + (double)eps;
+        if (!cert && n >= p.k) {
+            const double ek = lz_unord(bk[p.k - 1]);
+            const double e_coarse = p.metric == LZ_COSINE ? ek : 0.5 * (ek + qn * qn);
+            cert = e_coarse > (double)T + (double)eps;
+        }
         p.certified[q] = cert ? 1 : 0;
         if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
     }
@@ -834,7 +897,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
     const size_t items = (size_t)pl.n_qgroups * pl.cs * (pl.n_slices > 64 ? pl.n_slices : 64);
-    L.q_bf16 = take((size_t)n_queries * dim * 2);
+    L.q_bf16 = take((size_t)n_queries * (dim + 8) * 2);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
     L.gthr = take((size_t)n_queries * 4);
@@ -860,8 +923,8 @@ extern "C" int lz_debug_stats(unsigned long long* host_out, int reset) {
 }
 #endif
 
-extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, void* out_bf16,
-                               void* stream) {
+extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
+                               void* out_bf16, void* stream) {
     if (n <= 0) return LZ_OK;
     LZ_REQUIRE(rows && norms && out_bf16, "lz_rows_to_bf16: NULL pointer");
     LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_rows_to_bf16: dim=%d must be a multiple of 8", dim);
@@ -870,7 +933,8 @@ extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld
     if (sms <= 0) return LZ_ERR_DEVICE;
     int64_t blocks = (n + 7) / 8;
     if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
-    rows_to_bf16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms,
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_rows_to_bf16: unknown metric %d", metric);
+    rows_to_bf16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms, metric,
                                                                             (__nv_bfloat16*)out_bf16);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
@@ -886,7 +950,8 @@ extern "C" size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries,
 extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, int dim, const double* norms,
                                  const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
                                  int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
-                                 double margin_sigmas, int64_t id_base, void* scratch, size_t scratch_bytes,
+                                 double margin_sigmas, int metric, double max_row_norm, int64_t id_base,
+                                 void* scratch, size_t scratch_bytes,
                                  int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                                  void* stream) {
     if (n_queries <= 0) return LZ_OK;
@@ -903,6 +968,9 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
                "lz_search_batched: bad row range [%lld, %lld) of %lld", (long long)row_lo, (long long)row_hi,
                (long long)n_rows_total);
     LZ_REQUIRE(margin_sigmas > 0.0, "lz_search_batched: margin_sigmas must be positive");
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_batched: unknown metric %d", metric);
+    LZ_REQUIRE(metric == LZ_COSINE || max_row_norm >= 0.0, "lz_search_batched: LZ_L2 needs max_row_norm >= 0");
+    const int dim_s = metric == LZ_L2 ? dim + 8 : dim;         // columns of the shadow (and K of the contraction)
     Plan pl;
     if (int rc = make_plan(row_hi - row_lo, n_queries, k, &pl)) return rc;
     const ScratchLayout L = layout(pl, n_queries, k, dim);
@@ -920,20 +988,20 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     int32_t* fb_list = (int32_t*)(s + L.fb_list);
     int32_t* fb_count = (int32_t*)(s + L.fb_count);
     queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
-                                                                fb_count, want_tag, margin_sigmas);
+                                                                fb_count, want_tag, margin_sigmas, metric, max_row_norm);
     LZ_CUDA(cudaGetLastError());
 
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
-        if (int rc = make_tmap(&tq, q16, n_queries, dim, BM)) return rc;
+        if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
         // cta_group::2 (LZ_PAIR=1) measured no faster than two cta_group::1 CTAs with a multicast rows tile:
         // 12.50 vs 12.27 ms in bursts, 14.83 vs 14.10 ms under the power cap (10M x 768, batch 1024), so the
         // multicast form stays the default
         const bool pair = pl.cs == 2 && env_int("LZ_PAIR", 0) != 0;
-        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim, BN / pl.cs)) return rc;
+        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim_s, BN / pl.cs)) return rc;
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
-        g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim + BK - 1) / BK;
+        g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim_s + BK - 1) / BK;
         g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
@@ -993,7 +1061,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
-    sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr;
+    sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
     if (k <= kSmallK) {
         select_rescore_small_kernel<<<(n_queries + kSelThreads / 32 - 1) / (kSelThreads / 32), kSelThreads, 0, st>>>(sp, n_queries);
     } else {
@@ -1005,6 +1073,6 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
 
     // exact float64 scan for the queries that could not be certified (a no-op launch when all were)
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, nullptr, nullptr, tags ? gtag : nullptr, queries, q_ld,
-                                n_queries, 1, k, LZ_COSINE, pl.fb_chunks, id_base, s + L.fallback,
+                                n_queries, 1, k, metric, pl.fb_chunks, id_base, s + L.fallback,
                                 L.total - L.fallback, out_ids, out_scores, out_counts, fb_list, fb_count, stream);
 }

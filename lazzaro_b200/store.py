@@ -72,6 +72,7 @@ class B200Store:
         self.margin_sigmas = 4.0
         self._shadow: Optional[torch.Tensor] = None   # bf16 [capacity, dim_p] normalised copy of the rows
         self._shadow_n = 0                            # rows of the shadow that are up to date
+        self._max_norm = 0.0                          # largest row norm seen by the shadow (L2 margin)
         self._bscratch: Optional[torch.Tensor] = None
         self.last_certified: Optional[torch.Tensor] = None
         self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
@@ -94,18 +95,22 @@ class B200Store:
             tags[:self._n] = self._tags[:self._n]
         self._rows, self._norms, self._tags = rows, norms, tags
         if self._shadow is not None:
-            shadow = torch.empty((cap, self._dim_p), dtype=torch.bfloat16, device=self.device)
+            shadow = torch.empty((cap, self._shadow.shape[1]), dtype=torch.bfloat16, device=self.device)
             shadow[:self._shadow_n] = self._shadow[:self._shadow_n]
             self._shadow = shadow
 
     def _ensure_shadow(self):
         """Brings the normalised bf16 copy of the rows (read by the tensor-core pass) up to date."""
         if self._shadow is None:
-            self._shadow = torch.empty((self._rows.shape[0], self._dim_p), dtype=torch.bfloat16, device=self.device)
+            self._shadow = torch.empty((self._rows.shape[0], kernels.shadow_dim(self._dim_p, self._metric)),
+                                       dtype=torch.bfloat16, device=self.device)
             self._shadow_n = 0
+            self._max_norm = 0.0
         if self._shadow_n < self._n:
             a, b = self._shadow_n, self._n
-            kernels.rows_to_bf16(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b])
+            kernels.rows_to_bf16(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b], metric=self._metric)
+            if self._metric == _lib.L2:                 # the L2 error margin scales with the largest row norm
+                self._max_norm = max(self._max_norm, float(self._norms[a:b].max().item()))
             self._shadow_n = b
 
     def _reserve(self, extra: int):
@@ -335,7 +340,7 @@ class B200Store:
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
         tags = None if single_user else self._tags
         B = queries.shape[0]
-        batched = (self._metric == _lib.COSINE and k <= _lib.BATCHED_MAX_K and
+        batched = (k <= _lib.BATCHED_MAX_K and
                    (self.batched_search == "always" or
                     (self.batched_search == "auto" and (B >= self.min_batch or (B >= 2 and hi - lo >= self.min_rows_small_batch)))))
         if batched:
@@ -346,7 +351,8 @@ class B200Store:
             ids, sc, cnt, cert = kernels.search_batched(self._shadow, self._rows, self._dim_p, self._norms, tags,
                                                         -1 if tags is None else u, queries, k, row_range=(lo, hi),
                                                         margin_sigmas=self.margin_sigmas, id_base=id_base,
-                                                        scratch=self._bscratch, n_rows_total=self._n)
+                                                        scratch=self._bscratch, n_rows_total=self._n,
+                                                        metric=self._metric, max_row_norm=self._max_norm)
             self.last_certified = cert
             return ids, sc, cnt
         gs = 4 if B >= 4 else (2 if B >= 2 else 1)

@@ -10,17 +10,19 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 2_000_000
 B = int(sys.argv[2]) if len(sys.argv) > 2 else 256
 k = int(sys.argv[3]) if len(sys.argv) > 3 else 10
 iters = int(sys.argv[4]) if len(sys.argv) > 4 else 3
+metric = _lib.METRICS[sys.argv[5]] if len(sys.argv) > 5 else _lib.COSINE
 dim = 768
 rows, _ = synth.clustered_rows_device(n, dim, max(1, n // 9766), "cuda")
 qs = synth.queries_near_rows_device(rows, B)
 norms = K.row_norms(rows)
-shadow = K.rows_to_bf16(rows, dim, norms)
-out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+shadow = K.rows_to_bf16(rows, dim, norms, metric=metric)
+mx = float(norms.max())
+out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k, metric=metric, max_row_norm=mx)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(iters):
-    out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+    out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k, metric=metric, max_row_norm=mx)
 e1.record()
 torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / iters

@@ -85,3 +85,39 @@ def test_batched_cfg2_size_against_exact_scan():
     torch.cuda.synchronize()
     assert torch.equal(ids, eids) and torch.equal(sc, esc) and torch.equal(cnt, ecnt)
     assert cert.float().mean().item() > 0.9
+
+
+@pytest.mark.parametrize("n,dim,B,k", [(20000, 384, 130, 10), (33333, 768, 64, 10), (4096, 128, 128, 100), (3000, 72, 9, 3)])
+def test_batched_l2_matches_exact_scan_and_oracle(n, dim, B, k):
+    """LanceDB's default metric on the tensor cores: the L2 ranking comes out of the same contraction
+    (x.q - |x|^2/2 with the norm term carried as three extra bf16 columns)."""
+    from lazzaro_b200 import synth, _lib, kernels as K
+    rows_np, _ = synth.clustered_rows(n, dim, 8, seed=n + 1)
+    rows_np *= np.random.default_rng(n).uniform(0.5, 2.0, size=(n, 1)).astype(np.float32)   # un-normalised rows
+    qs_np = synth.queries_near_rows(rows_np, B, seed=B + 1) * np.float32(1.3)
+    rows, qs = torch.as_tensor(rows_np).cuda(), torch.as_tensor(qs_np).cuda()
+    norms = K.row_norms(rows)
+    shadow = K.rows_to_bf16(rows, dim, norms, metric=_lib.L2)
+    assert shadow.shape[1] == dim + 8
+    ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k, metric=_lib.L2)
+    eids, esc, ecnt = K.search_exact(rows, dim, norms, None, qs, k, _lib.L2)
+    torch.cuda.synchronize()
+    assert torch.equal(ids, eids) and torch.equal(cnt, ecnt) and torch.equal(sc, esc)
+    want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np[:8], k, "l2")
+    np.testing.assert_array_equal(ids[:8].cpu().numpy(), want_ids)
+    np.testing.assert_allclose(sc[:8].cpu().numpy(), want_sc, rtol=1e-12)
+    assert cert.float().mean().item() > 0.5
+
+
+def test_store_l2_batched_equals_single_queries():
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    rows_np, _ = synth.clustered_rows(12000, 96, 6, seed=3)
+    rows_np *= np.linspace(0.5, 1.5, 12000, dtype=np.float32)[:, None]
+    qs_np = synth.queries_near_rows(rows_np, 40, seed=4)
+    st = B200Store(metric="l2")
+    st.add_rows(rows_np, id_prefix="n")
+    got = st.search_batch(qs_np, limit=7)
+    assert st.last_certified is not None                                    # went through the tensor-core path
+    st.batched_search = "never"
+    assert got == [st.search_nodes(q.tolist(), limit=7) for q in qs_np]

@@ -50,11 +50,11 @@ def test_random_configurations(seed):
         np.testing.assert_allclose(sc.cpu().numpy()[ok], want_sc[ok], rtol=1e-12, atol=1e-14)
         assert cnt.cpu().numpy().tolist() == ok.sum(1).tolist()
     if kk <= 128:
-        shadow = K.rows_to_bf16(rows, dim, norms)
-        want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np, kk, "cosine", mask)
-        ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, tags, want_tag, qs, kk, row_range=(lo, hi))
-        ids_np, ok = ids.cpu().numpy(), want_ids >= 0
-        # rows tied at a coarse/exact score of exactly 0 (zero rows, zero queries) are legitimately
-        # interchangeable only by id, which both sides break the same way
-        np.testing.assert_array_equal(ids_np, want_ids)
-        np.testing.assert_allclose(sc.cpu().numpy()[ok], want_sc[ok], rtol=1e-12, atol=1e-14)
+        for metric in ("cosine", "l2"):
+            shadow = K.rows_to_bf16(rows, dim, norms, metric=_lib.METRICS[metric])
+            want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np, kk, metric, mask)
+            ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, tags, want_tag, qs, kk, row_range=(lo, hi),
+                                                  metric=_lib.METRICS[metric])
+            ids_np, ok = ids.cpu().numpy(), want_ids >= 0
+            np.testing.assert_array_equal(ids_np, want_ids)
+            np.testing.assert_allclose(sc.cpu().numpy()[ok], want_sc[ok], rtol=1e-12, atol=1e-14)
