@@ -87,6 +87,23 @@ def cfg4():
                  frac_tensor=2.0 * B * n * dim / ms / 1e9 / PEAKS["bf16_tflops"], certified=float(st.last_certified.float().mean()))
 
 
+def cfg4_two_level():
+    # approximate two-level search at batch 1: centroid routing, then only the nprobe best shards are scanned
+    n, dim, S = 10_000_000, 768, 1024
+    rows, shard = synth.clustered_rows_device(n, dim, S, "cuda")
+    st = B200Store(); st.adopt_rows(rows, id_prefix="node_")
+    st.set_shards(np.searchsorted(shard.cpu().numpy(), np.arange(S + 1)))
+    q = synth.queries_near_rows_device(rows, 64).cpu().numpy()
+    flat = st.search_batch(q, limit=10)
+    for nprobe in (1, 8, 32):
+        got = [st.search_two_level(q[i:i + 1], limit=10, nprobe=nprobe)[0] for i in range(64)]
+        recall = float(np.mean([len(set(a) & set(b)) / 10 for a, b in zip(got, flat)]))
+        ms, _ = timed(lambda: st.search_two_level(q[:1], limit=10, nprobe=nprobe), 20)
+        emit(f"cfg4 two-level batch 1, nprobe={nprobe} of {S} shards (host in/out)", ms, qps=1e3 / ms, recall_at_10=recall)
+    ms, _ = timed(lambda: st.search_nodes(q[0].tolist(), limit=10), 10)
+    emit("cfg4 flat batch 1 via search_nodes (host in/out)", ms, qps=1e3 / ms)
+
+
 def cfg5():
     # one GPU's share of 100k users x 1k memories under weak scaling over 8 GPUs: 12 500 users, D = 768
     users, per, dim = 12_500, 1000, 768
