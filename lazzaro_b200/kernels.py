@@ -162,7 +162,7 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
                    tags: Optional[torch.Tensor], want_tag: int, queries: torch.Tensor, k: int,
                    row_range: Optional[Tuple[int, int]] = None, margin_sigmas: float = 4.0, id_base: int = 0,
                    scratch: Optional[torch.Tensor] = None, n_rows_total: Optional[int] = None,
-                   metric: int = _lib.COSINE, max_row_norm: Optional[float] = None):
+                   metric: int = _lib.COSINE, max_row_norm: Optional[float] = None, out=None):
     """Batched exact cosine top-k on the tensor cores (lz_search_batched).
     Returns (ids int64 [B,k], scores float64 [B,k], counts int32 [B], certified int32 [B])."""
     dev = _dev(rows)
@@ -178,9 +178,10 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
         need = int(lib.lz_search_batched_scratch_bytes(hi - lo, B, k, dim))
         if scratch is None or scratch.numel() < need:
             scratch = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
-        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
-        scores = torch.empty((B, k), dtype=torch.float64, device=dev)
-        counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        if out is None:
+            out = (torch.empty((B, k), dtype=torch.int64, device=dev), torch.empty((B, k), dtype=torch.float64, device=dev),
+                   torch.empty((B,), dtype=torch.int32, device=dev))
+        ids, scores, counts = out
         cert = torch.empty((B,), dtype=torch.int32, device=dev)
         check(lib.lz_search_batched(ptr(shadow), ptr(rows), rows.stride(0), dim, ptr(norms), ptr(tags), int(want_tag),
                                     int(n_total), int(lo), int(hi), ptr(queries), queries.stride(0), B, k,

@@ -63,6 +63,10 @@ class B200Store:
         self._edges: List[Dict[str, Any]] = []
         self._profiles: Dict[str, Dict[str, Any]] = {}
         self._pin: Dict[str, torch.Tensor] = {}
+        self._io: Dict[tuple, tuple] = {}
+        self._graphs: Dict[tuple, object] = {}
+        self._gtags: Dict[tuple, torch.Tensor] = {}
+        self.use_graphs = True                 # CUDA-graph replay of the (launch-bound) exact path for host calls
         self._scratch: Optional[torch.Tensor] = None
         if batched_search not in ("auto", "never", "always"):
             raise ValueError("batched_search must be 'auto', 'never' or 'always'")
@@ -304,32 +308,70 @@ class B200Store:
             raise ValueError(f"limit={limit} exceeds the kernel's top-k bound of {_lib.MAX_K}")
         return max(k, 1)
 
+    def _io_buffers(self, B: int, k: int):
+        """Per-(B, k) reusable staging: pinned + device query buffers and ONE packed result buffer
+        (ids int64 | scores float64 | counts int32) on each side, so a search is one H2D copy, the kernel
+        launches and one D2H copy.  At the reference's own scale (10k rows) the call overhead is the cost."""
+        key = (B, k, self._dim_p)
+        io = self._io.get(key)
+        if io is None:
+            if len(self._io) > 32:
+                self._io.clear()
+            nb = B * k * 16 + B * 4
+            q_pin = torch.zeros((B, self._dim_p), dtype=torch.float32).pin_memory()
+            q_dev = torch.zeros((B, self._dim_p), dtype=torch.float32, device=self.device)
+            o_dev = torch.empty(nb, dtype=torch.uint8, device=self.device)
+            o_pin = torch.empty(nb, dtype=torch.uint8).pin_memory()
+
+            def views(t):
+                return (t[:B * k * 8].view(torch.int64).view(B, k), t[B * k * 8:B * k * 16].view(torch.float64).view(B, k),
+                        t[B * k * 16:].view(torch.int32))
+            io = self._io[key] = (q_pin, q_dev, o_dev, o_pin, views(o_dev), tuple(v.numpy() for v in views(o_pin)))
+        return io
+
     def _search_host(self, q: np.ndarray, u: int, limit: int):
-        """host queries [B, dim] -> (row ids int64 [B,k], scores float64 [B,k], counts int32 [B]) as
-        numpy, via pinned staging; one stream synchronisation at the end."""
+        """host queries [B, dim] -> (row ids int64 [B,k], scores float64 [B,k], counts int32 [B]) as numpy
+        views of a pinned buffer (valid until the next search), one stream synchronisation at the end."""
         if q.shape[1] != self.dim:
             raise ValueError(f"query has {q.shape[1]} dims, store has {self.dim}")
         k = self._check_limit(limit, u)
         B = q.shape[0]
+        q_pin, q_dev, o_dev, o_pin, dev_views, host_views = self._io_buffers(B, k)
         with torch.cuda.device(self.device):
-            stage = self._pinned("q", (B, self._dim_p), torch.float32)
-            if self._dim_p != self.dim:
-                stage.zero_()
-            stage[:, :self.dim] = torch.from_numpy(q)
-            qd = torch.empty((B, self._dim_p), dtype=torch.float32, device=self.device)
-            qd.copy_(stage, non_blocking=True)
-            ids, scores, counts = self.search_device(qd, u, k)
-            h_ids = self._pinned("ids", (B, k), torch.int64)
-            h_sc = self._pinned("sc", (B, k), torch.float64)
-            h_cnt = self._pinned("cnt", (B,), torch.int32)
-            h_ids.copy_(ids, non_blocking=True)
-            h_sc.copy_(scores, non_blocking=True)
-            h_cnt.copy_(counts, non_blocking=True)
+            q_pin[:, :self.dim] = torch.from_numpy(q)
+            lo, hi = self._span[u]
+            if self.use_graphs and not self._takes_batched_path(B, k, hi - lo):
+                # the exact path is launch-bound on small stores (the reference's own scale): replay the
+                # H2D copy, scan, merge and D2H copy as one CUDA graph, re-captured when the layout changes
+                key = (B, k, u, lo, hi, self._rows.data_ptr(), len(self._user_names) == 1 and self._live[u] == self._n)
+                graph = self._graphs.get(key)
+                if graph is None:
+                    if len(self._graphs) > 64:
+                        self._graphs.clear()
+                    torch.cuda.current_stream().synchronize()
+                    self.search_device(q_dev, u, k, out=dev_views)          # warm-up outside capture (sizes scratch)
+                    torch.cuda.current_stream().synchronize()
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph):
+                        q_dev.copy_(q_pin, non_blocking=True)
+                        self.search_device(q_dev, u, k, out=dev_views)
+                        o_pin.copy_(o_dev, non_blocking=True)
+                    self._graphs[key] = graph
+                graph.replay()
+            else:
+                q_dev.copy_(q_pin, non_blocking=True)
+                self.search_device(q_dev, u, k, out=dev_views)
+                o_pin.copy_(o_dev, non_blocking=True)
             torch.cuda.current_stream().synchronize()
-        return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()
+        return host_views
+
+    def _takes_batched_path(self, B: int, k: int, span: int) -> bool:
+        return (k <= _lib.BATCHED_MAX_K and
+                (self.batched_search == "always" or
+                 (self.batched_search == "auto" and (B >= self.min_batch or (B >= 2 and span >= self.min_rows_small_batch)))))
 
     def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0,
-                      row_range=None):
+                      row_range=None, out=None):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
         tensors, nothing synchronised.  The exact fp64 scan over the user's row span."""
         u = self._user(user) if isinstance(user, str) else user
@@ -340,9 +382,7 @@ class B200Store:
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
         tags = None if single_user else self._tags
         B = queries.shape[0]
-        batched = (k <= _lib.BATCHED_MAX_K and
-                   (self.batched_search == "always" or
-                    (self.batched_search == "auto" and (B >= self.min_batch or (B >= 2 and hi - lo >= self.min_rows_small_batch)))))
+        batched = self._takes_batched_path(B, k, hi - lo)
         if batched:
             self._ensure_shadow()
             need = int(_lib.load().lz_search_batched_scratch_bytes(hi - lo, B, k, self._dim_p))
@@ -352,19 +392,23 @@ class B200Store:
                                                         -1 if tags is None else u, queries, k, row_range=(lo, hi),
                                                         margin_sigmas=self.margin_sigmas, id_base=id_base,
                                                         scratch=self._bscratch, n_rows_total=self._n,
-                                                        metric=self._metric, max_row_norm=self._max_norm)
+                                                        metric=self._metric, max_row_norm=self._max_norm, out=out)
             self.last_certified = cert
             return ids, sc, cnt
         gs = 4 if B >= 4 else (2 if B >= 2 else 1)
         n_groups = (B + gs - 1) // gs
-        gtag = None if tags is None else torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
+        gtag = None
+        if tags is not None:
+            gtag = self._gtags.get((n_groups, u))
+            if gtag is None:
+                gtag = self._gtags[(n_groups, u)] = torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
         n_chunks = kernels.default_chunks(hi - lo, n_groups, self.device)
         need = int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks))
         if self._scratch is None or self._scratch.numel() < need:
             self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
         return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, self._metric,
                                     row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
-                                    scratch=self._scratch, id_base=id_base)
+                                    scratch=self._scratch, id_base=id_base, out=out)
 
     # ------------------------------------------------------------------ multi-tenant and two-level search
     def search_users(self, queries, user_ids: Sequence[str], limit: int = 5):
@@ -575,6 +619,8 @@ class B200Store:
         with self._lock:
             self._rows = self._norms = self._tags = self._scratch = self._shadow = self._bscratch = None
             self._pin.clear()
+            self._io.clear()
+            self._graphs.clear()
             self._n = 0
 
     # ------------------------------------------------------------------ legacy surface
