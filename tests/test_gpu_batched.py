@@ -121,3 +121,31 @@ def test_store_l2_batched_equals_single_queries():
     assert st.last_certified is not None                                    # went through the tensor-core path
     st.batched_search = "never"
     assert got == [st.search_nodes(q.tolist(), limit=7) for q in qs_np]
+
+
+def test_cfg4_size_10m_rows_properties():
+    """BASELINE configs[3] on one GPU: 10M x 768, batch 1024, top-100 and top-10 — size-independent properties:
+    planted rows are their own best match, results are sorted, every query certifies, the tensor-core
+    answer equals the exact float64 scan on a query subset bit for bit, and a sharded search (two halves
+    merged on the device) equals the whole."""
+    from lazzaro_b200 import synth, kernels as K, _lib
+    n, dim, B = 10_000_000, 768, 1024
+    rows, _ = synth.clustered_rows_device(n, dim, 1024, "cuda")
+    qs = synth.queries_near_rows_device(rows, B)
+    pick = torch.tensor([0, 123_456, 5_000_000, n - 1], device="cuda")
+    qs[:4] = rows[pick]
+    norms = K.row_norms(rows)
+    shadow = K.rows_to_bf16(rows, dim, norms)
+    for k in (100, 10):
+        ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
+        torch.cuda.synchronize()
+        assert ids[:4, 0].tolist() == pick.tolist()
+        assert (cnt == k).all() and (sc[:, 1:] <= sc[:, :-1]).all()
+        assert cert.float().mean().item() == 1.0
+        sub = qs[:8].contiguous()
+        eids, esc, _ = K.search_exact(rows, dim, norms, None, sub, k, _lib.COSINE)
+        assert torch.equal(ids[:8], eids) and torch.equal(sc[:8], esc)
+    half = n // 2
+    parts = [K.search_batched(shadow, rows, dim, norms, None, -1, qs, 10, row_range=r)[:2] for r in ((0, half), (half, n))]
+    mids, msc, _ = K.merge_topk(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]), _lib.COSINE)
+    assert torch.equal(mids, ids) and torch.equal(msc, sc)
