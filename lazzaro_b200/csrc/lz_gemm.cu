@@ -650,13 +650,10 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
 // largest threshold any slice dropped under.  Nothing is discarded here, so T is just that maximum.
 constexpr int kSmallK = 3;
 
-__global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(SelectParams p, int n_queries) {
-    const int lane = threadIdx.x & 31;
-    const int q = blockIdx.x * (kSelThreads / 32) + (threadIdx.x >> 5);
-    if (q >= n_queries) return;
+// pass 1: c_k = k-th largest group key among groups wholly inside the range (k rounds of warp max); returns the
+// rescoring cutoff c_k - 2 eps and the largest threshold any slice dropped candidates under (T).
+__device__ __forceinline__ float small_cutoff(const SelectParams& p, int q, int lane, float eps, float* T_out) {
     const int qt = q / BM, ql = q % BM;
-    const float eps = (float)p.eps[q];
-    // pass 1: c_k = k-th largest group key among groups wholly inside the range (k rounds of warp max)
     float T = -INFINITY;
     u64 below = ~0ull;                     // keys must be < below to be picked in this round
     float ck = -INFINITY;
@@ -683,7 +680,14 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
         below = best;
         ck = unord32((u32)(best >> 32));
     }
-    const float cutoff = (have_k && p.tags == nullptr) ? ck - 2.0f * eps : -INFINITY;
+    *T_out = T;
+    return (have_k && p.tags == nullptr) ? ck - 2.0f * eps : -INFINITY;
+}
+
+// pass 2, one warp: rescore the rows of every group at or above the cutoff straight from global memory; lane 0
+// keeps the best k, writes the result and certifies it.
+__device__ __forceinline__ void small_rescore_direct(const SelectParams& p, int q, int lane, float eps, float T, float cutoff) {
+    const int qt = q / BM, ql = q % BM;
     // pass 2: rescore the rows of every group at or above the cutoff; lane 0 keeps the best k
     const float* qv = p.queries + (int64_t)q * p.q_ld;
     double qs = 0.0;
@@ -704,55 +708,77 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
         const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
         const int cnt = p.cand_cnt[slot];
         const u64* src = p.cand + slot * p.cap;
-        for (int j = 0; j < cnt; ++j) {
-            const u64 kk = src[j];                                          // warp-uniform
-            if (unord32((u32)(kk >> 32)) < cutoff) continue;
-            const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
-            for (int r = 0; r < kSub; ++r) {
-                const int64_t row = r0 + r;
-                bool ok = row < p.row_hi;
-                if (ok && p.tags) {
-                    const int tg = p.tags[row];
-                    ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
-                }
-                if (!ok) continue;
-                const float* x = p.rows + row * p.ld;
-                double acc = 0.0;
-                for (int e = lane * 4; e < p.dim; e += 128) {
-                    const float4 xv = lz_ldg_stream(x + e);
-                    const float4 qq = *reinterpret_cast<const float4*>(qv + e);
-                    if (p.metric == LZ_COSINE) {
-                        acc = fma((double)xv.x, (double)qq.x, acc);
-                        acc = fma((double)xv.y, (double)qq.y, acc);
-                        acc = fma((double)xv.z, (double)qq.z, acc);
-                        acc = fma((double)xv.w, (double)qq.w, acc);
-                    } else {
-                        const double d0 = (double)xv.x - (double)qq.x, d1 = (double)xv.y - (double)qq.y;
-                        const double d2 = (double)xv.z - (double)qq.z, d3 = (double)xv.w - (double)qq.w;
-                        acc = fma(d0, d0, acc);
-                        acc = fma(d1, d1, acc);
-                        acc = fma(d2, d2, acc);
-                        acc = fma(d3, d3, acc);
-                    }
-                }
-                acc = lz_warp_sum(acc);
-                double s;
-                if (p.metric == LZ_COSINE) {
-                    const double den = p.norms[row] * qn;
-                    s = den > 0.0 ? acc / den : 0.0;
-                    s += 0.0;
-                } else {
-                    s = 0.0 - acc;
-                }
-                if (s != s) continue;
-                u64 key = lz_ord(s);
-                u32 id = (u32)row;
-                ++found;
+        // 32 entries are fetched at once (one per lane); the few at or above the cutoff are then walked by
+        // ballot — a lane-uniform loop over all entries would be one dependent L2 round trip per entry
+        for (int jb = 0; jb < cnt; jb += 32) {
+            const u64 mine = jb + lane < cnt ? src[jb + lane] : 0ull;
+            unsigned live = __ballot_sync(0xffffffffu, jb + lane < cnt && unord32((u32)(mine >> 32)) >= cutoff);
+            while (live) {
+                const int b = __ffs(live) - 1;
+                live &= live - 1;
+                const u64 kk = __shfl_sync(0xffffffffu, mine, b);
+                const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
+                // the group's rows four at a time: 4 x dim/128 independent 16-byte loads per lane in flight
+                for (int rb = 0; rb < kSub; rb += 4) {
+                    int64_t row[4];
+                    double acc[4];
 #pragma unroll
-                for (int i = 0; i < kSmallK; ++i) {                         // insertion into the sorted best-k
-                    if (i < p.k && lz_better(key, id, bk[i], bi[i])) {
-                        const u64 tk = bk[i]; const u32 ti = bi[i];
-                        bk[i] = key; bi[i] = id; key = tk; id = ti;
+                    for (int h = 0; h < 4; ++h) {
+                        row[h] = r0 + rb + h;
+                        bool ok = rb + h < kSub && row[h] < p.row_hi;
+                        if (ok && p.tags) {
+                            const int tg = p.tags[row[h]];
+                            ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
+                        }
+                        if (!ok) row[h] = -1;
+                        acc[h] = 0.0;
+                    }
+                    for (int e = lane * 4; e < p.dim; e += 128) {
+                        const float4 qq = *reinterpret_cast<const float4*>(qv + e);
+                        float4 xv[4];
+#pragma unroll
+                        for (int h = 0; h < 4; ++h)
+                            xv[h] = row[h] >= 0 ? lz_ldg_stream(p.rows + row[h] * p.ld + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                        for (int h = 0; h < 4; ++h) {
+                            if (p.metric == LZ_COSINE) {
+                                acc[h] = fma((double)xv[h].x, (double)qq.x, acc[h]);
+                                acc[h] = fma((double)xv[h].y, (double)qq.y, acc[h]);
+                                acc[h] = fma((double)xv[h].z, (double)qq.z, acc[h]);
+                                acc[h] = fma((double)xv[h].w, (double)qq.w, acc[h]);
+                            } else {
+                                const double d0 = (double)xv[h].x - (double)qq.x, d1 = (double)xv[h].y - (double)qq.y;
+                                const double d2 = (double)xv[h].z - (double)qq.z, d3 = (double)xv[h].w - (double)qq.w;
+                                acc[h] = fma(d0, d0, acc[h]);
+                                acc[h] = fma(d1, d1, acc[h]);
+                                acc[h] = fma(d2, d2, acc[h]);
+                                acc[h] = fma(d3, d3, acc[h]);
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int h = 0; h < 4; ++h) {
+                        const double dot = lz_warp_sum(acc[h]);
+                        if (row[h] < 0) continue;                                  // warp-uniform
+                        double s;
+                        if (p.metric == LZ_COSINE) {
+                            const double den = p.norms[row[h]] * qn;
+                            s = den > 0.0 ? dot / den : 0.0;
+                            s += 0.0;
+                        } else {
+                            s = 0.0 - dot;
+                        }
+                        if (s != s) continue;
+                        u64 key = lz_ord(s);
+                        u32 id = (u32)row[h];
+                        ++found;
+#pragma unroll
+                        for (int i = 0; i < kSmallK; ++i) {                     // insertion into the sorted best-k
+                            if (i < p.k && lz_better(key, id, bk[i], bi[i])) {
+                                const u64 tk = bk[i]; const u32 ti = bi[i];
+                                bk[i] = key; bi[i] = id; key = tk; id = ti;
+                            }
+                        }
                     }
                 }
             }
@@ -776,6 +802,175 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
         }
         p.certified[q] = cert ? 1 : 0;
         if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
+    }
+}
+
+__global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(SelectParams p, int n_queries) {
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * (kSelThreads / 32) + (threadIdx.x >> 5);
+    if (q >= n_queries) return;
+    const float eps = (float)p.eps[q];
+    float T;
+    const float cutoff = small_cutoff(p, q, lane, eps, &T);
+    small_rescore_direct(p, q, lane, eps, T, cutoff);
+}
+
+// Top-1 against a TINY table (shard reassignment: a million rows against ~1000 centroids).  There the
+// per-query rescoring above re-reads kSub centroid rows from L2 for every query — 8x the bytes of the query
+// itself — and the L2 becomes the bound.  Here a CTA takes kBucketQ consecutive queries, finds each one's
+// single surviving group, counting-sorts the queries by group in shared memory, and walks the groups: the
+// group's rows are staged in shared memory once and every query of the bucket is scored against them, two
+// queries per warp and step so each staged float4 feeds two FMAs chains.  Queries with several surviving
+// groups take the direct path.  Summation order is the canonical one, so scores equal the exact scan's.
+constexpr int kBucketQ = 1024;
+constexpr int kBucketGroups = 256;
+
+__global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParams p, int n_queries) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    float* s_rows = reinterpret_cast<float*>(smem);                          // [kSub][dim]
+    __shared__ int s_pick[kBucketQ];                                          // group of query i, or -1
+    __shared__ int s_sorted[kBucketQ];
+    __shared__ float s_T[kBucketQ];
+    __shared__ int s_hist[kBucketGroups], s_off[kBucketGroups + 1], s_cur[kBucketGroups];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kSelThreads / 32;
+    const int q0 = blockIdx.x * kBucketQ;
+    const int nq = min(kBucketQ, n_queries - q0);
+    for (int g = tid; g < kBucketGroups; g += kSelThreads) { s_hist[g] = 0; s_cur[g] = 0; }
+    __syncthreads();
+    // A. cutoff per query, survivors counted; a single survivor is bucketed, anything else scored directly
+    for (int i = warp; i < nq; i += kWarps) {
+        const int q = q0 + i;
+        const float eps = (float)p.eps[q];
+        float T;
+        const float cutoff = small_cutoff(p, q, lane, eps, &T);
+        const size_t slot = ((size_t)(q / BM)) * BM + q % BM;                 // n_slices == 1
+        const int cnt = p.cand_cnt[slot];
+        const u64* src = p.cand + slot * p.cap;
+        int n_live = 0;
+        u32 r_live = 0;
+        for (int jb = 0; jb < cnt; jb += 32) {
+            const u64 mine = jb + lane < cnt ? src[jb + lane] : 0ull;
+            const unsigned live = __ballot_sync(0xffffffffu, jb + lane < cnt && unord32((u32)(mine >> 32)) >= cutoff);
+            if (live) {
+                n_live += __popc(live);
+                r_live = 0xffffffffu - (u32)__shfl_sync(0xffffffffu, mine, __ffs(live) - 1);
+            }
+        }
+        int pick = -1;
+        if (n_live == 1 && (int64_t)r_live + kSub <= p.row_hi) pick = (int)((r_live - (u32)p.row_lo) / kSub);
+        if (pick >= 0 && pick < kBucketGroups) {
+            if (lane == 0) { s_pick[i] = pick; s_T[i] = T; atomicAdd(&s_hist[pick], 1); }
+        } else {
+            if (lane == 0) s_pick[i] = -1;
+            small_rescore_direct(p, q, lane, eps, T, cutoff);
+        }
+    }
+    __syncthreads();
+    // B. counting sort of the bucketed queries by group
+    if (tid == 0) {
+        int run = 0;
+        for (int g = 0; g < kBucketGroups; ++g) { s_off[g] = run; run += s_hist[g]; }
+        s_off[kBucketGroups] = run;
+    }
+    __syncthreads();
+    for (int i = tid; i < nq; i += kSelThreads) {
+        const int g = s_pick[i];
+        if (g >= 0) s_sorted[s_off[g] + atomicAdd(&s_cur[g], 1)] = i;
+    }
+    __syncthreads();
+    // C. group by group
+    const int n4 = p.dim / 4;
+    for (int g = 0; g < kBucketGroups; ++g) {
+        const int lo = s_off[g], hi = s_off[g + 1];
+        if (lo == hi) continue;                                               // CTA-uniform
+        __syncthreads();                                                      // previous group's readers done
+        const int64_t r0 = p.row_lo + (int64_t)g * kSub;
+        for (int i = tid; i < kSub * n4; i += kSelThreads) {
+            const int r = i / n4, e = i - r * n4;
+            reinterpret_cast<float4*>(s_rows)[i] = lz_ldg_stream(p.rows + (r0 + r) * p.ld + e * 4);
+        }
+        __syncthreads();
+        for (int j = lo + 2 * warp; j < hi; j += 2 * kWarps) {
+            const int ia = s_sorted[j];
+            const bool two = j + 1 < hi;
+            const int ib = two ? s_sorted[j + 1] : ia;
+            const float* qa = p.queries + (int64_t)(q0 + ia) * p.q_ld;
+            const float* qb = p.queries + (int64_t)(q0 + ib) * p.q_ld;
+            double acc[2][kSub];
+            double qs[2] = {0.0, 0.0};
+#pragma unroll
+            for (int r = 0; r < kSub; ++r) { acc[0][r] = 0.0; acc[1][r] = 0.0; }
+            for (int e = lane * 4; e < p.dim; e += 128) {
+                const float4 va = lz_ldg_stream(qa + e);
+                const float4 vb = lz_ldg_stream(qb + e);
+                qs[0] = fma((double)va.x, (double)va.x, qs[0]); qs[0] = fma((double)va.y, (double)va.y, qs[0]);
+                qs[0] = fma((double)va.z, (double)va.z, qs[0]); qs[0] = fma((double)va.w, (double)va.w, qs[0]);
+                qs[1] = fma((double)vb.x, (double)vb.x, qs[1]); qs[1] = fma((double)vb.y, (double)vb.y, qs[1]);
+                qs[1] = fma((double)vb.z, (double)vb.z, qs[1]); qs[1] = fma((double)vb.w, (double)vb.w, qs[1]);
+#pragma unroll
+                for (int r = 0; r < kSub; ++r) {
+                    const float4 x = *reinterpret_cast<const float4*>(s_rows + r * p.dim + e);
+                    if (p.metric == LZ_COSINE) {
+                        acc[0][r] = fma((double)x.x, (double)va.x, acc[0][r]); acc[0][r] = fma((double)x.y, (double)va.y, acc[0][r]);
+                        acc[0][r] = fma((double)x.z, (double)va.z, acc[0][r]); acc[0][r] = fma((double)x.w, (double)va.w, acc[0][r]);
+                        acc[1][r] = fma((double)x.x, (double)vb.x, acc[1][r]); acc[1][r] = fma((double)x.y, (double)vb.y, acc[1][r]);
+                        acc[1][r] = fma((double)x.z, (double)vb.z, acc[1][r]); acc[1][r] = fma((double)x.w, (double)vb.w, acc[1][r]);
+                    } else {
+                        double d;
+                        d = (double)x.x - (double)va.x; acc[0][r] = fma(d, d, acc[0][r]);
+                        d = (double)x.y - (double)va.y; acc[0][r] = fma(d, d, acc[0][r]);
+                        d = (double)x.z - (double)va.z; acc[0][r] = fma(d, d, acc[0][r]);
+                        d = (double)x.w - (double)va.w; acc[0][r] = fma(d, d, acc[0][r]);
+                        d = (double)x.x - (double)vb.x; acc[1][r] = fma(d, d, acc[1][r]);
+                        d = (double)x.y - (double)vb.y; acc[1][r] = fma(d, d, acc[1][r]);
+                        d = (double)x.z - (double)vb.z; acc[1][r] = fma(d, d, acc[1][r]);
+                        d = (double)x.w - (double)vb.w; acc[1][r] = fma(d, d, acc[1][r]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const double qn = sqrt(lz_warp_sum(qs[h]));
+                u64 bk = 0ull;
+                u32 bi = 0xffffffffu;
+                int found = 0;
+#pragma unroll
+                for (int r = 0; r < kSub; ++r) {
+                    const double dot = lz_warp_sum(acc[h][r]);
+                    const int64_t row = r0 + r;
+                    double s;
+                    if (p.metric == LZ_COSINE) {
+                        const double den = p.norms[row] * qn;
+                        s = den > 0.0 ? dot / den : 0.0;
+                        s += 0.0;
+                    } else {
+                        s = 0.0 - dot;
+                    }
+                    if (s != s) continue;
+                    ++found;
+                    const u64 key = lz_ord(s);
+                    if (lz_better(key, (u32)row, bk, bi)) { bk = key; bi = (u32)row; }
+                }
+                if (lane == 0 && (h == 0 || two)) {
+                    const int i = h == 0 ? ia : ib;
+                    const int q = q0 + i;
+                    const bool has = found > 0;
+                    const double v = has ? lz_unord(bk) : 0.0;
+                    p.out_ids[q] = has ? (int64_t)bi + p.id_base : -1;
+                    p.out_scores[q] = has ? (p.metric == LZ_COSINE ? v : 0.0 - v) : __longlong_as_double(0x7ff8000000000000ll);
+                    p.out_counts[q] = has ? 1 : 0;
+                    const float T = s_T[i];
+                    bool cert = T == -INFINITY;
+                    if (!cert && has) {
+                        const double e_coarse = p.metric == LZ_COSINE ? v : 0.5 * (v + qn * qn);
+                        cert = e_coarse > (double)T + p.eps[q];
+                    }
+                    p.certified[q] = cert ? 1 : 0;
+                    if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
+                }
+            }
+        }
     }
 }
 
@@ -1062,7 +1257,12 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.id_base = id_base;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
-    if (k <= kSmallK) {
+    const size_t rows_smem = (size_t)kSub * dim * 4;
+    if (k == 1 && tags == nullptr && pl.n_slices == 1 && row_hi - row_lo <= (int64_t)kBucketGroups * kSub &&
+        rows_smem <= 160 * 1024 && n_queries >= 4 * kBucketQ) {
+        LZ_CUDA(cudaFuncSetAttribute(assign_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rows_smem));
+        assign_rescore_kernel<<<(n_queries + kBucketQ - 1) / kBucketQ, kSelThreads, rows_smem, st>>>(sp, n_queries);
+    } else if (k <= kSmallK) {
         select_rescore_small_kernel<<<(n_queries + kSelThreads / 32 - 1) / (kSelThreads / 32), kSelThreads, 0, st>>>(sp, n_queries);
     } else {
         const size_t ssmem = (size_t)(sp.cap_a + sp.cap_b) * 12;

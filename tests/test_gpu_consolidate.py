@@ -81,20 +81,26 @@ def test_centroid_matches_reference(golden):
     np.testing.assert_allclose(got, golden["ce_centroid"], rtol=1e-13, atol=1e-16)
 
 
-@pytest.mark.parametrize("n,dim,K", [(5000, 64, 16), (20000, 384, 200), (7, 16, 3)])
+@pytest.mark.parametrize("n,dim,K", [(5000, 64, 16), (20000, 384, 200), (7, 16, 3), (30011, 128, 1024), (4099, 32, 2048)])
 def test_assign_and_update_match_oracle(n, dim, K):
+    # >= 4096 rows against <= 2048 centroids takes the bucketed top-1 kernel (rows staged per group of 8
+    # centroids); fewer rows, the warp-per-row kernel.  Rows arrive shuffled so every bucket sees many groups.
     from lazzaro_b200 import consolidate, synth
     rows_np, _ = synth.clustered_rows(n, dim, K, seed=n)
+    rows_np = rows_np[np.random.default_rng(n).permutation(n)]
     cen_np, _ = synth.clustered_rows(K, dim, K, seed=n + 1, sigma=2.0)
     cen_np *= np.linspace(0.5, 2.0, K, dtype=np.float32)[:, None]      # un-normalised centroids
     if K > 2:
-        cen_np[2] = cen_np[1]                                           # tie: lowest index wins
+        cen_np[2] = cen_np[1]                                           # tie inside a group: lowest index wins
+    if K > 16:
+        cen_np[13] = cen_np[4]                                          # tie across two groups of 8
     rows, cen = torch.as_tensor(rows_np).cuda(), torch.as_tensor(cen_np).cuda()
     idx, cos = consolidate.assign_to_centroids(rows, cen)
     want_idx, want_cos = graph_ops.assign_to_centroids(rows_np, cen_np)
     np.testing.assert_array_equal(idx.cpu().numpy(), want_idx)
     np.testing.assert_allclose(cos.cpu().numpy(), want_cos, rtol=1e-12)
     assert not (idx == 2).any() or K <= 2
+    assert not (idx == 13).any() or K <= 16
     means = consolidate.centroid_means(rows, assign=idx, n_centroids=K).cpu().numpy()
     np.testing.assert_allclose(means, graph_ops.centroid_means(rows_np, want_idx, K), rtol=1e-12, atol=1e-15)
 
