@@ -151,6 +151,8 @@ struct GemmParams {
     int32_t* cand_cnt;  // [n_items][BM]
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
     u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
+    const double* top1_eps;   // top-1 against a tiny table only (else null): per-query eps; the threshold then
+                              // follows the running best group at a distance of 3 eps (see scan_chunk)
 };
 
 // Warp-cooperative compaction of the candidate buffers of the lanes in `need` (each over kp entries):
@@ -225,7 +227,7 @@ __device__ __forceinline__ void warp_select(unsigned need, u64* my_buf, int& cou
 // coarse score and append the groups that beat the query's threshold.
 template <int EPL>
 __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_first, const GemmParams& p, u64* buf,
-                                           int& count, float& thr, int q, int lane) {
+                                           int& count, float& thr, float slack, int q, int lane) {
     float g[32 / kSub];
 #pragma unroll
     for (int j = 0; j < 32 / kSub; ++j) {
@@ -237,14 +239,35 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     float m = g[0];
 #pragma unroll
     for (int j = 1; j < 32 / kSub; ++j) m = fmaxf(m, g[j]);
+    // top-1 mode (slack = 3 eps, else +inf): only groups within 2 eps of the best group can hold the winner, so
+    // the threshold trails the running best by 3 eps — a handful of candidates per query instead of all of them,
+    // and the final threshold T = c_1 - 3 eps certifies by construction (exact best >= c_1 - eps > T + eps).
+    // Chunks reaching past the range are left out: their rows are not candidates.
+    if (row_first + 32 <= p.row_hi) thr = fmaxf(thr, m - slack);
+    const bool top1 = slack != INFINITY;
     if (m > thr) {
+        if (top1) {
+            // top-1 mode keeps single ROWS (a handful pass): the exact pass then rescores one row, not a group
 #pragma unroll
-        for (int j = 0; j < 32 / kSub; ++j) {
-            const int64_t r0 = row_first + j * kSub;
-            if (g[j] > thr && r0 < p.row_hi) buf[count++] = ((u64)ord32(g[j]) << 32) | (u64)(0xffffffffu - (u32)r0);
+            for (int j = 0; j < 32 / kSub; ++j) {
+                if (g[j] > thr) {
+#pragma unroll
+                    for (int i = 0; i < kSub; ++i) {
+                        const float val = __uint_as_float(v[j * kSub + i]);
+                        const int64_t r = row_first + j * kSub + i;
+                        if (val > thr && r < p.row_hi) buf[count++] = ((u64)ord32(val) << 32) | (u64)(0xffffffffu - (u32)r);
+                    }
+                }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 32 / kSub; ++j) {
+                const int64_t r0 = row_first + j * kSub;
+                if (g[j] > thr && r0 < p.row_hi) buf[count++] = ((u64)ord32(g[j]) << 32) | (u64)(0xffffffffu - (u32)r0);
+            }
         }
     }
-    const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - 32 / kSub);
+    const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - (top1 ? 32 : 32 / kSub));
     if (need) {
         warp_select<EPL>(need, buf, count, thr, p.kp, lane);
         if ((need >> lane) & 1u) atomicMax(p.gthr + q, ord32(thr));
@@ -384,6 +407,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             const bool valid = q < p.n_queries;
             int count = 0;
             float thr = valid ? -INFINITY : INFINITY;
+            const float slack = (p.top1_eps != nullptr && valid) ? fmaxf(3.0f * (float)p.top1_eps[q], 1e-30f) : INFINITY;
             for (int t = t0; t < t1; ++t) {
                 const int64_t row0 = p.row_lo + (int64_t)t * p.tile_mul * BN;
                 if (valid) {
@@ -408,10 +432,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int c = 0; c < BN / 32; c += 2) {
                     tmem_ld_wait();
                     tmem_ld32(tacc + (c + 1) * 32, vb);
-                    scan_chunk<EPL>(va, row0 + c * 32, p, buf, count, thr, q, lane);
+                    scan_chunk<EPL>(va, row0 + c * 32, p, buf, count, thr, slack, q, lane);
                     tmem_ld_wait();
                     if (c + 2 < BN / 32) tmem_ld32(tacc + (c + 2) * 32, va);
-                    scan_chunk<EPL>(vb, row0 + (c + 1) * 32, p, buf, count, thr, q, lane);
+                    scan_chunk<EPL>(vb, row0 + (c + 1) * 32, p, buf, count, thr, slack, q, lane);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -453,6 +477,7 @@ struct SelectParams {
     const int32_t* tags; int want_tag; int64_t row_lo, row_hi;
     const u64* cand; const int32_t* cand_cnt; const float* cand_thr;
     int n_qtiles_pad, n_slices, kp, cap, k, cap_a, cap_b;   // n_qtiles_pad = n_qgroups * cs
+    int sub;                // rows per candidate: kSub, or 1 in the top-1 tiny-table mode (small kernels only)
     int64_t id_base;
     int64_t* out_ids; double* out_scores; int32_t* out_counts; int32_t* certified;
     int32_t* fb_list; int32_t* fb_count;     // queries that failed certification, for the exact fallback
@@ -668,7 +693,7 @@ __device__ __forceinline__ float small_cutoff(const SelectParams& p, int q, int 
             for (int j = lane; j < cnt; j += 32) {
                 const u64 kk = src[j];
                 const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
-                if (kk < below && kk > best && (p.tags != nullptr || r0 + kSub <= p.row_hi)) best = kk;
+                if (kk < below && kk > best && (p.tags != nullptr || r0 + p.sub <= p.row_hi)) best = kk;
             }
         }
 #pragma unroll
@@ -719,13 +744,13 @@ __device__ __forceinline__ void small_rescore_direct(const SelectParams& p, int 
                 const u64 kk = __shfl_sync(0xffffffffu, mine, b);
                 const int64_t r0 = (int64_t)(0xffffffffu - (u32)kk);
                 // the group's rows four at a time: 4 x dim/128 independent 16-byte loads per lane in flight
-                for (int rb = 0; rb < kSub; rb += 4) {
+                for (int rb = 0; rb < p.sub; rb += 4) {
                     int64_t row[4];
                     double acc[4];
 #pragma unroll
                     for (int h = 0; h < 4; ++h) {
                         row[h] = r0 + rb + h;
-                        bool ok = rb + h < kSub && row[h] < p.row_hi;
+                        bool ok = rb + h < p.sub && row[h] < p.row_hi;
                         if (ok && p.tags) {
                             const int tg = p.tags[row[h]];
                             ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
@@ -815,58 +840,70 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_small_kernel(Selec
     small_rescore_direct(p, q, lane, eps, T, cutoff);
 }
 
-// Top-1 against a TINY table (shard reassignment: a million rows against ~1000 centroids).  There the
-// per-query rescoring above re-reads kSub centroid rows from L2 for every query — 8x the bytes of the query
-// itself — and the L2 becomes the bound.  Here a CTA takes kBucketQ consecutive queries, finds each one's
-// single surviving group, counting-sorts the queries by group in shared memory, and walks the groups: the
-// group's rows are staged in shared memory once and every query of the bucket is scored against them, two
-// queries per warp and step so each staged float4 feeds two FMAs chains.  Queries with several surviving
-// groups take the direct path.  Summation order is the canonical one, so scores equal the exact scan's.
+// Top-1 against a TINY table (shard reassignment: a million rows against ~1000 centroids).  The coarse pass
+// runs in its top-1 mode there (single-row candidates within 3 eps of the running best: a handful per
+// query).  Rescoring one warp per query straight from global memory would re-read a centroid row from L2
+// for every query — as many bytes again as the queries themselves — so a CTA takes kBucketQ consecutive
+// queries, finds each one's single surviving row (one thread per query), counting-sorts the queries by the
+// row's group of kSub in shared memory, and walks the groups: the group's rows are staged in shared memory
+// once and each query is scored against its row in float64, canonical summation order (scores equal the
+// exact scan's bit for bit).  Queries with several surviving rows take the direct path.
+__device__ __noinline__ void small_direct_call(const SelectParams& p, int q, int lane) {
+    const float eps = (float)p.eps[q];
+    float T;
+    const float cutoff = small_cutoff(p, q, lane, eps, &T);
+    small_rescore_direct(p, q, lane, eps, T, cutoff);
+}
+
 constexpr int kBucketQ = 1024;
 constexpr int kBucketGroups = 256;
 
 __global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParams p, int n_queries) {
     extern __shared__ __align__(16) unsigned char smem[];
     float* s_rows = reinterpret_cast<float*>(smem);                          // [kSub][dim]
-    __shared__ int s_pick[kBucketQ];                                          // group of query i, or -1
+    __shared__ int s_pick[kBucketQ];                                          // surviving row - row_lo, or -2
     __shared__ int s_sorted[kBucketQ];
     __shared__ float s_T[kBucketQ];
     __shared__ int s_hist[kBucketGroups], s_off[kBucketGroups + 1], s_cur[kBucketGroups];
+    __shared__ double s_norm[kSub];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kSelThreads / 32;
     const int q0 = blockIdx.x * kBucketQ;
     const int nq = min(kBucketQ, n_queries - q0);
     for (int g = tid; g < kBucketGroups; g += kSelThreads) { s_hist[g] = 0; s_cur[g] = 0; }
     __syncthreads();
-    // A. cutoff per query, survivors counted; a single survivor is bucketed, anything else scored directly
-    for (int i = warp; i < nq; i += kWarps) {
-        const int q = q0 + i;
-        const float eps = (float)p.eps[q];
-        float T;
-        const float cutoff = small_cutoff(p, q, lane, eps, &T);
-        const size_t slot = ((size_t)(q / BM)) * BM + q % BM;                 // n_slices == 1
-        const int cnt = p.cand_cnt[slot];
-        const u64* src = p.cand + slot * p.cap;
-        int n_live = 0;
-        u32 r_live = 0;
-        for (int jb = 0; jb < cnt; jb += 32) {
-            const u64 mine = jb + lane < cnt ? src[jb + lane] : 0ull;
-            const unsigned live = __ballot_sync(0xffffffffu, jb + lane < cnt && unord32((u32)(mine >> 32)) >= cutoff);
-            if (live) {
-                n_live += __popc(live);
-                r_live = 0xffffffffu - (u32)__shfl_sync(0xffffffffu, mine, __ffs(live) - 1);
-            }
+    // A. one THREAD per query: best candidate row, cutoff = its key - 2 eps, survivors counted.  A single
+    // survivor is bucketed; anything else is scored by a warp straight from global memory afterwards.
+    for (int i = tid; i < nq; i += kSelThreads) {
+        const int q = q0 + i;                                                 // n_slices == 1: slot == query
+        const int cnt = p.cand_cnt[q];
+        const u64* src = p.cand + (size_t)q * p.cap;
+        u64 best = 0ull;
+        for (int j = 0; j < cnt; ++j) {
+            const u64 kk = src[j];
+            best = kk > best ? kk : best;
         }
-        int pick = -1;
-        if (n_live == 1 && (int64_t)r_live + kSub <= p.row_hi) pick = (int)((r_live - (u32)p.row_lo) / kSub);
-        if (pick >= 0 && pick < kBucketGroups) {
-            if (lane == 0) { s_pick[i] = pick; s_T[i] = T; atomicAdd(&s_hist[pick], 1); }
-        } else {
-            if (lane == 0) s_pick[i] = -1;
-            small_rescore_direct(p, q, lane, eps, T, cutoff);
+        int pick = -2;
+        if (best != 0ull) {
+            const float cutoff = unord32((u32)(best >> 32)) - 2.0f * (float)p.eps[q];
+            int n_live = 0;
+            for (int j = 0; j < cnt; ++j) n_live += unord32((u32)(src[j] >> 32)) >= cutoff;
+            const int rel = (int)((0xffffffffu - (u32)best) - (u32)p.row_lo);
+            if (n_live == 1 && rel < kBucketGroups * kSub) pick = rel;
         }
+        s_pick[i] = pick;
+        s_T[i] = p.cand_thr[q];
+        // neighbouring rows mostly share a group: one shared-memory atomic per distinct group and warp
+        const int g = pick >= 0 ? pick / kSub : -1;
+        const unsigned act = __activemask();
+        const unsigned same = __match_any_sync(act, g);
+        if (g >= 0 && lane == __ffs(same) - 1) atomicAdd(&s_hist[g], __popc(same));
     }
     __syncthreads();
+    for (int i = warp; i < nq; i += kWarps) {
+        if (s_pick[i] != -2) continue;                                        // warp-uniform
+        small_direct_call(p, q0 + i, lane);                                   // rare: kept out of line
+    }
     // B. counting sort of the bucketed queries by group
     if (tid == 0) {
         int run = 0;
@@ -875,8 +912,14 @@ __global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParam
     }
     __syncthreads();
     for (int i = tid; i < nq; i += kSelThreads) {
-        const int g = s_pick[i];
-        if (g >= 0) s_sorted[s_off[g] + atomicAdd(&s_cur[g], 1)] = i;
+        const int g = s_pick[i] >= 0 ? s_pick[i] / kSub : -1;
+        const unsigned act = __activemask();
+        const unsigned same = __match_any_sync(act, g);
+        const int leader = __ffs(same) - 1;
+        int base = 0;
+        if (g >= 0 && lane == leader) base = atomicAdd(&s_cur[g], __popc(same));
+        base = __shfl_sync(act, base, leader);
+        if (g >= 0) s_sorted[s_off[g] + base + __popc(same & ((1u << lane) - 1u))] = i;
     }
     __syncthreads();
     // C. group by group
@@ -886,89 +929,78 @@ __global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParam
         if (lo == hi) continue;                                               // CTA-uniform
         __syncthreads();                                                      // previous group's readers done
         const int64_t r0 = p.row_lo + (int64_t)g * kSub;
-        for (int i = tid; i < kSub * n4; i += kSelThreads) {
+        const int n_in = (int)min((int64_t)kSub, p.row_hi - r0);
+        for (int i = tid; i < n_in * n4; i += kSelThreads) {
             const int r = i / n4, e = i - r * n4;
             reinterpret_cast<float4*>(s_rows)[i] = lz_ldg_stream(p.rows + (r0 + r) * p.ld + e * 4);
         }
+        if (tid < n_in) s_norm[tid] = p.norms[r0 + tid];
         __syncthreads();
+        // two queries per warp and step: both queries' loads are in flight together
         for (int j = lo + 2 * warp; j < hi; j += 2 * kWarps) {
-            const int ia = s_sorted[j];
             const bool two = j + 1 < hi;
-            const int ib = two ? s_sorted[j + 1] : ia;
-            const float* qa = p.queries + (int64_t)(q0 + ia) * p.q_ld;
-            const float* qb = p.queries + (int64_t)(q0 + ib) * p.q_ld;
-            double acc[2][kSub];
-            double qs[2] = {0.0, 0.0};
+            const int iq[2] = {s_sorted[j], two ? s_sorted[j + 1] : s_sorted[j]};
+            const float* qp[2] = {p.queries + (int64_t)(q0 + iq[0]) * p.q_ld, p.queries + (int64_t)(q0 + iq[1]) * p.q_ld};
+            const int rr[2] = {s_pick[iq[0]] - g * kSub, s_pick[iq[1]] - g * kSub};
+            double dot[2] = {0.0, 0.0}, qs[2] = {0.0, 0.0};
+            constexpr int kSeg = 6;                      // segments of 128 floats fetched per round trip
+            for (int e0 = lane * 4; e0 < p.dim; e0 += 128 * kSeg) {
+                float4 qv[2][kSeg];
 #pragma unroll
-            for (int r = 0; r < kSub; ++r) { acc[0][r] = 0.0; acc[1][r] = 0.0; }
-            for (int e = lane * 4; e < p.dim; e += 128) {
-                const float4 va = lz_ldg_stream(qa + e);
-                const float4 vb = lz_ldg_stream(qb + e);
-                qs[0] = fma((double)va.x, (double)va.x, qs[0]); qs[0] = fma((double)va.y, (double)va.y, qs[0]);
-                qs[0] = fma((double)va.z, (double)va.z, qs[0]); qs[0] = fma((double)va.w, (double)va.w, qs[0]);
-                qs[1] = fma((double)vb.x, (double)vb.x, qs[1]); qs[1] = fma((double)vb.y, (double)vb.y, qs[1]);
-                qs[1] = fma((double)vb.z, (double)vb.z, qs[1]); qs[1] = fma((double)vb.w, (double)vb.w, qs[1]);
+                for (int sg = 0; sg < kSeg; ++sg) {
+                    const int e = e0 + 128 * sg;
 #pragma unroll
-                for (int r = 0; r < kSub; ++r) {
-                    const float4 x = *reinterpret_cast<const float4*>(s_rows + r * p.dim + e);
-                    if (p.metric == LZ_COSINE) {
-                        acc[0][r] = fma((double)x.x, (double)va.x, acc[0][r]); acc[0][r] = fma((double)x.y, (double)va.y, acc[0][r]);
-                        acc[0][r] = fma((double)x.z, (double)va.z, acc[0][r]); acc[0][r] = fma((double)x.w, (double)va.w, acc[0][r]);
-                        acc[1][r] = fma((double)x.x, (double)vb.x, acc[1][r]); acc[1][r] = fma((double)x.y, (double)vb.y, acc[1][r]);
-                        acc[1][r] = fma((double)x.z, (double)vb.z, acc[1][r]); acc[1][r] = fma((double)x.w, (double)vb.w, acc[1][r]);
-                    } else {
-                        double d;
-                        d = (double)x.x - (double)va.x; acc[0][r] = fma(d, d, acc[0][r]);
-                        d = (double)x.y - (double)va.y; acc[0][r] = fma(d, d, acc[0][r]);
-                        d = (double)x.z - (double)va.z; acc[0][r] = fma(d, d, acc[0][r]);
-                        d = (double)x.w - (double)va.w; acc[0][r] = fma(d, d, acc[0][r]);
-                        d = (double)x.x - (double)vb.x; acc[1][r] = fma(d, d, acc[1][r]);
-                        d = (double)x.y - (double)vb.y; acc[1][r] = fma(d, d, acc[1][r]);
-                        d = (double)x.z - (double)vb.z; acc[1][r] = fma(d, d, acc[1][r]);
-                        d = (double)x.w - (double)vb.w; acc[1][r] = fma(d, d, acc[1][r]);
+                    for (int h = 0; h < 2; ++h)
+                        qv[h][sg] = e < p.dim ? lz_ldg_stream(qp[h] + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int sg = 0; sg < kSeg; ++sg) {
+                    const int e = e0 + 128 * sg;
+                    if (e >= p.dim) break;
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const float4 x = *reinterpret_cast<const float4*>(s_rows + rr[h] * p.dim + e);
+                        const double q0d = qv[h][sg].x, q1d = qv[h][sg].y, q2d = qv[h][sg].z, q3d = qv[h][sg].w;
+                        qs[h] = fma(q0d, q0d, qs[h]); qs[h] = fma(q1d, q1d, qs[h]);
+                        qs[h] = fma(q2d, q2d, qs[h]); qs[h] = fma(q3d, q3d, qs[h]);
+                        if (p.metric == LZ_COSINE) {
+                            dot[h] = fma((double)x.x, q0d, dot[h]); dot[h] = fma((double)x.y, q1d, dot[h]);
+                            dot[h] = fma((double)x.z, q2d, dot[h]); dot[h] = fma((double)x.w, q3d, dot[h]);
+                        } else {
+                            const double d0 = (double)x.x - q0d, d1 = (double)x.y - q1d;
+                            const double d2 = (double)x.z - q2d, d3 = (double)x.w - q3d;
+                            dot[h] = fma(d0, d0, dot[h]); dot[h] = fma(d1, d1, dot[h]);
+                            dot[h] = fma(d2, d2, dot[h]); dot[h] = fma(d3, d3, dot[h]);
+                        }
                     }
                 }
             }
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
+                const double d = lz_warp_sum(dot[h]);
                 const double qn = sqrt(lz_warp_sum(qs[h]));
-                u64 bk = 0ull;
-                u32 bi = 0xffffffffu;
-                int found = 0;
-#pragma unroll
-                for (int r = 0; r < kSub; ++r) {
-                    const double dot = lz_warp_sum(acc[h][r]);
-                    const int64_t row = r0 + r;
-                    double s;
-                    if (p.metric == LZ_COSINE) {
-                        const double den = p.norms[row] * qn;
-                        s = den > 0.0 ? dot / den : 0.0;
-                        s += 0.0;
-                    } else {
-                        s = 0.0 - dot;
-                    }
-                    if (s != s) continue;
-                    ++found;
-                    const u64 key = lz_ord(s);
-                    if (lz_better(key, (u32)row, bk, bi)) { bk = key; bi = (u32)row; }
+                if (lane != 0 || (h == 1 && !two)) continue;
+                const int q = q0 + iq[h];
+                double sc;
+                if (p.metric == LZ_COSINE) {
+                    const double den = s_norm[rr[h]] * qn;
+                    sc = den > 0.0 ? d / den : 0.0;
+                    sc += 0.0;
+                } else {
+                    sc = 0.0 - d;
                 }
-                if (lane == 0 && (h == 0 || two)) {
-                    const int i = h == 0 ? ia : ib;
-                    const int q = q0 + i;
-                    const bool has = found > 0;
-                    const double v = has ? lz_unord(bk) : 0.0;
-                    p.out_ids[q] = has ? (int64_t)bi + p.id_base : -1;
-                    p.out_scores[q] = has ? (p.metric == LZ_COSINE ? v : 0.0 - v) : __longlong_as_double(0x7ff8000000000000ll);
-                    p.out_counts[q] = has ? 1 : 0;
-                    const float T = s_T[i];
-                    bool cert = T == -INFINITY;
-                    if (!cert && has) {
-                        const double e_coarse = p.metric == LZ_COSINE ? v : 0.5 * (v + qn * qn);
-                        cert = e_coarse > (double)T + p.eps[q];
-                    }
-                    p.certified[q] = cert ? 1 : 0;
-                    if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
+                const bool has = sc == sc;
+                p.out_ids[q] = has ? r0 + rr[h] + p.id_base : -1;
+                p.out_scores[q] = has ? (p.metric == LZ_COSINE ? sc : 0.0 - sc) : __longlong_as_double(0x7ff8000000000000ll);
+                p.out_counts[q] = has ? 1 : 0;
+                const float T = s_T[iq[h]];
+                bool cert = T == -INFINITY;
+                if (!cert && has) {
+                    const double e_coarse = p.metric == LZ_COSINE ? sc : 0.5 * (sc + qn * qn);
+                    cert = e_coarse > (double)T + p.eps[q];
                 }
+                p.certified[q] = cert ? 1 : 0;
+                if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
             }
         }
     }
@@ -1186,6 +1218,10 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
                                                                 fb_count, want_tag, margin_sigmas, metric, max_row_norm);
     LZ_CUDA(cudaGetLastError());
 
+    // top-1 against a tiny table (shard reassignment): trailing threshold in the coarse pass, bucketed exact pass
+    const size_t rows_smem = (size_t)kSub * dim * 4;
+    const bool tiny_top1 = k == 1 && tags == nullptr && pl.n_slices == 1 && row_hi - row_lo <= (int64_t)kBucketGroups * kSub &&
+                           rows_smem <= 160 * 1024 && n_queries >= 4 * kBucketQ;
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
@@ -1199,7 +1235,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim_s + BK - 1) / BK;
         g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
-        g.tags = tags; g.want_tag = want_tag; g.gthr = gthr;
+        g.tags = tags; g.want_tag = want_tag; g.gthr = gthr; g.top1_eps = tiny_top1 ? eps : nullptr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = 1024 + (size_t)196608 + (2 * 6 + 4) * 8 + 16;   // 4 x 48 KiB or 6 x 32 KiB of stages
         auto kern = pair ? (pl.kp == 32 ? gemm_topk_kernel<2, true> : pl.kp == 128 ? gemm_topk_kernel<8, true>
@@ -1254,12 +1290,10 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
     sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
-    sp.id_base = id_base;
+    sp.id_base = id_base; sp.sub = tiny_top1 ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
-    const size_t rows_smem = (size_t)kSub * dim * 4;
-    if (k == 1 && tags == nullptr && pl.n_slices == 1 && row_hi - row_lo <= (int64_t)kBucketGroups * kSub &&
-        rows_smem <= 160 * 1024 && n_queries >= 4 * kBucketQ) {
+    if (tiny_top1) {
         LZ_CUDA(cudaFuncSetAttribute(assign_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rows_smem));
         assign_rescore_kernel<<<(n_queries + kBucketQ - 1) / kBucketQ, kSelThreads, rows_smem, st>>>(sp, n_queries);
     } else if (k <= kSmallK) {
