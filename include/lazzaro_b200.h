@@ -221,6 +221,26 @@ int lz_salience_decay(float* salience, int64_t n, double rate, double floor, voi
 int lz_connected_components(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes,
                             int32_t* labels, void* stream);
 
+/* ---- buffer-limit eviction (stands behind MemorySystem._enforce_buffer_limit,
+ *      core/memory_system.py:535-578) ------------------------------------------------------------------ */
+
+/* importance[i] = salience*0.5 + min(1, access_count/10)*0.3 + (1/(1 + (now - last_accessed)/86400))*0.2,
+ * float64, rounded operation by operation as the reference's Python expression (memory_system.py:545-550);
+ * the k LEAST important nodes with skip[i] == 0 come back in (importance ascending, index ascending) order —
+ * the reference's stable ascending sort (memory_system.py:552-553) when the caller's index order is the
+ * reference's iteration order (shards in dict order, nodes in dict order; super-nodes flagged in `skip`).
+ * The reference reads the clock once per node; here `now` is one value for the whole sweep.
+ * salience: float32 [n] (salience_is_f64 = 0, the stored column type, vector_store.py:42) or float64 [n];
+ * access_count int32 [n]; last_accessed float64 [n] (epoch seconds); skip uint8 [n] or NULL.
+ * k <= LZ_MAX_K (evict in rounds beyond that, flagging the evicted in `skip`).  NaN importances are never
+ * evicted.  out_idx int64 [k], out_importance float64 [k], out_count int32 [1] (all device);
+ * out_all_importance float64 [n] or NULL receives every node's importance. */
+size_t lz_evict_lowest_scratch_bytes(int64_t n, int k);
+int lz_evict_lowest(const void* salience, int salience_is_f64, const int32_t* access_count,
+                    const double* last_accessed, const uint8_t* skip, int64_t n, double now, int k,
+                    void* scratch, size_t scratch_bytes, int64_t* out_idx, double* out_importance,
+                    int32_t* out_count, double* out_all_importance, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -523,3 +523,126 @@ extern "C" int lz_segment_mean(const float* rows, int64_t ld, int dim, const int
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
+
+// ---- importance scoring + lowest-k selection (buffer-limit eviction) ---------------------------------------
+// Stands behind MemorySystem._enforce_buffer_limit (core/memory_system.py:535-578):
+//   days_old   = (now - last_accessed) / 86400
+//   importance = salience * 0.5 + min(1.0, access_count / 10) * 0.3 + (1.0 / (1.0 + days_old)) * 0.2
+// evaluated in float64 with the reference's operation order (no fused multiply-adds: every product and sum is
+// rounded as Python rounds it), then the `k` LEAST important eligible nodes in (importance asc, index asc)
+// order — the reference's stable ascending sort over its iteration order, which the caller's index order must
+// follow.  One streaming pass: 17 bytes per node (float32 salience) or 21 (float64), per-CTA selector, then the
+// per-list merge the scan uses.  HBM-bound.
+namespace {
+constexpr int kEvictPerThread = 8;
+constexpr int kEvictChunk = kThreads * kEvictPerThread;
+
+struct EvictParams {
+    const float* sal32; const double* sal64; const int32_t* access; const double* last; const uint8_t* skip;
+    int64_t n; double now; int k, cap, n_chunks;
+    double* out_all;                                       // optional: importance of every node
+    u64* part_key; u32* part_id; int32_t* part_cnt;
+};
+
+__device__ __forceinline__ double importance_of(double sal, int access, double last, double now) {
+    const double days = __ddiv_rn(__dsub_rn(now, last), 86400.0);
+    const double t1 = __dmul_rn(sal, 0.5);
+    const double t2 = __dmul_rn(fmin(1.0, __ddiv_rn((double)access, 10.0)), 0.3);
+    const double t3 = __dmul_rn(__ddiv_rn(1.0, __dadd_rn(1.0, days)), 0.2);
+    return __dadd_rn(__dadd_rn(t1, t2), t3);
+}
+
+__global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* keys = reinterpret_cast<u64*>(smem);
+    u32* ids = reinterpret_cast<u32*>(keys + p.cap);
+    __shared__ LzSelector sel;
+    const int tid = threadIdx.x;
+    if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
+    __syncthreads();
+    const int64_t n_tiles = (p.n + kEvictChunk - 1) / kEvictChunk;
+    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const int64_t base = t * kEvictChunk;
+#pragma unroll
+        for (int j = 0; j < kEvictPerThread; ++j) {
+            const int64_t i = base + (int64_t)j * kThreads + tid;          // coalesced across the CTA
+            if (i < p.n) {
+                const double s = p.sal64 ? p.sal64[i] : (double)p.sal32[i];
+                const double imp = importance_of(s, p.access[i], p.last[i], p.now);
+                if (p.out_all) p.out_all[i] = imp;
+                // larger key = better = LESS important; NaN importance is never evicted
+                if (imp == imp && !(p.skip && p.skip[i])) lz_sel_push(&sel, lz_ord(0.0 - imp), (u32)i);
+            }
+        }
+        lz_sel_maybe_compact<kThreads>(&sel, kEvictChunk);
+    }
+    __syncthreads();
+    lz_sel_compact<kThreads>(&sel);
+    const int n = min(sel.count, p.k);
+    const size_t slot = blockIdx.x;
+    for (int j = tid; j < n; j += kThreads) {
+        p.part_key[slot * p.k + j] = sel.key[j];
+        p.part_id[slot * p.k + j] = sel.id[j];
+    }
+    if (tid == 0) p.part_cnt[slot] = n;
+}
+
+int evict_chunks(int64_t n) {
+    const int sms = lz_sm_count();
+    int64_t tiles = (n + kEvictChunk - 1) / kEvictChunk;
+    int64_t want = (int64_t)(sms > 0 ? sms : 1) * 2;
+    return (int)(tiles < want ? (tiles < 1 ? 1 : tiles) : want);
+}
+}  // namespace
+
+extern "C" size_t lz_evict_lowest_scratch_bytes(int64_t n, int k) {
+    if (n <= 0 || k <= 0) return 0;
+    return lz_search_exact_scratch_bytes(1, k, evict_chunks(n));
+}
+
+extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const int32_t* access_count,
+                               const double* last_accessed, const uint8_t* skip, int64_t n, double now, int k,
+                               void* scratch, size_t scratch_bytes, int64_t* out_idx, double* out_importance,
+                               int32_t* out_count, double* out_all_importance, void* stream) {
+    LZ_REQUIRE(out_count != nullptr, "lz_evict_lowest: out_count is NULL");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n <= 0 || k <= 0) {
+        LZ_CUDA(cudaMemsetAsync(out_count, 0, sizeof(int32_t), st));
+        return LZ_OK;
+    }
+    LZ_REQUIRE(salience && access_count && last_accessed && out_idx && out_importance && scratch,
+               "lz_evict_lowest: NULL pointer");
+    LZ_REQUIRE(k <= LZ_MAX_K, "lz_evict_lowest: k=%d exceeds %d (evict in rounds)", k, LZ_MAX_K);
+    LZ_REQUIRE(n <= 0xfffffffeLL, "lz_evict_lowest: n=%lld exceeds 32-bit indices", (long long)n);
+    const int chunks = evict_chunks(n);
+    const size_t need = lz_search_exact_scratch_bytes(1, k, chunks);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_evict_lowest: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    EvictParams p;
+    p.sal32 = salience_is_f64 ? nullptr : (const float*)salience;
+    p.sal64 = salience_is_f64 ? (const double*)salience : nullptr;
+    p.access = access_count; p.last = last_accessed; p.skip = skip; p.n = n; p.now = now;
+    p.k = k; p.cap = lz_next_pow2(k + kEvictChunk); p.n_chunks = chunks; p.out_all = out_all_importance;
+    unsigned char* s = (unsigned char*)scratch;
+    const size_t slots = (size_t)chunks;
+    p.part_key = (u64*)s;
+    p.part_id = (u32*)(s + slots * k * sizeof(u64));
+    p.part_cnt = (int32_t*)(s + (((slots * k * (sizeof(u64) + sizeof(u32))) + 15) & ~(size_t)15));
+    const size_t smem = (size_t)p.cap * 12;
+    LZ_CUDA(cudaFuncSetAttribute(importance_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    importance_select_kernel<<<chunks, kThreads, smem, st>>>(p);
+    LZ_CUDA(cudaGetLastError());
+    MergeParams m;
+    m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
+    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = 1;
+    m.n_lists = chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = LZ_L2;   // L2 form returns -key = importance
+    m.id_base = 0; m.work_list = nullptr; m.work_count = nullptr;
+    m.out_ids = out_idx; m.out_scores = out_importance; m.out_counts = out_count;
+    const size_t msmem = (size_t)m.cap * 12;
+    LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+    merge_kernel<<<1, kThreads, msmem, st>>>(m);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -211,3 +211,29 @@ def connected_components(src: torch.Tensor, dst: torch.Tensor, n_edges: int, n_n
         check(_lib.load().lz_connected_components(ptr(src), ptr(dst), int(n_edges), int(n_nodes), ptr(labels),
                                                   stream_ptr(dev)), "lz_connected_components")
     return labels
+
+
+def evict_lowest(salience: torch.Tensor, access_count: torch.Tensor, last_accessed: torch.Tensor, now: float, k: int,
+                 skip: Optional[torch.Tensor] = None, want_all: bool = False):
+    """The k least important nodes (lz_evict_lowest): (idx int64 [count], importance float64 [count]) in
+    (importance asc, index asc) order, plus every node's importance when want_all.  salience float32 or
+    float64 [n]; access_count int32 [n]; last_accessed float64 [n]; skip uint8 [n] or None."""
+    dev = _dev(salience)
+    n = salience.numel()
+    assert salience.dtype in (torch.float32, torch.float64) and access_count.dtype == torch.int32
+    assert last_accessed.dtype == torch.float64 and (skip is None or skip.dtype == torch.uint8)
+    lib = _lib.load()
+    k = int(k)
+    kk = max(k, 1)
+    idx = torch.empty(kk, dtype=torch.int64, device=dev)
+    imp = torch.empty(kk, dtype=torch.float64, device=dev)
+    cnt = torch.zeros(1, dtype=torch.int32, device=dev)
+    all_imp = torch.empty(n, dtype=torch.float64, device=dev) if want_all else None
+    nbytes = int(lib.lz_evict_lowest_scratch_bytes(n, k))
+    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.lz_evict_lowest(ptr(salience), int(salience.dtype == torch.float64), ptr(access_count), ptr(last_accessed),
+                                  ptr(skip), n, float(now), k, ptr(scratch), nbytes, ptr(idx), ptr(imp), ptr(cnt),
+                                  ptr(all_imp), stream_ptr(dev)), "lz_evict_lowest")
+    c = int(cnt.item())
+    return (idx[:c], imp[:c], all_imp) if want_all else (idx[:c], imp[:c])

@@ -433,28 +433,39 @@ class MemorySystem:
 
     def _enforce_buffer_limit(self):
         """memory_system.py:535-578: evict the least important non-super nodes beyond max_buffer_size.
-        Host-side bookkeeping (SURVEY §8a row 13, next on the device)."""
+        Importance scoring and the lowest-`excess` selection run on the device (lz_evict_lowest, in rounds of
+        LZ_MAX_K); node fields are gathered in the reference's iteration order (shards, then nodes, in dict
+        order) so index order = its stable-sort order.  One `now` for the sweep (the reference reads the clock
+        per node)."""
         total, _ = self.buffer.size()
         if total <= self.max_buffer_size:
             return
         excess = total - self.max_buffer_size
         now = time.time()
-        scored = []
-        for shard in self.shards.values():
-            for nid, n in shard.nodes.items():
-                if not n.is_super_node:
-                    days = (now - n.last_accessed) / 86400
-                    scored.append((nid, n.salience * 0.5 + min(1.0, n.access_count / 10) * 0.3 + (1.0 / (1.0 + days)) * 0.2,
-                                   n.shard_key))
-        scored.sort(key=lambda x: x[1])                   # stable ascending, as the reference
+        order = [n for shard in self.shards.values() for n in shard.nodes.values()]
+        if not order:
+            return
+        dev = self.store.device
+        sal = torch.tensor([n.salience for n in order], dtype=torch.float64, device=dev)
+        acc = torch.tensor([n.access_count for n in order], dtype=torch.int32, device=dev)
+        last = torch.tensor([n.last_accessed for n in order], dtype=torch.float64, device=dev)
+        skip = torch.tensor([1 if n.is_super_node else 0 for n in order], dtype=torch.uint8, device=dev)
+        chosen: List[int] = []
+        while len(chosen) < excess:
+            idx, _ = kernels.evict_lowest(sal, acc, last, now, min(excess - len(chosen), _lib.MAX_K), skip=skip)
+            if idx.numel() == 0:
+                break
+            skip[idx] = 1
+            chosen.extend(idx.tolist())
         removed = []
-        for nid, _, key in scored[:excess]:
-            shard = self.shards.get(key)
-            if shard is not None and nid in shard.nodes:
-                shard.remove_node(nid)
-                removed.append(nid)
+        for i in chosen:
+            n = order[i]
+            shard = self.shards.get(n.shard_key)
+            if shard is not None and n.id in shard.nodes:
+                shard.remove_node(n.id)
+                removed.append(n.id)
         if removed:
-            self.store.delete_nodes([nid for nid, _, _ in scored[:excess]], user_id=self.user_id)
+            self.store.delete_nodes([order[i].id for i in chosen], user_id=self.user_id)
 
     def _merge_similar_nodes(self, similarity_threshold: float = 0.95) -> int:
         """memory_system.py:1065-1120.  As written in the reference the pair loop sits outside the outer

@@ -123,3 +123,25 @@ def importance(salience, access_count, days_old):
     return (np.asarray(salience, np.float64) * 0.5
             + np.minimum(1.0, np.asarray(access_count, np.float64) / 10) * 0.3
             + (1.0 / (1.0 + np.asarray(days_old, np.float64))) * 0.2)
+
+
+def evict_lowest(salience, access_count, last_accessed, now: float, k: int, skip=None):
+    """core/memory_system.py:541-553 for one `now`: importance of every node in the caller's (= the
+    reference's iteration) order, stable ascending sort, first k non-skipped. Returns (indices, importances)."""
+    imp = importance(salience, access_count, (now - np.asarray(last_accessed, np.float64)) / 86400)
+    cand = np.arange(len(imp)) if skip is None else np.nonzero(~np.asarray(skip, bool))[0]
+    cand = cand[~np.isnan(imp[cand])]
+    order = cand[np.argsort(imp[cand], kind="stable")][:k]
+    return order.astype(np.int64), imp[order]
+
+
+def neighbors(src, dst, weight, node: int, min_weight: float = 0.3):
+    """core/memory_shard.py:54-62: neighbour ids of `node` in edge order (edge i = (src[i], dst[i])); an edge
+    contributes once (its source end is tested first, so a self-loop yields the node itself once)."""
+    out = []
+    for s, t, w in zip(np.asarray(src).tolist(), np.asarray(dst).tolist(), np.asarray(weight, np.float64).tolist()):
+        if s == node and w >= min_weight:
+            out.append(t)
+        elif t == node and w >= min_weight:
+            out.append(s)
+    return out

@@ -16,3 +16,10 @@ def pytest_configure(config):
 def golden():
     import numpy as np
     return np.load(os.path.join(ROOT, "tests", "golden", "ref_python_path.npz"))
+
+
+@pytest.fixture(scope="session")
+def golden_next():
+    """Reference outputs for the SURVEY §8f rows (eviction, neighbours); tests/golden/make_golden.py."""
+    import numpy as np
+    return np.load(os.path.join(ROOT, "tests", "golden", "ref_next_rows.npz"))

@@ -13,6 +13,9 @@ What is recorded (inputs AND reference outputs, so tests need nothing but numpy)
   search_mem    memory_system.py:1460-1472 over an injected flat store, cfg1-like (2k x 64)
   pins          the expectations of the reference's own tests, reproduced by running its code
   msys          memory_system.py:580-785 end to end: three conversations (dedup, linking, super-nodes, decay, prune)
+and, in ref_next_rows.npz:
+  eviction      memory_system.py:535-578 (_enforce_buffer_limit) under a frozen clock
+  neighbors     memory_shard.py:54-62 (get_neighbors) on a random edge set
 """
 from __future__ import annotations
 
@@ -266,6 +269,78 @@ def gold_memory_system(lz):
                                           "retrieval": orr, "components": comps, "dim": dim})))
 
 
+def gold_eviction(lz):
+    """_enforce_buffer_limit (memory_system.py:535-578) with the clock frozen: three shards, super-nodes mixed
+    in, ties in importance (equal fields) to pin the stable order, edges touching evicted nodes."""
+    import types
+    from lazzaro.core import memory_system as ref_ms
+    from lazzaro.models.graph import Edge, Node
+    NOW = 1_750_000_000.25
+    rng = np.random.default_rng(71)
+    out = {}
+    for case, (n, limit) in enumerate([(64, 40), (300, 120), (12, 11)]):
+        store = FlatStore()
+        ms = quiet(ref_harness.make_memory_system, store, max_buffer_size=limit)
+        sal = np.round(rng.uniform(0.05, 1.0, n), 2)
+        acc = rng.integers(0, 15, n)
+        last = NOW - rng.choice([0.0, 3600.0, 86400.0, 5 * 86400.0, 40 * 86400.0, 400 * 86400.0], n) - rng.uniform(0, 50, n).round(1)
+        sup = rng.random(n) < 0.08
+        sal[5] = sal[3]; acc[5] = acc[3]; last[5] = last[3]; sup[3] = sup[5] = False      # exact ties
+        if n > 40:
+            sal[33] = sal[3]; acc[33] = acc[3]; last[33] = last[3]; sup[33] = False
+        shard_of = rng.integers(0, 3, n)
+        for i in range(n):
+            ms.buffer.add_node(Node(id=f"n{i}", content=f"c{i}", embedding=[0.0] * 4, salience=float(sal[i]),
+                                    access_count=int(acc[i]), last_accessed=float(last[i]), is_super_node=bool(sup[i]),
+                                    shard_key=f"s{shard_of[i]}"))
+        for _ in range(2 * n):
+            a, b = rng.integers(0, n, 2)
+            if a != b:
+                ms.buffer.add_edge(Edge(source=f"n{a}", target=f"n{b}", weight=0.7))
+        order = [nid for sh in ms.shards.values() for nid in sh.nodes]          # the reference's iteration order
+        store.add_nodes([{"id": nid, "content": nid, "embedding": [0.0] * 4} for nid in order])
+        deleted = []
+        store.delete_nodes = lambda ids, user_id="default", _d=deleted: _d.extend(ids)
+        real_time = ref_ms.time
+        ref_ms.time = types.SimpleNamespace(time=lambda: NOW)
+        try:
+            quiet(ms._enforce_buffer_limit)
+        finally:
+            ref_ms.time = real_time
+        idx = [int(nid[1:]) for nid in order]
+        out.update({f"ev{case}_order": np.array(idx, np.int64), f"ev{case}_sal": sal[idx], f"ev{case}_acc": acc[idx].astype(np.int32),
+                    f"ev{case}_last": last[idx], f"ev{case}_super": sup[idx], f"ev{case}_limit": np.int64(limit),
+                    f"ev{case}_deleted": np.array([int(x[1:]) for x in deleted], np.int64),
+                    f"ev{case}_left_nodes": np.array(sorted(int(nid[1:]) for sh in ms.shards.values() for nid in sh.nodes), np.int64),
+                    f"ev{case}_left_edges": np.array(json.dumps(sorted([a, b] for sh in ms.shards.values() for (a, b) in sh.edges)))})
+    out["ev_now"] = np.float64(NOW)
+    return out
+
+
+def gold_neighbors(lz):
+    """MemoryShard.get_neighbors (memory_shard.py:54-62): neighbour ids in edge-dict order, weight >= min_weight."""
+    from lazzaro.core.memory_shard import MemoryShard
+    from lazzaro.models.graph import Edge, Node
+    rng = np.random.default_rng(72)
+    n, ne = 200, 1500
+    sh = MemoryShard("s")
+    for i in range(n):
+        sh.add_node(Node(id=f"n{i}", content="", embedding=[]))
+    src, dst = rng.integers(0, n, ne), rng.integers(0, n, ne)
+    w = rng.uniform(0, 1, ne).astype(np.float32)
+    w[::7] = np.float32(0.3)                                                     # exactly at the default gate
+    for a, b, x in zip(src, dst, w):
+        sh.add_edge(Edge(source=f"n{a}", target=f"n{b}", weight=float(x)))     # repeats reinforce (memory_shard.py:42-52)
+    keys = list(sh.edges.keys())
+    e_src = np.array([int(a[1:]) for a, _ in keys], np.int32)
+    e_dst = np.array([int(b[1:]) for _, b in keys], np.int32)
+    e_w = np.array([sh.edges[k].weight for k in keys], np.float64)
+    res = {}
+    for mw in (0.3, 0.5, 0.0):
+        res[str(mw)] = [[int(x[1:]) for x in sh.get_neighbors(f"n{i}", mw)] for i in range(n)]
+    return dict(nb_src=e_src, nb_dst=e_dst, nb_w=e_w, nb_n=np.int64(n), nb_lists=np.array(json.dumps(res)))
+
+
 def main():
     lz = ref_harness.import_reference()
     ms = quiet(ref_harness.make_memory_system, FlatStore())
@@ -276,6 +351,13 @@ def main():
         print("ok", fn.__name__)
     path = os.path.join(OUT, "ref_python_path.npz")
     np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes")
+    nxt = {}
+    for fn in (gold_eviction, gold_neighbors):
+        nxt.update(fn(lz))
+        print("ok", fn.__name__)
+    path = os.path.join(OUT, "ref_next_rows.npz")
+    np.savez_compressed(path, **nxt)
     print("wrote", path, os.path.getsize(path), "bytes")
 
 

@@ -108,3 +108,31 @@ def test_buffer_limit_evicts_least_important_and_syncs_store():
     assert sorted(ms.buffer.nodes) == ["n0", "n2", "n4"]                     # n1 (0.1) and n3 (0.2) evicted
     assert set(ms.buffer.edges) == {("n0", "n2")}
     assert sorted(ms.store.search_nodes([0.1] * 8, limit=10)) == ["n0", "n2", "n4"]
+
+
+def test_buffer_limit_replays_reference_evictions(golden_next, monkeypatch):
+    """The reference's _enforce_buffer_limit (memory_system.py:535-578) recorded under a frozen clock
+    (tests/golden/make_golden.py gold_eviction): same deleted ids in the same order, same surviving nodes."""
+    import types
+    from lazzaro_b200 import memory_system as msmod
+    from lazzaro_b200.graph import Node
+    g = golden_next
+    now = float(g["ev_now"])
+    monkeypatch.setattr(msmod, "time", types.SimpleNamespace(time=lambda: now))
+    for c in range(3):
+        order, sal, acc = g[f"ev{c}_order"], g[f"ev{c}_sal"], g[f"ev{c}_acc"]
+        last, sup = g[f"ev{c}_last"], g[f"ev{c}_super"]
+        ms = msmod.MemorySystem(llm_provider=ScriptedLLM(), embedding_provider=TableEmbedder({}, 4),
+                                max_buffer_size=int(g[f"ev{c}_limit"]))
+        # one shard holding the nodes in the reference's iteration order reproduces its stable-sort order
+        for j, i in enumerate(order.tolist()):
+            ms.buffer.add_node(Node(id=f"n{i}", content=f"c{i}", embedding=[0.0] * 4, salience=float(sal[j]),
+                                    access_count=int(acc[j]), last_accessed=float(last[j]), is_super_node=bool(sup[j]),
+                                    shard_key="s"))
+        ms.store.add_nodes([{"id": f"n{i}", "content": "", "embedding": [0.0] * 4} for i in order.tolist()])
+        deleted = []
+        real_delete = ms.store.delete_nodes
+        monkeypatch.setattr(ms.store, "delete_nodes", lambda ids, user_id="default": (deleted.extend(ids), real_delete(ids, user_id))[1])
+        ms._enforce_buffer_limit()
+        assert [int(x[1:]) for x in deleted] == g[f"ev{c}_deleted"].tolist()
+        assert sorted(int(x[1:]) for sh in ms.shards.values() for x in sh.nodes) == g[f"ev{c}_left_nodes"].tolist()

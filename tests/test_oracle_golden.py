@@ -170,3 +170,26 @@ def test_flat_search_ties_and_filter():
     assert idx.tolist() == [0, 1, 3] and d.tolist() == [0.0, 0.0, 1.0]
     ids, sc = flat_search.merge_topk([[0, 3], [1, 2]], [[1.0, 0.5], [1.0, 0.7]], 3)
     assert ids.tolist() == [0, 1, 2]
+
+
+def test_eviction_matches_reference(golden_next):
+    # memory_system.py:535-578 run under a frozen clock: which nodes the reference deleted, in its order
+    g = golden_next
+    for c in range(3):
+        sal, acc, last, sup = g[f"ev{c}_sal"], g[f"ev{c}_acc"], g[f"ev{c}_last"], g[f"ev{c}_super"]
+        excess = len(sal) - int(g[f"ev{c}_limit"])
+        idx, imp = graph_ops.evict_lowest(sal, acc, last, float(g["ev_now"]), excess, skip=sup)
+        assert g[f"ev{c}_order"][idx].tolist() == g[f"ev{c}_deleted"].tolist()
+        assert (np.diff(imp) >= 0).all() and not sup[idx].any()
+        left = sorted(set(g[f"ev{c}_order"].tolist()) - set(g[f"ev{c}_deleted"].tolist()))
+        assert left == g[f"ev{c}_left_nodes"].tolist()
+
+
+def test_neighbors_match_reference(golden_next):
+    # memory_shard.py:54-62 on 1500 edges (with reinforced repeats and weights exactly at the gate)
+    import json
+    g = golden_next
+    lists = json.loads(str(g["nb_lists"]))
+    for mw, want in lists.items():
+        for node in range(0, int(g["nb_n"]), 3):
+            assert graph_ops.neighbors(g["nb_src"], g["nb_dst"], g["nb_w"], node, float(mw)) == want[node]
