@@ -241,6 +241,27 @@ int lz_evict_lowest(const void* salience, int salience_is_f64, const int32_t* ac
                     void* scratch, size_t scratch_bytes, int64_t* out_idx, double* out_importance,
                     int32_t* out_count, double* out_all_importance, void* stream);
 
+/* ---- adjacency: CSR over the edge table + neighbour lookup (stands behind MemoryShard.get_neighbors,
+ *      core/memory_shard.py:54-62, fan-out core/buffer_graph.py:72-77) ----------------------------------- */
+
+/* Index the undirected adjacency of edges (src[e], dst[e]), e < n_edges, over nodes 0..n_nodes-1.
+ * offsets int64 [n_nodes + 1]; adj uint32 [2 * n_edges]: node v's entries are adj[offsets[v] .. offsets[v+1])
+ * in ASCENDING EDGE ORDER (the reference's edge-dict order), entry = 2*e + (1 if v is the edge's dst end, 0 if
+ * its src end); a self-loop appears once (src end); edges with an endpoint outside [0, n_nodes) are left out.
+ * offsets[n_nodes] = number of entries.  n_edges < 2^30.  Deterministic (stable radix sort). */
+size_t lz_csr_build_scratch_bytes(int64_t n_edges, int32_t n_nodes);
+int lz_csr_build(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes, void* scratch,
+                 size_t scratch_bytes, int64_t* offsets, uint32_t* adj, void* stream);
+
+/* For each queried node: the other endpoint of every incident edge with (double)weight[e] >= min_weight, in
+ * edge order (memory_shard.py:57-61: `>=`, source end tested first).  nodes int32 [n_queries] (ids outside
+ * [0, n_nodes) give 0 neighbours).  out_count[q] = number of qualifying edges; the first min(count, max_out)
+ * are written to out_nbr[q*max_out ..] (and their edge indices to out_edge if not NULL) — a count above
+ * max_out means the list was truncated and the call should be repeated with a larger max_out. */
+int lz_neighbors(const int64_t* offsets, const uint32_t* adj, const int32_t* src, const int32_t* dst,
+                 const float* weight, int32_t n_nodes, const int32_t* nodes, int n_queries, double min_weight,
+                 int max_out, int32_t* out_nbr, int32_t* out_edge, int32_t* out_count, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -43,6 +43,9 @@ SIGNATURES = {
     "lz_salience_decay": (_i32, [_p, _i64, _f64, _f64, _p]),
     "lz_evict_lowest_scratch_bytes": (_sz, [_i64, _i32]),
     "lz_evict_lowest": (_i32, [_p, _i32, _p, _p, _p, _i64, _f64, _i32, _p, _sz, _p, _p, _p, _p, _p]),
+    "lz_csr_build_scratch_bytes": (_sz, [_i64, _i32]),
+    "lz_csr_build": (_i32, [_p, _p, _i64, _i32, _p, _sz, _p, _p, _p]),
+    "lz_neighbors": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _i32, _f64, _i32, _p, _p, _p, _p]),
 }
 
 

@@ -1,0 +1,341 @@
+// Adjacency on the device: a CSR over the edge table's (src, dst) columns and the neighbour lookup on it.
+//
+// Stands behind MemoryShard.get_neighbors (core/memory_shard.py:54-62; fan-out core/buffer_graph.py:72-77):
+// the reference walks EVERY edge of the shard per call and returns the other endpoint of each edge that
+// touches the node with weight >= min_weight, in edge-dict (= insertion = edge index) order.  Here the edges
+// are indexed once per edge-table version:
+//   entries   two per edge, (key = src, val = 2e) and (key = dst, val = 2e + 1); a self-loop keeps only the
+//             first (the reference's `if src == node ... elif tgt == node` yields it once); edges with an
+//             endpoint outside [0, n_nodes) get the sentinel key n_nodes and sort to the end
+//   sort      stable LSD radix sort by key, 8 bits per pass, ceil(bits(n_nodes + 1) / 8) passes — stable, so
+//             each node's entries stay in ascending edge order, which IS the reference's list order
+//   offsets   degree histogram (one atomic per entry) + exclusive scan
+// and a lookup is one warp per queried node over its own entries (weights are read live from the edge
+// table, so decay does not invalidate the index; prune / insert do).  All passes are HBM-bound streaming
+// kernels; nothing here waits on another CTA.
+#include "lz_common.cuh"
+
+namespace {
+
+constexpr int kT = 256;                       // threads per CTA everywhere in this file
+constexpr int kScanPer = 8;
+constexpr int kScanTile = kT * kScanPer;      // 2048 elements per scan tile
+
+// ---- exclusive scan int32 -> int64, three launches ------------------------------------------------------
+__device__ __forceinline__ long long block_exclusive(long long v, long long* s_warp, long long* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    long long incl = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    long long base = 0, all = 0;
+#pragma unroll
+    for (int w = 0; w < kT / 32; ++w) {
+        const long long t = s_warp[w];
+        if (w < warp) base += t;
+        all += t;
+    }
+    if (total) *total = all;
+    __syncthreads();
+    return base + incl - v;
+}
+
+__global__ void __launch_bounds__(kT) scan_sums_kernel(const int32_t* __restrict__ in, int64_t n, int64_t* __restrict__ sums) {
+    __shared__ long long s_warp[kT / 32];
+    const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+    long long v = 0;
+#pragma unroll
+    for (int j = 0; j < kScanPer; ++j) if (base + j < n) v += in[base + j];
+    long long total;
+    block_exclusive(v, s_warp, &total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+// one CTA: exclusive scan of the tile sums in place; the grand total goes to *total (may be NULL)
+__global__ void __launch_bounds__(1024) scan_single_kernel(int64_t* __restrict__ sums, int n_tiles, int64_t* __restrict__ total) {
+    __shared__ long long s_warp[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (n_tiles + 1023) / 1024;
+    const int lo = tid * per, hi = min(n_tiles, lo + per);
+    long long sum = 0;
+    for (int i = lo; i < hi; ++i) sum += sums[i];
+    long long incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const long long t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        long long w = s_warp[lane], wi = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        s_warp[lane] = wi - w;
+        if (lane == 31 && total) *total = wi;
+    }
+    __syncthreads();
+    long long run = s_warp[warp] + incl - sum;
+    for (int i = lo; i < hi; ++i) { const long long c = sums[i]; sums[i] = run; run += c; }
+}
+
+__global__ void __launch_bounds__(kT) scan_apply_kernel(const int32_t* __restrict__ in, int64_t n,
+                                                        const int64_t* __restrict__ tile_off, int64_t* __restrict__ out) {
+    __shared__ long long s_warp[kT / 32];
+    const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+    int32_t x[kScanPer];
+    long long v = 0;
+#pragma unroll
+    for (int j = 0; j < kScanPer; ++j) { x[j] = base + j < n ? in[base + j] : 0; v += x[j]; }
+    long long run = block_exclusive(v, s_warp, nullptr) + tile_off[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < kScanPer; ++j) {
+        if (base + j < n) out[base + j] = run;
+        run += x[j];
+    }
+}
+
+int scan_tiles(int64_t n) { return (int)((n + kScanTile - 1) / kScanTile); }
+
+// out[i] = sum of in[0..i), i < n; *total = sum of all (device pointer, may be NULL). tmp: scan_tiles(n) int64.
+int exclusive_scan(const int32_t* in, int64_t n, int64_t* out, int64_t* tmp, int64_t* total, cudaStream_t st) {
+    if (n <= 0) return LZ_OK;
+    const int tiles = scan_tiles(n);
+    scan_sums_kernel<<<tiles, kT, 0, st>>>(in, n, tmp);
+    scan_single_kernel<<<1, 1024, 0, st>>>(tmp, tiles, total);
+    scan_apply_kernel<<<tiles, kT, 0, st>>>(in, n, tmp, out);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+// ---- entries + degrees --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kT) csr_entries_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                         int64_t n_edges, int32_t n_nodes, u32* __restrict__ keys,
+                                                         u32* __restrict__ vals, int32_t* __restrict__ deg) {
+    const int64_t stride = (int64_t)gridDim.x * kT;
+    for (int64_t e = (int64_t)blockIdx.x * kT + threadIdx.x; e < n_edges; e += stride) {
+        const int32_t a = src[e], b = dst[e];
+        const bool ok = a >= 0 && a < n_nodes && b >= 0 && b < n_nodes;
+        const u32 ka = ok ? (u32)a : (u32)n_nodes;
+        const u32 kb = (ok && b != a) ? (u32)b : (u32)n_nodes;
+        keys[2 * e] = ka;     vals[2 * e] = (u32)(2 * e);
+        keys[2 * e + 1] = kb; vals[2 * e + 1] = (u32)(2 * e + 1);
+        if (ka != (u32)n_nodes) atomicAdd(deg + ka, 1);
+        if (kb != (u32)n_nodes) atomicAdd(deg + kb, 1);
+    }
+}
+
+// ---- stable LSD radix sort of (key, val) pairs, 8 bits per pass -------------------------------------------
+constexpr int kRWarps = kT / 32;
+constexpr int kRRounds = 16;
+constexpr int kRWarpItems = 32 * kRRounds;            // 512 consecutive items per warp
+constexpr int kRTile = kRWarps * kRWarpItems;         // 4096 items per CTA
+
+__global__ void __launch_bounds__(kT) radix_hist_kernel(const u32* __restrict__ keys, int64_t n, int shift,
+                                                        int32_t* __restrict__ hist, int n_tiles) {
+    __shared__ int h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * kRTile;
+#pragma unroll
+    for (int r = 0; r < kRTile / kT; ++r) {
+        const int64_t i = base + (int64_t)r * kT + threadIdx.x;
+        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    hist[(size_t)threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];       // digit-major: a flat scan gives the bases
+}
+
+// Item order inside a tile is index order: warp w owns items [w*512, (w+1)*512) and walks them 32 at a time,
+// so (warp, round, lane) order = index order and the ranks below are stable.
+__global__ void __launch_bounds__(kT) radix_scatter_kernel(const u32* __restrict__ keys_in, const u32* __restrict__ vals_in,
+                                                           u32* __restrict__ keys_out, u32* __restrict__ vals_out,
+                                                           int64_t n, int shift, const int64_t* __restrict__ base,
+                                                           int n_tiles) {
+    __shared__ int wcnt[kRWarps][256];
+    __shared__ long long wbase[kRWarps][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < kRWarps * 256; i += kT) (&wcnt[0][0])[i] = 0;
+    __syncthreads();
+    const int64_t start = (int64_t)blockIdx.x * kRTile + (int64_t)warp * kRWarpItems;
+    u32 key[kRRounds], val[kRRounds];
+    int rank[kRRounds];
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kRRounds; ++r) {
+        const int64_t i = start + r * 32 + lane;
+        const bool valid = i < n;
+        key[r] = valid ? keys_in[i] : 0u;
+        val[r] = valid ? vals_in[i] : 0u;
+        const unsigned live = __ballot_sync(0xffffffffu, valid);
+        rank[r] = 0;
+        if (valid) {
+            const int d = (int)((key[r] >> shift) & 255u);
+            const unsigned peers = __match_any_sync(live, d);
+            const int leader = __ffs(peers) - 1;
+            int old = 0;
+            if (lane == leader) { old = wcnt[warp][d]; wcnt[warp][d] = old + __popc(peers); }
+            old = __shfl_sync(peers, old, leader);
+            rank[r] = old + __popc(peers & lt);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    {
+        const int d = threadIdx.x;                                            // 256 threads <-> 256 digits
+        long long run = base[(size_t)d * n_tiles + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < kRWarps; ++w) { wbase[w][d] = run; run += wcnt[w][d]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kRRounds; ++r) {
+        const int64_t i = start + r * 32 + lane;
+        if (i < n) {
+            const int d = (int)((key[r] >> shift) & 255u);
+            const long long pos = wbase[warp][d] + rank[r];
+            keys_out[pos] = key[r];
+            vals_out[pos] = val[r];
+        }
+    }
+}
+
+int radix_tiles(int64_t n) { return (int)((n + kRTile - 1) / kRTile); }
+
+int key_passes(int32_t n_nodes) {
+    int bits = 1;
+    while (bits < 32 && (1ll << bits) <= (long long)n_nodes) ++bits;           // keys go up to n_nodes (the sentinel)
+    return (bits + 7) / 8;
+}
+
+struct CsrLayout { size_t keys0, keys1, vals1, deg, hist, hist_off, tmp, total; };
+
+CsrLayout csr_layout(int64_t n_edges, int32_t n_nodes) {
+    CsrLayout L;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
+    const size_t n_ent = (size_t)2 * n_edges;
+    const size_t rt = (size_t)radix_tiles((int64_t)n_ent);
+    L.keys0 = take(n_ent * 4);
+    L.keys1 = take(n_ent * 4);
+    L.vals1 = take(n_ent * 4);
+    L.deg = take(((size_t)n_nodes + 1) * 4);
+    L.hist = take(256 * rt * 4);
+    L.hist_off = take(256 * rt * 8);
+    const size_t st_hist = (size_t)scan_tiles((int64_t)(256 * rt)), st_deg = (size_t)scan_tiles((int64_t)n_nodes + 1);
+    L.tmp = take((st_hist > st_deg ? st_hist : st_deg) * 8 + 8);
+    L.total = off;
+    return L;
+}
+
+__global__ void __launch_bounds__(kT) neighbors_kernel(const int64_t* __restrict__ offsets, const u32* __restrict__ adj,
+                                                       const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                       const float* __restrict__ weight, int32_t n_nodes,
+                                                       const int32_t* __restrict__ nodes, int n_queries, double min_weight,
+                                                       int max_out, int32_t* __restrict__ out_nbr, int32_t* __restrict__ out_edge,
+                                                       int32_t* __restrict__ out_count) {
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * (kT / 32) + (threadIdx.x >> 5);
+    if (q >= n_queries) return;
+    const int32_t v = nodes[q];
+    int cnt = 0;
+    if (v >= 0 && v < n_nodes) {
+        const int64_t lo = offsets[v], hi = offsets[v + 1];
+        const unsigned lt = (1u << lane) - 1u;
+        for (int64_t base = lo; base < hi; base += 32) {
+            const int64_t i = base + lane;
+            bool ok = false;
+            int32_t nb = -1, e = -1;
+            if (i < hi) {
+                const u32 ent = adj[i];
+                e = (int32_t)(ent >> 1);
+                ok = (double)weight[e] >= min_weight;                         // the reference compares float64 >= float64
+                nb = (ent & 1u) ? src[e] : dst[e];
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, ok);
+            if (ok) {
+                const int pos = cnt + __popc(m & lt);
+                if (pos < max_out) {
+                    out_nbr[(size_t)q * max_out + pos] = nb;
+                    if (out_edge) out_edge[(size_t)q * max_out + pos] = e;
+                }
+            }
+            cnt += __popc(m);
+        }
+    }
+    if (lane == 0) out_count[q] = cnt;
+}
+
+}  // namespace
+
+extern "C" size_t lz_csr_build_scratch_bytes(int64_t n_edges, int32_t n_nodes) {
+    if (n_edges <= 0 || n_nodes <= 0) return 0;
+    return csr_layout(n_edges, n_nodes).total;
+}
+
+extern "C" int lz_csr_build(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes, void* scratch,
+                            size_t scratch_bytes, int64_t* offsets, uint32_t* adj, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(n_nodes >= 0 && n_edges >= 0, "lz_csr_build: negative size");
+    LZ_REQUIRE(offsets != nullptr, "lz_csr_build: offsets is NULL");
+    if (n_edges == 0 || n_nodes == 0) {
+        LZ_CUDA(cudaMemsetAsync(offsets, 0, ((size_t)n_nodes + 1) * 8, st));
+        return LZ_OK;
+    }
+    LZ_REQUIRE(src && dst && adj && scratch, "lz_csr_build: NULL pointer");
+    LZ_REQUIRE(n_edges <= 0x3fffffffLL, "lz_csr_build: n_edges=%lld exceeds 2^30 - 1", (long long)n_edges);
+    const CsrLayout L = csr_layout(n_edges, n_nodes);
+    if (scratch_bytes < L.total) {
+        lz_set_error("lz_csr_build: scratch has %zu bytes, needs %zu", scratch_bytes, L.total);
+        return LZ_ERR_SCRATCH;
+    }
+    unsigned char* s = (unsigned char*)scratch;
+    const int64_t n_ent = 2 * n_edges;
+    const int passes = key_passes(n_nodes);
+    u32* kbuf[2] = {(u32*)(s + L.keys0), (u32*)(s + L.keys1)};
+    // the last pass must land in `adj`: with an even number of passes the entries start there
+    u32* vbuf[2];
+    vbuf[0] = (passes % 2 == 0) ? adj : (u32*)(s + L.vals1);
+    vbuf[1] = (passes % 2 == 0) ? (u32*)(s + L.vals1) : adj;
+    int32_t* deg = (int32_t*)(s + L.deg);
+    int32_t* hist = (int32_t*)(s + L.hist);
+    int64_t* hist_off = (int64_t*)(s + L.hist_off);
+    int64_t* tmp = (int64_t*)(s + L.tmp);
+    LZ_CUDA(cudaMemsetAsync(deg, 0, ((size_t)n_nodes + 1) * 4, st));
+    const int sms = lz_sm_count();
+    int64_t eblocks = (n_edges + kT - 1) / kT;
+    if (eblocks > (int64_t)sms * 16) eblocks = (int64_t)sms * 16;
+    csr_entries_kernel<<<(unsigned)eblocks, kT, 0, st>>>(src, dst, n_edges, n_nodes, kbuf[0], vbuf[0], deg);
+    LZ_CUDA(cudaGetLastError());
+    // offsets[v] = first entry of node v; offsets[n_nodes] = number of real entries (deg[n_nodes] is 0)
+    if (int rc = exclusive_scan(deg, (int64_t)n_nodes + 1, offsets, tmp, nullptr, st)) return rc;
+    const int rt = radix_tiles(n_ent);
+    for (int pass = 0; pass < passes; ++pass) {
+        const int in = pass & 1, out = in ^ 1;
+        radix_hist_kernel<<<rt, kT, 0, st>>>(kbuf[in], n_ent, pass * 8, hist, rt);
+        if (int rc = exclusive_scan(hist, (int64_t)256 * rt, hist_off, tmp, nullptr, st)) return rc;
+        radix_scatter_kernel<<<rt, kT, 0, st>>>(kbuf[in], vbuf[in], kbuf[out], vbuf[out], n_ent, pass * 8, hist_off, rt);
+        LZ_CUDA(cudaGetLastError());
+    }
+    return LZ_OK;
+}
+
+extern "C" int lz_neighbors(const int64_t* offsets, const uint32_t* adj, const int32_t* src, const int32_t* dst,
+                            const float* weight, int32_t n_nodes, const int32_t* nodes, int n_queries, double min_weight,
+                            int max_out, int32_t* out_nbr, int32_t* out_edge, int32_t* out_count, void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    LZ_REQUIRE(offsets && nodes && out_count, "lz_neighbors: NULL pointer");
+    LZ_REQUIRE(max_out >= 0 && (max_out == 0 || out_nbr != nullptr), "lz_neighbors: max_out=%d without an output buffer", max_out);
+    LZ_REQUIRE(n_nodes >= 0, "lz_neighbors: n_nodes=%d", n_nodes);
+    neighbors_kernel<<<(n_queries + kT / 32 - 1) / (kT / 32), kT, 0, (cudaStream_t)stream>>>(
+        offsets, adj, src, dst, weight, n_nodes, nodes, n_queries, min_weight, max_out, out_nbr, out_edge, out_count);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -147,6 +147,7 @@ class MemoryShard:
         self._edge_meta: Dict[Tuple[int, int], Tuple[str, float]] = {}   # (edge_type, last_updated)
         self._index: Optional[Dict[Tuple[int, int], int]] = None         # (src,dst) -> row, lazily rebuilt
         self._pending: List[Tuple[int, int, float, int]] = []            # edges not yet uploaded
+        self._csr = None                                                  # (offsets, adj, n_nodes): adjacency index of the table
 
     # -- nodes
     def _slot_of(self, node_id: str) -> int:
@@ -167,6 +168,7 @@ class MemoryShard:
             s, d, w, c = zip(*self._pending)
             self._table.append(np.int32(s), np.int32(d), np.float32(w), np.int32(c))
             self._pending.clear()
+            self._csr = None
 
     def _edge_index(self) -> Dict[Tuple[int, int], int]:
         if self._index is None:
@@ -209,6 +211,7 @@ class MemoryShard:
             self._table = EdgeTable.from_arrays(s[keep], d[keep], w[keep], c[keep], device=self._table.device) \
                 if keep.any() else EdgeTable(self._table.device)
             self._index = None
+            self._csr = None
 
     @property
     def edges(self) -> Dict[Tuple[str, str], Edge]:
@@ -221,15 +224,30 @@ class MemoryShard:
             out[(self._names[a], self._names[b])] = Edge(self._names[a], self._names[b], ww, et, cc, lu)
         return out
 
+    def _adjacency(self):
+        """The CSR over the current edge table (lz_csr_build), rebuilt after inserts / prunes / removals;
+        weights are read live by the lookup, so decay alone keeps it valid."""
+        self._flush()
+        n_nodes = len(self._names)
+        if self._csr is None or self._csr[2] != n_nodes:
+            off, adj = kernels.csr_build(self._table.src, self._table.dst, self._table.n, n_nodes)
+            self._csr = (off, adj, n_nodes)
+        return self._csr
+
+    def get_neighbors_batch(self, node_ids: List[str], min_weight: float = 0.3) -> List[List[str]]:
+        """get_neighbors for many nodes in one launch (one warp per node on the device CSR)."""
+        if not node_ids:
+            return []
+        off, adj, n_nodes = self._adjacency()
+        slots = torch.tensor([self._slot.get(i, -1) for i in node_ids], dtype=torch.int32, device=self._table.device)
+        nbr, cnt = kernels.neighbors(off, adj, self._table.src, self._table.dst, self._table.weight, n_nodes, slots, min_weight)
+        nbr, cnt = nbr.cpu().tolist(), cnt.cpu().tolist()
+        return [[self._names[x] for x in row[:c]] for row, c in zip(nbr, cnt)]
+
     def get_neighbors(self, node_id: str, min_weight: float = 0.3) -> List[str]:
-        """memory_shard.py:54-62 (host loop over a device->host copy; the CSR kernel is SURVEY §8f)."""
-        out = []
-        for (src, tgt), e in self.edges.items():
-            if src == node_id and e.weight >= min_weight:
-                out.append(tgt)
-            elif tgt == node_id and e.weight >= min_weight:
-                out.append(src)
-        return out
+        """memory_shard.py:54-62: the other endpoints of the node's edges with weight >= min_weight, in edge
+        order — a lookup on the device CSR (lz_neighbors) instead of the reference's walk over every edge."""
+        return self.get_neighbors_batch([node_id], min_weight)[0]
 
     # -- the hot path
     def _salience_sweep(self, decay_rate: float):
@@ -253,6 +271,7 @@ class MemoryShard:
         pruned = self._table.decay_prune(1.0, threshold)
         if pruned:
             self._index = None
+            self._csr = None
         return pruned
 
     def decay_and_prune(self, decay_rate: float = 0.01, threshold: float = 0.5) -> int:
@@ -263,6 +282,7 @@ class MemoryShard:
         self._salience_sweep(decay_rate)
         if pruned:
             self._index = None
+            self._csr = None
         return pruned
 
     def size(self) -> Tuple[int, int]:

@@ -237,3 +237,39 @@ def evict_lowest(salience: torch.Tensor, access_count: torch.Tensor, last_access
                                   ptr(all_imp), stream_ptr(dev)), "lz_evict_lowest")
     c = int(cnt.item())
     return (idx[:c], imp[:c], all_imp) if want_all else (idx[:c], imp[:c])
+
+
+def csr_build(src: torch.Tensor, dst: torch.Tensor, n_edges: int, n_nodes: int):
+    """(offsets int64 [n_nodes+1], adj int32-as-uint32 [2*n_edges]) — lz_csr_build; node v's entries are
+    adj[offsets[v]:offsets[v+1]] in ascending edge order, entry = 2*edge + (1 if v is the dst end)."""
+    dev = _dev(src)
+    lib = _lib.load()
+    offsets = torch.empty(n_nodes + 1, dtype=torch.int64, device=dev)
+    adj = torch.empty(max(2 * n_edges, 1), dtype=torch.int32, device=dev)       # uint32 payload, < 2^31
+    nbytes = int(lib.lz_csr_build_scratch_bytes(int(n_edges), int(n_nodes)))
+    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.lz_csr_build(ptr(src), ptr(dst), int(n_edges), int(n_nodes), ptr(scratch), nbytes, ptr(offsets), ptr(adj),
+                               stream_ptr(dev)), "lz_csr_build")
+    return offsets, adj
+
+
+def neighbors(offsets: torch.Tensor, adj: torch.Tensor, src: torch.Tensor, dst: torch.Tensor, weight: torch.Tensor,
+              n_nodes: int, nodes: torch.Tensor, min_weight: float = 0.3, max_out: int = 64, want_edges: bool = False):
+    """Per queried node the neighbours over edges with weight >= min_weight, in edge order (lz_neighbors).
+    Returns (nbr int32 [q, width], count int32 [q][, edge int32 [q, width]]); width grows until nothing is truncated."""
+    dev = _dev(offsets)
+    assert nodes.dtype == torch.int32 and weight.dtype == torch.float32
+    q = nodes.numel()
+    lib = _lib.load()
+    cnt = torch.zeros(q, dtype=torch.int32, device=dev)
+    while True:
+        nbr = torch.full((q, max(max_out, 1)), -1, dtype=torch.int32, device=dev)
+        edge = torch.full((q, max(max_out, 1)), -1, dtype=torch.int32, device=dev) if want_edges else None
+        with torch.cuda.device(dev):
+            check(lib.lz_neighbors(ptr(offsets), ptr(adj), ptr(src), ptr(dst), ptr(weight), int(n_nodes), ptr(nodes), q,
+                                   float(min_weight), int(max_out), ptr(nbr), ptr(edge), ptr(cnt), stream_ptr(dev)), "lz_neighbors")
+        most = int(cnt.max().item()) if q else 0
+        if most <= max_out:
+            return (nbr, cnt, edge) if want_edges else (nbr, cnt)
+        max_out = most

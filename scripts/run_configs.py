@@ -137,6 +137,32 @@ def cfg5():
     emit("cfg5 salience decay 12.5M nodes", ms, gbs=8 * sal.numel() / ms / 1e6)
 
 
+def cfg5_graph():
+    # the node / adjacency sweeps at one GPU's cfg5 share: 12.5M nodes, 50M edges
+    nn, ne = 12_500_000, 50_000_000
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    sal = torch.rand(nn, device="cuda", generator=g)
+    acc = torch.randint(0, 30, (nn,), device="cuda", generator=g, dtype=torch.int32)
+    last = 1.76e9 - torch.rand(nn, device="cuda", generator=g, dtype=torch.float64) * 86400 * 400
+    skip = (torch.rand(nn, device="cuda", generator=g) < 0.01).to(torch.uint8)
+    for k in (64, 1024):
+        ms, _ = timed(lambda: K.evict_lowest(sal, acc, last, 1.76e9, k, skip=skip), 10)
+        emit(f"cfg5 eviction sweep: importance + lowest-{k} of 12.5M nodes", ms, nodes_per_s=nn / ms * 1e3,
+             gbs=17 * nn / ms / 1e6, frac_hbm=17 * nn / ms / 1e6 / PEAKS["hbm_gbs"])
+    del sal, acc, last, skip
+    src, dst, w, _ = synth.edge_table(ne, nn)
+    src, dst, w = (torch.as_tensor(a).cuda() for a in (src, dst, w))
+    ms, (off, adj) = timed(lambda: K.csr_build(src, dst, ne, nn), 5)
+    passes = 3                                                      # bits(12.5M + 1) = 24
+    moved = ne * (8 + 16) + nn * 12 + passes * 2 * ne * (4 + 16)    # entries written, degrees scanned, 3 x (hist read + pairs read/written)
+    emit("cfg5 adjacency build: CSR over 50M edges / 12.5M nodes (stable radix sort, 3 passes)", ms,
+         edges_per_s=ne / ms * 1e3, gbs_moved=moved / ms / 1e6, frac_hbm_moved=moved / ms / 1e6 / PEAKS["hbm_gbs"])
+    for q in (1, 4096, 1_000_000):
+        nodes = torch.randint(0, nn, (q,), device="cuda", generator=g, dtype=torch.int32)
+        ms, _ = timed(lambda: K.neighbors(off, adj, src, dst, w, nn, nodes, 0.3, max_out=64), 10)
+        emit(f"cfg5 get_neighbors on the CSR, {q} nodes per launch (mean degree 8)", ms, lookups_per_s=q / ms * 1e3)
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["cfg2", "cfg3", "cfg4", "cfg5"]
     for name in which:
