@@ -115,31 +115,36 @@ int exclusive_scan(const int32_t* in, int64_t n, int64_t* out, int64_t* tmp, int
     return LZ_OK;
 }
 
-// ---- entries + degrees --------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kT) csr_entries_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
-                                                         int64_t n_edges, int32_t n_nodes, u32* __restrict__ keys,
-                                                         u32* __restrict__ vals, int32_t* __restrict__ deg) {
-    const int64_t stride = (int64_t)gridDim.x * kT;
-    for (int64_t e = (int64_t)blockIdx.x * kT + threadIdx.x; e < n_edges; e += stride) {
-        const int32_t a = src[e], b = dst[e];
-        const bool ok = a >= 0 && a < n_nodes && b >= 0 && b < n_nodes;
-        const u32 ka = ok ? (u32)a : (u32)n_nodes;
-        const u32 kb = (ok && b != a) ? (u32)b : (u32)n_nodes;
-        keys[2 * e] = ka;     vals[2 * e] = (u32)(2 * e);
-        keys[2 * e + 1] = kb; vals[2 * e + 1] = (u32)(2 * e + 1);
-        if (ka != (u32)n_nodes) atomicAdd(deg + ka, 1);
-        if (kb != (u32)n_nodes) atomicAdd(deg + kb, 1);
-    }
-}
-
-// ---- stable LSD radix sort of (key, val) pairs, 8 bits per pass -------------------------------------------
+// ---- stable LSD radix sort of the edge endpoints, 8 bits per pass ------------------------------------------
+// An entry is a packed pair (key << 32 | val): key = the node an edge end belongs to, val = 2*edge + side.
+// Entry i of the unsorted sequence is edge i/2, side i%2 — pass 0 generates it from (src, dst) on the fly
+// (GEN), so the unsorted sequence is never written.  Item order inside a tile is index order: warp w owns
+// items [w*512, (w+1)*512) and walks them 32 at a time, so (warp, round, lane) order = index order and the
+// ranks below are stable.  A tile's items are first placed in shared memory in digit order and then written
+// out in runs (all items of one digit go to consecutive addresses), so global writes are coalesced.
 constexpr int kRWarps = kT / 32;
 constexpr int kRRounds = 16;
 constexpr int kRWarpItems = 32 * kRRounds;            // 512 consecutive items per warp
 constexpr int kRTile = kRWarps * kRWarpItems;         // 4096 items per CTA
 
-__global__ void __launch_bounds__(kT) radix_hist_kernel(const u32* __restrict__ keys, int64_t n, int shift,
-                                                        int32_t* __restrict__ hist, int n_tiles) {
+__device__ __forceinline__ u64 gen_entry(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                         int32_t n_nodes, int64_t i) {
+    const int64_t e = i >> 1;
+    const int32_t a = src[e], b = dst[e];
+    const bool ok = a >= 0 && a < n_nodes && b >= 0 && b < n_nodes;
+    u32 key = (u32)n_nodes;                                                    // sentinel: sorts behind every node
+    if (ok) {
+        if ((i & 1) == 0) key = (u32)a;
+        else if (b != a) key = (u32)b;                                         // a self-loop keeps only its src end
+    }
+    return ((u64)key << 32) | (u64)(u32)i;
+}
+
+template <bool GEN>
+__global__ void __launch_bounds__(kT) radix_hist_kernel(const u64* __restrict__ pairs, const int32_t* __restrict__ src,
+                                                        const int32_t* __restrict__ dst, int32_t n_nodes, int64_t n,
+                                                        int shift, int32_t* __restrict__ hist, int n_tiles,
+                                                        int32_t* __restrict__ deg) {
     __shared__ int h[256];
     h[threadIdx.x] = 0;
     __syncthreads();
@@ -147,37 +152,43 @@ __global__ void __launch_bounds__(kT) radix_hist_kernel(const u32* __restrict__ 
 #pragma unroll
     for (int r = 0; r < kRTile / kT; ++r) {
         const int64_t i = base + (int64_t)r * kT + threadIdx.x;
-        if (i < n) atomicAdd(&h[(keys[i] >> shift) & 255u], 1);
+        if (i < n) {
+            const u64 pr = GEN ? gen_entry(src, dst, n_nodes, i) : pairs[i];
+            const u32 key = (u32)(pr >> 32);
+            atomicAdd(&h[(key >> shift) & 255u], 1);
+            if (GEN && key != (u32)n_nodes) atomicAdd(deg + key, 1);          // degrees, once, while generating
+        }
     }
     __syncthreads();
     hist[(size_t)threadIdx.x * n_tiles + blockIdx.x] = h[threadIdx.x];       // digit-major: a flat scan gives the bases
 }
 
-// Item order inside a tile is index order: warp w owns items [w*512, (w+1)*512) and walks them 32 at a time,
-// so (warp, round, lane) order = index order and the ranks below are stable.
-__global__ void __launch_bounds__(kT) radix_scatter_kernel(const u32* __restrict__ keys_in, const u32* __restrict__ vals_in,
-                                                           u32* __restrict__ keys_out, u32* __restrict__ vals_out,
+template <bool GEN, bool LAST>
+__global__ void __launch_bounds__(kT) radix_scatter_kernel(const u64* __restrict__ pairs_in, const int32_t* __restrict__ src,
+                                                           const int32_t* __restrict__ dst, int32_t n_nodes,
+                                                           u64* __restrict__ pairs_out, u32* __restrict__ vals_out,
                                                            int64_t n, int shift, const int64_t* __restrict__ base,
                                                            int n_tiles) {
-    __shared__ int wcnt[kRWarps][256];
-    __shared__ long long wbase[kRWarps][256];
+    __shared__ u64 stage[kRTile];                                             // 32 KB: the tile in digit order
+    __shared__ int wcnt[kRWarps][256];                                        // per (warp, digit): count, then local start
+    __shared__ long long gdelta[256];                                         // global position - local position, per digit
+    __shared__ int s_warp_tot[kRWarps];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < kRWarps * 256; i += kT) (&wcnt[0][0])[i] = 0;
     __syncthreads();
     const int64_t start = (int64_t)blockIdx.x * kRTile + (int64_t)warp * kRWarpItems;
-    u32 key[kRRounds], val[kRRounds];
+    u64 pr[kRRounds];
     int rank[kRRounds];
     const unsigned lt = (1u << lane) - 1u;
 #pragma unroll
     for (int r = 0; r < kRRounds; ++r) {
         const int64_t i = start + r * 32 + lane;
         const bool valid = i < n;
-        key[r] = valid ? keys_in[i] : 0u;
-        val[r] = valid ? vals_in[i] : 0u;
+        pr[r] = valid ? (GEN ? gen_entry(src, dst, n_nodes, i) : pairs_in[i]) : 0ull;
         const unsigned live = __ballot_sync(0xffffffffu, valid);
         rank[r] = 0;
         if (valid) {
-            const int d = (int)((key[r] >> shift) & 255u);
+            const int d = (int)((pr[r] >> (32 + shift)) & 255ull);
             const unsigned peers = __match_any_sync(live, d);
             const int leader = __ffs(peers) - 1;
             int old = 0;
@@ -189,21 +200,44 @@ __global__ void __launch_bounds__(kT) radix_scatter_kernel(const u32* __restrict
     }
     __syncthreads();
     {
-        const int d = threadIdx.x;                                            // 256 threads <-> 256 digits
-        long long run = base[(size_t)d * n_tiles + blockIdx.x];
+        // thread d: the digit's count over the warps, an exclusive scan over digits for its start in the tile,
+        // then every warp's start inside the digit's run
+        const int d = threadIdx.x;
+        int tot = 0;
 #pragma unroll
-        for (int w = 0; w < kRWarps; ++w) { wbase[w][d] = run; run += wcnt[w][d]; }
+        for (int w = 0; w < kRWarps; ++w) tot += wcnt[w][d];
+        int incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp_tot[warp] = incl;
+        __syncthreads();
+        int before = 0;
+#pragma unroll
+        for (int w = 0; w < kRWarps; ++w) if (w < warp) before += s_warp_tot[w];
+        int run = before + incl - tot;                                        // first tile-local slot of digit d
+        gdelta[d] = base[(size_t)d * n_tiles + blockIdx.x] - run;
+#pragma unroll
+        for (int w = 0; w < kRWarps; ++w) { const int c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
     }
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < kRRounds; ++r) {
         const int64_t i = start + r * 32 + lane;
         if (i < n) {
-            const int d = (int)((key[r] >> shift) & 255u);
-            const long long pos = wbase[warp][d] + rank[r];
-            keys_out[pos] = key[r];
-            vals_out[pos] = val[r];
+            const int d = (int)((pr[r] >> (32 + shift)) & 255ull);
+            stage[wcnt[warp][d] + rank[r]] = pr[r];
         }
+    }
+    __syncthreads();
+    const int n_here = (int)min((int64_t)kRTile, n - (int64_t)blockIdx.x * kRTile);
+    for (int j = threadIdx.x; j < n_here; j += kT) {
+        const u64 v = stage[j];
+        const long long pos = gdelta[(int)((v >> (32 + shift)) & 255ull)] + j;
+        if (LAST) vals_out[pos] = (u32)v;
+        else pairs_out[pos] = v;
     }
 }
 
@@ -215,7 +249,7 @@ int key_passes(int32_t n_nodes) {
     return (bits + 7) / 8;
 }
 
-struct CsrLayout { size_t keys0, keys1, vals1, deg, hist, hist_off, tmp, total; };
+struct CsrLayout { size_t pairs0, pairs1, deg, hist, hist_off, tmp, total; };
 
 CsrLayout csr_layout(int64_t n_edges, int32_t n_nodes) {
     CsrLayout L;
@@ -223,9 +257,9 @@ CsrLayout csr_layout(int64_t n_edges, int32_t n_nodes) {
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
     const size_t n_ent = (size_t)2 * n_edges;
     const size_t rt = (size_t)radix_tiles((int64_t)n_ent);
-    L.keys0 = take(n_ent * 4);
-    L.keys1 = take(n_ent * 4);
-    L.vals1 = take(n_ent * 4);
+    const int passes = key_passes(n_nodes);
+    L.pairs0 = take(passes >= 2 ? n_ent * 8 : 0);
+    L.pairs1 = take(passes >= 3 ? n_ent * 8 : 0);
     L.deg = take(((size_t)n_nodes + 1) * 4);
     L.hist = take(256 * rt * 4);
     L.hist_off = take(256 * rt * 8);
@@ -299,32 +333,29 @@ extern "C" int lz_csr_build(const int32_t* src, const int32_t* dst, int64_t n_ed
     unsigned char* s = (unsigned char*)scratch;
     const int64_t n_ent = 2 * n_edges;
     const int passes = key_passes(n_nodes);
-    u32* kbuf[2] = {(u32*)(s + L.keys0), (u32*)(s + L.keys1)};
-    // the last pass must land in `adj`: with an even number of passes the entries start there
-    u32* vbuf[2];
-    vbuf[0] = (passes % 2 == 0) ? adj : (u32*)(s + L.vals1);
-    vbuf[1] = (passes % 2 == 0) ? (u32*)(s + L.vals1) : adj;
+    u64* pbuf[2] = {(u64*)(s + L.pairs0), (u64*)(s + L.pairs1)};
     int32_t* deg = (int32_t*)(s + L.deg);
     int32_t* hist = (int32_t*)(s + L.hist);
     int64_t* hist_off = (int64_t*)(s + L.hist_off);
     int64_t* tmp = (int64_t*)(s + L.tmp);
     LZ_CUDA(cudaMemsetAsync(deg, 0, ((size_t)n_nodes + 1) * 4, st));
-    const int sms = lz_sm_count();
-    int64_t eblocks = (n_edges + kT - 1) / kT;
-    if (eblocks > (int64_t)sms * 16) eblocks = (int64_t)sms * 16;
-    csr_entries_kernel<<<(unsigned)eblocks, kT, 0, st>>>(src, dst, n_edges, n_nodes, kbuf[0], vbuf[0], deg);
-    LZ_CUDA(cudaGetLastError());
-    // offsets[v] = first entry of node v; offsets[n_nodes] = number of real entries (deg[n_nodes] is 0)
-    if (int rc = exclusive_scan(deg, (int64_t)n_nodes + 1, offsets, tmp, nullptr, st)) return rc;
     const int rt = radix_tiles(n_ent);
     for (int pass = 0; pass < passes; ++pass) {
-        const int in = pass & 1, out = in ^ 1;
-        radix_hist_kernel<<<rt, kT, 0, st>>>(kbuf[in], n_ent, pass * 8, hist, rt);
+        const bool first = pass == 0, last = pass == passes - 1;
+        const u64* in = first ? nullptr : pbuf[(pass - 1) & 1];
+        u64* out = last ? nullptr : pbuf[pass & 1];
+        const int shift = pass * 8;
+        if (first) radix_hist_kernel<true><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, n_ent, shift, hist, rt, deg);
+        else radix_hist_kernel<false><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, n_ent, shift, hist, rt, deg);
         if (int rc = exclusive_scan(hist, (int64_t)256 * rt, hist_off, tmp, nullptr, st)) return rc;
-        radix_scatter_kernel<<<rt, kT, 0, st>>>(kbuf[in], vbuf[in], kbuf[out], vbuf[out], n_ent, pass * 8, hist_off, rt);
+        if (first && last) radix_scatter_kernel<true, true><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, out, adj, n_ent, shift, hist_off, rt);
+        else if (first) radix_scatter_kernel<true, false><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, out, adj, n_ent, shift, hist_off, rt);
+        else if (last) radix_scatter_kernel<false, true><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, out, adj, n_ent, shift, hist_off, rt);
+        else radix_scatter_kernel<false, false><<<rt, kT, 0, st>>>(in, src, dst, n_nodes, out, adj, n_ent, shift, hist_off, rt);
         LZ_CUDA(cudaGetLastError());
     }
-    return LZ_OK;
+    // offsets[v] = first entry of node v; offsets[n_nodes] = number of real entries (deg[n_nodes] stays 0)
+    return exclusive_scan(deg, (int64_t)n_nodes + 1, offsets, tmp, nullptr, st);
 }
 
 extern "C" int lz_neighbors(const int64_t* offsets, const uint32_t* adj, const int32_t* src, const int32_t* dst,

@@ -194,10 +194,13 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
 }
 
 // One CTA per query: stream the per-chunk lists through a selector.
+constexpr int kMergePer = 8;
+constexpr int kMergeMaxLists = 8192;
 struct MergeParams {
     const u64* part_key; const u32* part_id; const int32_t* part_cnt;   // form A: scan partials
     const int64_t* in_ids; const double* in_scores; int n_queries;      // form B: (id, score) lists
     int n_lists; int k; int cap; int metric; int64_t id_base;
+    int max_lists;                                                      // lists whose prefix offsets fit behind the selector (0: flat merge)
     const int32_t* work_list; const int32_t* work_count;
     int64_t* out_ids; double* out_scores; int32_t* out_counts;
 };
@@ -213,25 +216,138 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
     const int q = p.work_list ? p.work_list[item] : item;
     if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
     __syncthreads();
+    // Every list arrives sorted best-first.  Take each list's r-th best entry m_c; the ceil(k/r)-th largest m_c is
+    // a value T with at least ceil(k/r) lists holding r entries >= T, i.e. at least k entries >= T overall, so T
+    // is a lower bound of the merged k-th best: start from it (ties admitted).  With lists that are slices of
+    // one population (per-CTA partials) a small r makes T tight, and only about k entries get past it — a full
+    // list's own k-th entry (r = k) is a far weaker bound, and admitting n_lists * k entries through the
+    // selector was most of this kernel's time.
+    {
+        int r = (4 * p.k + p.n_lists - 1) / p.n_lists;
+        r = r < 1 ? 1 : (r > p.k ? p.k : r);
+        const int need = (p.k + r - 1) / r;
+        if (tid == 0) sel.k = need;
+        __syncthreads();
+        for (int base = 0; base < p.n_lists; base += kThreads) {
+            const int c = base + tid;
+            if (c < p.n_lists) {
+                u64 m = 0ull;
+                if (p.part_key) {
+                    const size_t slot = (size_t)q * p.n_lists + c;
+                    if (p.part_cnt[slot] >= r) m = p.part_key[slot * p.k + r - 1];
+                } else {
+                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + r - 1;
+                    const double sc = p.in_scores[at];
+                    if (p.in_ids[at] >= 0 && sc == sc) m = lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc);
+                }
+                if (m != 0ull) lz_sel_push(&sel, m, (u32)c);
+            }
+            lz_sel_maybe_compact<kThreads>(&sel, kThreads);
+        }
+        __syncthreads();
+        lz_sel_compact<kThreads>(&sel);
+        if (tid == 0) {
+            const u64 T = sel.count >= need ? sel.key[need - 1] : 0ull;
+            lz_sel_init(&sel, keys, ids, p.cap, p.k);
+            if (T != 0ull) { sel.thr_key = T - 1; sel.thr_id = 0u; }       // beat (T-1, 0): any entry with key >= T
+        }
+        __syncthreads();
+    }
+    if (p.n_lists <= p.max_lists) {
+        // The lists are sorted best-first (valid entries first), so the entries that can matter are a PREFIX of
+        // each list: those at or above the seed, or simply the valid ones when no list was full.  One binary
+        // search per list finds the prefix length, a scan lays the prefixes end to end, and only those entries
+        // (about k in all when seeded) are fetched — not n_lists * k slots.
+        int* s_off = reinterpret_cast<int*>(ids + p.cap);                     // [n_lists + 1], behind the selector
+        const u64 seed = sel.thr_key != 0ull ? sel.thr_key + 1 : 1ull;        // key 0 = invalid slot
+        const int per = (p.n_lists + kThreads - 1) / kThreads;
+        const int c0 = min(p.n_lists, tid * per), c1 = min(p.n_lists, c0 + per);
+        int mine = 0;
+        for (int c = c0; c < c1; ++c) {
+            const size_t slot = (size_t)q * p.n_lists + c;
+            int lo = 0, hi = p.part_key ? p.part_cnt[slot] : p.k;              // first j in [lo, hi] with key_j < seed
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                u64 key;
+                if (p.part_key) {
+                    key = p.part_key[slot * p.k + mid];
+                } else {
+                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + mid;
+                    const double sc = p.in_scores[at];
+                    key = (p.in_ids[at] >= 0 && sc == sc) ? lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc) : 0ull;
+                }
+                if (key >= seed) lo = mid + 1; else hi = mid;
+            }
+            s_off[c + 1] = lo;                                                  // prefix length, scanned below
+            mine += lo;
+        }
+        __shared__ int s_wsum[kThreads / 32];
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if ((tid & 31) >= o) incl += t;
+        }
+        if ((tid & 31) == 31) s_wsum[tid >> 5] = incl;
+        __syncthreads();
+        int run = incl - mine;
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; ++w) if (w < (tid >> 5)) run += s_wsum[w];
+        for (int c = c0; c < c1; ++c) { const int len = s_off[c + 1]; s_off[c + 1] = run + len; run += len; }
+        if (tid == 0) s_off[0] = 0;
+        __syncthreads();
+        const int Q = s_off[p.n_lists];
+        for (int base = 0; base < Q; base += kMergePer * kThreads) {
+#pragma unroll
+            for (int u = 0; u < kMergePer; ++u) {
+                const int t = base + u * kThreads + tid;
+                if (t < Q) {
+                    int lo = 0, hi = p.n_lists - 1;                             // the list c with s_off[c] <= t < s_off[c+1]
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (s_off[mid] <= t) lo = mid; else hi = mid - 1;
+                    }
+                    const int c = lo, j = t - s_off[c];
+                    if (p.part_key) {
+                        const size_t slot = (size_t)q * p.n_lists + c;
+                        lz_sel_push(&sel, p.part_key[slot * p.k + j], p.part_id[slot * p.k + j]);
+                    } else {
+                        const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
+                        const double sc = p.in_scores[at];
+                        lz_sel_push(&sel, lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc), (u32)p.in_ids[at]);
+                    }
+                }
+            }
+            lz_sel_maybe_compact<kThreads>(&sel, kMergePer * kThreads);
+        }
+    } else {
+    // kMergePer entries per thread and round, loads issued together: one memory round trip per 2048 entries
     const int64_t total = (int64_t)p.n_lists * p.k;
-    for (int64_t base = 0; base < total; base += kThreads) {
-        const int64_t i = base + tid;
-        if (i < total) {
-            const int c = (int)(i / p.k), j = (int)(i - (int64_t)c * p.k);
-            if (p.part_key) {
-                const size_t slot = (size_t)q * p.n_lists + c;
-                if (j < p.part_cnt[slot]) lz_sel_push(&sel, p.part_key[slot * p.k + j], p.part_id[slot * p.k + j]);
-            } else {
-                const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
-                const int64_t id = p.in_ids[at];
-                const double s = p.in_scores[at];
-                if (id >= 0 && s == s) {
-                    const double v = (p.metric == LZ_COSINE) ? s + 0.0 : 0.0 - s;
-                    lz_sel_push(&sel, lz_ord(v), (u32)id);
+    for (int64_t base = 0; base < total; base += kMergePer * kThreads) {
+        u64 mk[kMergePer];
+        u32 mi[kMergePer];
+#pragma unroll
+        for (int u = 0; u < kMergePer; ++u) {
+            const int64_t i = base + (int64_t)u * kThreads + tid;
+            mk[u] = 0ull; mi[u] = 0u;
+            if (i < total) {
+                const int c = (int)(i / p.k), j = (int)(i - (int64_t)c * p.k);
+                if (p.part_key) {
+                    const size_t slot = (size_t)q * p.n_lists + c;
+                    if (j < p.part_cnt[slot]) { mk[u] = p.part_key[slot * p.k + j]; mi[u] = p.part_id[slot * p.k + j]; }
+                } else {
+                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
+                    const int64_t id = p.in_ids[at];
+                    const double s = p.in_scores[at];
+                    if (id >= 0 && s == s) { mk[u] = lz_ord((p.metric == LZ_COSINE) ? s + 0.0 : 0.0 - s); mi[u] = (u32)id; }
                 }
             }
         }
-        lz_sel_maybe_compact<kThreads>(&sel, kThreads);
+#pragma unroll
+        for (int u = 0; u < kMergePer; ++u)
+            if (mk[u] != 0ull) lz_sel_push(&sel, mk[u], mi[u]);
+        lz_sel_maybe_compact<kThreads>(&sel, kMergePer * kThreads);
+    }
     }
     __syncthreads();
     lz_sel_compact<kThreads>(&sel);
@@ -412,10 +528,11 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
     m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries;
-    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = id_base;
+    m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = metric; m.id_base = id_base;
     m.work_list = work_list; m.work_count = work_count;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
-    const size_t msmem = (size_t)m.cap * 12;
+    m.max_lists = m.n_lists <= kMergeMaxLists ? kMergeMaxLists : 0;
+    const size_t msmem = (size_t)m.cap * 12 + (m.max_lists ? ((size_t)m.n_lists + 1) * 4 : 0);
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
     int mgrid = n_queries;
     if (work_list && mgrid > lz_sm_count() * 8) mgrid = lz_sm_count() * 8;
@@ -444,10 +561,11 @@ extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int
     MergeParams m;
     m.part_key = nullptr; m.part_id = nullptr; m.part_cnt = nullptr;
     m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries;
-    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = metric; m.id_base = 0;
+    m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = metric; m.id_base = 0;
     m.work_list = nullptr; m.work_count = nullptr;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
-    const size_t msmem = (size_t)m.cap * 12;
+    m.max_lists = m.n_lists <= kMergeMaxLists ? kMergeMaxLists : 0;
+    const size_t msmem = (size_t)m.cap * 12 + (m.max_lists ? ((size_t)m.n_lists + 1) * 4 : 0);
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
     merge_kernel<<<n_queries, kThreads, msmem, (cudaStream_t)stream>>>(m);
     LZ_CUDA(cudaGetLastError());
@@ -542,12 +660,24 @@ struct EvictParams {
     int64_t n; double now; int k, cap, n_chunks;
     double* out_all;                                       // optional: importance of every node
     u64* part_key; u32* part_id; int32_t* part_cnt;
+    u64* gthr;                                             // best k-th key any CTA has reached (0 = none yet)
+    int64_t stride;                                        // 1, or > 1 in the sampling pass (CTA b reads tile b*stride)
+    int sample;                                            // sampling pass: publish the threshold, write no list
 };
 
 __device__ __forceinline__ double importance_of(double sal, int access, double last, double now) {
     const double days = __ddiv_rn(__dsub_rn(now, last), 86400.0);
     const double t1 = __dmul_rn(sal, 0.5);
-    const double t2 = __dmul_rn(fmin(1.0, __ddiv_rn((double)access, 10.0)), 0.3);
+    // access / 10 for 0 <= access < 10 is the correctly rounded quotient = the double nearest to the decimal
+    // tenth, which is what these literals are; >= 10 saturates at 1.0 (saves one float64 division per node)
+    double frac;
+    switch (access) {
+        case 0: frac = 0.0; break; case 1: frac = 0.1; break; case 2: frac = 0.2; break; case 3: frac = 0.3; break;
+        case 4: frac = 0.4; break; case 5: frac = 0.5; break; case 6: frac = 0.6; break; case 7: frac = 0.7; break;
+        case 8: frac = 0.8; break; case 9: frac = 0.9; break;
+        default: frac = access >= 10 ? 1.0 : fmin(1.0, __ddiv_rn((double)access, 10.0));
+    }
+    const double t2 = __dmul_rn(frac, 0.3);
     const double t3 = __dmul_rn(__ddiv_rn(1.0, __dadd_rn(1.0, days)), 0.2);
     return __dadd_rn(__dadd_rn(t1, t2), t3);
 }
@@ -561,23 +691,40 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
     if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
     __syncthreads();
     const int64_t n_tiles = (p.n + kEvictChunk - 1) / kEvictChunk;
-    for (int64_t t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+    for (int64_t t = (int64_t)blockIdx.x * p.stride; t < n_tiles; t += (int64_t)gridDim.x * p.stride) {
         const int64_t base = t * kEvictChunk;
+        // any CTA's k-th best key bounds the global k-th best from below: every thread filters against the best
+        // one published so far (ties admitted), so after the first tiles almost nothing is pushed any more
+        u64 g;
+        asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(g) : "l"(p.gthr) : "memory");
+        // all of the tile's loads are issued before the first push (a push is a warp vote + shared-memory
+        // traffic the compiler will not move loads across): one memory round trip per tile, not sixteen
+        u64 key[kEvictPerThread];
 #pragma unroll
         for (int j = 0; j < kEvictPerThread; ++j) {
-            const int64_t i = base + (int64_t)j * kThreads + tid;          // coalesced across the CTA
+            const int64_t i = base + (int64_t)j * kThreads + tid;                // coalesced across the CTA
+            key[j] = 0ull;                                                        // 0 = nothing to push
             if (i < p.n) {
                 const double s = p.sal64 ? p.sal64[i] : (double)p.sal32[i];
                 const double imp = importance_of(s, p.access[i], p.last[i], p.now);
-                if (p.out_all) p.out_all[i] = imp;
+                if (p.out_all && !p.sample) p.out_all[i] = imp;
                 // larger key = better = LESS important; NaN importance is never evicted
-                if (imp == imp && !(p.skip && p.skip[i])) lz_sel_push(&sel, lz_ord(0.0 - imp), (u32)i);
+                const u64 kk = lz_ord(0.0 - imp);
+                if (imp == imp && kk >= g && !(p.skip && p.skip[i])) key[j] = kk;
             }
         }
+#pragma unroll
+        for (int j = 0; j < kEvictPerThread; ++j)
+            lz_sel_push_warp(&sel, key[j], (u32)(base + (int64_t)j * kThreads + tid), key[j] != 0ull);
         lz_sel_maybe_compact<kThreads>(&sel, kEvictChunk);
+        if (tid == 0 && sel.thr_key != 0ull) atomicMax(p.gthr, sel.thr_key);
     }
     __syncthreads();
     lz_sel_compact<kThreads>(&sel);
+    if (p.sample) {                                        // the sample's k-th best bounds the k-th best of everything
+        if (tid == 0 && sel.thr_key != 0ull) atomicMax(p.gthr, sel.thr_key);
+        return;
+    }
     const int n = min(sel.count, p.k);
     const size_t slot = blockIdx.x;
     for (int j = tid; j < n; j += kThreads) {
@@ -587,17 +734,17 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
     if (tid == 0) p.part_cnt[slot] = n;
 }
 
-int evict_chunks(int64_t n) {
+int evict_chunks(int64_t n, int k) {
     const int sms = lz_sm_count();
     int64_t tiles = (n + kEvictChunk - 1) / kEvictChunk;
-    int64_t want = (int64_t)(sms > 0 ? sms : 1) * 2;
+    int64_t want = (int64_t)(sms > 0 ? sms : 1) * (k <= 256 ? 4 : 2);      // selector: 12 B x next_pow2(k + 2048) of shared memory
     return (int)(tiles < want ? (tiles < 1 ? 1 : tiles) : want);
 }
 }  // namespace
 
 extern "C" size_t lz_evict_lowest_scratch_bytes(int64_t n, int k) {
     if (n <= 0 || k <= 0) return 0;
-    return lz_search_exact_scratch_bytes(1, k, evict_chunks(n));
+    return lz_search_exact_scratch_bytes(1, k, evict_chunks(n, k)) + 256;       // + the shared threshold word
 }
 
 extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const int32_t* access_count,
@@ -614,8 +761,9 @@ extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const 
                "lz_evict_lowest: NULL pointer");
     LZ_REQUIRE(k <= LZ_MAX_K, "lz_evict_lowest: k=%d exceeds %d (evict in rounds)", k, LZ_MAX_K);
     LZ_REQUIRE(n <= 0xfffffffeLL, "lz_evict_lowest: n=%lld exceeds 32-bit indices", (long long)n);
-    const int chunks = evict_chunks(n);
-    const size_t need = lz_search_exact_scratch_bytes(1, k, chunks);
+    const int chunks = evict_chunks(n, k);
+    const size_t part_bytes = lz_search_exact_scratch_bytes(1, k, chunks);
+    const size_t need = part_bytes + 256;
     if (scratch_bytes < need) {
         lz_set_error("lz_evict_lowest: scratch has %zu bytes, needs %zu", scratch_bytes, need);
         return LZ_ERR_SCRATCH;
@@ -630,17 +778,21 @@ extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const 
     p.part_key = (u64*)s;
     p.part_id = (u32*)(s + slots * k * sizeof(u64));
     p.part_cnt = (int32_t*)(s + (((slots * k * (sizeof(u64) + sizeof(u32))) + 15) & ~(size_t)15));
+    p.gthr = (u64*)(s + part_bytes);
+    LZ_CUDA(cudaMemsetAsync(p.gthr, 0, 8, st));
     const size_t smem = (size_t)p.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(importance_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    p.stride = 1; p.sample = 0;
     importance_select_kernel<<<chunks, kThreads, smem, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
     m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = 1;
-    m.n_lists = chunks; m.k = k; m.cap = lz_next_pow2(k + kThreads); m.metric = LZ_L2;   // L2 form returns -key = importance
+    m.n_lists = chunks; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = LZ_L2;   // L2 form returns -key = importance
     m.id_base = 0; m.work_list = nullptr; m.work_count = nullptr;
     m.out_ids = out_idx; m.out_scores = out_importance; m.out_counts = out_count;
-    const size_t msmem = (size_t)m.cap * 12;
+    m.max_lists = m.n_lists <= kMergeMaxLists ? kMergeMaxLists : 0;
+    const size_t msmem = (size_t)m.cap * 12 + (m.max_lists ? ((size_t)m.n_lists + 1) * 4 : 0);
     LZ_CUDA(cudaFuncSetAttribute(merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
     merge_kernel<<<1, kThreads, msmem, st>>>(m);
     LZ_CUDA(cudaGetLastError());

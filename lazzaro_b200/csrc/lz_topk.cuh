@@ -33,6 +33,23 @@ __device__ __forceinline__ void lz_sel_push(LzSelector* s, u64 key, u32 id) {
     }
 }
 
+// All 32 lanes of a warp, convergently; `want` says whether this lane has an entry.  One shared-memory atomic
+// per warp instead of one per entry (hundreds of lanes hammering the one counter serialise).
+__device__ __forceinline__ void lz_sel_push_warp(LzSelector* s, u64 key, u32 id, bool want) {
+    const bool ok = want && lz_better(key, id, s->thr_key, s->thr_id);
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if (m == 0u) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(&s->count, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (ok) {
+        const int pos = base + __popc(m & ((1u << lane) - 1u));
+        s->key[pos] = key;
+        s->id[pos] = id;
+    }
+}
+
 // All threads of the CTA (T threads). Sorts descending, keeps the best k, tightens the threshold.
 template <int T>
 __device__ void lz_sel_compact(LzSelector* s) {

@@ -21,7 +21,7 @@ rows = list(csv.reader(io.StringIO(src)))
 h = rows[1]
 ismp, iex, isrc = h.index("# Samples"), h.index("Instructions Executed"), h.index("Source")
 stall = [i for i, x in enumerate(h) if x.startswith("stall_") and "Not Issued" not in x]
-data = [(int(r[ismp] or 0), int(r[iex] or 0), r[isrc], r) for r in rows[2:] if len(r) > iex]
+data = [(int(r[ismp] or 0), int(r[iex] or 0), r[isrc], r) for r in rows[2:] if len(r) > iex and (r[ismp] or "0").isdigit()]
 print("total samples", sum(d[0] for d in data), "total inst", sum(d[1] for d in data))
 for d in sorted(data, key=lambda x: -x[0])[:top]:
     st = sorted(((int(d[3][i] or 0), h[i]) for i in stall), reverse=True)[:2]
