@@ -149,14 +149,20 @@ __global__ void __launch_bounds__(kT) radix_hist_kernel(const u64* __restrict__ 
     h[threadIdx.x] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * kRTile;
+    // all loads of the tile first (atomics are ordering points the compiler keeps loads behind)
+    u32 key[kRTile / kT];
+#pragma unroll
+    for (int r = 0; r < kRTile / kT; ++r) {
+        const int64_t i = base + (int64_t)r * kT + threadIdx.x;
+        key[r] = 0xffffffffu;
+        if (i < n) key[r] = (u32)((GEN ? gen_entry(src, dst, n_nodes, i) : pairs[i]) >> 32);
+    }
 #pragma unroll
     for (int r = 0; r < kRTile / kT; ++r) {
         const int64_t i = base + (int64_t)r * kT + threadIdx.x;
         if (i < n) {
-            const u64 pr = GEN ? gen_entry(src, dst, n_nodes, i) : pairs[i];
-            const u32 key = (u32)(pr >> 32);
-            atomicAdd(&h[(key >> shift) & 255u], 1);
-            if (GEN && key != (u32)n_nodes) atomicAdd(deg + key, 1);          // degrees, once, while generating
+            atomicAdd(&h[(key[r] >> shift) & 255u], 1);
+            if (GEN && key[r] != (u32)n_nodes) atomicAdd(deg + key[r], 1);    // degrees, once, while generating
         }
     }
     __syncthreads();
@@ -189,7 +195,14 @@ __global__ void __launch_bounds__(kT) radix_scatter_kernel(const u64* __restrict
         rank[r] = 0;
         if (valid) {
             const int d = (int)((pr[r] >> (32 + shift)) & 255ull);
-            const unsigned peers = __match_any_sync(live, d);
+            // lanes holding the same digit: eight votes, one per digit bit (measured: MATCH.ANY's result latency
+            // made this loop the kernel's bound — 28 short-scoreboard stall cycles per issue)
+            unsigned peers = live;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                const unsigned m = __ballot_sync(live, (d >> b) & 1);
+                peers &= ((d >> b) & 1) ? m : ~m;
+            }
             const int leader = __ffs(peers) - 1;
             int old = 0;
             if (lane == leader) { old = wcnt[warp][d]; wcnt[warp][d] = old + __popc(peers); }
