@@ -262,6 +262,20 @@ int lz_neighbors(const int64_t* offsets, const uint32_t* adj, const int32_t* src
                  const float* weight, int32_t n_nodes, const int32_t* nodes, int n_queries, double min_weight,
                  int max_out, int32_t* out_nbr, int32_t* out_edge, int32_t* out_count, void* stream);
 
+/* ---- edge upsert (stands behind MemoryShard.add_edge, core/memory_shard.py:42-52) ------------------------ */
+
+/* out_edge[q] = index of the edge with src == q_src[q] and dst == q_dst[q] (the reference's dict key
+ * (source, target), memory_shard.py:44), or -1; found on the CSR of lz_csr_build (`dst` is the edge table's
+ * column).  q_src, q_dst, out_edge: int32 [n_queries]. */
+int lz_edge_find(const int64_t* offsets, const uint32_t* adj, const int32_t* dst, int32_t n_nodes,
+                 const int32_t* q_src, const int32_t* q_dst, int n_queries, int32_t* out_edge, void* stream);
+
+/* Reinforcement of existing edges (memory_shard.py:45-49): for each i < m, `times[i]` times (1 if times is NULL)
+ * weight[e] = min(1.0, weight[e] + 0.1) — float64 add and min, stored float32 — and co_occurrence[e] += times[i],
+ * e = edge_idx[i].  Indices outside [0, n_edges) are skipped; an index must not repeat within one call. */
+int lz_edge_reinforce(float* weight, int32_t* co_occurrence, int64_t n_edges, const int32_t* edge_idx,
+                      const int32_t* times, int64_t m, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

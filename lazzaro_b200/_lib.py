@@ -46,6 +46,8 @@ SIGNATURES = {
     "lz_csr_build_scratch_bytes": (_sz, [_i64, _i32]),
     "lz_csr_build": (_i32, [_p, _p, _i64, _i32, _p, _sz, _p, _p, _p]),
     "lz_neighbors": (_i32, [_p, _p, _p, _p, _p, _i32, _p, _i32, _f64, _i32, _p, _p, _p, _p]),
+    "lz_edge_find": (_i32, [_p, _p, _p, _i32, _p, _p, _i32, _p, _p]),
+    "lz_edge_reinforce": (_i32, [_p, _p, _i64, _p, _p, _i64, _p]),
 }
 
 

@@ -383,3 +383,70 @@ extern "C" int lz_neighbors(const int64_t* offsets, const uint32_t* adj, const i
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
+
+// ---- edge lookup and reinforcement (stands behind MemoryShard.add_edge, core/memory_shard.py:42-52) ----------
+// add_edge keys its dict by (source, target): an existing key is reinforced (weight = min(1, weight + 0.1),
+// co_occurrence += 1), a new one is inserted.  The lookup runs on the CSR: a warp walks the source node's
+// entries and reports the edge whose source end it is and whose target matches (the lowest such edge index).
+namespace {
+__global__ void __launch_bounds__(kT) edge_find_kernel(const int64_t* __restrict__ offsets, const u32* __restrict__ adj,
+                                                       const int32_t* __restrict__ dst, int32_t n_nodes,
+                                                       const int32_t* __restrict__ q_src, const int32_t* __restrict__ q_dst,
+                                                       int n_queries, int32_t* __restrict__ out_edge) {
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * (kT / 32) + (threadIdx.x >> 5);
+    if (q >= n_queries) return;
+    const int32_t a = q_src[q], b = q_dst[q];
+    int32_t found = -1;
+    if (a >= 0 && a < n_nodes) {
+        const int64_t lo = offsets[a], hi = offsets[a + 1];
+        for (int64_t base = lo; base < hi && found < 0; base += 32) {
+            const int64_t i = base + lane;
+            bool hit = false;
+            u32 ent = 0u;
+            if (i < hi) {
+                ent = adj[i];
+                hit = (ent & 1u) == 0u && dst[ent >> 1] == b;                 // a's source end of an edge to b
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, hit);
+            if (m) found = (int32_t)(__shfl_sync(0xffffffffu, ent, __ffs(m) - 1) >> 1);   // entries ascend by edge
+        }
+    }
+    if (lane == 0) out_edge[q] = found;
+}
+
+__global__ void __launch_bounds__(kT) edge_reinforce_kernel(float* __restrict__ weight, int32_t* __restrict__ cooc,
+                                                            const int32_t* __restrict__ edge_idx,
+                                                            const int32_t* __restrict__ times, int64_t m, int64_t n_edges) {
+    const int64_t i = (int64_t)blockIdx.x * kT + threadIdx.x;
+    if (i >= m) return;
+    const int32_t e = edge_idx[i];
+    const int t = times ? times[i] : 1;
+    if (e < 0 || e >= n_edges || t <= 0) return;
+    float w = weight[e];
+    for (int r = 0; r < t; ++r) w = (float)fmin(1.0, __dadd_rn((double)w, 0.1));   // float64 add, stored float32
+    weight[e] = w;
+    cooc[e] += t;
+}
+}  // namespace
+
+extern "C" int lz_edge_find(const int64_t* offsets, const uint32_t* adj, const int32_t* dst, int32_t n_nodes,
+                            const int32_t* q_src, const int32_t* q_dst, int n_queries, int32_t* out_edge, void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    LZ_REQUIRE(offsets && q_src && q_dst && out_edge, "lz_edge_find: NULL pointer");
+    LZ_REQUIRE(n_nodes >= 0, "lz_edge_find: n_nodes=%d", n_nodes);
+    edge_find_kernel<<<(n_queries + kT / 32 - 1) / (kT / 32), kT, 0, (cudaStream_t)stream>>>(
+        offsets, adj, dst, n_nodes, q_src, q_dst, n_queries, out_edge);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" int lz_edge_reinforce(float* weight, int32_t* co_occurrence, int64_t n_edges, const int32_t* edge_idx,
+                                 const int32_t* times, int64_t m, void* stream) {
+    if (m <= 0) return LZ_OK;
+    LZ_REQUIRE(weight && co_occurrence && edge_idx, "lz_edge_reinforce: NULL pointer");
+    edge_reinforce_kernel<<<(unsigned)((m + kT - 1) / kT), kT, 0, (cudaStream_t)stream>>>(weight, co_occurrence, edge_idx,
+                                                                                         times, m, n_edges);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

@@ -145,7 +145,7 @@ class MemoryShard:
         self._names: List[str] = []
         self._table = EdgeTable(device)
         self._edge_meta: Dict[Tuple[int, int], Tuple[str, float]] = {}   # (edge_type, last_updated)
-        self._index: Optional[Dict[Tuple[int, int], int]] = None         # (src,dst) -> row, lazily rebuilt
+        self._pending_keys: Dict[Tuple[int, int], int] = {}             # (src,dst) of the not-yet-uploaded edges
         self._pending: List[Tuple[int, int, float, int]] = []            # edges not yet uploaded
         self._csr = None                                                  # (offsets, adj, n_nodes): adjacency index of the table
 
@@ -168,34 +168,89 @@ class MemoryShard:
             s, d, w, c = zip(*self._pending)
             self._table.append(np.int32(s), np.int32(d), np.float32(w), np.int32(c))
             self._pending.clear()
+            self._pending_keys.clear()
             self._csr = None
 
-    def _edge_index(self) -> Dict[Tuple[int, int], int]:
-        if self._index is None:
-            self._flush()
-            s, d, _, _ = self._table.to_numpy()
-            self._index = {(int(a), int(b)): i for i, (a, b) in enumerate(zip(s, d))}
-        return self._index
+    def _find_rows(self, keys: List[Tuple[int, int]]) -> List[int]:
+        """Row of each (src slot, dst slot) key in the UPLOADED edge table, or -1: one lz_edge_find launch on the
+        table's CSR (edges still pending on the host are not in it; callers check `_pending_keys` first)."""
+        if not keys or self._table.n == 0:
+            return [-1] * len(keys)
+        if self._csr is None:
+            off, adj = kernels.csr_build(self._table.src, self._table.dst, self._table.n, len(self._names))
+            self._csr = (off, adj, len(self._names))
+        off, adj, n_nodes = self._csr                  # slots created after the build have no uploaded edges: -1
+        dev = self._table.device
+        qs = torch.tensor([k[0] for k in keys], dtype=torch.int32, device=dev)
+        qd = torch.tensor([k[1] for k in keys], dtype=torch.int32, device=dev)
+        return kernels.edge_find(off, adj, self._table.dst, n_nodes, qs, qd).cpu().tolist()
+
+    def _reinforce(self, rows: List[int], times: List[int]) -> None:
+        dev = self._table.device
+        kernels.edge_reinforce(self._table.weight, self._table.cooc, self._table.n,
+                               torch.tensor(rows, dtype=torch.int32, device=dev),
+                               torch.tensor(times, dtype=torch.int32, device=dev))
+
+    def add_edges(self, edges: List[Edge]) -> None:
+        """A run of add_edge calls (memory_shard.py:42-52) as one batch with the same outcome as calling them
+        in order: the first occurrence of a key that is not in the table inserts it, every other occurrence
+        reinforces (+0.1 capped at 1, co_occurrence += 1).  Lookup and reinforcement run on the device
+        (lz_edge_find on the CSR, lz_edge_reinforce)."""
+        if not edges:
+            return
+        self._flush()
+        first: Dict[Tuple[int, int], Edge] = {}
+        count: Dict[Tuple[int, int], int] = {}
+        for e in edges:
+            key = (self._slot_of(e.source), self._slot_of(e.target))
+            if key not in first:
+                first[key] = e
+            count[key] = count.get(key, 0) + 1
+        keys = list(first)
+        rows = self._find_rows(keys)
+        hit_rows, hit_times, fresh = [], [], []
+        for key, row in zip(keys, rows):
+            if row >= 0:
+                hit_rows.append(row); hit_times.append(count[key])
+            else:
+                fresh.append(key)
+        base = self._table.n
+        for key in fresh:
+            e = first[key]
+            self._pending.append((key[0], key[1], float(e.weight), int(e.co_occurrence)))
+            self._edge_meta[key] = (e.edge_type, e.last_updated)
+        self._flush()
+        for j, key in enumerate(fresh):
+            if count[key] > 1:
+                hit_rows.append(base + j); hit_times.append(count[key] - 1)
+        if hit_rows:
+            self._reinforce(hit_rows, hit_times)
 
     def add_edge(self, edge: Edge) -> None:
         """memory_shard.py:42-52: an existing (source, target) key is reinforced (+0.1 capped at 1,
-        co_occurrence += 1), otherwise the edge is appended."""
+        co_occurrence += 1), otherwise the edge is appended (uploaded with the next sweep or lookup batch)."""
         key = (self._slot_of(edge.source), self._slot_of(edge.target))
-        idx = self._edge_index()
-        row = idx.get(key)
-        if row is not None:
-            self._flush()
-            w = float(self._table.weight[row].item())
-            self._table.weight[row] = float(np.float32(min(1.0, w + 0.1)))
-            self._table.cooc[row] += 1
+        if key in self._pending_keys:
+            self._flush()                                # the edge to reinforce must be in the device table
+        row = self._find_rows([key])[0]
+        if row >= 0:
+            self._reinforce([row], [1])
         else:
-            idx[key] = self._table.n + len(self._pending)
+            self._pending_keys[key] = len(self._pending)
             self._pending.append((key[0], key[1], float(edge.weight), int(edge.co_occurrence)))
             self._edge_meta[key] = (edge.edge_type, edge.last_updated)
 
+    def has_edges(self, pairs: List[Tuple[str, str]]) -> List[bool]:
+        """Whether each (source, target) key exists (directional, as the reference's dict lookup)."""
+        keys = [(self._slot.get(a, -1), self._slot.get(b, -1)) for a, b in pairs]
+        out = [k in self._pending_keys for k in keys]
+        todo = [i for i, k in enumerate(keys) if not out[i] and k[0] >= 0 and k[1] >= 0]
+        for i, row in zip(todo, self._find_rows([keys[i] for i in todo])):
+            out[i] = row >= 0
+        return out
+
     def has_edge(self, source: str, target: str) -> bool:
-        a, b = self._slot.get(source), self._slot.get(target)
-        return a is not None and b is not None and (a, b) in self._edge_index()
+        return self.has_edges([(source, target)])[0]
 
     def remove_node(self, node_id: str) -> None:
         """Drops a node and every edge touching it (memory_system.py:559-571).  Host-side rebuild of the
@@ -210,7 +265,6 @@ class MemoryShard:
         if not keep.all():
             self._table = EdgeTable.from_arrays(s[keep], d[keep], w[keep], c[keep], device=self._table.device) \
                 if keep.any() else EdgeTable(self._table.device)
-            self._index = None
             self._csr = None
 
     @property
@@ -270,7 +324,6 @@ class MemoryShard:
         self._flush()
         pruned = self._table.decay_prune(1.0, threshold)
         if pruned:
-            self._index = None
             self._csr = None
         return pruned
 
@@ -281,7 +334,6 @@ class MemoryShard:
         pruned = self._table.decay_prune(1.0 - decay_rate, threshold)
         self._salience_sweep(decay_rate)
         if pruned:
-            self._index = None
             self._csr = None
         return pruned
 

@@ -273,3 +273,25 @@ def neighbors(offsets: torch.Tensor, adj: torch.Tensor, src: torch.Tensor, dst: 
         if most <= max_out:
             return (nbr, cnt, edge) if want_edges else (nbr, cnt)
         max_out = most
+
+
+def edge_find(offsets: torch.Tensor, adj: torch.Tensor, dst: torch.Tensor, n_nodes: int, q_src: torch.Tensor,
+              q_dst: torch.Tensor) -> torch.Tensor:
+    """int32 [q]: index of the edge (q_src, q_dst) in the table indexed by csr_build, or -1 (lz_edge_find)."""
+    dev = _dev(offsets)
+    assert q_src.dtype == torch.int32 and q_dst.dtype == torch.int32
+    out = torch.empty(q_src.numel(), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_edge_find(ptr(offsets), ptr(adj), ptr(dst), int(n_nodes), ptr(q_src), ptr(q_dst), q_src.numel(),
+                                       ptr(out), stream_ptr(dev)), "lz_edge_find")
+    return out
+
+
+def edge_reinforce(weight: torch.Tensor, cooc: torch.Tensor, n_edges: int, edge_idx: torch.Tensor,
+                   times: Optional[torch.Tensor] = None) -> None:
+    """weight[e] = min(1, weight[e] + 0.1) `times` times, cooc[e] += times, in place (lz_edge_reinforce)."""
+    dev = _dev(weight)
+    assert edge_idx.dtype == torch.int32 and (times is None or times.dtype == torch.int32)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_edge_reinforce(ptr(weight), ptr(cooc), int(n_edges), ptr(edge_idx), ptr(times), edge_idx.numel(),
+                                            stream_ptr(dev)), "lz_edge_reinforce")

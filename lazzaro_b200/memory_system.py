@@ -347,14 +347,12 @@ class MemorySystem:
             if len(ids) < 2:
                 continue
             shard = self.shards[key]
-            for a, b in zip(ids[:-1], ids[1:]):
-                shard.add_edge(Edge(source=a, target=b, weight=0.5, edge_type="relates_to"))
+            batch = [Edge(source=a, target=b, weight=0.5, edge_type="relates_to") for a, b in zip(ids[:-1], ids[1:])]
             new_set = set(ids)
             older = [(oid, n) for oid, n in shard.nodes.items() if oid not in new_set]
-            if not older:
-                continue
             dims = {len(n.embedding) for _, n in older} | {len(shard.nodes[i].embedding) for i in ids}
-            if len(dims) != 1 or 0 in dims:
+            if not older or len(dims) != 1 or 0 in dims:
+                shard.add_edges(batch)
                 continue
             a = np.repeat(np.asarray([shard.nodes[i].embedding for i in ids], np.float32), len(older), axis=0)
             b = np.tile(np.asarray([n.embedding for _, n in older], np.float32), (len(ids), 1))
@@ -363,8 +361,9 @@ class MemorySystem:
                 order = np.argsort(-sims[i], kind="stable")[:3]         # stable: ties by insertion order
                 for j in order:
                     if sims[i, j] > 0.5:
-                        shard.add_edge(Edge(source=nid, target=older[j][0], weight=float(sims[i, j]) * 0.8,
-                                            edge_type="relates_to"))
+                        batch.append(Edge(source=nid, target=older[j][0], weight=float(sims[i, j]) * 0.8,
+                                          edge_type="relates_to"))
+            shard.add_edges(batch)                      # one device lookup + upsert for the shard, same outcome as in order
 
     def _cross_link_candidates(self, new_nodes):
         """memory_system.py:838-867: per new node the 3 best existing rows above 0.5 (one batched search)."""
@@ -384,16 +383,32 @@ class MemorySystem:
     def _apply_cross_links(self, new_nodes, cross):
         """memory_system.py:866-889: skip a link whose edge exists in either direction in any shard; the
         edge goes to the new node's shard."""
+        cand = []
         for nid, key in new_nodes:
             for target, sim, weight in cross.get(nid, []):
                 node = self.buffer.get_node(target)
-                if node is None or node.is_super_node:
-                    continue
-                if any(s.has_edge(nid, target) or s.has_edge(target, nid) for s in self.shards.values()):
-                    continue
-                shard = self.shards.get(key)
-                if shard is not None:
-                    shard.add_edge(Edge(source=nid, target=target, weight=weight, edge_type="relates_to"))
+                if node is not None and not node.is_super_node:
+                    cand.append((nid, key, target, weight))
+        if not cand:
+            return
+        # the existence checks of all candidates in one device lookup per shard; edges added inside this loop
+        # are tracked in `added`, so the outcome is that of the reference's one-by-one loop
+        pairs = [(nid, target) for nid, _, target, _ in cand] + [(target, nid) for nid, _, target, _ in cand]
+        exists = [False] * len(cand)
+        for s in self.shards.values():
+            got = s.has_edges(pairs)
+            for i in range(len(cand)):
+                exists[i] = exists[i] or got[i] or got[len(cand) + i]
+        added = set()
+        per_shard: Dict[str, List[Edge]] = defaultdict(list)
+        for i, (nid, key, target, weight) in enumerate(cand):
+            if exists[i] or (nid, target) in added or (target, nid) in added:
+                continue
+            if key in self.shards:
+                per_shard[key].append(Edge(source=nid, target=target, weight=weight, edge_type="relates_to"))
+                added.add((nid, target))
+        for key, batch in per_shard.items():
+            self.shards[key].add_edges(batch)
 
     def _link_to_existing_memories(self, new_nodes):
         """Reference-shaped entry point (memory_system.py:838-891) for nodes already in the store: the scan

@@ -120,3 +120,83 @@ def test_csr_empty():
     assert off.cpu().tolist() == [0] * 6
     nbr, cnt = K.neighbors(off, adj, e, e, torch.zeros(0, device="cuda"), 5, torch.tensor([0, 4], dtype=torch.int32, device="cuda"))
     assert cnt.cpu().tolist() == [0, 0]
+
+
+def _replay_edges(golden_next, batch):
+    from lazzaro_b200.graph import Edge, MemoryShard, Node
+    n = int(golden_next["nb_n"])
+    rng = np.random.default_rng(72)                                                      # gold_neighbors' stream
+    src, dst = rng.integers(0, n, 1500), rng.integers(0, n, 1500)
+    w = rng.uniform(0, 1, 1500).astype(np.float32)
+    w[::7] = np.float32(0.3)
+    sh = MemoryShard("s")
+    for i in range(n):
+        sh.add_node(Node(id=f"n{i}", content="", embedding=[]))
+    edges = [Edge(source=f"n{a}", target=f"n{b}", weight=float(x)) for a, b, x in zip(src, dst, w)]
+    if batch:
+        for lo in range(0, len(edges), batch):
+            sh.add_edges(edges[lo:lo + batch])
+    else:
+        for e in edges:
+            sh.add_edge(e)
+    sh._flush()
+    return sh
+
+
+@pytest.mark.parametrize("batch", [0, 1, 64, 1500])
+def test_edge_upsert_replays_reference(golden_next, batch):
+    """memory_shard.py:42-52 through the device lookup + reinforcement: same edge order as the reference's dict,
+    same co-occurrence counts, weights equal up to the float32 storage of each reinforcement step."""
+    g = golden_next
+    sh = _replay_edges(g, batch)
+    es, ed, ew, ec = sh._table.to_numpy()
+    np.testing.assert_array_equal(es, g["nb_src"])
+    np.testing.assert_array_equal(ed, g["nb_dst"])
+    np.testing.assert_allclose(ew, g["nb_w"], rtol=0, atol=3e-7)
+    # restatement of the rule on float32 storage: bit-equal
+    rng = np.random.default_rng(72)
+    n = int(g["nb_n"])
+    src, dst = rng.integers(0, n, 1500), rng.integers(0, n, 1500)
+    w = rng.uniform(0, 1, 1500).astype(np.float32); w[::7] = np.float32(0.3)
+    table = {}
+    for a, b, x in zip(src.tolist(), dst.tolist(), w.tolist()):
+        if (a, b) in table:
+            ww, cc = table[(a, b)]
+            table[(a, b)] = (float(np.float32(min(1.0, ww + 0.1))), cc + 1)
+        else:
+            table[(a, b)] = (float(np.float32(x)), 1)
+    np.testing.assert_array_equal(ew, np.float32([v[0] for v in table.values()]))
+    np.testing.assert_array_equal(ec, np.int32([v[1] for v in table.values()]))
+    assert sh.has_edges([("n%d" % es[0], "n%d" % ed[0]), ("n%d" % ed[0], "ghost"), ("ghost", "n1")]) == [True, False, False]
+
+
+def test_edge_find_and_reinforce_kernels():
+    from lazzaro_b200 import kernels as K
+    rng = np.random.default_rng(5)
+    n_nodes, n_edges = 5000, 60000
+    src, dst = rng.integers(0, n_nodes, n_edges), rng.integers(0, n_nodes, n_edges)
+    src[100:200] = 7                                               # a long source list
+    s, d, off, adj = _csr(src, dst, n_nodes)
+    first = {}
+    for e, (a, b) in enumerate(zip(src.tolist(), dst.tolist())):
+        first.setdefault((a, b), e)
+    qa = np.concatenate([src[::13], rng.integers(0, n_nodes, 500), [-1, n_nodes]])
+    qb = np.concatenate([dst[::13], rng.integers(0, n_nodes, 500), [0, 0]])
+    got = K.edge_find(off, adj, d, n_nodes, torch.as_tensor(np.int32(qa)).cuda(), torch.as_tensor(np.int32(qb)).cuda()).cpu().tolist()
+    assert got == [first.get((a, b), -1) for a, b in zip(qa.tolist(), qb.tolist())]
+    w = rng.uniform(0, 1, n_edges).astype(np.float32)
+    c = np.ones(n_edges, np.int32)
+    wt, ct = torch.as_tensor(w).cuda(), torch.as_tensor(c).cuda()
+    idx = rng.permutation(n_edges)[:1000].astype(np.int32)
+    times = rng.integers(0, 12, 1000).astype(np.int32)
+    K.edge_reinforce(wt, ct, n_edges, torch.as_tensor(np.concatenate([idx, [-1, n_edges]]).astype(np.int32)).cuda(),
+                     torch.as_tensor(np.concatenate([times, [3, 3]]).astype(np.int32)).cuda())
+    want = w.copy()
+    for i, t in zip(idx.tolist(), times.tolist()):
+        x = want[i]
+        for _ in range(t):
+            x = np.float32(min(1.0, float(x) + 0.1))
+        want[i] = x
+    c[idx] += times
+    np.testing.assert_array_equal(wt.cpu().numpy(), want)
+    np.testing.assert_array_equal(ct.cpu().numpy(), c)
