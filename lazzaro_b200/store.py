@@ -80,6 +80,12 @@ class B200Store:
         self._bscratch: Optional[torch.Tensor] = None
         self.last_certified: Optional[torch.Tensor] = None
         self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
+        # search policy: "exact" (the parity mode: every row of the user is scored) or "two_level" (approximate:
+        # centroid routing, then only the `nprobe` best shards — set_shards() first; reported with recall, never
+        # as parity; see recall_report)
+        self.search_policy = "exact"
+        self.nprobe: Optional[int] = None
+        self._centroids = None
         if dim is not None:
             self._set_dim(int(dim))
 
@@ -284,8 +290,45 @@ class B200Store:
             if self._n == 0 or u < 0 or self._live[u] == 0 or limit <= 0:   # vector_store.py:133-134
                 return []
             q = np.asarray(query_emb, dtype=np.float32).reshape(1, -1)
+            if self.search_policy == "two_level":
+                return self._search_policy_two_level(q, u, limit)[0]
             ids, _, counts = self._search_host(q, u, limit)
             return [self._id_of(r) for r in ids[0, :counts[0]].tolist()]
+
+    def _search_policy_two_level(self, q: np.ndarray, u: int, limit: int):
+        if self.search_policy not in ("exact", "two_level"):
+            raise ValueError(f"search_policy must be 'exact' or 'two_level', got {self.search_policy!r}")
+        if self._centroids is None:
+            raise RuntimeError("search_policy='two_level' needs set_shards() first")
+        if len(self._user_names) != 1:
+            raise RuntimeError("search_policy='two_level' serves single-tenant stores; per-user spans use the exact path")
+        return self.search_two_level(q, limit=limit, nprobe=self.nprobe)
+
+    def recall_report(self, queries, limit: int = 10, nprobes: Sequence[int] = (1, 2, 4, 8, 16, 32)):
+        """Approximate-mode report: for each nprobe the recall@limit of the two-level search
+        against the exact flat search on the same queries, the fraction of rows its member scans touch, and its
+        time per batch (CUDA events).  Returns a list of dicts; nothing here is a parity claim."""
+        with self._lock:
+            q = np.ascontiguousarray(queries, dtype=np.float32)
+            exact = self.search_batch(q, self._user_names[0], limit)
+            S = int(self._centroids.shape[0])
+            sizes = self._shard_off_host[1:] - self._shard_off_host[:-1]
+            out = []
+            for p in nprobes:
+                p = max(1, min(int(p), S))
+                self.search_two_level(q, limit, nprobe=p)                                  # warm-up
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                rows, _, cnt = self.search_two_level(q, limit, nprobe=p, return_rows=True)
+                e1.record()
+                torch.cuda.synchronize(self.device)
+                rows, cnt = rows.cpu().numpy(), cnt.cpu().numpy()
+                got = [[self._id_of(int(r)) for r in rows[b, :cnt[b]]] for b in range(q.shape[0])]
+                rec = float(np.mean([len(set(a) & set(b)) / max(1, len(b)) for a, b in zip(got, exact)]))
+                out.append({"nprobe": p, "shards": S, f"recall_at_{limit}": rec,
+                            "rows_scanned_fraction_upper": float(np.sort(sizes)[::-1][:p].sum() / max(1, sizes.sum())),
+                            "ms_per_batch": e0.elapsed_time(e1), "batch": int(q.shape[0])})
+            return out
 
     def search_batch(self, queries, user_id: str = "default", limit: int = 5, return_scores: bool = False):
         """Batched form of `search_nodes` (our addition): queries float32 [B, dim] on the host.

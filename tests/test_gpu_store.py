@@ -149,3 +149,28 @@ def test_two_level_search_parity_and_recall():
     approx = st.search_two_level(qs, limit=10, nprobe=2)
     recall = np.mean([len(set(a) & set(w)) / 10 for a, w in zip(approx, want)])
     assert recall > 0.95                                                     # neighbours live in the query's shard
+
+
+def test_two_level_policy_and_recall_report():
+    """the approximate mode as a store policy, reported with recall (never as parity)."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    n, dim, S = 30000, 64, 24
+    rows, shard = synth.clustered_rows(n, dim, S, seed=51)
+    st = B200Store()
+    st.add_rows(rows, id_prefix="node_")
+    qs = synth.queries_near_rows(rows, 16, seed=52)
+    exact = [st.search_nodes(q.tolist(), limit=10) for q in qs]
+    st.search_policy = "two_level"
+    with pytest.raises(RuntimeError):
+        st.search_nodes(qs[0].tolist(), limit=10)                  # no shard layout declared yet
+    st.set_shards(np.searchsorted(shard, np.arange(S + 1)))
+    assert [st.search_nodes(q.tolist(), limit=10) for q in qs] == exact          # nprobe None = every shard = exact
+    st.nprobe = 2
+    approx = [st.search_nodes(q.tolist(), limit=10) for q in qs]
+    assert np.mean([len(set(a) & set(b)) / 10 for a, b in zip(approx, exact)]) > 0.9
+    rep = st.recall_report(qs, limit=10, nprobes=(1, 4, S))
+    assert [r["nprobe"] for r in rep] == [1, 4, S] and rep[-1]["recall_at_10"] == 1.0
+    assert rep[0]["rows_scanned_fraction_upper"] < rep[1]["rows_scanned_fraction_upper"] <= 1.0
+    st.search_policy = "exact"
+    assert [st.search_nodes(q.tolist(), limit=10) for q in qs] == exact
