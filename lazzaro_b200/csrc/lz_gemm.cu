@@ -1082,8 +1082,41 @@ int env_int(const char* name, int dflt) {
 }
 
 // cs = CTAs per cluster sharing each rows tile by TMA multicast (one q-tile each).  Measured at 10M x 768,
-// batch 1024 on B200: cs=1 20.9 ms, cs=2 18.4 ms, cs=4 31.8 ms, cs=8 38.0 ms — larger clusters couple
-// more epilogues to one pipeline (and leave SMs idle), so the default is 2; LZ_CLUSTER overrides.
+// batch 1024 on B200 (ms per batch): cs=1 13.8, cs=2 12.0, cs=4 12.7, cs=8 13.5 — so the default is 2;
+// LZ_CLUSTER overrides.
+constexpr size_t kGemmSmem = 1024 + (size_t)196608 + (2 * 6 + 4) * 8 + 16;   // 4 x 48 KiB or 6 x 32 KiB of stages
+
+// How many clusters of `cs` CTAs the device can hold at once.  Clusters are placed inside one GPC, and GPCs do
+// not all have a multiple of `cs` usable SMs, so this can be less than SMs / cs — and a persistent grid with more
+// clusters than that runs its surplus clusters as a second wave (measured: cs = 4 took 20.1 ms instead of ~12).
+int active_clusters(int cs) {
+    static int cache[16][9];                                  // [device][cs]
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16 || cs < 1 || cs > 8) return 0;
+    if (cache[dev][cs] > 0) return cache[dev][cs];
+    const int sms = lz_sm_count();
+    int n = sms / cs;
+    if (cs > 1) {
+        auto kern = gemm_topk_kernel<8, false>;
+        cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);
+        if (cs > 4) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(sms / cs * cs));
+        cfg.blockDim = dim3(kGemmThreads);
+        cfg.dynamicSmemBytes = kGemmSmem;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = (unsigned)cs; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        int got = 0;
+        if (cudaOccupancyMaxActiveClusters(&got, kern, &cfg) == cudaSuccess && got > 0 && got < n) n = got;
+        else cudaGetLastError();
+    }
+    if (n < 1) n = 1;
+    cache[dev][cs] = n;
+    return n;
+}
+
 int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     const int sms = lz_sm_count();
     if (sms <= 0) return LZ_ERR_DEVICE;
@@ -1094,7 +1127,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     pl->cs = cs;
     pl->n_qgroups = (pl->n_qtiles + cs - 1) / cs;
     pl->n_tiles = (int)((n_rows + BN - 1) / BN);
-    const int n_clusters = sms / cs > 0 ? sms / cs : 1;
+    const int n_clusters = active_clusters(cs) > 0 ? active_clusters(cs) : 1;
     int want = (2 * n_clusters) / pl->n_qgroups;
     if (want < 1) want = 1;
     if (want > pl->n_tiles) want = pl->n_tiles;
@@ -1237,7 +1270,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr; g.top1_eps = tiny_top1 ? eps : nullptr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
-        const size_t smem = 1024 + (size_t)196608 + (2 * 6 + 4) * 8 + 16;   // 4 x 48 KiB or 6 x 32 KiB of stages
+        const size_t smem = kGemmSmem;
         auto kern = pair ? (pl.kp == 32 ? gemm_topk_kernel<2, true> : pl.kp == 128 ? gemm_topk_kernel<8, true>
                             : pl.kp == 256 ? gemm_topk_kernel<16, true> : gemm_topk_kernel<32, true>)
                          : (pl.kp == 32 ? gemm_topk_kernel<2, false> : pl.kp == 128 ? gemm_topk_kernel<8, false>
