@@ -485,7 +485,7 @@ struct SelectParams {
     int metric;                              // LZ_COSINE, or LZ_L2 (coarse key = x.q - |x|^2/2 = -(d - |q|^2)/2)
 };
 
-__global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParams p) {
+__global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     u64* key_a = reinterpret_cast<u64*>(smem);
     u64* key_b = key_a + p.cap_a;
@@ -528,6 +528,54 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
     int total = 0;
 #pragma unroll
     for (int w = 0; w < kSelThreads / 32; ++w) { T = fmaxf(T, s_tw[w]); total += s_nw[w]; }
+    constexpr int kMaxSlices = 1024;
+    __shared__ int s_off[kMaxSlices + 1];
+    if (p.n_slices <= kMaxSlices) {
+        // With shared thresholds most slices leave only a few entries: lay the slices' counts end to end (block
+        // scan) and walk the ENTRIES, 512 per round — not the n_slices * kp slots, most of them empty, each of
+        // which cost a dependent count-then-entry round trip.
+        const int per = (p.n_slices + kSelThreads - 1) / kSelThreads;
+        const int c0 = min(p.n_slices, tid * per), c1 = min(p.n_slices, c0 + per);
+        int mine = 0;
+        for (int sl = c0; sl < c1; ++sl) {
+            const int c = p.cand_cnt[((size_t)sl * p.n_qtiles_pad + qt) * BM + ql];
+            s_off[sl + 1] = c;
+            mine += c;
+        }
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        __shared__ int s_ps[kSelThreads / 32];
+        if (lane == 31) s_ps[warp] = incl;
+        __syncthreads();
+        int run = incl - mine;
+#pragma unroll
+        for (int w = 0; w < kSelThreads / 32; ++w) if (w < warp) run += s_ps[w];
+        for (int sl = c0; sl < c1; ++sl) { const int c = s_off[sl + 1]; s_off[sl + 1] = run + c; run += c; }
+        if (tid == 0) s_off[0] = 0;
+        __syncthreads();
+        const int Q = s_off[p.n_slices];
+        for (int base = 0; base < Q; base += 2 * kSelThreads) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int t = base + h * kSelThreads + tid;
+                if (t < Q) {
+                    int lo = 0, hi = p.n_slices - 1;                            // slice with s_off[sl] <= t < s_off[sl+1]
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) >> 1;
+                        if (s_off[mid] <= t) lo = mid; else hi = mid - 1;
+                    }
+                    const size_t slot = ((size_t)lo * p.n_qtiles_pad + qt) * BM + ql;
+                    const u64 kk = p.cand[slot * p.cap + (t - s_off[lo])];
+                    lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
+                }
+            }
+            lz_sel_maybe_compact<kSelThreads>(&sa, 2 * kSelThreads);
+        }
+    } else {
     const int64_t flat = (int64_t)p.n_slices * p.kp;                          // each slice left at most kp entries
     for (int64_t base = 0; base < flat; base += 2 * kSelThreads) {
 #pragma unroll
@@ -543,6 +591,7 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
             }
         }
         lz_sel_maybe_compact<kSelThreads>(&sa, 2 * kSelThreads);
+    }
     }
     __syncthreads();
     lz_sel_compact<kSelThreads>(&sa);
@@ -581,17 +630,18 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
         qs = fma((double)x.w, (double)x.w, qs);
     }
     const double qn = sqrt(lz_warp_sum(qs));
-    // (group, row) pairs are walked flat, two per warp and step, so each warp keeps two rows' loads in flight
+    // (group, row) pairs are walked flat, four per warp and step, and a step issues all of its loads (4 rows x up to
+    // 3 segments of 128 floats) before the first use: the rows come from HBM, and with two rows and one segment in
+    // flight this loop was a chain of memory round trips (the kernel's top stall)
+    constexpr int kRow = 4, kSeg = 3, kW = kSelThreads / 32, kSteps = 4;
     const int n_pairs = m * kSub;
-    for (int base = 0; base < n_pairs; base += 2 * (kSelThreads / 32) * 8) {
-        for (int it = 0; it < 8; ++it) {
-            const int pa = base + (it * 2 + 0) * (kSelThreads / 32) + warp;
-            const int pb = base + (it * 2 + 1) * (kSelThreads / 32) + warp;
-            int64_t row[2] = {-1, -1};
-            if (pa < n_pairs) row[0] = (int64_t)id_a[pa / kSub] + pa % kSub;
-            if (pb < n_pairs) row[1] = (int64_t)id_a[pb / kSub] + pb % kSub;
+    for (int base = 0; base < n_pairs; base += kRow * kW * kSteps) {
+        for (int it = 0; it < kSteps; ++it) {
+            int64_t row[kRow];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < kRow; ++h) {
+                const int pi = base + (it * kRow + h) * kW + warp;
+                row[h] = pi < n_pairs ? (int64_t)id_a[pi / kSub] + pi % kSub : -1;
                 bool ok = row[h] >= 0 && row[h] < p.row_hi;
                 if (ok && p.tags) {
                     const int tg = p.tags[row[h]];
@@ -599,32 +649,45 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
                 }
                 if (!ok) row[h] = -1;
             }
-            double acc[2] = {0.0, 0.0};
-            for (int e = lane * 4; e < p.dim; e += 128) {
-                const float4 qq = *reinterpret_cast<const float4*>(qv + e);
-                float4 xv[2];
+            if (row[0] < 0 && row[1] < 0 && row[2] < 0 && row[3] < 0) continue;      // warp-uniform
+            double acc[kRow];
 #pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    xv[h] = row[h] >= 0 ? lz_ldg_stream(p.rows + row[h] * p.ld + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+            for (int h = 0; h < kRow; ++h) acc[h] = 0.0;
+            for (int e0 = lane * 4; e0 < p.dim; e0 += 128 * kSeg) {
+                float4 xv[kRow][kSeg];
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (p.metric == LZ_COSINE) {
-                        acc[h] = fma((double)xv[h].x, (double)qq.x, acc[h]);
-                        acc[h] = fma((double)xv[h].y, (double)qq.y, acc[h]);
-                        acc[h] = fma((double)xv[h].z, (double)qq.z, acc[h]);
-                        acc[h] = fma((double)xv[h].w, (double)qq.w, acc[h]);
-                    } else {
-                        const double d0 = (double)xv[h].x - (double)qq.x, d1 = (double)xv[h].y - (double)qq.y;
-                        const double d2 = (double)xv[h].z - (double)qq.z, d3 = (double)xv[h].w - (double)qq.w;
-                        acc[h] = fma(d0, d0, acc[h]);
-                        acc[h] = fma(d1, d1, acc[h]);
-                        acc[h] = fma(d2, d2, acc[h]);
-                        acc[h] = fma(d3, d3, acc[h]);
+                for (int sg = 0; sg < kSeg; ++sg) {
+                    const int e = e0 + 128 * sg;
+#pragma unroll
+                    for (int h = 0; h < kRow; ++h)
+                        xv[h][sg] = (row[h] >= 0 && e < p.dim) ? lz_ldg_stream(p.rows + row[h] * p.ld + e)
+                                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int sg = 0; sg < kSeg; ++sg) {
+                    const int e = e0 + 128 * sg;
+                    if (e >= p.dim) break;
+                    const float4 qq = *reinterpret_cast<const float4*>(qv + e);
+#pragma unroll
+                    for (int h = 0; h < kRow; ++h) {
+                        if (p.metric == LZ_COSINE) {
+                            acc[h] = fma((double)xv[h][sg].x, (double)qq.x, acc[h]);
+                            acc[h] = fma((double)xv[h][sg].y, (double)qq.y, acc[h]);
+                            acc[h] = fma((double)xv[h][sg].z, (double)qq.z, acc[h]);
+                            acc[h] = fma((double)xv[h][sg].w, (double)qq.w, acc[h]);
+                        } else {
+                            const double d0 = (double)xv[h][sg].x - (double)qq.x, d1 = (double)xv[h][sg].y - (double)qq.y;
+                            const double d2 = (double)xv[h][sg].z - (double)qq.z, d3 = (double)xv[h][sg].w - (double)qq.w;
+                            acc[h] = fma(d0, d0, acc[h]);
+                            acc[h] = fma(d1, d1, acc[h]);
+                            acc[h] = fma(d2, d2, acc[h]);
+                            acc[h] = fma(d3, d3, acc[h]);
+                        }
                     }
                 }
             }
 #pragma unroll
-            for (int h = 0; h < 2; ++h) {
+            for (int h = 0; h < kRow; ++h) {
                 const double dot = lz_warp_sum(acc[h]);
                 if (lane == 0 && row[h] >= 0) {
                     double s;
@@ -639,7 +702,7 @@ __global__ void __launch_bounds__(kSelThreads) select_rescore_kernel(SelectParam
                 }
             }
         }
-        lz_sel_maybe_compact<kSelThreads>(&sb, 2 * (kSelThreads / 32) * 8);
+        lz_sel_maybe_compact<kSelThreads>(&sb, kRow * kW * kSteps);
     }
     __syncthreads();
     lz_sel_compact<kSelThreads>(&sb);
