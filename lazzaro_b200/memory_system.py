@@ -14,6 +14,7 @@ and graph of this package:
     _enforce_buffer_limit      memory_system.py:535-578
     _merge_similar_nodes       memory_system.py:1065-1120 (a no-op as written in the reference — SURVEY Q1 — and here)
     run_consolidation          memory_system.py:935-1010  (merge, components, prune; profile extraction is out of scope)
+    _load_from_persistence / check_for_updates / switch_user   memory_system.py:1304-1428, 1474-1486
 
 What differs is where the arithmetic runs: every cosine, top-k, mean, decay and prune is a kernel call
 (batched where the reference loops), and the reference's one-search-per-memory loops become one batched
@@ -131,7 +132,7 @@ class MemorySystem:
                  user_id: str = "default", enable_sharding: bool = True, enable_hierarchy: bool = True,
                  super_node_threshold: int = 20, auto_consolidate: bool = True, consolidate_every: int = 3,
                  auto_prune: bool = True, prune_threshold: float = 0.5, max_buffer_size: int = 10,
-                 metric: str = "cosine", device: Optional[str] = None, **_ignored):
+                 metric: str = "cosine", device: Optional[str] = None, load_from_disk: bool = False, **_ignored):
         if llm_provider is None or embedding_provider is None:
             raise ValueError("lazzaro_b200.MemorySystem needs llm_provider and embedding_provider (no network here)")
         self.llm, self.embedder, self.user_id = llm_provider, embedding_provider, user_id
@@ -151,6 +152,10 @@ class MemorySystem:
         self.node_counter = 0
         self.conversation_count = 0
         self.metrics = {"embedding_calls": 0, "llm_calls": 0, "retrieval_times": [], "consolidation_times": []}
+        self.profile: Optional[dict] = None
+        self._last_nodes_version = 0
+        if load_from_disk:                                # memory_system.py:131-132
+            self._load_from_persistence()
 
     # ------------------------------------------------------------------ small helpers
     def _generate_node_id(self) -> str:
@@ -335,6 +340,86 @@ class MemorySystem:
                  for shard in self.shards.values() for e in shard.edges.values()]
         if edges:
             self.store.add_edges(edges, user_id=self.user_id)
+
+    def _load_from_persistence(self):
+        """memory_system.py:1304-1410: rebuild shards, super-nodes, edges and the id counter from the store's rows
+        of this user.  Nodes keep the store's row order; an edge goes to the shard its source node (or super-node)
+        names; a shard's edges are upserted in one device batch (same outcome as the reference's add_edge loop)."""
+        node_dicts = self.store.get_nodes(user_id=self.user_id)
+        if not node_dicts:
+            return
+        self.shards, self.super_nodes = {}, {}
+        fields = Node.__dataclass_fields__
+        for nd in node_dicts:
+            nd = dict(nd)
+            if "vector" in nd:
+                nd["embedding"] = nd.pop("vector")
+            node = Node(**{k: v for k, v in nd.items() if k in fields})
+            if node.is_super_node:
+                self.super_nodes[node.id] = node
+            else:
+                if node.shard_key not in self.shards:
+                    self.shards[node.shard_key] = MemoryShard(node.shard_key, device=str(self.store.device))
+                self.shards[node.shard_key].add_node(node)
+        per_shard: Dict[str, List[Edge]] = defaultdict(list)
+        efields = Edge.__dataclass_fields__
+        edge_dicts = self.store.get_edges(user_id=self.user_id)
+        for ed in edge_dicts:
+            ed = dict(ed)
+            if "source_id" in ed:
+                ed["source"] = ed.pop("source_id")
+            if "target_id" in ed:
+                ed["target"] = ed.pop("target_id")
+            if "type" in ed and "edge_type" not in ed:
+                ed["edge_type"] = ed.pop("type")
+            edge = Edge(**{k: v for k, v in ed.items() if k in efields})
+            src = self.super_nodes.get(edge.source)
+            if src is None:
+                for shard in self.shards.values():
+                    if edge.source in shard.nodes:
+                        src = shard.nodes[edge.source]
+                        break
+            if src is not None and src.shard_key in self.shards:
+                per_shard[src.shard_key].append(edge)
+        for key, batch in per_shard.items():
+            self.shards[key].add_edges(batch)
+        self.profile = self.store.load_profile(user_id=self.user_id)
+        self._last_nodes_version = self.store.get_latest_version()
+        self.buffer = BufferGraph(self.shards, self.super_nodes)
+        self.buffer._device = str(self.store.device)
+        max_id = 0
+        for nid in self.buffer.nodes:
+            if nid.startswith("node_"):
+                try:
+                    max_id = max(max_id, int(nid.split("_")[1]))
+                except ValueError:
+                    pass
+        if self.buffer.nodes:
+            self.node_counter = max_id
+
+    def check_for_updates(self) -> bool:
+        """memory_system.py:1412-1428."""
+        current = self.store.get_latest_version()
+        if current > self._last_nodes_version:
+            self._load_from_persistence()
+            return True
+        return False
+
+    def get_all_users(self) -> List[str]:
+        """memory_system.py:1430-1458 (the reference reaches into the store's node table; here the store answers)."""
+        table = getattr(self.store, "_nodes_table", None)
+        if table is None:
+            return [self.user_id]
+        return sorted({r["user_id"] for r in table.search().select(["user_id"]).to_list()})
+
+    def switch_user(self, new_user_id: str):
+        """memory_system.py:1474-1486."""
+        if self.conversation_active:
+            self.end_conversation()
+        else:
+            self._save_to_persistence()
+        self.user_id = new_user_id
+        self._load_from_persistence()      # as in the reference, a user with no saved rows leaves the resident graph as it is
 
     def _link_within_shards(self, new_nodes: List[Tuple[str, str]]):
         """memory_system.py:797-836: chain edges (0.5) between consecutive new nodes of a shard, then for

@@ -16,6 +16,7 @@ What is recorded (inputs AND reference outputs, so tests need nothing but numpy)
 and, in ref_next_rows.npz:
   eviction      memory_system.py:535-578 (_enforce_buffer_limit) under a frozen clock
   neighbors     memory_shard.py:54-62 (get_neighbors) on a random edge set
+  reload        memory_system.py:1304-1410 (_load_from_persistence) of the msys scenario's saved state
 """
 from __future__ import annotations
 
@@ -226,10 +227,8 @@ def gold_pins(lz):
                 pin_pruned=np.int64(pruned), pin_merge_noop=np.int64(merged))
 
 
-def gold_memory_system(lz):
-    """Three conversations through the reference's own MemorySystem (end_conversation -> consolidation,
-    dedup, linking, super-nodes, decay, prune) with scripted facts and table embeddings; the state after
-    each conversation and a few retrievals are recorded for the device mirror to reproduce."""
+def _run_msys_scenario():
+    """Three conversations through the reference's own MemorySystem with scripted facts and table embeddings."""
     dim, per = 32, 9
     topics = ["work", "health", "learning"]
     rows, shard = synth.clustered_rows(3 * 3 * per, dim, 3, seed=61, sigma=0.6)
@@ -243,8 +242,8 @@ def gold_memory_system(lz):
     for j, v in enumerate(queries):
         table[f"query {j}"] = v.astype(np.float64).tolist()
     store, llm, emb = FlatStore(metric="cosine"), ref_harness.ScriptedLLM(), ref_harness.TableEmbedder(table, dim)
-    ms = quiet(ref_harness.make_memory_system, store, llm, emb, max_buffer_size=10**6, super_node_threshold=12,
-               auto_consolidate=True, consolidate_every=3, prune_threshold=0.45)
+    kw = dict(max_buffer_size=10**6, super_node_threshold=12, auto_consolidate=True, consolidate_every=3, prune_threshold=0.45)
+    ms = quiet(ref_harness.make_memory_system, store, llm, emb, **kw)
     convs = [facts[:per * 3], facts[per * 3:per * 6], facts[per * 6:]]
     script, states = [], []
     for ci, conv in enumerate(convs):
@@ -262,11 +261,38 @@ def gold_memory_system(lz):
             "edges": {f"{a}|{b}": [e.weight, e.co_occurrence] for sh in ms.shards.values() for (a, b), e in sh.edges.items()},
             "super": {sid: [n.shard_key, n.child_ids, n.embedding] for sid, n in ms.super_nodes.items()},
         })
+    return dict(ms=ms, store=store, llm=llm, emb=emb, kw=kw, table=table, script=script, states=states,
+                queries=queries, dim=dim)
+
+
+def gold_memory_system(lz):
+    """Three conversations through the reference's own MemorySystem (end_conversation -> consolidation,
+    dedup, linking, super-nodes, decay, prune) with scripted facts and table embeddings; the state after
+    each conversation and a few retrievals are recorded for the device mirror to reproduce."""
+    r = _run_msys_scenario()
+    ms, table, queries = r["ms"], r["table"], r["queries"]
     sm = [[n.id for n in ms.search_memories(f"query {j}", limit=5)] for j in range(len(queries))]
     orr = [ms._optimized_retrieval(table[f"query {j}"], f"query {j}") for j in range(len(queries))]
     comps = sorted(sorted(c) for c in ms.buffer.get_connected_components() if len(c) >= 3)
-    return dict(msys=np.array(json.dumps({"table": table, "script": script, "states": states, "search": sm,
-                                          "retrieval": orr, "components": comps, "dim": dim})))
+    return dict(msys=np.array(json.dumps({"table": table, "script": r["script"], "states": r["states"], "search": sm,
+                                          "retrieval": orr, "components": comps, "dim": r["dim"]})))
+
+
+def gold_reload(lz):
+    """_load_from_persistence (memory_system.py:1304-1410) of the state the scenario above saved: a second reference
+    MemorySystem on the same store with load_from_disk=True; what it restored is recorded."""
+    r = _run_msys_scenario()
+    ms2 = quiet(ref_harness.make_memory_system, r["store"], r["llm"], r["emb"], load_from_disk=True, **r["kw"])
+    state = {
+        "shards": {k: list(sh.nodes) for k, sh in ms2.shards.items()},
+        "nodes": {nid: [n.content, n.salience, n.access_count, n.shard_key, n.parent_id, n.is_super_node, n.child_ids]
+                  for nid, n in ms2.buffer.nodes.items()},
+        "super": list(ms2.super_nodes),
+        "edges": {k: [[a, b, e.weight, e.co_occurrence] for (a, b), e in sh.edges.items()] for k, sh in ms2.shards.items()},
+        "node_counter": ms2.node_counter,
+        "search": [[n.id for n in ms2.search_memories(f"query {j}", limit=5)] for j in range(len(r["queries"]))],
+    }
+    return dict(reload=np.array(json.dumps(state)))
 
 
 def gold_eviction(lz):
@@ -353,7 +379,7 @@ def main():
     np.savez_compressed(path, **out)
     print("wrote", path, os.path.getsize(path), "bytes")
     nxt = {}
-    for fn in (gold_eviction, gold_neighbors):
+    for fn in (gold_eviction, gold_neighbors, gold_reload):
         nxt.update(fn(lz))
         print("ok", fn.__name__)
     path = os.path.join(OUT, "ref_next_rows.npz")
