@@ -151,6 +151,7 @@ struct GemmParams {
     int32_t* cand_cnt;  // [n_items][BM]
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
     u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
+    int row_mode;             // candidates are single rows (two-level test: group max first), not groups of kSub
     const double* top1_eps;   // top-1 against a tiny table only (else null): per-query eps; the threshold then
                               // follows the running best group at a distance of 3 eps (see scan_chunk)
 };
@@ -244,10 +245,11 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     // and the final threshold T = c_1 - 3 eps certifies by construction (exact best >= c_1 - eps > T + eps).
     // Chunks reaching past the range are left out: their rows are not candidates.
     if (row_first + 32 <= p.row_hi) thr = fmaxf(thr, m - slack);
-    const bool top1 = slack != INFINITY;
+    const bool top1 = slack != INFINITY || p.row_mode != 0;       // single-row candidates
     if (m > thr) {
         if (top1) {
-            // top-1 mode keeps single ROWS (a handful pass): the exact pass then rescores one row, not a group
+            // row mode keeps single ROWS: the group max is tested first, so the common case (nothing passes) costs
+            // the same, and the exact pass rescores the rows themselves instead of kSub rows per candidate
 #pragma unroll
             for (int j = 0; j < 32 / kSub; ++j) {
                 if (g[j] > thr) {
@@ -607,7 +609,7 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
         if (p.tags == nullptr) {
             int full = 0;
             for (int j = 0; j < m; ++j) {
-                if ((int64_t)id_a[j] + kSub <= p.row_hi && ++full == p.k) {
+                if ((int64_t)id_a[j] + p.sub <= p.row_hi && ++full == p.k) {
                     const float cutoff = unord32((u32)key_a[j]) - 2.0f * (float)p.eps[q];
                     keep = j + 1;
                     while (keep < m && unord32((u32)key_a[keep]) >= cutoff) ++keep;
@@ -634,14 +636,14 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
     // 3 segments of 128 floats) before the first use: the rows come from HBM, and with two rows and one segment in
     // flight this loop was a chain of memory round trips (the kernel's top stall)
     constexpr int kRow = 4, kSeg = 3, kW = kSelThreads / 32, kSteps = 4;
-    const int n_pairs = m * kSub;
+    const int n_pairs = m * p.sub;
     for (int base = 0; base < n_pairs; base += kRow * kW * kSteps) {
         for (int it = 0; it < kSteps; ++it) {
             int64_t row[kRow];
 #pragma unroll
             for (int h = 0; h < kRow; ++h) {
                 const int pi = base + (it * kRow + h) * kW + warp;
-                row[h] = pi < n_pairs ? (int64_t)id_a[pi / kSub] + pi % kSub : -1;
+                row[h] = pi < n_pairs ? (int64_t)id_a[pi / p.sub] + pi % p.sub : -1;
                 bool ok = row[h] >= 0 && row[h] < p.row_hi;
                 if (ok && p.tags) {
                     const int tg = p.tags[row[h]];
@@ -1318,6 +1320,11 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     const size_t rows_smem = (size_t)kSub * dim * 4;
     const bool tiny_top1 = k == 1 && tags == nullptr && pl.n_slices == 1 && row_hi - row_lo <= (int64_t)kBucketGroups * kSub &&
                            rows_smem <= 160 * 1024 && n_queries >= 4 * kBucketQ;
+    // Single-row candidates for every k (LZ_ROWMODE=1) were tried to shrink the exact pass (kSub rows per group
+    // candidate: 2.0 ms per batch of 1024 at k = 100): measured slower overall — 18.0 vs 15.6 ms at k = 100, 14.6 vs
+    // 12.0 ms at k = 10 (10M x 768) — because more entries pass the group-level seeds and the epilogue compacts
+    // more often, which stalls the MMA pipeline.  Off by default; the top-1 tiny-table mode is the one user.
+    const bool row_mode = !tiny_top1 && tags == nullptr && env_int("LZ_ROWMODE", 0) != 0;
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
@@ -1332,6 +1339,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr; g.top1_eps = tiny_top1 ? eps : nullptr;
+        g.row_mode = row_mode ? 1 : 0;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = kGemmSmem;
         auto kern = pair ? (pl.kp == 32 ? gemm_topk_kernel<2, true> : pl.kp == 128 ? gemm_topk_kernel<8, true>
@@ -1356,6 +1364,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         constexpr int kSampleTiles = 64;
         if (pl.n_tiles >= 8 * kSampleTiles && kSampleTiles * (BN / kSub) >= 4 * pl.kp && env_int("LZ_SEED", 1) != 0) {
             GemmParams gs = g;
+            gs.row_mode = 0;                                   // the sample ranks groups: kp groups above S are kp rows above S
             gs.n_tiles = kSampleTiles; gs.n_slices = kSampleTiles; gs.tiles_per_slice = 1;
             gs.tile_mul = pl.n_tiles / kSampleTiles;
             const int n_clusters = pl.grid / pl.cs;
@@ -1386,7 +1395,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
     sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
-    sp.id_base = id_base; sp.sub = tiny_top1 ? 1 : kSub;
+    sp.id_base = id_base; sp.sub = (tiny_top1 || row_mode) ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
     if (tiny_top1) {
