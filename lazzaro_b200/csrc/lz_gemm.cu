@@ -130,7 +130,8 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
 }
 
 #ifdef LZ_STATS
-__device__ unsigned long long g_stats[8];   // 0 epi busy, 1 epi max, 2 mma wait tempty, 3 mma wait full, 4 prod wait empty, 5 tiles
+__device__ unsigned long long g_stats[8];
+__device__ unsigned long long g_sel_stats[4];   // exact pass: sum of merged groups, of groups kept by the prune, queries   // 0 epi busy, 1 epi max, 2 mma wait tempty, 3 mma wait full, 4 prod wait empty, 5 tiles
 #define LZ_T0 long long t0_ = clock64();
 #define LZ_ACC(i) atomicAdd(&g_stats[i], (unsigned long long)(clock64() - t0_));
 #else
@@ -618,6 +619,11 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
             }
         }
         m_eff = keep;
+#ifdef LZ_STATS
+        atomicAdd(&g_sel_stats[0], (unsigned long long)m);
+        atomicAdd(&g_sel_stats[1], (unsigned long long)keep);
+        atomicAdd(&g_sel_stats[2], 1ull);
+#endif
     }
     __syncthreads();
     m = m_eff;
@@ -1243,7 +1249,11 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
 extern "C" int lz_debug_stats(unsigned long long* host_out, int reset) {
     LZ_CUDA(cudaDeviceSynchronize());
     LZ_CUDA(cudaMemcpyFromSymbol(host_out, g_stats, sizeof(unsigned long long) * 8));
-    if (reset) { unsigned long long z[8] = {0}; LZ_CUDA(cudaMemcpyToSymbol(g_stats, z, sizeof(z))); }
+    unsigned long long ss[4];
+    LZ_CUDA(cudaMemcpyFromSymbol(ss, g_sel_stats, sizeof(ss)));
+    if (ss[2]) fprintf(stderr, "[lz stats] exact pass: %.1f groups merged, %.1f kept by the prune, per query (%llu queries)\n",
+                       (double)ss[0] / ss[2], (double)ss[1] / ss[2], ss[2]);
+    if (reset) { unsigned long long z[8] = {0}; LZ_CUDA(cudaMemcpyToSymbol(g_stats, z, sizeof(z))); LZ_CUDA(cudaMemcpyToSymbol(g_sel_stats, z, sizeof(ss))); }
     return LZ_OK;
 }
 #endif
@@ -1374,7 +1384,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
             SelectParams ss = {};
             ss.cand = (const u64*)(s + L.cand); ss.cand_cnt = (const int32_t*)(s + L.cand_cnt);
             ss.n_qtiles_pad = pl.n_qgroups * pl.cs; ss.n_slices = kSampleTiles; ss.kp = pl.kp; ss.cap = pl.cap;
-            ss.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads);
+            ss.cap_a = lz_next_pow2(2 * pl.kp + 2 * kSelThreads);     // room for kp survivors + a round of pushes + slack, so not every round compacts
             const size_t ssm = (size_t)ss.cap_a * 12;
             LZ_CUDA(cudaFuncSetAttribute(seed_threshold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm));
             seed_threshold_kernel<<<n_queries, kSelThreads, ssm, st>>>(ss, gthr);
@@ -1394,7 +1404,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
-    sp.cap_a = lz_next_pow2(pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
+    sp.cap_a = lz_next_pow2(2 * pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base; sp.sub = (tiny_top1 || row_mode) ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
