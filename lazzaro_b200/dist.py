@@ -102,3 +102,53 @@ class ShardedSearch:
             h_cnt.copy_(cnt, non_blocking=True)
             torch.cuda.current_stream().synchronize()
         return h_ids.numpy().copy(), h_sc.numpy().copy(), h_cnt.numpy().copy()
+
+    # -- pipelined host interface: the next batch's staging + H2D copy overlap the current batch's search
+    def submit_host(self, queries: np.ndarray, k: int, slot: int = 0) -> "_PendingSearch":
+        """Starts a search of host queries without waiting for it: stage into pinned memory, H2D on a copy
+        stream, the search and the D2H of the result on the current stream.  `slot` (0 or 1) picks one of two
+        sets of staging buffers — resubmit a slot only after its previous result() was taken.  Same answer as
+        search_host; a loop that keeps one search in flight hides the copies and the host work behind it."""
+        st = self.store
+        q = np.ascontiguousarray(queries, dtype=np.float32)
+        B = q.shape[0]
+        with torch.cuda.device(st.device):
+            if not hasattr(self, "_copy_stream"):
+                self._copy_stream = torch.cuda.Stream(device=st.device)
+                self._qdev = {}
+            stage = st._pinned(f"q{slot}", (B, st._dim_p), torch.float32)
+            if st._dim_p != st.dim:
+                stage.zero_()
+            stage[:, :st.dim] = torch.from_numpy(q)
+            key = (slot, B)
+            if key not in self._qdev:
+                self._qdev[key] = torch.empty((B, st._dim_p), dtype=torch.float32, device=st.device)
+            qd = self._qdev[key]
+            main = torch.cuda.current_stream()
+            # no wait on `main` here: the slot's previous search finished before its result() returned, and waiting
+            # on the stream would queue this copy behind the search that is running now
+            with torch.cuda.stream(self._copy_stream):
+                qd.copy_(stage, non_blocking=True)
+                ready = torch.cuda.Event()
+                ready.record()
+            main.wait_event(ready)
+            ids, sc, cnt = self.search_device(qd, k)
+            h_ids = st._pinned(f"ids{slot}", (B, k), torch.int64)
+            h_sc = st._pinned(f"sc{slot}", (B, k), torch.float64)
+            h_cnt = st._pinned(f"cnt{slot}", (B,), torch.int32)
+            h_ids.copy_(ids, non_blocking=True)
+            h_sc.copy_(sc, non_blocking=True)
+            h_cnt.copy_(cnt, non_blocking=True)
+            done = torch.cuda.Event()
+            done.record()
+        return _PendingSearch(done, h_ids, h_sc, h_cnt)
+
+
+class _PendingSearch:
+    def __init__(self, done, h_ids, h_sc, h_cnt):
+        self._done, self._bufs = done, (h_ids, h_sc, h_cnt)
+
+    def result(self):
+        """Waits for the search and returns host (ids int64 [B,k], scores float64 [B,k], counts int32 [B])."""
+        self._done.synchronize()
+        return tuple(b.numpy().copy() for b in self._bufs)

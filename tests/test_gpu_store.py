@@ -174,3 +174,29 @@ def test_two_level_policy_and_recall_report():
     assert rep[0]["rows_scanned_fraction_upper"] < rep[1]["rows_scanned_fraction_upper"] <= 1.0
     st.search_policy = "exact"
     assert [st.search_nodes(q.tolist(), limit=10) for q in qs] == exact
+
+
+def test_pipelined_host_search_equals_blocking():
+    """ShardedSearch.submit_host keeps one search in flight (staging + H2D of the next batch overlap it): same
+    ids, scores and counts as search_host and as the oracle, batch after batch, both staging slots."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.dist import ShardedSearch
+    from lazzaro_b200.store import B200Store
+    from oracle import flat_search
+    rows, _ = synth.clustered_rows(20000, 72, 8, seed=91)         # dim 72: padded to 72? exercises the staging pad path if any
+    st = B200Store()
+    st.add_rows(rows, id_prefix="node_")
+    ss = ShardedSearch(st, world=1)
+    batches = [synth.queries_near_rows(rows, 16, seed=92 + i) for i in range(5)]
+    pend, got = None, []
+    for i, q in enumerate(batches):
+        h = ss.submit_host(q, 10, slot=i & 1)
+        if pend is not None:
+            got.append(pend.result())
+        pend = h
+    got.append(pend.result())
+    for q, (ids, sc, cnt) in zip(batches, got):
+        b_ids, b_sc, b_cnt = ss.search_host(q, 10)
+        np.testing.assert_array_equal(ids, b_ids); np.testing.assert_array_equal(sc, b_sc); np.testing.assert_array_equal(cnt, b_cnt)
+        want, _ = flat_search.flat_topk_batch(rows, q, 10)
+        np.testing.assert_array_equal(ids, want)
