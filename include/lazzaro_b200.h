@@ -139,6 +139,12 @@ int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, in
  * slot), in_scores float64 same shape; outputs as lz_search_exact.  Uses no scratch. */
 int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,
                   int metric, int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
+/* Same, with `list_stride` elements (>= n_queries * k) between two consecutive lists in BOTH input arrays: lets
+ * one all-gather of a packed [ids | scores] block per GPU feed the merge directly (ids of list c at
+ * in_ids + c*list_stride, scores at in_scores + c*list_stride).  No reference counterpart. */
+int lz_merge_topk_strided(const int64_t* in_ids, const double* in_scores, int64_t list_stride, int n_lists,
+                          int n_queries, int k, int metric, int64_t* out_ids, double* out_scores,
+                          int32_t* out_counts, void* stream);
 
 /* Exact float64 scores of explicit (query, row) pairs — the rescoring step after a coarse pass and
  * the pairwise cosine of memory_system.py:197-203.  pair_q int32 [n_pairs], pair_row int64

@@ -33,6 +33,7 @@ SIGNATURES = {
     "lz_search_batched": (_i32, [_p, _p, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _i32, _i32, _f64,
                                  _i32, _f64, _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
+    "lz_merge_topk_strided": (_i32, [_p, _p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),
     "lz_segment_mean": (_i32, [_p, _i64, _i32, _p, _p, _i32, _p, _p]),
     "lz_edge_decay_prune_scratch_bytes": (_sz, [_i64]),

@@ -200,6 +200,7 @@ struct MergeParams {
     const u64* part_key; const u32* part_id; const int32_t* part_cnt;   // form A: scan partials
     const int64_t* in_ids; const double* in_scores; int n_queries;      // form B: (id, score) lists
     int n_lists; int k; int cap; int metric; int64_t id_base;
+    int64_t list_stride;                                                // form B: elements between two lists
     int max_lists;                                                      // lists whose prefix offsets fit behind the selector (0: flat merge)
     const int32_t* work_list; const int32_t* work_count;
     int64_t* out_ids; double* out_scores; int32_t* out_counts;
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
                     const size_t slot = (size_t)q * p.n_lists + c;
                     if (p.part_cnt[slot] >= r) m = p.part_key[slot * p.k + r - 1];
                 } else {
-                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + r - 1;
+                    const size_t at = (size_t)c * p.list_stride + (size_t)q * p.k + r - 1;
                     const double sc = p.in_scores[at];
                     if (p.in_ids[at] >= 0 && sc == sc) m = lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc);
                 }
@@ -272,7 +273,7 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
                 if (p.part_key) {
                     key = p.part_key[slot * p.k + mid];
                 } else {
-                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + mid;
+                    const size_t at = (size_t)c * p.list_stride + (size_t)q * p.k + mid;
                     const double sc = p.in_scores[at];
                     key = (p.in_ids[at] >= 0 && sc == sc) ? lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc) : 0ull;
                 }
@@ -312,7 +313,7 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
                         const size_t slot = (size_t)q * p.n_lists + c;
                         lz_sel_push(&sel, p.part_key[slot * p.k + j], p.part_id[slot * p.k + j]);
                     } else {
-                        const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
+                        const size_t at = (size_t)c * p.list_stride + (size_t)q * p.k + j;
                         const double sc = p.in_scores[at];
                         lz_sel_push(&sel, lz_ord((p.metric == LZ_COSINE) ? sc + 0.0 : 0.0 - sc), (u32)p.in_ids[at]);
                     }
@@ -336,7 +337,7 @@ __global__ void __launch_bounds__(kThreads) merge_kernel(MergeParams p) {
                     const size_t slot = (size_t)q * p.n_lists + c;
                     if (j < p.part_cnt[slot]) { mk[u] = p.part_key[slot * p.k + j]; mi[u] = p.part_id[slot * p.k + j]; }
                 } else {
-                    const size_t at = ((size_t)c * p.n_queries + q) * p.k + j;
+                    const size_t at = (size_t)c * p.list_stride + (size_t)q * p.k + j;
                     const int64_t id = p.in_ids[at];
                     const double s = p.in_scores[at];
                     if (id >= 0 && s == s) { mk[u] = lz_ord((p.metric == LZ_COSINE) ? s + 0.0 : 0.0 - s); mi[u] = (u32)id; }
@@ -527,7 +528,7 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     if (rc) return rc;
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
-    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries;
+    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = n_queries; m.list_stride = 0;
     m.n_lists = n_chunks; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = metric; m.id_base = id_base;
     m.work_list = work_list; m.work_count = work_count;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
@@ -554,13 +555,21 @@ extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const dou
 
 extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,
                              int metric, int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream) {
+    return lz_merge_topk_strided(in_ids, in_scores, (int64_t)n_queries * k, n_lists, n_queries, k, metric, out_ids,
+                                 out_scores, out_counts, stream);
+}
+
+extern "C" int lz_merge_topk_strided(const int64_t* in_ids, const double* in_scores, int64_t list_stride, int n_lists,
+                                     int n_queries, int k, int metric, int64_t* out_ids, double* out_scores,
+                                     int32_t* out_counts, void* stream) {
     if (n_queries <= 0) return LZ_OK;
     LZ_REQUIRE(in_ids && in_scores && out_ids && out_scores && out_counts, "lz_merge_topk: NULL pointer");
+    LZ_REQUIRE(list_stride >= (int64_t)n_queries * k, "lz_merge_topk: list_stride=%lld below n_queries*k", (long long)list_stride);
     LZ_REQUIRE(n_lists >= 1 && k >= 1 && k <= LZ_MAX_K, "lz_merge_topk: n_lists=%d k=%d", n_lists, k);
     LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_merge_topk: unknown metric %d", metric);
     MergeParams m;
     m.part_key = nullptr; m.part_id = nullptr; m.part_cnt = nullptr;
-    m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries;
+    m.in_ids = in_ids; m.in_scores = in_scores; m.n_queries = n_queries; m.list_stride = list_stride;
     m.n_lists = n_lists; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = metric; m.id_base = 0;
     m.work_list = nullptr; m.work_count = nullptr;
     m.out_ids = out_ids; m.out_scores = out_scores; m.out_counts = out_counts;
@@ -787,7 +796,7 @@ extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const 
     LZ_CUDA(cudaGetLastError());
     MergeParams m;
     m.part_key = p.part_key; m.part_id = p.part_id; m.part_cnt = p.part_cnt;
-    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = 1;
+    m.in_ids = nullptr; m.in_scores = nullptr; m.n_queries = 1; m.list_stride = 0;
     m.n_lists = chunks; m.k = k; m.cap = lz_next_pow2(k + kMergePer * kThreads); m.metric = LZ_L2;   // L2 form returns -key = importance
     m.id_base = 0; m.work_list = nullptr; m.work_count = nullptr;
     m.out_ids = out_idx; m.out_scores = out_importance; m.out_counts = out_count;

@@ -50,11 +50,12 @@ class ShardedSearch:
         self.world = world if world is not None else (dist.get_world_size(group) if dist.is_initialized() else 1)
         self._local = local_search or self._local_cuda
         self._merge = merge or self._merge_cuda
-        self._gather_ids = self._gather_sc = None
+        self._packed_merge = merge is None            # product path: lz_merge_topk_strided straight from the gathered block
+        self._gather = self._part = self._cnt = None
 
     # -- the product path
-    def _local_cuda(self, queries: torch.Tensor, k: int):
-        ids, sc, cnt = self.store.search_device(queries, 0, k, id_base=self.row_offset)
+    def _local_cuda(self, queries: torch.Tensor, k: int, out=None):
+        ids, sc, cnt = self.store.search_device(queries, 0, k, id_base=self.row_offset, out=out)
         return ids, sc, cnt
 
     def _merge_cuda(self, ids: torch.Tensor, scores: torch.Tensor):
@@ -63,17 +64,30 @@ class ShardedSearch:
 
     def search_device(self, queries: torch.Tensor, k: int):
         """queries float32 [B, dim_p] on this rank's GPU (same batch on every rank) -> global
-        (ids int64 [B,k], scores float64 [B,k], counts int32 [B]) on every rank."""
-        ids, sc, cnt = self._local(queries, k)
+        (ids int64 [B,k], scores float64 [B,k], counts int32 [B]) on every rank.
+
+        The exchange is ONE all-gather per search: each rank's local search writes its ids and its scores' bits
+        into one int64 block [2, B, k], the blocks are gathered into [world, 2, B, k], and the merge kernel reads
+        the gathered block in place (lz_merge_topk_strided)."""
         if self.world == 1:
-            return ids, sc, cnt
-        B = ids.shape[0]
-        if self._gather_ids is None or self._gather_ids.shape[1:] != (B, k):
-            self._gather_ids = torch.empty((self.world, B, k), dtype=torch.int64, device=ids.device)
-            self._gather_sc = torch.empty((self.world, B, k), dtype=torch.float64, device=ids.device)
-        self._all_gather(self._gather_ids, ids)
-        self._all_gather(self._gather_sc, sc)
-        return self._merge(self._gather_ids, self._gather_sc)
+            return self._local(queries, k)
+        B, dev = queries.shape[0], queries.device
+        if self._gather is None or self._gather.shape[2:] != (B, k) or self._gather.device != dev:
+            self._part = torch.empty((2, B, k), dtype=torch.int64, device=dev)
+            self._gather = torch.empty((self.world, 2, B, k), dtype=torch.int64, device=dev)
+            self._cnt = torch.empty((B,), dtype=torch.int32, device=dev)
+        part = self._part
+        if self._local == self._local_cuda:
+            self._local(queries, k, out=(part[0], part[1].view(torch.float64), self._cnt))    # written in place
+        else:                                                # injected local search (CPU tests of the bookkeeping)
+            ids, sc, _ = self._local(queries, k)
+            part[0].copy_(ids)
+            part[1].copy_(sc.contiguous().view(torch.int64))
+        self._all_gather(self._gather, part)
+        if self._packed_merge:
+            from . import kernels
+            return kernels.merge_topk_packed(self._gather, self.store._metric)
+        return self._merge(self._gather[:, 0].contiguous(), self._gather[:, 1].contiguous().view(torch.float64))
 
     def _all_gather(self, out: torch.Tensor, part: torch.Tensor):
         if dist.get_backend(self.group) == "gloo":           # CPU tests of the bookkeeping

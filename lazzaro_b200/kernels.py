@@ -91,6 +91,21 @@ def merge_topk(in_ids: torch.Tensor, in_scores: torch.Tensor, metric: int = _lib
     return ids, scores, counts
 
 
+def merge_topk_packed(packed: torch.Tensor, metric: int = _lib.COSINE):
+    """Merge from ONE gathered buffer: packed int64 [n_lists, 2, B, k], [:, 0] = ids, [:, 1] = the float64
+    scores' bits (lz_merge_topk_strided with list_stride = 2*B*k)."""
+    dev = _dev(packed)
+    assert packed.dtype == torch.int64 and packed.is_contiguous() and packed.dim() == 4 and packed.shape[1] == 2
+    L, _, B, k = packed.shape
+    ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+    scores = torch.empty((B, k), dtype=torch.float64, device=dev)
+    counts = torch.empty((B,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_merge_topk_strided(packed.data_ptr(), packed.data_ptr() + B * k * 8, 2 * B * k, L, B, k, metric,
+                                                ptr(ids), ptr(scores), ptr(counts), stream_ptr(dev)), "lz_merge_topk_strided")
+    return ids, scores, counts
+
+
 def score_pairs(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], queries: torch.Tensor,
                 pair_q: torch.Tensor, pair_row: torch.Tensor, metric: int = _lib.COSINE) -> torch.Tensor:
     """Exact float64 score of each (query, row) pair (lz_score_pairs)."""
