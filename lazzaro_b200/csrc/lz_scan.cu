@@ -661,7 +661,7 @@ extern "C" int lz_segment_mean(const float* rows, int64_t ld, int dim, const int
 // follow.  One streaming pass: 17 bytes per node (float32 salience) or 21 (float64), per-CTA selector, then the
 // per-list merge the scan uses.  HBM-bound.
 namespace {
-constexpr int kEvictPerThread = 8;
+constexpr int kEvictPerThread = 4;       // 1024 nodes per tile: a 24 KB selector, 8 CTAs per SM to hide the division latency
 constexpr int kEvictChunk = kThreads * kEvictPerThread;
 
 struct EvictParams {
@@ -671,23 +671,21 @@ struct EvictParams {
     u64* part_key; u32* part_id; int32_t* part_cnt;
     u64* gthr;                                             // best k-th key any CTA has reached (0 = none yet)
     int64_t stride;                                        // 1, or > 1 in the sampling pass (CTA b reads tile b*stride)
-    int sample;                                            // sampling pass: publish the threshold, write no list
+    int sample;                                            // sampling pass: one tile per CTA, its sel_k-th best goes to sample_keys
+    int sel_k;                                             // selector size in the sampling pass (the rank r)
+    u64* sample_keys;                                      // [gridDim.x] in the sampling pass
 };
 
-__device__ __forceinline__ double importance_of(double sal, int access, double last, double now) {
+__device__ __forceinline__ double importance_of(double sal, int access, double last, double now, const double* tenth) {
     const double days = __ddiv_rn(__dsub_rn(now, last), 86400.0);
     const double t1 = __dmul_rn(sal, 0.5);
     // access / 10 for 0 <= access < 10 is the correctly rounded quotient = the double nearest to the decimal
-    // tenth, which is what these literals are; >= 10 saturates at 1.0 (saves one float64 division per node)
-    double frac;
-    switch (access) {
-        case 0: frac = 0.0; break; case 1: frac = 0.1; break; case 2: frac = 0.2; break; case 3: frac = 0.3; break;
-        case 4: frac = 0.4; break; case 5: frac = 0.5; break; case 6: frac = 0.6; break; case 7: frac = 0.7; break;
-        case 8: frac = 0.8; break; case 9: frac = 0.9; break;
-        default: frac = access >= 10 ? 1.0 : fmin(1.0, __ddiv_rn((double)access, 10.0));
-    }
+    // tenth, which is what the table holds; >= 10 saturates at 1.0 (saves one float64 division per node).  A table
+    // in shared memory, not a switch: a switch compiles to a jump table and a warp with ten different counts runs
+    // its ten arms one after the other.
+    const double frac = access >= 10 ? 1.0 : (access >= 0 ? tenth[access] : fmin(1.0, __ddiv_rn((double)access, 10.0)));
     const double t2 = __dmul_rn(frac, 0.3);
-    const double t3 = __dmul_rn(__ddiv_rn(1.0, __dadd_rn(1.0, days)), 0.2);
+    const double t3 = __dmul_rn(__drcp_rn(__dadd_rn(1.0, days)), 0.2);       // 1.0 / x, correctly rounded
     return __dadd_rn(__dadd_rn(t1, t2), t3);
 }
 
@@ -696,10 +694,16 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
     u64* keys = reinterpret_cast<u64*>(smem);
     u32* ids = reinterpret_cast<u32*>(keys + p.cap);
     __shared__ LzSelector sel;
+    __shared__ double s_tenth[10];
     const int tid = threadIdx.x;
-    if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.k);
+    if (tid == 0) lz_sel_init(&sel, keys, ids, p.cap, p.sample ? p.sel_k : p.k);
+    if (tid < 10) {
+        const double t[10] = {0.0, 0.1, 0.2, 0.3, 0.4, 0.5, 0.6, 0.7, 0.8, 0.9};
+        s_tenth[tid] = t[tid];
+    }
     __syncthreads();
-    const int64_t n_tiles = (p.n + kEvictChunk - 1) / kEvictChunk;
+    const int64_t n_all = (p.n + kEvictChunk - 1) / kEvictChunk;
+    const int64_t n_tiles = p.sample ? min(n_all, (int64_t)blockIdx.x * p.stride + 1) : n_all;     // sampling: one tile
     for (int64_t t = (int64_t)blockIdx.x * p.stride; t < n_tiles; t += (int64_t)gridDim.x * p.stride) {
         const int64_t base = t * kEvictChunk;
         // any CTA's k-th best key bounds the global k-th best from below: every thread filters against the best
@@ -715,7 +719,7 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
             key[j] = 0ull;                                                        // 0 = nothing to push
             if (i < p.n) {
                 const double s = p.sal64 ? p.sal64[i] : (double)p.sal32[i];
-                const double imp = importance_of(s, p.access[i], p.last[i], p.now);
+                const double imp = importance_of(s, p.access[i], p.last[i], p.now, s_tenth);
                 if (p.out_all && !p.sample) p.out_all[i] = imp;
                 // larger key = better = LESS important; NaN importance is never evicted
                 const u64 kk = lz_ord(0.0 - imp);
@@ -726,12 +730,12 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
         for (int j = 0; j < kEvictPerThread; ++j)
             lz_sel_push_warp(&sel, key[j], (u32)(base + (int64_t)j * kThreads + tid), key[j] != 0ull);
         lz_sel_maybe_compact<kThreads>(&sel, kEvictChunk);
-        if (tid == 0 && sel.thr_key != 0ull) atomicMax(p.gthr, sel.thr_key);
+        if (tid == 0 && !p.sample && sel.thr_key != 0ull) atomicMax(p.gthr, sel.thr_key);
     }
     __syncthreads();
     lz_sel_compact<kThreads>(&sel);
-    if (p.sample) {                                        // the sample's k-th best bounds the k-th best of everything
-        if (tid == 0 && sel.thr_key != 0ull) atomicMax(p.gthr, sel.thr_key);
+    if (p.sample) {                                        // this tile's r-th best, for evict_seed_kernel
+        if (tid == 0) p.sample_keys[blockIdx.x] = sel.count >= p.sel_k ? sel.key[p.sel_k - 1] : 0ull;
         return;
     }
     const int n = min(sel.count, p.k);
@@ -743,17 +747,40 @@ __global__ void __launch_bounds__(kThreads) importance_select_kernel(EvictParams
     if (tid == 0) p.part_cnt[slot] = n;
 }
 
+// The `need`-th largest of the sampled tiles' r-th best keys: at least `need` tiles hold r nodes at or above it,
+// so at least need * r >= k nodes are — a lower bound of the k-th best key, found before the full pass starts,
+// so that the full pass filters from its first node instead of filling and sorting every CTA's buffer.
+__global__ void __launch_bounds__(kThreads) evict_seed_kernel(const u64* __restrict__ sample_keys, int n_keys, int need,
+                                                              int cap, u64* __restrict__ gthr) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    u64* keys = reinterpret_cast<u64*>(smem);
+    u32* ids = reinterpret_cast<u32*>(keys + cap);
+    __shared__ LzSelector sel;
+    const int tid = threadIdx.x;
+    if (tid == 0) lz_sel_init(&sel, keys, ids, cap, need);
+    __syncthreads();
+    for (int base = 0; base < n_keys; base += kThreads) {
+        const int i = base + tid;
+        const u64 k = i < n_keys ? sample_keys[i] : 0ull;
+        if (k != 0ull) lz_sel_push(&sel, k, (u32)i);
+        lz_sel_maybe_compact<kThreads>(&sel, kThreads);
+    }
+    __syncthreads();
+    lz_sel_compact<kThreads>(&sel);
+    if (tid == 0 && sel.count >= need) *gthr = sel.key[need - 1];
+}
+
 int evict_chunks(int64_t n, int k) {
     const int sms = lz_sm_count();
     int64_t tiles = (n + kEvictChunk - 1) / kEvictChunk;
-    int64_t want = (int64_t)(sms > 0 ? sms : 1) * (k <= 256 ? 4 : 2);      // selector: 12 B x next_pow2(k + 2048) of shared memory
+    int64_t want = (int64_t)(sms > 0 ? sms : 1) * (k <= 256 ? 8 : 2);      // selector: 12 B x next_pow2(k + 1024) of shared memory
     return (int)(tiles < want ? (tiles < 1 ? 1 : tiles) : want);
 }
 }  // namespace
 
 extern "C" size_t lz_evict_lowest_scratch_bytes(int64_t n, int k) {
     if (n <= 0 || k <= 0) return 0;
-    return lz_search_exact_scratch_bytes(1, k, evict_chunks(n, k)) + 256;       // + the shared threshold word
+    return lz_search_exact_scratch_bytes(1, k, evict_chunks(n, k)) + 256 + (size_t)evict_chunks(n, k) * 8;   // + threshold word + sample keys
 }
 
 extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const int32_t* access_count,
@@ -772,7 +799,7 @@ extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const 
     LZ_REQUIRE(n <= 0xfffffffeLL, "lz_evict_lowest: n=%lld exceeds 32-bit indices", (long long)n);
     const int chunks = evict_chunks(n, k);
     const size_t part_bytes = lz_search_exact_scratch_bytes(1, k, chunks);
-    const size_t need = part_bytes + 256;
+    const size_t need = part_bytes + 256 + (size_t)chunks * 8;
     if (scratch_bytes < need) {
         lz_set_error("lz_evict_lowest: scratch has %zu bytes, needs %zu", scratch_bytes, need);
         return LZ_ERR_SCRATCH;
@@ -791,7 +818,25 @@ extern "C" int lz_evict_lowest(const void* salience, int salience_is_f64, const 
     LZ_CUDA(cudaMemsetAsync(p.gthr, 0, 8, st));
     const size_t smem = (size_t)p.cap * 12;
     LZ_CUDA(cudaFuncSetAttribute(importance_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    p.stride = 1; p.sample = 0;
+    p.stride = 1; p.sample = 0; p.sel_k = k; p.sample_keys = (u64*)(s + part_bytes + 256);
+    {
+        // sampling pass: G tiles spread evenly over the nodes, one per CTA; see evict_seed_kernel
+        const int64_t n_tiles = (n + kEvictChunk - 1) / kEvictChunk;
+        const int g_max = chunks < 2 * lz_sm_count() ? chunks : 2 * lz_sm_count();   // a few hundred tiles rank k <= 1024 well
+        const int G = (int)(n_tiles / 8 < g_max ? n_tiles / 8 : g_max);
+        int r = G > 0 ? (4 * k + G - 1) / G : 0;
+        if (r < 1) r = 1;
+        const int need_tiles = (k + r - 1) / r;
+        if (G >= 16 && r <= kEvictChunk / 4 && need_tiles <= G) {
+            EvictParams ps = p;
+            ps.sample = 1; ps.sel_k = r; ps.stride = n_tiles / G; ps.out_all = nullptr;
+            importance_select_kernel<<<G, kThreads, smem, st>>>(ps);
+            const int scap = lz_next_pow2(need_tiles + kThreads);
+            const size_t ssmem = (size_t)scap * 12;
+            LZ_CUDA(cudaFuncSetAttribute(evict_seed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
+            evict_seed_kernel<<<1, kThreads, ssmem, st>>>(p.sample_keys, G, need_tiles, scap, p.gthr);
+        }
+    }
     importance_select_kernel<<<chunks, kThreads, smem, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     MergeParams m;
