@@ -200,3 +200,36 @@ def test_edge_find_and_reinforce_kernels():
     c[idx] += times
     np.testing.assert_array_equal(wt.cpu().numpy(), want)
     np.testing.assert_array_equal(ct.cpu().numpy(), c)
+
+
+def test_cfg5_size_adjacency_properties():
+    """BASELINE configs[4] edge count on one GPU: 50M edges over 12.5M nodes — size-independent properties of the
+    index (checked on the device): offsets = prefix sums of the degrees, every node's entries are its own and in
+    ascending edge order, and sampled neighbour lists equal a brute-force scan of the edge columns."""
+    from lazzaro_b200 import kernels as K
+    nn, ne = 12_500_000, 50_000_000
+    g = torch.Generator(device="cuda"); g.manual_seed(11)
+    src = torch.randint(0, nn, (ne,), device="cuda", generator=g, dtype=torch.int32)
+    dst = torch.randint(0, nn, (ne,), device="cuda", generator=g, dtype=torch.int32)
+    dst[::1000] = src[::1000]                                     # self-loops: one entry each
+    w = torch.rand(ne, device="cuda", generator=g)
+    off, adj = K.csr_build(src, dst, ne, nn)
+    loops = int((src == dst).sum())
+    assert int(off[0]) == 0 and int(off[-1]) == 2 * ne - loops
+    deg = torch.bincount(src.long(), minlength=nn) + torch.bincount(dst[src != dst].long(), minlength=nn)
+    assert bool((off[1:] - off[:-1] == deg).all())
+    del deg
+    ent = adj[: 2 * ne - loops].long()
+    e, side = ent >> 1, ent & 1
+    owner = torch.where(side == 1, dst[e].long(), src[e].long())
+    assert bool((owner[1:] >= owner[:-1]).all())                  # grouped by node ...
+    same = owner[1:] == owner[:-1]
+    assert bool((ent[1:][same] > ent[:-1][same]).all())           # ... ascending edge order inside a node
+    del ent, e, side, owner, same
+    nodes = torch.randint(0, nn, (64,), device="cuda", generator=g, dtype=torch.int32)
+    nbr, cnt, edge = K.neighbors(off, adj, src, dst, w, nn, nodes, 0.3, want_edges=True)
+    for j, v in enumerate(nodes.tolist()):
+        hit = ((src == v) | (dst == v)) & (w.double() >= 0.3)
+        idx = torch.nonzero(hit).flatten()
+        assert edge[j, :int(cnt[j])].tolist() == idx.tolist()
+        assert nbr[j, :int(cnt[j])].tolist() == torch.where(src[idx] == v, dst[idx], src[idx]).tolist()

@@ -59,3 +59,26 @@ def test_eviction_edge_cases():
     assert idx.numel() == 0
     with pytest.raises(_lib.LazzaroB200Error):
         _evict(np.ones(5000, np.float32), np.ones(5000), np.ones(5000), 10.0, 2000)
+
+
+def test_cfg5_size_eviction_equals_device_sort():
+    """12.5M nodes (one GPU's share of BASELINE configs[4]): the k least important nodes equal a stable float64 sort of
+    the same expression evaluated operation by operation with torch on the device (each torch op rounds once, as the
+    reference's Python expression does)."""
+    from lazzaro_b200 import kernels as K
+    n, now = 12_500_000, 1.76e9
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    sal = (torch.randint(0, 101, (n,), device="cuda", generator=g).float() / 100).contiguous()      # many exact ties
+    acc = torch.randint(0, 15, (n,), device="cuda", generator=g, dtype=torch.int32)
+    last = now - torch.randint(0, 400, (n,), device="cuda", generator=g).double() * 86400.0
+    skip = (torch.rand(n, device="cuda", generator=g) < 0.02).to(torch.uint8)
+    c = lambda v: torch.tensor(v, dtype=torch.float64, device="cuda")     # tensor divisors: torch turns `x / python_scalar`
+    days = (now - last) / c(86400.0)                                       # into a multiplication by the reciprocal
+    imp = sal.double() * 0.5 + torch.clamp(acc.double() / c(10.0), max=1.0) * 0.3 + torch.reciprocal(1.0 + days) * 0.2
+    masked = torch.where(skip.bool(), torch.full_like(imp, float("inf")), imp)
+    for k in (1, 64, 1024):
+        idx, val, all_imp = K.evict_lowest(sal, acc, last, now, k, skip=skip, want_all=True)
+        assert bool((all_imp == imp).all())
+        order = torch.sort(masked, stable=True).indices[:k]
+        assert idx.tolist() == order.tolist()
+        assert bool((val == imp[order]).all())
