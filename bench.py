@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--cpu-sample-rows", type=int, default=400_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--edges", type=int, default=50_000_000, help="edge-table size for the decay+prune sub-result (0 = skip)")
+    ap.add_argument("--no-consolidation", action="store_true", help="skip the consolidation sub-result (BASELINE configs[2])")
     return ap.parse_args()
 
 
@@ -357,7 +358,57 @@ def main():
                                             "frac": ach_e / hbm_peak, "traffic": None,
                                             "kernel": "count_kernel + tile_scan_kernel + decay_prune_kernel (lz_edge_decay_prune)",
                                             "algorithmic_bytes_per_launch": ebytes}}
+    if world == 1 and not args.no_consolidation and n_local >= 1_000_000 and args.dim == 768:
+        # north_star (2) / BASELINE configs[2]: a 10k-node episodic buffer deduplicated against a 1M-node graph (top-1 +
+        # cosine gate), then one k-means style shard reassignment with k = 1024 (assign + centroid update) — on the first
+        # 1M resident rows; the 1024 starting centroids are the means of 1024 equal slabs of those rows
+        from lazzaro_b200 import consolidate
+        n_g, n_new, kc = 1_000_000, 10_000, 1024
+        graph = rows[:n_g]
+        new = synth.queries_near_rows_device(graph, n_new, noise=0.25, seed=synth.SEED_QUERY + 7)
+        f_dedup = lambda: store.search_device(new, 0, 1, row_range=(0, n_g))
+        # two centroid layouts, both reported: 1024 well-separated centroids (random rows of the graph), and the means of
+        # 1024 equal slabs of the rows = ~10 nearly coincident centroids per true cluster, which is what k-means with
+        # k > #clusters produces and where every row has several candidates within the rescoring margin
+        seg = torch.linspace(0, n_g, kc + 1, device=dev).long()
+        cen = consolidate.centroid_means(graph, seg_offsets=seg).float().contiguous()
+        cen_sep = graph[torch.randperm(n_g, device=dev, generator=torch.Generator(device=dev).manual_seed(9))[:kc]].contiguous()
+        f_assign = lambda: consolidate.assign_to_centroids(graph, cen_sep)
+        f_assign_co = lambda: consolidate.assign_to_centroids(graph, cen)
+        f_update = lambda: consolidate.centroid_means(graph, seg_offsets=seg)
+        parts = {}
+        for name, fn, flops in (("dedup_10k_x_1M_top1", f_dedup, 2.0 * n_new * n_g * args.dim),
+                                ("assign_1M_x_1024_separated", f_assign, 2.0 * n_g * kc * args.dim),
+                                ("assign_1M_x_1024_coincident", f_assign_co, 2.0 * n_g * kc * args.dim),
+                                ("centroid_update_1M", f_update, None)):
+            for _ in range(2):
+                fn()
+            ms_c, _ = timed(fn, 5)
+            parts[name] = {"ms": ms_c / 5}
+            if flops:
+                parts[name]["tflops"] = flops / (ms_c / 5 * 1e-3) / 1e12
+                parts[name]["frac_of_sustained_bf16_peak"] = parts[name]["tflops"] / tc_peak
+            else:
+                parts[name]["gbs"] = n_g * args.dim * 4 / (ms_c / 5 * 1e-3) / 1e9
+                parts[name]["frac_of_hbm_peak"] = parts[name]["gbs"] / hbm_peak
+        line["consolidation"] = {"metric": "consolidation wall time: dedup 10k x 1M + shard reassignment (k=1024) + centroid update, 768-d",
+                                 "value": sum(v["ms"] for k_, v in parts.items() if k_ != "assign_1M_x_1024_coincident"),
+                                 "value_with_coincident_centroids": sum(v["ms"] for k_, v in parts.items() if k_ != "assign_1M_x_1024_separated"),
+                                 "unit": "ms", "higher_is_better": False,
+                                 "parts": parts, "gpu_launches": 5 * (7 + 3 + 1)}
+        del new, cen, cen_sep
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        if "consolidation" in line:
+            # the reference's dedup is one flat scan per new memory (memory_system.py:719-742): numpy port on a bounded sample
+            rs = np.random.default_rng(5).standard_normal((50_000, args.dim)).astype(np.float32)
+            qs_ = np.random.default_rng(6).standard_normal((1_000, args.dim)).astype(np.float32)
+            t0 = time.perf_counter()
+            from oracle import flat_search
+            flat_search.fast_topk_f32(rs, qs_, 1)
+            dt = time.perf_counter() - t0
+            line["consolidation"]["cpu_baseline"] = {"value": dt * 1e3 * (1_000_000 / 50_000) * (10_000 / 1_000), "unit": "ms",
+                                                     "cores": os.cpu_count(), "kind": "port",
+                                                     "sample": "numpy sgemm + argmax dedup of 1000 x 50000 rows, scaled linearly to 10k x 1M (dedup part only)"}
         qps, desc, cores, _ = cpu_search_qps(args, 3, 1)
         line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
         if "decay_prune" in line:
