@@ -121,7 +121,11 @@ size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int
  * it.  Results are those of lz_search_exact with the same metric whenever the margin holds; the margin is
  * statistical: margin_sigmas standard deviations of the bf16 rounding error (4 is the default used
  * by the Python layer).
- *   shadow_bf16   bf16 [n_rows_total, dim (+ 8 for LZ_L2)] from lz_rows_to_bf16 with the same metric
+ *   shadow_bf16   bf16 [n_rows_total, dim (+ 8 for LZ_L2)] from lz_rows_to_bf16 with the same metric.  Must be plain
+ *                 device memory allocated on the CURRENT GPU (checked; LZ_ERR_ARG otherwise): the coarse pass loads
+ *                 it by TMA multicast, and TMA multicast loads here read only this GPU's memory, since on B200 a
+ *                 TMA multicast load from another GPU's memory hung the GPU.  A multi-GPU search keeps one shadow
+ *                 per GPU and merges the per-GPU results (lz_merge_topk) — it never hands one GPU another's rows
  *   max_row_norm  LZ_L2 only: an upper bound of the row norms (scales the error margin)
  *   tags/want_tag as lz_search_exact with one tag for the whole batch (want_tag < 0: any live row)
  *   row_lo,row_hi the row range every query scans

@@ -31,7 +31,7 @@ using namespace sm100;
 constexpr int BM = 128;                 // queries per tile  (MMA M, one TMEM lane per query)
 constexpr int BN = 256;                 // rows per tile     (MMA N, one TMEM column per row)
 constexpr int BK = 64;                  // bf16 elements per pipeline stage = one 128-byte swizzle row
-constexpr int A_BYTES = BM * BK * 2;    // 16 KiB per stage; the rows tile adds 32 KiB (16 KiB per CTA in pair mode)
+constexpr int A_BYTES = BM * BK * 2;    // 16 KiB per stage; the rows tile adds 32 KiB
 constexpr int kGemmThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
 constexpr int kTmemCols = 512;          // two 128x256 fp32 accumulators
 constexpr int kSelThreads = 256;
@@ -152,7 +152,6 @@ struct GemmParams {
     int32_t* cand_cnt;  // [n_items][BM]
     float* cand_thr;    // [n_items][BM]  every row dropped by this (item, query) had coarse <= thr
     u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
-    int row_mode;             // candidates are single rows (two-level test: group max first), not groups of kSub
     const double* top1_eps;   // top-1 against a tiny table only (else null): per-query eps; the threshold then
                               // follows the running best group at a distance of 3 eps (see scan_chunk)
 };
@@ -246,7 +245,7 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     // and the final threshold T = c_1 - 3 eps certifies by construction (exact best >= c_1 - eps > T + eps).
     // Chunks reaching past the range are left out: their rows are not candidates.
     if (row_first + 32 <= p.row_hi) thr = fmaxf(thr, m - slack);
-    const bool top1 = slack != INFINITY || p.row_mode != 0;       // single-row candidates
+    const bool top1 = slack != INFINITY;                          // single-row candidates
     if (m > thr) {
         if (top1) {
             // row mode keeps single ROWS: the group max is tested first, so the common case (nothing passes) costs
@@ -277,16 +276,18 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     }
 }
 
-// PAIR = true: the 2-CTA cluster runs as one tcgen05 cta_group::2 unit — M = 256 (each CTA's 128 queries),
-// the 256-row rows tile split across the two CTAs' shared memories (128 rows each, read by the MMA from
-// both), one MMA issuer in the leader CTA.  Per CTA and K step that is 8 KB of operand reads and 8 KB of
-// TMA writes instead of 12 + 12 with multicast copies, which is what the 128 B/clk shared-memory port
-// can sustain; the ring is 6 stages of 32 KB.  PAIR = false: the cta_group::1 form (any cluster size).
-template <int EPL, bool PAIR>
+// cta_group::1 MMAs; a cluster of cs (1 or 2) CTAs shares each rows tile.  (A cta_group::2 form — M = 256 across a
+// CTA pair, rows tile split over the two shared memories — and clusters of 4 and 8 were built and measured in
+// round 1: 12.50 ms, 12.7 ms and 13.5 ms against 12.0-12.3 ms for this form at 10M x 768, batch 1024; removed.)
+//
+// The rows tile is loaded with TMA MULTICAST when cs == 2: tmap_x must cover memory of THIS GPU only.  TMA
+// multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+// memory hung the GPU; lz_search_batched rejects a shadow that is not an allocation of the current device.
+template <int EPL>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_x, GemmParams p) {
-    constexpr int kStages = PAIR ? 6 : 4;
-    constexpr int B_BYTES = PAIR ? BN * BK : BN * BK * 2;            // half the rows tile per CTA in pair mode
+    constexpr int kStages = 4;
+    constexpr int B_BYTES = BN * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     extern __shared__ unsigned char smem_raw[];
     unsigned char* tiles = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // 1024-byte aligned
@@ -308,16 +309,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (threadIdx.x == 0) {
         prefetch_tmap(&tmap_q);
         prefetch_tmap(&tmap_x);
-        // pair mode: one multicast commit from the leader releases a stage in both CTAs; the leader's
-        // tempty collects the four epilogue warps of both CTAs
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], PAIR ? 1 : cs); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], PAIR ? 8 : 4); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], cs); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
         fence_mbar_init();
     }
-    if (warp == 1) {
-        if (PAIR) tmem_alloc_pair(tmem_slot, kTmemCols);
-        else tmem_alloc(tmem_slot, kTmemCols);
-    }
+    if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
     tc_fence_before();
     __syncthreads();
     if (cs > 1) cluster_sync();          // every CTA's barriers exist before anyone multicasts into them
@@ -338,14 +334,6 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     for (int kb = 0; kb < p.kblocks; ++kb) {
                         { LZ_T0 mbar_wait(&empty[stage], phase ^ 1); LZ_ACC(4) }   // all cs consumers have released the stage
                         unsigned char* st = tiles + stage * STAGE_BYTES;
-                        if (PAIR) {
-                            // both CTAs' bytes are counted on the leader's barrier, which its MMA thread waits on
-                            if (rank == 0) mbar_expect_tx(&full[stage], 2 * STAGE_BYTES);
-                            tma_load_2d_pair(st, &tmap_q, &full[stage], kb * BK, qt * BM);
-                            tma_load_2d_pair(st + A_BYTES, &tmap_x, &full[stage], kb * BK, row0 + rank * (BN / 2));
-                            if (++stage == kStages) { stage = 0; phase ^= 1; }
-                            continue;
-                        }
                         mbar_expect_tx(&full[stage], STAGE_BYTES);
                         tma_load_2d(st, &tmap_q, &full[stage], kb * BK, qt * BM);
                         if (cs > 1)
@@ -360,9 +348,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         __syncwarp();
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread; in pair mode only the leader CTA issues) =====
-        if (lane == 0 && (!PAIR || rank == 0)) {
-            constexpr uint32_t idesc = idesc_bf16_f32(PAIR ? 2 * BM : BM, BN);
+        // ===== MMA issuer (one thread) =====
+        if (lane == 0) {
+            constexpr uint32_t idesc = idesc_bf16_f32(BM, BN);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (int item = cluster_id; item < n_items; item += n_clusters) {
                 const int sl = item / p.n_qgroups;
@@ -379,16 +367,13 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                         const uint64_t db = smem_desc_sw128(tiles + stage * STAGE_BYTES + A_BYTES);
 #pragma unroll
                         for (int k = 0; k < BK / 16; ++k) {     // 32 bytes along K per MMA: +2 in 16-byte units
-                            if (PAIR) mma_bf16_ss_pair(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
-                            else mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                            mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
                         }
-                        if (PAIR) mma_commit_pair(&empty[stage], 3);         // frees the stage in both CTAs
-                        else if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
+                        if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
                         else mma_commit(&empty[stage]);          // frees the smem stage when these MMAs retire
                         if (++stage == kStages) { stage = 0; phase ^= 1; }
                     }
-                    if (PAIR) mma_commit_pair(&tfull[acc], 3);   // accumulator complete, in both CTAs
-                    else mma_commit(&tfull[acc]);
+                    mma_commit(&tfull[acc]);                      // accumulator complete
                     acc ^= 1;
                     if (acc == 0) acc_phase ^= 1;
                 }
@@ -450,10 +435,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                     if (d > 6000) atomicAdd(&g_stats[7], d - 6000);
                 }
 #endif
-                if (lane == 0) {
-                    if (PAIR) mbar_arrive_remote(&tempty[acc], 0);   // the leader's MMA thread owns the pair's accumulators
-                    else mbar_arrive(&tempty[acc]);
-                }
+                if (lane == 0) mbar_arrive(&tempty[acc]);
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
@@ -468,8 +450,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     if (cs > 1) cluster_sync();          // no CTA leaves while a peer may still signal its barriers
     if (warp == 1) {
         tc_fence_after();
-        if (PAIR) tmem_dealloc_pair(tmem_base, kTmemCols);
-        else tmem_dealloc(tmem_base, kTmemCols);
+        tmem_dealloc(tmem_base, kTmemCols);
     }
 }
 
@@ -1143,6 +1124,27 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t n_rows, int dim, int box
     return LZ_OK;
 }
 
+// The rows tile of the coarse pass is fetched by TMA multicast, and TMA multicast loads here read only this
+// GPU's memory (on B200 a TMA multicast load from another GPU's memory hung the GPU).  So the shadow must be
+// plain device memory allocated on the CURRENT device: peer, IPC-imported, managed and host-mapped pointers
+// are rejected before any tensor map is built over them.
+int require_local_device_memory(const void* p, const char* what) {
+    int dev = -1;
+    LZ_CUDA(cudaGetDevice(&dev));
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        lz_set_error("%s is not a CUDA allocation", what);
+        return LZ_ERR_ARG;
+    }
+    if (at.type != cudaMemoryTypeDevice || at.device != dev) {
+        lz_set_error("%s must be device memory allocated on the current GPU (device %d); got memory type %d on device %d",
+                     what, dev, (int)at.type, at.device);
+        return LZ_ERR_ARG;
+    }
+    return LZ_OK;
+}
+
 struct Plan {
     int n_qtiles, cs, n_qgroups, n_tiles, n_slices, tiles_per_slice, kp, cap, fb_chunks, grid;
 };
@@ -1153,24 +1155,22 @@ int env_int(const char* name, int dflt) {
 }
 
 // cs = CTAs per cluster sharing each rows tile by TMA multicast (one q-tile each).  Measured at 10M x 768,
-// batch 1024 on B200 (ms per batch): cs=1 13.8, cs=2 12.0, cs=4 12.7, cs=8 13.5 — so the default is 2;
-// LZ_CLUSTER overrides.
-constexpr size_t kGemmSmem = 1024 + (size_t)196608 + (2 * 6 + 4) * 8 + 16;   // 4 x 48 KiB or 6 x 32 KiB of stages
+// batch 1024 on B200 (ms per batch): cs=1 13.8, cs=2 12.0 — so the default is 2; LZ_CLUSTER=1 overrides.
+constexpr size_t kGemmSmem = 1024 + (size_t)196608 + (2 * 4 + 4) * 8 + 16;   // 4 x 48 KiB of stages
 
 // How many clusters of `cs` CTAs the device can hold at once.  Clusters are placed inside one GPC, and GPCs do
 // not all have a multiple of `cs` usable SMs, so this can be less than SMs / cs — and a persistent grid with more
 // clusters than that runs its surplus clusters as a second wave (measured: cs = 4 took 20.1 ms instead of ~12).
 int active_clusters(int cs) {
-    static int cache[16][9];                                  // [device][cs]
+    static int cache[16][3];                                  // [device][cs]
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16 || cs < 1 || cs > 8) return 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16 || cs < 1 || cs > 2) return 0;
     if (cache[dev][cs] > 0) return cache[dev][cs];
     const int sms = lz_sm_count();
     int n = sms / cs;
     if (cs > 1) {
-        auto kern = gemm_topk_kernel<8, false>;
+        auto kern = gemm_topk_kernel<8>;
         cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem);
-        if (cs > 4) cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
         cudaLaunchConfig_t cfg = {};
         cfg.gridDim = dim3((unsigned)(sms / cs * cs));
         cfg.blockDim = dim3(kGemmThreads);
@@ -1193,7 +1193,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     if (sms <= 0) return LZ_ERR_DEVICE;
     pl->n_qtiles = (n_queries + BM - 1) / BM;
     int cs = env_int("LZ_CLUSTER", 2);
-    if (cs != 1 && cs != 2 && cs != 4 && cs != 8) cs = 2;
+    if (cs != 1 && cs != 2) cs = 2;
     while (cs > 1 && cs / 2 >= pl->n_qtiles) cs /= 2;             // no larger than the q-tiles there are
     pl->cs = cs;
     pl->n_qgroups = (pl->n_qtiles + cs - 1) / cs;
@@ -1305,6 +1305,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     LZ_REQUIRE(margin_sigmas > 0.0, "lz_search_batched: margin_sigmas must be positive");
     LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_batched: unknown metric %d", metric);
     LZ_REQUIRE(metric == LZ_COSINE || max_row_norm >= 0.0, "lz_search_batched: LZ_L2 needs max_row_norm >= 0");
+    if (int rc = require_local_device_memory(shadow_bf16, "lz_search_batched: shadow_bf16")) return rc;
     const int dim_s = metric == LZ_L2 ? dim + 8 : dim;         // columns of the shadow (and K of the contraction)
     Plan pl;
     if (int rc = make_plan(row_hi - row_lo, n_queries, k, &pl)) return rc;
@@ -1330,18 +1331,12 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     const size_t rows_smem = (size_t)kSub * dim * 4;
     const bool tiny_top1 = k == 1 && tags == nullptr && pl.n_slices == 1 && row_hi - row_lo <= (int64_t)kBucketGroups * kSub &&
                            rows_smem <= 160 * 1024 && n_queries >= 4 * kBucketQ;
-    // Single-row candidates for every k (LZ_ROWMODE=1) were tried to shrink the exact pass (kSub rows per group
-    // candidate: 2.0 ms per batch of 1024 at k = 100): measured slower overall — 18.0 vs 15.6 ms at k = 100, 14.6 vs
-    // 12.0 ms at k = 10 (10M x 768) — because more entries pass the group-level seeds and the epilogue compacts
-    // more often, which stalls the MMA pipeline.  Off by default; the top-1 tiny-table mode is the one user.
-    const bool row_mode = !tiny_top1 && tags == nullptr && env_int("LZ_ROWMODE", 0) != 0;
+    // (Single-row candidates for every k were tried to shrink the exact pass and measured slower overall — 18.0 vs
+    // 15.6 ms at k = 100, 14.6 vs 12.0 ms at k = 10 at 10M x 768: more entries pass the group-level seeds and the
+    // epilogue compacts more often, which stalls the MMA pipeline.  The top-1 tiny-table mode is the one user.)
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
-        // cta_group::2 (LZ_PAIR=1) measured no faster than two cta_group::1 CTAs with a multicast rows tile:
-        // 12.50 vs 12.27 ms in bursts, 14.83 vs 14.10 ms under the power cap (10M x 768, batch 1024), so the
-        // multicast form stays the default
-        const bool pair = pl.cs == 2 && env_int("LZ_PAIR", 0) != 0;
         if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim_s, BN / pl.cs)) return rc;
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
@@ -1349,15 +1344,11 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr; g.top1_eps = tiny_top1 ? eps : nullptr;
-        g.row_mode = row_mode ? 1 : 0;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
         const size_t smem = kGemmSmem;
-        auto kern = pair ? (pl.kp == 32 ? gemm_topk_kernel<2, true> : pl.kp == 128 ? gemm_topk_kernel<8, true>
-                            : pl.kp == 256 ? gemm_topk_kernel<16, true> : gemm_topk_kernel<32, true>)
-                         : (pl.kp == 32 ? gemm_topk_kernel<2, false> : pl.kp == 128 ? gemm_topk_kernel<8, false>
-                            : pl.kp == 256 ? gemm_topk_kernel<16, false> : gemm_topk_kernel<32, false>);
+        auto kern = pl.kp == 32 ? gemm_topk_kernel<2> : pl.kp == 128 ? gemm_topk_kernel<8>
+                    : pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>;
         LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        if (pl.cs > 4) LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         cudaLaunchConfig_t cfg = {};
         cfg.blockDim = dim3(kGemmThreads);
         cfg.dynamicSmemBytes = smem;
@@ -1374,7 +1365,6 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         constexpr int kSampleTiles = 64;
         if (pl.n_tiles >= 8 * kSampleTiles && kSampleTiles * (BN / kSub) >= 4 * pl.kp && env_int("LZ_SEED", 1) != 0) {
             GemmParams gs = g;
-            gs.row_mode = 0;                                   // the sample ranks groups: kp groups above S are kp rows above S
             gs.n_tiles = kSampleTiles; gs.n_slices = kSampleTiles; gs.tiles_per_slice = 1;
             gs.tile_mul = pl.n_tiles / kSampleTiles;
             const int n_clusters = pl.grid / pl.cs;
@@ -1405,7 +1395,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
     sp.cap_a = lz_next_pow2(2 * pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
-    sp.id_base = id_base; sp.sub = (tiny_top1 || row_mode) ? 1 : kSub;
+    sp.id_base = id_base; sp.sub = tiny_top1 ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
     if (tiny_top1) {
