@@ -103,25 +103,37 @@ int lz_search_exact(const float* rows, int64_t ld, int dim, const double* norms,
 
 #define LZ_BATCHED_MAX_K 128   /* largest k lz_search_batched accepts (larger k: lz_search_exact) */
 
-/* The bf16 copy of the rows that the coarse pass reads; refresh the rows you add.  dim % 8 == 0.
- *   LZ_COSINE: shadow[i][j] = bf16(rows[i][j] / norms[i]) (zeros for a zero row), bf16 [n, dim] dense
- *   LZ_L2    : shadow[i] = [bf16(rows[i]), h, m, l, 0, 0, 0, 0], bf16 [n, dim + 8] dense, h + m + l = a three-way
- *              bf16 split of -|row|^2 / 2, so that one contraction yields x.q - |x|^2/2 (L2 ranking) */
-int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
-                    void* shadow_bf16, void* stream);
+/* The fp16 copy of the rows ("shadow") that the coarse pass reads; refresh the rows you add.  dim % 8 == 0.
+ * (fp16 rather than bf16: same tensor-core rate, and its 11 significant bits keep the coarse score's rounding
+ * error 8x smaller — small enough for the deterministic certification margin below to be practical.)
+ *   LZ_COSINE: shadow[i][j] = fp16(rows[i][j] / norms[i]) (zeros for a zero row), fp16 [n, dim] dense
+ *   LZ_L2    : shadow[i] = [fp16(rows[i]), h, m, l, 0, 0, 0, 0], fp16 [n, dim + 8] dense, h + m + l = a three-way
+ *              fp16 split of -|row|^2 / 2, so that one contraction yields x.q - |x|^2/2 (L2 ranking)
+ *   row_err   optional float32 [n] (NULL to skip): an upper bound of the 2-norm of each row's rounding error,
+ *             |shadow - row/|row|| (LZ_COSINE) or |fp16(row) - row| (LZ_L2); +inf for a row whose components or
+ *             norm term leave fp16's range.  The largest value over the rows a search scans is what
+ *             lz_search_batched's deterministic margin takes as det_row_err. */
+int lz_rows_to_shadow(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
+                      void* shadow, float* row_err, void* stream);
 
 /* Bytes of device scratch lz_search_batched needs for a scan of n_rows = row_hi - row_lo rows. */
 size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int dim);
 
 /*
- * Exact top-k (LZ_COSINE or LZ_L2) for a batch of queries, computed as: bf16 tcgen05 GEMM (queries x rows, never
+ * Exact top-k (LZ_COSINE or LZ_L2) for a batch of queries, computed as: fp16 tcgen05 GEMM (queries x rows, never
  * materialised) with a fused per-query candidate selection -> float64 rescoring of the candidates from
  * the float32 rows -> top-k with the id tie-break -> certification (k-th exact score must exceed the
- * best dropped coarse score by the bf16 error margin) -> exact float64 scan of the queries that fail
- * it.  Results are those of lz_search_exact with the same metric whenever the margin holds; the margin is
- * statistical: margin_sigmas standard deviations of the bf16 rounding error (4 is the default used
- * by the Python layer).
- *   shadow_bf16   bf16 [n_rows_total, dim (+ 8 for LZ_L2)] from lz_rows_to_bf16 with the same metric.  Must be plain
+ * best dropped coarse score by the fp16 error margin) -> exact float64 scan of the queries that fail
+ * it.  Results are those of lz_search_exact with the same metric whenever the margin holds.  Two margins:
+ *   det_row_err < 0   STATISTICAL: margin_sigmas standard deviations of the fp16 rounding error of the coarse
+ *                     score, assuming the operands' rounding errors are independent (true of real-valued
+ *                     embeddings; NOT of quantised / fp16-derived / near-constant vectors, whose errors line
+ *                     up: such a row can be dropped and the query still reported certified).
+ *   det_row_err >= 0  DETERMINISTIC: |coarse - exact| <= det_row_err*|q^| + dq*|x^| + det_row_err*dq + the
+ *                     fp32 accumulation bound (Cauchy-Schwarz; dq is measured per query), valid for any data.
+ *                     det_row_err = max of lz_rows_to_shadow's row_err over [row_lo, row_hi).  Some 10x wider
+ *                     than the statistical margin on Gaussian-like rows (5e-4 against 4e-5 at dim 768).
+ *   shadow        fp16 [n_rows_total, dim (+ 8 for LZ_L2)] from lz_rows_to_shadow with the same metric.  Must be plain
  *                 device memory allocated on the CURRENT GPU (checked; LZ_ERR_ARG otherwise): the coarse pass loads
  *                 it by TMA multicast, and TMA multicast loads here read only this GPU's memory, since on B200 a
  *                 TMA multicast load from another GPU's memory hung the GPU.  A multi-GPU search keeps one shadow
@@ -131,10 +143,11 @@ size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries, int k, int
  *   row_lo,row_hi the row range every query scans
  *   out_certified optional int32 [n_queries]: 1 = answered by the tensor-core pass, 0 = by the fallback
  */
-int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, int dim, const double* norms,
+int lz_search_batched(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
                       const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo, int64_t row_hi,
                       const float* queries, int64_t q_ld, int n_queries, int k, double margin_sigmas,
-                      int metric, double max_row_norm, int64_t id_base, void* scratch, size_t scratch_bytes,
+                      int metric, double max_row_norm, double det_row_err, int64_t id_base,
+                      void* scratch, size_t scratch_bytes,
                       int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                       void* stream);
 

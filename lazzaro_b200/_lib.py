@@ -28,10 +28,10 @@ SIGNATURES = {
     "lz_search_exact_default_chunks": (_i32, [_i64, _i32]),
     "lz_search_exact": (_i32, [_p, _i64, _i32, _p, _p, _i64, _i64, _p, _p, _p, _p, _i64, _i32, _i32,
                                _i32, _i32, _i32, _i64, _p, _sz, _p, _p, _p, _p]),
-    "lz_rows_to_bf16": (_i32, [_p, _i64, _i32, _i64, _p, _i32, _p, _p]),
+    "lz_rows_to_shadow": (_i32, [_p, _i64, _i32, _i64, _p, _i32, _p, _p, _p]),
     "lz_search_batched_scratch_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "lz_search_batched": (_i32, [_p, _p, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _i32, _i32, _f64,
-                                 _i32, _f64, _i64, _p, _sz, _p, _p, _p, _p, _p]),
+                                 _i32, _f64, _f64, _i64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_merge_topk_strided": (_i32, [_p, _p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),

@@ -96,7 +96,7 @@ def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigm
     norms = kernels.row_norms(cen)
     n = rows.shape[0]
     if n >= 8 and dim % 8 == 0:
-        shadow = kernels.rows_to_bf16(cen, dim, norms)
+        shadow = kernels.rows_to_shadow(cen, dim, norms)
         ids, sc, cnt, _ = kernels.search_batched(shadow, cen, dim, norms, None, -1, rows, 1, margin_sigmas=margin_sigmas)
     else:
         ids, sc, cnt = kernels.search_exact(cen, dim, norms, None, rows, 1, _lib.COSINE)

@@ -1,6 +1,6 @@
 // K2: batched cosine search as a tensor-core contraction with a fused candidate epilogue.
 //
-//   coarse pass   scores[q, row] = bf16(q/|q|) . bf16(x/|x|), fp32 accumulate in TMEM: a persistent,
+//   coarse pass   scores[q, row] = fp16(q/|q|) . fp16(x/|x|), fp32 accumulate in TMEM: a persistent,
 //                 warp-specialised tcgen05 GEMM (TMA 128B-swizzled tiles -> shared memory ring ->
 //                 tcgen05.mma 128x256x16 -> double-buffered TMEM accumulators).  The B x N score matrix
 //                 is never written: four epilogue warps read each accumulator tile with tcgen05.ld
@@ -17,7 +17,7 @@
 //
 // Stands behind LanceDBStore.search_nodes (core/vector_store.py:132-140) for query batches, and behind
 // the dedup / linking scans of core/memory_system.py:719-742, 838-891 (same contraction, small k).
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include "lz_common.cuh"
@@ -30,7 +30,7 @@ using namespace sm100;
 
 constexpr int BM = 128;                 // queries per tile  (MMA M, one TMEM lane per query)
 constexpr int BN = 256;                 // rows per tile     (MMA N, one TMEM column per row)
-constexpr int BK = 64;                  // bf16 elements per pipeline stage = one 128-byte swizzle row
+constexpr int BK = 64;                  // fp16 elements per pipeline stage = one 128-byte swizzle row
 constexpr int A_BYTES = BM * BK * 2;    // 16 KiB per stage; the rows tile adds 32 KiB
 constexpr int kGemmThreads = 192;       // warp 0: TMA, warp 1: MMA + TMEM owner, warps 2-5: epilogue
 constexpr int kTmemCols = 512;          // two 128x256 fp32 accumulators
@@ -49,14 +49,25 @@ __device__ __forceinline__ float unord32(u32 k) {
     return __uint_as_float(b);
 }
 
-// ---- preparation: normalised bf16 copies ------------------------------------------------------------
-// LZ_COSINE: out[r] = bf16(x / |x|), dim columns.  LZ_L2: out[r] = [bf16(x), h, m, l, 0, 0, 0, 0], dim + 8 columns,
-// where h + m + l is a three-way bf16 split of -|x|^2 / 2 (24 significant bits): against the query
-// [bf16(q), 1, 1, 1, 0, ...] the contraction gives x.q - |x|^2/2 = -(|x - q|^2 - |q|^2) / 2, i.e. the L2
-// ranking comes out of the same GEMM, largest = nearest.
-__global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restrict__ rows, int64_t n, int dim, int64_t ld,
-                                                           const double* __restrict__ norms, int metric,
-                                                           __nv_bfloat16* __restrict__ out) {
+// ---- preparation: the 16-bit shadow --------------------------------------------------------------------
+// The coarse pass reads an fp16 copy of the rows ("shadow") and of the query batch.  fp16, not bf16: the tensor
+// cores run both at the same rate, the operands are normalised (cosine) or of embedding scale (L2) so fp16's
+// range is ample, and its 11 significant bits make the rounding error 8x smaller than bf16's 8 — small enough
+// that the DETERMINISTIC certification margin below (no independence assumption) certifies ordinary data.
+//
+// LZ_COSINE: out[r] = fp16(x / |x|), dim columns.  LZ_L2: out[r] = [fp16(x), h, m, l, 0, 0, 0, 0], dim + 8 columns,
+// where h + m + l is a three-way fp16 split of -|x|^2 / 2: against the query [fp16(q), 1, 1, 1, 0, ...] the
+// contraction gives x.q - |x|^2/2 = -(|x - q|^2 - |q|^2) / 2, i.e. the L2 ranking comes out of the same GEMM,
+// largest = nearest.
+//
+// row_err (optional) receives, per row, an upper bound of the 2-norm of the rounding error of its shadow:
+// |shadow - x/|x|| for LZ_COSINE (the normalisation's own fp32 rounding included), |fp16(x) - x| for LZ_L2 —
+// +inf when a component or the norm term leaves fp16's range (such a row certifies nothing: every query then
+// takes the exact fallback, slow but right).  The largest of them over the scanned rows is the row-side term of
+// the deterministic margin.
+__global__ void __launch_bounds__(256) rows_to_shadow_kernel(const float* __restrict__ rows, int64_t n, int dim, int64_t ld,
+                                                             const double* __restrict__ norms, int metric,
+                                                             __half* __restrict__ out, float* __restrict__ row_err) {
     const int lane = threadIdx.x & 31;
     const int64_t warp = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     const int64_t nwarps = (int64_t)gridDim.x * 8;
@@ -64,32 +75,48 @@ __global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* __restri
     for (int64_t r = warp; r < n; r += nwarps) {
         const double nr = norms[r];
         const float inv = metric == LZ_L2 ? 1.f : (nr > 0.0 ? (float)(1.0 / nr) : 0.f);
+        const double inv_d = metric == LZ_L2 ? 1.0 : (nr > 0.0 ? 1.0 / nr : 0.0);
         const float* x = rows + r * ld;
-        __nv_bfloat16* o = out + r * odim;
+        __half* o = out + r * odim;
+        double err2 = 0.0;
         for (int e = lane * 4; e < dim; e += 128) {
             const float4 v = lz_ldg_stream(x + e);
-            __nv_bfloat162 a = __floats2bfloat162_rn(v.x * inv, v.y * inv);
-            __nv_bfloat162 b = __floats2bfloat162_rn(v.z * inv, v.w * inv);
+            __half2 a = __floats2half2_rn(v.x * inv, v.y * inv);
+            __half2 b = __floats2half2_rn(v.z * inv, v.w * inv);
             uint2 pk;
             pk.x = *reinterpret_cast<u32*>(&a);
             pk.y = *reinterpret_cast<u32*>(&b);
             *reinterpret_cast<uint2*>(o + e) = pk;
+            if (row_err != nullptr) {
+                const double d0 = (double)__low2float(a) - (double)v.x * inv_d, d1 = (double)__high2float(a) - (double)v.y * inv_d;
+                const double d2 = (double)__low2float(b) - (double)v.z * inv_d, d3 = (double)__high2float(b) - (double)v.w * inv_d;
+                err2 = fma(d0, d0, err2); err2 = fma(d1, d1, err2); err2 = fma(d2, d2, err2); err2 = fma(d3, d3, err2);
+            }
         }
-        if (metric == LZ_L2 && lane < 8) {
+        bool split_ok = true;
+        if (metric == LZ_L2) {
             const double v = -0.5 * nr * nr;
-            const __nv_bfloat16 h = __double2bfloat16(v);
-            const __nv_bfloat16 m = __double2bfloat16(v - (double)__bfloat162float(h));
-            const __nv_bfloat16 l = __double2bfloat16(v - (double)__bfloat162float(h) - (double)__bfloat162float(m));
-            o[dim + lane] = lane == 0 ? h : lane == 1 ? m : lane == 2 ? l : __float2bfloat16_rn(0.f);
+            const __half h = __double2half(v);
+            const __half m = __double2half(v - (double)__half2float(h));
+            const __half l = __double2half(v - (double)__half2float(h) - (double)__half2float(m));
+            if (lane < 8) o[dim + lane] = lane == 0 ? h : lane == 1 ? m : lane == 2 ? l : __float2half_rn(0.f);
+            const double back = (double)__half2float(h) + (double)__half2float(m) + (double)__half2float(l);
+            split_ok = fabs(back - v) <= 1e-6 * fabs(v) + 1e-12;          // false for inf / NaN too
+        }
+        if (row_err != nullptr) {
+            err2 = lz_warp_sum(err2);                                       // inf / NaN if a component overflowed
+            const double e = sqrt(err2) * (1.0 + 1e-9);
+            if (lane == 0) row_err[r] = (split_ok && e == e) ? __double2float_ru(e) : INFINITY;
         }
     }
 }
 
-// one warp per query: normalised bf16 copy + the certification margin eps[q]
-__global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
-                                                              __nv_bfloat16* __restrict__ out, double* __restrict__ eps,
-                                                              int32_t* __restrict__ gtag, u32* __restrict__ gthr, int32_t* __restrict__ fb_count,
-                                                              int want_tag, double sigmas, int metric, double max_norm) {
+// one warp per query: fp16 copy (normalised for cosine) + the certification margin eps[q]
+__global__ void __launch_bounds__(256) queries_to_shadow_kernel(const float* __restrict__ q, int n, int dim, int64_t q_ld,
+                                                                __half* __restrict__ out, double* __restrict__ eps,
+                                                                int32_t* __restrict__ gtag, u32* __restrict__ gthr, int32_t* __restrict__ fb_count,
+                                                                int want_tag, double sigmas, int metric, double max_norm,
+                                                                double det_row_err) {
     const int lane = threadIdx.x & 31;
     const int w = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (blockIdx.x == 0 && threadIdx.x == 0) *fb_count = 0;
@@ -106,21 +133,56 @@ __global__ void __launch_bounds__(256) queries_to_bf16_kernel(const float* __res
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     const double nr = sqrt(ss);
+    // Two margins (u = 2^-11, fp16's unit roundoff).
+    // Statistical (det_row_err < 0): each operand carries an independent relative rounding error uniform in +-u,
+    // so the coarse dot errs with std <= u*sqrt(2/3)*max|q_i|*|x|; eps = sigmas * that + an accumulation term.  It
+    // holds for embeddings whose rounding errors are uncorrelated and FAILS for correlated ones (quantised or
+    // near-constant vectors whose components all round the same way).
+    // Deterministic (det_row_err >= 0, an upper bound of the rows' shadow error norms dx = |shadow - x^| from
+    // lz_rows_to_shadow): with dq = |fp16(q^) - q^| measured here, Cauchy-Schwarz gives
+    // |coarse - exact| <= dx |q^| + dq |x^| + dx dq for ANY data, plus the fp32 accumulation of dim products
+    // (dim * 2^-23 * |q^||x^|: a truncating add per product assumed).
+    constexpr double kU = 4.8828125e-4;                // 2^-11
+    constexpr double kAcc = 1.1920928955078125e-7;     // 2^-23
     if (metric == LZ_L2) {
-        __nv_bfloat16* o = out + (int64_t)w * (dim + 8);
-        for (int e = lane; e < dim; e += 32) o[e] = __float2bfloat16_rn(v[e]);
-        if (lane < 8) o[dim + lane] = __float2bfloat16_rn(lane < 3 ? 1.f : 0.f);
-        if (lane == 0)   // error of bf16(x).bf16(q) with |x| <= max_norm, plus the split's and the fp32 accumulator's residue
-            eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)mx * max_norm +
-                     2e-6 * (max_norm * nr + max_norm * max_norm) + 1e-30;
+        __half* o = out + (int64_t)w * (dim + 8);
+        double e2 = 0.0;
+        for (int e = lane; e < dim; e += 32) {
+            const __half b = __float2half_rn(v[e]);
+            o[e] = b;
+            const double d = (double)__half2float(b) - (double)v[e];
+            e2 = fma(d, d, e2);
+        }
+        if (lane < 8) o[dim + lane] = __float2half_rn(lane < 3 ? 1.f : 0.f);
+        const double dq = sqrt(lz_warp_sum(e2)) * (1.0 + 1e-9);
+        if (lane == 0) {  // resid: the norm split's residue (<= 1e-6 |x|^2 / 2, checked per row) and float32 inputs' own spacing
+            const double resid = 2e-6 * (max_norm * nr + max_norm * max_norm) + 1e-30;
+            double ev;
+            if (det_row_err >= 0.0)
+                ev = det_row_err * nr + dq * max_norm + det_row_err * dq +
+                     (double)(dim + 8) * kAcc * (max_norm * nr + max_norm * max_norm) + resid;
+            else
+                ev = sigmas * kU * 0.816496580927726 * (double)mx * max_norm + resid;
+            eps[w] = ev == ev ? ev : INFINITY;
+        }
     } else {
         const float inv = nr > 0.0 ? (float)(1.0 / nr) : 0.f;
-        for (int e = lane; e < dim; e += 32) out[(int64_t)w * dim + e] = __float2bfloat16_rn(v[e] * inv);
+        const double inv_d = nr > 0.0 ? 1.0 / nr : 0.0;
+        double e2 = 0.0;
+        for (int e = lane; e < dim; e += 32) {
+            const __half b = __float2half_rn(v[e] * inv);
+            out[(int64_t)w * dim + e] = b;
+            const double d = (double)__half2float(b) - (double)v[e] * inv_d;
+            e2 = fma(d, d, e2);
+        }
+        const double dq = sqrt(lz_warp_sum(e2)) * (1.0 + 1e-9);
         if (lane == 0) {
-            // bf16 rounding: each operand carries an independent relative error uniform in +-2^-9, so the
-            // coarse dot of unit vectors errs with std <= 2^-9*sqrt(2/3)*max|q_i| (sum x_i^2 q_i^2 <=
-            // max q_i^2); fp32 accumulation adds a few 1e-7.  eps = sigmas * that + 8e-6.
-            eps[w] = sigmas * 0.001953125 * 0.816496580927726 * (double)(mx * inv) + 8e-6;
+            double ev;
+            if (det_row_err >= 0.0)
+                ev = det_row_err + dq + det_row_err * dq + (double)dim * kAcc * 1.01 + 1e-9;
+            else
+                ev = sigmas * kU * 0.816496580927726 * (double)(mx * inv) + 8e-6;
+            eps[w] = ev == ev ? ev : INFINITY;
         }
     }
     if (lane == 0) {
@@ -350,7 +412,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     } else if (warp == 1) {
         // ===== MMA issuer (one thread) =====
         if (lane == 0) {
-            constexpr uint32_t idesc = idesc_bf16_f32(BM, BN);
+            constexpr uint32_t idesc = idesc_f16_f32(BM, BN);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (int item = cluster_id; item < n_items; item += n_clusters) {
                 const int sl = item / p.n_qgroups;
@@ -367,7 +429,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                         const uint64_t db = smem_desc_sw128(tiles + stage * STAGE_BYTES + A_BYTES);
 #pragma unroll
                         for (int k = 0; k < BK / 16; ++k) {     // 32 bytes along K per MMA: +2 in 16-byte units
-                            mma_bf16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                            mma_f16_ss(d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
                         }
                         if (cs > 1) mma_commit_mc(&empty[stage], mc_mask);   // release the stage in every CTA of the cluster
                         else mma_commit(&empty[stage]);          // frees the smem stage when these MMAs retire
@@ -1109,7 +1171,7 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// bf16 [n_rows, dim] row-major, box = 64 elements x box_rows rows, 128-byte swizzle, zero fill out of bounds
+// fp16 [n_rows, dim] row-major, box = 64 elements x box_rows rows, 128-byte swizzle, zero fill out of bounds
 int make_tmap(CUtensorMap* m, const void* base, int64_t n_rows, int dim, int box_rows) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) { lz_set_error("cuTensorMapEncodeTiled is not available from the driver"); return LZ_ERR_CUDA; }
@@ -1117,7 +1179,7 @@ int make_tmap(CUtensorMap* m, const void* base, int64_t n_rows, int dim, int box
     cuuint64_t gstride[1] = {(cuuint64_t)dim * 2};
     cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { lz_set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return LZ_ERR_CUDA; }
@@ -1220,7 +1282,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
 }
 
 struct ScratchLayout {
-    size_t q_bf16, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
+    size_t q16, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
 };
 
 ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
@@ -1228,7 +1290,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
     const size_t items = (size_t)pl.n_qgroups * pl.cs * (pl.n_slices > 64 ? pl.n_slices : 64);
-    L.q_bf16 = take((size_t)n_queries * (dim + 8) * 2);
+    L.q16 = take((size_t)n_queries * (dim + 8) * 2);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
     L.gthr = take((size_t)n_queries * 4);
@@ -1258,19 +1320,19 @@ extern "C" int lz_debug_stats(unsigned long long* host_out, int reset) {
 }
 #endif
 
-extern "C" int lz_rows_to_bf16(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
-                               void* out_bf16, void* stream) {
+extern "C" int lz_rows_to_shadow(const float* rows, int64_t n, int dim, int64_t ld, const double* norms, int metric,
+                                 void* out_shadow, float* row_err, void* stream) {
     if (n <= 0) return LZ_OK;
-    LZ_REQUIRE(rows && norms && out_bf16, "lz_rows_to_bf16: NULL pointer");
-    LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_rows_to_bf16: dim=%d must be a multiple of 8", dim);
-    LZ_REQUIRE((((uintptr_t)rows | (uintptr_t)out_bf16) & 15) == 0, "lz_rows_to_bf16: pointers must be 16-byte aligned");
+    LZ_REQUIRE(rows && norms && out_shadow, "lz_rows_to_shadow: NULL pointer");
+    LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_rows_to_shadow: dim=%d must be a multiple of 8", dim);
+    LZ_REQUIRE((((uintptr_t)rows | (uintptr_t)out_shadow) & 15) == 0, "lz_rows_to_shadow: pointers must be 16-byte aligned");
     const int sms = lz_sm_count();
     if (sms <= 0) return LZ_ERR_DEVICE;
     int64_t blocks = (n + 7) / 8;
     if (blocks > (int64_t)sms * 16) blocks = (int64_t)sms * 16;
-    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_rows_to_bf16: unknown metric %d", metric);
-    rows_to_bf16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms, metric,
-                                                                            (__nv_bfloat16*)out_bf16);
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_rows_to_shadow: unknown metric %d", metric);
+    rows_to_shadow_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(rows, n, dim, ld, norms, metric,
+                                                                              (__half*)out_shadow, row_err);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
@@ -1282,21 +1344,21 @@ extern "C" size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries,
     return layout(pl, n_queries, k, dim).total;
 }
 
-extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int64_t ld, int dim, const double* norms,
+extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
                                  const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
                                  int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
-                                 double margin_sigmas, int metric, double max_row_norm, int64_t id_base,
-                                 void* scratch, size_t scratch_bytes,
+                                 double margin_sigmas, int metric, double max_row_norm, double det_row_err,
+                                 int64_t id_base, void* scratch, size_t scratch_bytes,
                                  int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                                  void* stream) {
     if (n_queries <= 0) return LZ_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    LZ_REQUIRE(shadow_bf16 && rows && norms && queries && scratch && out_ids && out_scores && out_counts,
+    LZ_REQUIRE(shadow && rows && norms && queries && scratch && out_ids && out_scores && out_counts,
                "lz_search_batched: NULL pointer");
     LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0, "lz_search_batched: dim=%d must be a multiple of 8", dim);
     LZ_REQUIRE(q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
                "lz_search_batched: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
-    LZ_REQUIRE((((uintptr_t)shadow_bf16 | (uintptr_t)rows | (uintptr_t)scratch) & 15) == 0,
+    LZ_REQUIRE((((uintptr_t)shadow | (uintptr_t)rows | (uintptr_t)scratch) & 15) == 0,
                "lz_search_batched: pointers must be 16-byte aligned");
     LZ_REQUIRE(k >= 1 && k <= LZ_BATCHED_MAX_K, "lz_search_batched: k=%d outside 1..%d", k, LZ_BATCHED_MAX_K);
     LZ_REQUIRE(0 <= row_lo && row_lo <= row_hi && row_hi <= n_rows_total && n_rows_total <= 0x7fffff00LL,
@@ -1305,7 +1367,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     LZ_REQUIRE(margin_sigmas > 0.0, "lz_search_batched: margin_sigmas must be positive");
     LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_batched: unknown metric %d", metric);
     LZ_REQUIRE(metric == LZ_COSINE || max_row_norm >= 0.0, "lz_search_batched: LZ_L2 needs max_row_norm >= 0");
-    if (int rc = require_local_device_memory(shadow_bf16, "lz_search_batched: shadow_bf16")) return rc;
+    if (int rc = require_local_device_memory(shadow, "lz_search_batched: shadow")) return rc;
     const int dim_s = metric == LZ_L2 ? dim + 8 : dim;         // columns of the shadow (and K of the contraction)
     Plan pl;
     if (int rc = make_plan(row_hi - row_lo, n_queries, k, &pl)) return rc;
@@ -1315,7 +1377,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
         return LZ_ERR_SCRATCH;
     }
     unsigned char* s = (unsigned char*)scratch;
-    __nv_bfloat16* q16 = (__nv_bfloat16*)(s + L.q_bf16);
+    __half* q16 = (__half*)(s + L.q16);
     double* eps = (double*)(s + L.eps);
     int32_t* cert = out_certified ? out_certified : (int32_t*)(s + L.certified);
 
@@ -1323,8 +1385,9 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     u32* gthr = (u32*)(s + L.gthr);
     int32_t* fb_list = (int32_t*)(s + L.fb_list);
     int32_t* fb_count = (int32_t*)(s + L.fb_count);
-    queries_to_bf16_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
-                                                                fb_count, want_tag, margin_sigmas, metric, max_row_norm);
+    queries_to_shadow_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
+                                                                fb_count, want_tag, margin_sigmas, metric, max_row_norm,
+                                                                det_row_err);
     LZ_CUDA(cudaGetLastError());
 
     // top-1 against a tiny table (shard reassignment): trailing threshold in the coarse pass, bucketed exact pass
@@ -1337,7 +1400,7 @@ extern "C" int lz_search_batched(const void* shadow_bf16, const float* rows, int
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
-        if (int rc = make_tmap(&tx, shadow_bf16, n_rows_total, dim_s, BN / pl.cs)) return rc;
+        if (int rc = make_tmap(&tx, shadow, n_rows_total, dim_s, BN / pl.cs)) return rc;
         GemmParams g;
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim_s + BK - 1) / BK;

@@ -83,8 +83,9 @@ __device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
 }
 
-// D[tmem] (+)= A[smem] * B[smem]^T, bf16 inputs, fp32 accumulate; one thread issues.
-__device__ __forceinline__ void mma_bf16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+// D[tmem] (+)= A[smem] * B[smem]^T, 16-bit float inputs (format from the instruction descriptor), fp32 accumulate;
+// one thread issues.
+__device__ __forceinline__ void mma_f16_ss(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
@@ -119,7 +120,7 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ---------------------------------------------------------------------------------
-// Shared-memory matrix descriptor for a K-major bf16 tile whose rows are 128 bytes (64 elements),
+// Shared-memory matrix descriptor for a K-major 16-bit tile whose rows are 128 bytes (64 elements),
 // stored densely row after row with the 128-byte swizzle (what TMA SWIZZLE_128B writes):
 //   bits [0,14)  start address >> 4         bits [16,30) leading byte offset >> 4 (unused for swizzled K-major: 1)
 //   bits [32,46) stride byte offset >> 4 = 1024 B between 8-row groups
@@ -132,10 +133,10 @@ __device__ __forceinline__ uint64_t smem_desc_sw128(const void* tile) {
     d |= (uint64_t)2 << 61;
     return d;
 }
-// Instruction descriptor, kind::f16: D fp32 (bits[4,6)=1), A,B bf16 (bits[7,10)=1, [10,13)=1), both K-major,
-// N>>3 at bits [17,23), M>>4 at bits [24,29).
-__host__ __device__ constexpr uint32_t idesc_bf16_f32(int m, int n) {
-    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+// Instruction descriptor, kind::f16: D fp32 (bits[4,6)=1), A and B formats at bits [7,10) and [10,13) (0 = fp16,
+// 1 = bf16), both K-major, N>>3 at bits [17,23), M>>4 at bits [24,29).
+__host__ __device__ constexpr uint32_t idesc_f16_f32(int m, int n) {
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 }  // namespace sm100

@@ -158,18 +158,20 @@ def shadow_dim(dim: int, metric: int = _lib.COSINE) -> int:
     return dim + 8 if metric == _lib.L2 else dim
 
 
-def rows_to_bf16(rows: torch.Tensor, dim: int, norms: torch.Tensor, out: Optional[torch.Tensor] = None,
-                 metric: int = _lib.COSINE) -> torch.Tensor:
-    """bf16 shadow of float32 rows (lz_rows_to_bf16): normalised rows for cosine; raw rows plus a three-way
-    split of -|row|^2/2 (8 extra columns) for L2."""
+def rows_to_shadow(rows: torch.Tensor, dim: int, norms: torch.Tensor, out: Optional[torch.Tensor] = None,
+                 metric: int = _lib.COSINE, row_err: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bf16 shadow of float32 rows (lz_rows_to_shadow): normalised rows for cosine; raw rows plus a three-way
+    split of -|row|^2/2 (8 extra columns) for L2.  `row_err` (float32 [n], optional) receives each row's
+    rounding-error norm — its maximum is the `det_row_err` of the deterministic certification margin."""
     dev = _dev(rows)
     n, sd = rows.shape[0], shadow_dim(dim, metric)
     if out is None:
-        out = torch.empty((n, sd), dtype=torch.bfloat16, device=dev)
-    assert out.dtype == torch.bfloat16 and out.is_contiguous() and out.shape[1] == sd
+        out = torch.empty((n, sd), dtype=torch.float16, device=dev)
+    assert out.dtype == torch.float16 and out.is_contiguous() and out.shape[1] == sd
+    assert row_err is None or (row_err.dtype == torch.float32 and row_err.is_contiguous() and row_err.numel() >= n)
     with torch.cuda.device(dev):
-        check(_lib.load().lz_rows_to_bf16(ptr(rows), n, dim, rows.stride(0), ptr(norms), int(metric), ptr(out),
-                                          stream_ptr(dev)), "lz_rows_to_bf16")
+        check(_lib.load().lz_rows_to_shadow(ptr(rows), n, dim, rows.stride(0), ptr(norms), int(metric), ptr(out),
+                                          ptr(row_err), stream_ptr(dev)), "lz_rows_to_shadow")
     return out
 
 
@@ -177,11 +179,14 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
                    tags: Optional[torch.Tensor], want_tag: int, queries: torch.Tensor, k: int,
                    row_range: Optional[Tuple[int, int]] = None, margin_sigmas: float = 4.0, id_base: int = 0,
                    scratch: Optional[torch.Tensor] = None, n_rows_total: Optional[int] = None,
-                   metric: int = _lib.COSINE, max_row_norm: Optional[float] = None, out=None):
+                   metric: int = _lib.COSINE, max_row_norm: Optional[float] = None, out=None,
+                   det_row_err: Optional[float] = None):
     """Batched exact cosine top-k on the tensor cores (lz_search_batched).
-    Returns (ids int64 [B,k], scores float64 [B,k], counts int32 [B], certified int32 [B])."""
+    Returns (ids int64 [B,k], scores float64 [B,k], counts int32 [B], certified int32 [B]).
+    det_row_err = None: statistical margin (margin_sigmas); a float >= 0: the deterministic (worst-case)
+    margin with that bound of the rows' rounding-error norms (max of rows_to_shadow's row_err)."""
     dev = _dev(rows)
-    assert shadow.dtype == torch.bfloat16 and shadow.is_contiguous() and shadow.shape[1] == shadow_dim(dim, metric)
+    assert shadow.dtype == torch.float16 and shadow.is_contiguous() and shadow.shape[1] == shadow_dim(dim, metric)
     if metric == _lib.L2 and max_row_norm is None:
         max_row_norm = float(norms[:n_rows_total if n_rows_total is not None else norms.shape[0]].max().item())
     assert queries.dtype == torch.float32 and queries.stride(1) == 1 and rows.stride(1) == 1
@@ -200,7 +205,8 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
         cert = torch.empty((B,), dtype=torch.int32, device=dev)
         check(lib.lz_search_batched(ptr(shadow), ptr(rows), rows.stride(0), dim, ptr(norms), ptr(tags), int(want_tag),
                                     int(n_total), int(lo), int(hi), ptr(queries), queries.stride(0), B, k,
-                                    float(margin_sigmas), int(metric), float(max_row_norm or 0.0), int(id_base),
+                                    float(margin_sigmas), int(metric), float(max_row_norm or 0.0),
+                                    -1.0 if det_row_err is None else float(det_row_err), int(id_base),
                                     ptr(scratch), scratch.numel(),
                                     ptr(ids), ptr(scores), ptr(counts), ptr(cert), stream_ptr(dev)), "lz_search_batched")
     return ids, scores, counts, cert

@@ -68,12 +68,20 @@ class B200Store:
         self._gtags: Dict[tuple, torch.Tensor] = {}
         self.use_graphs = True                 # CUDA-graph replay of the (launch-bound) exact path for host calls
         self._scratch: Optional[torch.Tensor] = None
+        self._gen = 0                          # bumped whenever rows / norms / tags are reallocated or repacked
         if batched_search not in ("auto", "never", "always"):
             raise ValueError("batched_search must be 'auto', 'never' or 'always'")
         self.batched_search = batched_search
         self.min_batch = 8                    # 'auto': query batches this large go to the tensor-core path
         self.min_rows_small_batch = 500_000   # ... and batches of 2-7 too when the scan is this long (measured: 3.5 vs 5-7 ms at 10M rows)
         self.margin_sigmas = 4.0
+        # certification margin of the tensor-core path: "worst_case" = deterministic bound from the measured bf16
+        # rounding-error norms of rows and query (valid for any data; the default, because north_star asks for
+        # bit-exact ids); "statistical" = margin_sigmas standard deviations under independent rounding errors
+        # (narrower, fewer fallbacks, but not a proof — see DESIGN.md §4)
+        self.margin = "worst_case"
+        self._row_err: Optional[torch.Tensor] = None  # float32 [capacity] rounding-error norm of each shadow row
+        self._max_err = 0.0
         self._shadow: Optional[torch.Tensor] = None   # bf16 [capacity, dim_p] normalised copy of the rows
         self._shadow_n = 0                            # rows of the shadow that are up to date
         self._max_norm = 0.0                          # largest row norm seen by the shadow (L2 margin)
@@ -104,23 +112,32 @@ class B200Store:
             norms[:self._n] = self._norms[:self._n]
             tags[:self._n] = self._tags[:self._n]
         self._rows, self._norms, self._tags = rows, norms, tags
+        self._gen += 1
+        self._graphs.clear()                   # captured graphs hold the old columns' addresses
         if self._shadow is not None:
-            shadow = torch.empty((cap, self._shadow.shape[1]), dtype=torch.bfloat16, device=self.device)
+            shadow = torch.empty((cap, self._shadow.shape[1]), dtype=torch.float16, device=self.device)
             shadow[:self._shadow_n] = self._shadow[:self._shadow_n]
             self._shadow = shadow
+            self._row_err = torch.empty(cap, dtype=torch.float32, device=self.device)
 
     def _ensure_shadow(self):
         """Brings the normalised bf16 copy of the rows (read by the tensor-core pass) up to date."""
         if self._shadow is None:
             self._shadow = torch.empty((self._rows.shape[0], kernels.shadow_dim(self._dim_p, self._metric)),
-                                       dtype=torch.bfloat16, device=self.device)
+                                       dtype=torch.float16, device=self.device)
+            self._row_err = torch.empty(self._rows.shape[0], dtype=torch.float32, device=self.device)
             self._shadow_n = 0
             self._max_norm = 0.0
+            self._max_err = 0.0
         if self._shadow_n < self._n:
             a, b = self._shadow_n, self._n
-            kernels.rows_to_bf16(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b], metric=self._metric)
+            kernels.rows_to_shadow(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b], metric=self._metric,
+                                 row_err=self._row_err[a:b])
             if self._metric == _lib.L2:                 # the L2 error margin scales with the largest row norm
                 self._max_norm = max(self._max_norm, float(self._norms[a:b].max().item()))
+            # row side of the deterministic margin: the largest rounding-error norm of any shadow row (deleted rows
+            # included — an upper bound is all that is needed)
+            self._max_err = max(self._max_err, float(self._row_err[a:b].max().item()))
             self._shadow_n = b
 
     def _reserve(self, extra: int):
@@ -252,6 +269,8 @@ class B200Store:
             self.device = rows.device
             n = rows.shape[0]
             self._rows = rows
+            self._gen += 1
+            self._graphs.clear()
             self._norms = torch.empty(n, dtype=torch.float64, device=self.device)
             self._tags = torch.empty(n, dtype=torch.int32, device=self.device)
             self._row_user = np.full(n, -1, np.int32)
@@ -386,21 +405,27 @@ class B200Store:
             if self.use_graphs and not self._takes_batched_path(B, k, hi - lo):
                 # the exact path is launch-bound on small stores (the reference's own scale): replay the
                 # H2D copy, scan, merge and D2H copy as one CUDA graph, re-captured when the layout changes
-                key = (B, k, u, lo, hi, self._rows.data_ptr(), len(self._user_names) == 1 and self._live[u] == self._n)
-                graph = self._graphs.get(key)
-                if graph is None:
+                key = (B, k, u, lo, hi, self._gen, len(self._user_names) == 1 and self._live[u] == self._n)
+                entry = self._graphs.get(key)
+                if entry is None:
                     if len(self._graphs) > 64:
                         self._graphs.clear()
+                    # A captured graph replays raw addresses.  Everything it touches besides the store's columns (whose
+                    # reallocation bumps _gen) is owned by the graph's own entry and lives exactly as long as the graph:
+                    # its scratch (never the shared, growable self._scratch), its group tags and its I/O buffers.
+                    io = (q_pin, q_dev, o_dev, o_pin, dev_views, host_views)
+                    own = {"scratch": torch.empty(self._exact_scratch_bytes(B, k, hi - lo), dtype=torch.uint8, device=self.device),
+                           "gtag": None}
                     torch.cuda.current_stream().synchronize()
-                    self.search_device(q_dev, u, k, out=dev_views)          # warm-up outside capture (sizes scratch)
+                    self.search_device(q_dev, u, k, out=dev_views, _own=own)          # warm-up outside capture
                     torch.cuda.current_stream().synchronize()
                     graph = torch.cuda.CUDAGraph()
                     with torch.cuda.graph(graph):
                         q_dev.copy_(q_pin, non_blocking=True)
-                        self.search_device(q_dev, u, k, out=dev_views)
+                        self.search_device(q_dev, u, k, out=dev_views, _own=own)
                         o_pin.copy_(o_dev, non_blocking=True)
-                    self._graphs[key] = graph
-                graph.replay()
+                    entry = self._graphs[key] = (graph, own, io)
+                entry[0].replay()
             else:
                 q_dev.copy_(q_pin, non_blocking=True)
                 self.search_device(q_dev, u, k, out=dev_views)
@@ -408,15 +433,32 @@ class B200Store:
             torch.cuda.current_stream().synchronize()
         return host_views
 
+    def _det_row_err(self) -> Optional[float]:
+        if self.margin == "worst_case":
+            return self._max_err
+        if self.margin != "statistical":
+            raise ValueError(f"margin must be 'worst_case' or 'statistical', got {self.margin!r}")
+        return None
+
     def _takes_batched_path(self, B: int, k: int, span: int) -> bool:
         return (k <= _lib.BATCHED_MAX_K and
                 (self.batched_search == "always" or
                  (self.batched_search == "auto" and (B >= self.min_batch or (B >= 2 and span >= self.min_rows_small_batch)))))
 
+    def _exact_groups(self, B: int):
+        gs = 4 if B >= 4 else (2 if B >= 2 else 1)
+        return gs, (B + gs - 1) // gs
+
+    def _exact_scratch_bytes(self, B: int, k: int, span: int) -> int:
+        _, n_groups = self._exact_groups(B)
+        n_chunks = kernels.default_chunks(span, n_groups, self.device)
+        return max(16, int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks)))
+
     def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0,
-                      row_range=None, out=None):
+                      row_range=None, out=None, _own=None):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
-        tensors, nothing synchronised.  The exact fp64 scan over the user's row span."""
+        tensors, nothing synchronised.  The exact fp64 scan over the user's row span.
+        `_own` (internal): scratch / group tags owned by a captured CUDA graph instead of the store's shared ones."""
         u = self._user(user) if isinstance(user, str) else user
         lo, hi = self._span[u]
         if row_range is not None:                      # e.g. one semantic shard's contiguous rows
@@ -435,23 +477,35 @@ class B200Store:
                                                         -1 if tags is None else u, queries, k, row_range=(lo, hi),
                                                         margin_sigmas=self.margin_sigmas, id_base=id_base,
                                                         scratch=self._bscratch, n_rows_total=self._n,
-                                                        metric=self._metric, max_row_norm=self._max_norm, out=out)
+                                                        metric=self._metric, max_row_norm=self._max_norm, out=out,
+                                                        det_row_err=self._det_row_err())
             self.last_certified = cert
             return ids, sc, cnt
-        gs = 4 if B >= 4 else (2 if B >= 2 else 1)
-        n_groups = (B + gs - 1) // gs
+        gs, n_groups = self._exact_groups(B)
         gtag = None
         if tags is not None:
-            gtag = self._gtags.get((n_groups, u))
-            if gtag is None:
-                gtag = self._gtags[(n_groups, u)] = torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
+            if _own is not None:
+                if _own["gtag"] is None:
+                    _own["gtag"] = torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
+                gtag = _own["gtag"]
+            else:
+                gtag = self._gtags.get((n_groups, u))
+                if gtag is None:
+                    if len(self._gtags) > 256:
+                        self._gtags.clear()
+                    gtag = self._gtags[(n_groups, u)] = torch.full((n_groups,), u, dtype=torch.int32, device=self.device)
         n_chunks = kernels.default_chunks(hi - lo, n_groups, self.device)
         need = int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks))
-        if self._scratch is None or self._scratch.numel() < need:
-            self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+        if _own is not None:
+            scratch = _own["scratch"]
+            assert scratch.numel() >= need
+        else:
+            if self._scratch is None or self._scratch.numel() < need:
+                self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            scratch = self._scratch
         return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, self._metric,
                                     row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
-                                    scratch=self._scratch, id_base=id_base, out=out)
+                                    scratch=scratch, id_base=id_base, out=out)
 
     # ------------------------------------------------------------------ multi-tenant and two-level search
     def search_users(self, queries, user_ids: Sequence[str], limit: int = 5):
@@ -579,6 +633,7 @@ class B200Store:
             t[:m] = t.index_select(0, idx)
         if self._shadow is not None:
             self._shadow_n = 0                         # rebuilt lazily by the next batched search
+            self._max_err = self._max_norm = 0.0
         remap = {int(old): new for new, old in enumerate(live.tolist())}
         self._row_id = {remap[r]: v for r, v in self._row_id.items() if r in remap}
         self._row_meta = {remap[r]: v for r, v in self._row_meta.items() if r in remap}
@@ -593,6 +648,8 @@ class B200Store:
                     self._row_id[remap[r]] = f"{prefix}{first + r - lo}"
                     self._id_rows.setdefault((int(self._row_user[r]), f"{prefix}{first + r - lo}"), []).append(remap[r])
         self._blocks = blocks
+        self._gen += 1
+        self._graphs.clear()
         self._row_user[:m] = self._row_user[live]
         self._row_user[m:self._n] = -1
         self._tags[m:self._n] = -1

@@ -15,7 +15,7 @@ dim = 768
 rows, _ = synth.clustered_rows_device(n, dim, max(1, n // 9766), "cuda")
 qs = synth.queries_near_rows_device(rows, B)
 norms = K.row_norms(rows)
-shadow = K.rows_to_bf16(rows, dim, norms, metric=metric)
+shadow = K.rows_to_shadow(rows, dim, norms, metric=metric)
 mx = float(norms.max())
 out = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k, metric=metric, max_row_norm=mx)
 torch.cuda.synchronize()

@@ -9,7 +9,7 @@ lib = _lib.load()
 n, B, k = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3])
 rows, _ = synth.clustered_rows_device(n, 768, max(1, n // 9766), "cuda")
 qs = synth.queries_near_rows_device(rows, B)
-norms = K.row_norms(rows); shadow = K.rows_to_bf16(rows, 768, norms)
+norms = K.row_norms(rows); shadow = K.rows_to_shadow(rows, 768, norms)
 K.search_batched(shadow, rows, 768, norms, None, -1, qs, k)
 buf = (C.c_ulonglong * 8)()
 lib.lz_debug_stats.argtypes = [C.c_void_p, C.c_int]

@@ -15,7 +15,7 @@ for metric in (_lib.COSINE, _lib.L2):
         K.search_exact(rows, 200, norms, None, qs[:B].contiguous(), k, metric)
 tags = torch.as_tensor((np.arange(6000) % 3).astype(np.int32)).cuda()
 K.search_exact(rows, 200, norms, tags, qs[:5].contiguous(), 9, _lib.COSINE, group_tag=torch.full((5,), 1, dtype=torch.int32, device="cuda"), group_size=1)
-shadow = K.rows_to_bf16(rows, 200, norms)
+shadow = K.rows_to_shadow(rows, 200, norms)
 for B, k in ((20, 10), (9, 1), (20, 100), (3, 3)):
     K.search_batched(shadow, rows, 200, norms, None, -1, qs[:B].contiguous(), k)
 K.search_batched(shadow, rows, 200, norms, tags, 2, qs, 10, row_range=(100, 5003))

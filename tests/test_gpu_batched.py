@@ -13,7 +13,7 @@ def setup(rows_np):
     from lazzaro_b200 import kernels as K
     rows = torch.as_tensor(np.ascontiguousarray(rows_np, np.float32)).cuda()
     norms = K.row_norms(rows)
-    shadow = K.rows_to_bf16(rows, rows.shape[1], norms)
+    shadow = K.rows_to_shadow(rows, rows.shape[1], norms)
     return K, rows, norms, shadow
 
 
@@ -23,7 +23,7 @@ def test_shadow_is_normalised_bf16():
     rows_np *= np.linspace(0.5, 3.0, 1000, dtype=np.float32)[:, None]
     rows_np[7] = 0
     K, rows, norms, shadow = setup(rows_np)
-    want = torch.as_tensor(rows_np / np.maximum(np.linalg.norm(rows_np, axis=1, keepdims=True), 1e-30)).to(torch.bfloat16)
+    want = torch.as_tensor(rows_np / np.maximum(np.linalg.norm(rows_np, axis=1, keepdims=True), 1e-30)).to(torch.float16)
     got = shadow.cpu()
     assert (got[7] == 0).all()
     assert torch.allclose(got.float(), want.float(), atol=2 ** -8, rtol=2 ** -7)
@@ -79,7 +79,7 @@ def test_batched_cfg2_size_against_exact_scan():
     rows, _ = synth.clustered_rows_device(n, dim, 64, "cuda")
     qs = synth.queries_near_rows_device(rows, B)
     norms = K.row_norms(rows)
-    shadow = K.rows_to_bf16(rows, dim, norms)
+    shadow = K.rows_to_shadow(rows, dim, norms)
     ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
     eids, esc, ecnt = K.search_exact(rows, dim, norms, None, qs, k, _lib.COSINE)
     torch.cuda.synchronize()
@@ -97,7 +97,7 @@ def test_batched_l2_matches_exact_scan_and_oracle(n, dim, B, k):
     qs_np = synth.queries_near_rows(rows_np, B, seed=B + 1) * np.float32(1.3)
     rows, qs = torch.as_tensor(rows_np).cuda(), torch.as_tensor(qs_np).cuda()
     norms = K.row_norms(rows)
-    shadow = K.rows_to_bf16(rows, dim, norms, metric=_lib.L2)
+    shadow = K.rows_to_shadow(rows, dim, norms, metric=_lib.L2)
     assert shadow.shape[1] == dim + 8
     ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k, metric=_lib.L2)
     eids, esc, ecnt = K.search_exact(rows, dim, norms, None, qs, k, _lib.L2)
@@ -135,7 +135,7 @@ def test_cfg4_size_10m_rows_properties():
     pick = torch.tensor([0, 123_456, 5_000_000, n - 1], device="cuda")
     qs[:4] = rows[pick]
     norms = K.row_norms(rows)
-    shadow = K.rows_to_bf16(rows, dim, norms)
+    shadow = K.rows_to_shadow(rows, dim, norms)
     for k in (100, 10):
         ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, None, -1, qs, k)
         torch.cuda.synchronize()

@@ -51,7 +51,7 @@ def test_random_configurations(seed):
         assert cnt.cpu().numpy().tolist() == ok.sum(1).tolist()
     if kk <= 128:
         for metric in ("cosine", "l2"):
-            shadow = K.rows_to_bf16(rows, dim, norms, metric=_lib.METRICS[metric])
+            shadow = K.rows_to_shadow(rows, dim, norms, metric=_lib.METRICS[metric])
             want_ids, want_sc = flat_search.flat_topk_batch(rows_np, qs_np, kk, metric, mask)
             ids, sc, cnt, cert = K.search_batched(shadow, rows, dim, norms, tags, want_tag, qs, kk, row_range=(lo, hi),
                                                   metric=_lib.METRICS[metric])

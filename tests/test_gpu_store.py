@@ -200,3 +200,35 @@ def test_pipelined_host_search_equals_blocking():
         np.testing.assert_array_equal(ids, b_ids); np.testing.assert_array_equal(sc, b_sc); np.testing.assert_array_equal(cnt, b_cnt)
         want, _ = flat_search.flat_topk_batch(rows, q, 10)
         np.testing.assert_array_equal(ids, want)
+
+
+def test_graph_replay_survives_interleaved_shapes():
+    """Cached CUDA graphs replay raw addresses: each graph owns its scratch, so a later search that needs a larger
+    scratch (other batch size / limit) or any allocation in between must not disturb an earlier graph's replay."""
+    import torch
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    rows, _ = synth.clustered_rows(6000, 64, 6, seed=31)
+    qs = synth.queries_near_rows(rows, 8, seed=32)
+    st, ref = B200Store(capacity=8192), FlatStore()
+    for s in (st, ref):
+        s.add_nodes([{"id": f"n{i}", "content": "c", "embedding": rows[i].tolist()} for i in range(3000)], user_id="a")
+        s.add_nodes([{"id": f"m{i}", "content": "c", "embedding": rows[3000 + i].tolist()} for i in range(3000)], user_id="b")
+    st.batched_search = "never"                     # every shape below takes the graph-replayed exact path
+    want5 = [ref.search_nodes(q.tolist(), "a", 5) for q in qs]
+    assert st.search_nodes(qs[0].tolist(), "a", 5) == want5[0]                    # captures graph (B=1, k=5)
+    hog = []
+    for round_ in range(3):
+        assert st.search_batch(qs[:4], "b", 100) == [ref.search_nodes(q.tolist(), "b", 100) for q in qs[:4]]   # larger scratch
+        assert st.search_nodes(qs[1].tolist(), "b", 50) == ref.search_nodes(qs[1].tolist(), "b", 50)
+        # allocations that would land in a freed scratch block if a graph's scratch had been released
+        hog.append(torch.full((1 << 18,), 7.0, device=st.device))
+        guard = torch.full((1 << 16,), 3.0, device=st.device)
+        for i, q in enumerate(qs):
+            assert st.search_nodes(q.tolist(), "a", 5) == want5[i]                # replays the first graph
+        assert float(guard.min()) == 3.0 and float(guard.max()) == 3.0
+        assert all(float(h.min()) == 7.0 and float(h.max()) == 7.0 for h in hog)
+    n_graphs = len(st._graphs)
+    st.add_nodes([{"id": f"x{i}", "content": "c", "embedding": rows[i].tolist()} for i in range(4000)], user_id="c")   # grows the columns
+    assert len(st._graphs) < n_graphs or st._rows.shape[0] == 8192
+    assert st.search_nodes(qs[0].tolist(), "a", 5) == want5[0]
