@@ -160,8 +160,8 @@ def run_reference(args):
 
 
 def workload(args):
-    return {"workload": f"{args.rows} x {args.dim} fp32 memories in {args.shards} semantic shards, batch-{args.batch} "
-                        f"top-{args.k} exhaustive cosine search (BASELINE configs[3] at k={args.k})",
+    return {"workload": f"top-{args.k} batch-{args.batch} exhaustive cosine search over {args.rows} x {args.dim} fp32 memories in "
+                        f"{args.shards} semantic shards (BASELINE metric; configs[3] at k={args.k})",
             "rows": args.rows, "dim": args.dim, "batch": args.batch, "k": args.k,
             "l2_policy": "inputs (rows) are far larger than the 126 MB L2; no flush needed",
             "partitioning": f"rows split evenly over {args.gpus} GPU(s) by semantic shard; per-GPU top-k merged after an all-gather"}
@@ -198,10 +198,29 @@ def main():
     store = B200Store(device=str(dev))
     store.adopt_rows(rows, id_prefix="node_")
     sharded = ShardedSearch(store, row_offset=lo, world=world)
-    # the same queries on every rank (near rows of rank 0's slab; broadcast when distributed)
-    queries = synth.queries_near_rows_device(rows, args.batch, seed=synth.SEED_QUERY)
+    # ---- multi-GPU parity record: before anything is timed, the sharded search must equal a single-GPU exact
+    # search bit for bit on the same rows (lazzaro_b200.dist.parity_check); a mismatch ends the run with rc != 0
+    dist_parity = None
     if world > 1:
-        dist.broadcast(queries, src=0)
+        from lazzaro_b200.dist import parity_check
+        cases = parity_check()
+        dist_parity = {"status": "ok" if all(c["ok"] for c in cases) else "MISMATCH", "cases": cases,
+                       "check": "sharded search (local search + one packed all-gather + strided merge) vs lz_search_exact over "
+                                "all rows on one GPU: ids, float64 scores, counts bitwise; device and host API"}
+        if dist_parity["status"] != "ok":
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "dist_parity": dist_parity, "error": "multi-GPU result differs from single-GPU"}), flush=True)
+            dist.destroy_process_group()
+            sys.exit(3)
+    # the same query batch on every rank; query i is drawn near a row of rank i % world, so the true neighbours of
+    # a batch are spread over all GPUs (each rank draws near its own rows, the draws are all-gathered)
+    queries = synth.queries_near_rows_device(rows, args.batch, seed=synth.SEED_QUERY + rank)
+    if world > 1:
+        allq = torch.empty((world,) + tuple(queries.shape), dtype=queries.dtype, device=dev)
+        dist.all_gather_into_tensor(allq, queries.contiguous())
+        pick = torch.arange(args.batch, device=dev) % world
+        queries = allq[pick, torch.arange(args.batch, device=dev)].contiguous()
+        del allq
     q_host = queries.cpu().numpy()
     torch.cuda.synchronize()
 
@@ -298,7 +317,7 @@ def main():
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16 coarse + f64 exact" if batched else "f64", "data": "synthetic", "config": workload(args),
+        "dtype": "fp16 coarse (tcgen05, fp32 accumulate) + f64 exact" if batched else "f64", "data": "synthetic", "config": workload(args),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int(args.batch * store._dim_p * 4),
                 "d2h_bytes_per_step": int(args.batch * args.k * 16 + args.batch * 4),
                 "api": "B200Store.search_nodes (List[float] -> List[str])" if args.batch == 1 and world == 1
@@ -309,6 +328,22 @@ def main():
         "roofline": roof,
         "clocks": clocks.summary(),
     }
+    if dist_parity is not None:
+        line["dist_parity"] = dist_parity
+    if batched:
+        # the same search under the other certification margin (the store default is the deterministic one)
+        margins = {store.margin: {"ms_per_step": ms_kernel / args.steps,
+                                  "certified_fraction": float(store.last_certified.float().mean().item())}}
+        other = "statistical" if store.margin == "worst_case" else "worst_case"
+        keep = store.margin
+        store.margin = other
+        for _ in range(3):
+            store.search_device(queries, 0, args.k)
+        ms_o, _ = timed(lambda: store.search_device(queries, 0, args.k), args.steps)
+        margins[other] = {"ms_per_step": ms_o / args.steps, "certified_fraction": float(store.last_certified.float().mean().item())}
+        store.margin = keep
+        line["roofline"]["margins"] = margins
+        line["roofline"]["margin"] = keep
     if not args.no_batch1 and args.batch != 1:
         q1 = queries[:1].contiguous()
         q1_host = q_host[:1]

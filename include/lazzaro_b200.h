@@ -244,6 +244,28 @@ int lz_salience_decay(float* salience, int64_t n, double rate, double floor, voi
 int lz_connected_components(const int32_t* src, const int32_t* dst, int64_t n_edges, int32_t n_nodes,
                             int32_t* labels, void* stream);
 
+/* Components exactly as the reference's traversal forms them (core/buffer_graph.py:99-120): nodes are visited in
+ * index order, and an edge is followed from an endpoint only if that endpoint may walk it — the reference looks a
+ * node's neighbours up among the edges of the shard the node lives in (buffer_graph.py:72-77), so an edge whose
+ * other endpoint lives in another shard (or is not resident) is one-way, and where such a target lands depends on
+ * the visiting order.  Result: labels[v] = the smallest index among the nodes that can reach v (= the root the
+ * reference's DFS assigns when indices are its dict order); components in ascending label order are the
+ * reference's list.  walk uint8 [n_edges]: bit 0 = walkable src->dst, bit 1 = walkable dst->src, 0 = ignored
+ * (NULL: every edge both ways, i.e. lz_connected_components).  Deterministic.
+ *   scratch  >= lz_reach_components_scratch_bytes(n_edges, n_nodes); labels int32 [n_nodes] */
+size_t lz_reach_components_scratch_bytes(int64_t n_edges, int32_t n_nodes);
+int lz_reach_components(const int32_t* src, const int32_t* dst, const uint8_t* walk, int64_t n_edges, int32_t n_nodes,
+                        void* scratch, size_t scratch_bytes, int32_t* labels, void* stream);
+
+/* Prepares one shard's edge table for lz_reach_components: maps the shard-local endpoint slots to the caller's
+ * global node indices and derives the walk flags from residency — out_walk[e] = (slot_resident[src[e]] ? 1 : 0) |
+ * (slot_resident[dst[e]] ? 2 : 0), or 0 (edge ignored, endpoints -1) when (double)weight[e] < min_weight (the
+ * reference passes min_weight = 0.0, buffer_graph.py:110) or a slot is out of range.  weight may be NULL.
+ *   slot_global int32 [n_slots], slot_resident uint8 [n_slots]; outputs [n] */
+int lz_edge_endpoints_to_global(const int32_t* src, const int32_t* dst, const float* weight, int64_t n,
+                                const int32_t* slot_global, const uint8_t* slot_resident, int32_t n_slots,
+                                double min_weight, int32_t* out_src, int32_t* out_dst, uint8_t* out_walk, void* stream);
+
 /* ---- buffer-limit eviction (stands behind MemorySystem._enforce_buffer_limit,
  *      core/memory_system.py:535-578) ------------------------------------------------------------------ */
 

@@ -41,6 +41,9 @@ SIGNATURES = {
     "lz_edge_decay_prune_noalloc": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p]),
     "lz_edge_decay": (_i32, [_p, _i64, _f64, _p]),
     "lz_connected_components": (_i32, [_p, _p, _i64, _i32, _p, _p]),
+    "lz_reach_components_scratch_bytes": (_sz, [_i64, _i32]),
+    "lz_reach_components": (_i32, [_p, _p, _p, _i64, _i32, _p, _sz, _p, _p]),
+    "lz_edge_endpoints_to_global": (_i32, [_p, _p, _p, _i64, _p, _p, _i32, _f64, _p, _p, _p, _p]),
     "lz_salience_decay": (_i32, [_p, _i64, _f64, _f64, _p]),
     "lz_evict_lowest_scratch_bytes": (_sz, [_i64, _i32]),
     "lz_evict_lowest": (_i32, [_p, _i32, _p, _p, _p, _i64, _f64, _i32, _p, _sz, _p, _p, _p, _p, _p]),

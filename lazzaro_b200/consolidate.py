@@ -41,15 +41,21 @@ def _queries_on_device(store, emb) -> torch.Tensor:
     return out
 
 
-def dedup_against_store(store, new_emb, user_id: str = "default", gate: float = DEDUP_GATE):
-    """For each new embedding: the store's best row for `user_id` and whether it is a semantic duplicate.
+MARGIN = "worst_case"   # certification margin of the tensor-core searches below: the deterministic one, because a
+                        # wrong top-1 here silently merges (or fails to merge) a memory; "statistical" is narrower
+                        # (slightly fewer rows rescored) but assumes uncorrelated rounding errors
+
+
+def dedup_against_store(store, new_emb, user_id: str = "default", gate: float = DEDUP_GATE, margin: str = MARGIN):
+    """For each new embedding: the store's best row for `user_id` (ranked by the STORE's metric, as the reference's
+    search_nodes call is) and whether it is a semantic duplicate (cosine > gate, whatever the store metric).
     Returns (ids: list of str or None, cosine float64 [n], is_duplicate bool [n])."""
     n = len(new_emb)
     u = store._user(user_id)
     if n == 0 or store.n_rows == 0 or u < 0 or store._live[u] == 0:
         return [None] * n, np.zeros(n), np.zeros(n, bool)
     with store._lock:
-        ids, sc, cnt = store.search_device(_queries_on_device(store, new_emb), u, 1)
+        ids, sc, cnt = store.search_device(_queries_on_device(store, new_emb), u, 1, margin=margin)
         torch.cuda.current_stream(store.device).synchronize()
         ids, sc, cnt = ids.cpu().numpy()[:, 0], sc.cpu().numpy()[:, 0], cnt.cpu().numpy()
         if store.metric != "cosine":                    # the gate is a cosine whatever the search metric
@@ -63,20 +69,19 @@ def dedup_against_store(store, new_emb, user_id: str = "default", gate: float = 
 
 
 def link_candidates(store, new_emb, user_id: str = "default", m: int = LINK_TOP, threshold: float = LINK_GATE,
-                    scale: float = LINK_SCALE, row_range: Optional[Tuple[int, int]] = None):
+                    scale: float = LINK_SCALE, row_range: Optional[Tuple[int, int]] = None, margin: str = MARGIN):
     """For each new embedding the up-to-m best existing rows with cosine > threshold, best first, as
     (id, cosine, edge_weight = scale * cosine).  `row_range` restricts the scan to one shard's rows
-    (_link_within_shards); the default scans every row of the user (_link_to_existing_memories)."""
+    (_link_within_shards); the default scans every row of the user (_link_to_existing_memories).
+    Always ranked and gated by COSINE, as memory_system.py:858-867 does over the resident nodes — also on a
+    store whose own metric is l2 (the store then keeps a cosine shadow beside its l2 one)."""
     n = len(new_emb)
     u = store._user(user_id)
     if n == 0 or store.n_rows == 0 or u < 0 or store._live[u] == 0:
         return [[] for _ in range(n)]
     with store._lock:
         q = _queries_on_device(store, new_emb)
-        if row_range is None:
-            ids, sc, cnt = store.search_device(q, u, m)
-        else:
-            ids, sc, cnt = store.search_device(q, u, m, row_range=row_range)
+        ids, sc, cnt = store.search_device(q, u, m, row_range=row_range, metric="cosine", margin=margin)
         torch.cuda.current_stream(store.device).synchronize()
         ids, sc, cnt = ids.cpu().numpy(), sc.cpu().numpy(), cnt.cpu().numpy()
         out = []
@@ -86,7 +91,7 @@ def link_candidates(store, new_emb, user_id: str = "default", m: int = LINK_TOP,
         return out
 
 
-def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigmas: float = 4.0):
+def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigmas: float = 4.0, margin: str = MARGIN):
     """argmax_c cosine(row, centroid_c) for float32 CUDA tensors rows [n, dim], centroids [K, dim]
     (dim % 8 == 0).  Returns (index int64 [n], cosine float64 [n]) on the device; ties go to the lowest
     centroid index.  Rows are the query side of the contraction, centroids the scanned side."""
@@ -96,8 +101,13 @@ def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigm
     norms = kernels.row_norms(cen)
     n = rows.shape[0]
     if n >= 8 and dim % 8 == 0:
-        shadow = kernels.rows_to_shadow(cen, dim, norms)
-        ids, sc, cnt, _ = kernels.search_batched(shadow, cen, dim, norms, None, -1, rows, 1, margin_sigmas=margin_sigmas)
+        err = torch.empty(cen.shape[0], dtype=torch.float32, device=cen.device)
+        shadow = kernels.rows_to_shadow(cen, dim, norms, row_err=err)
+        if margin not in ("worst_case", "statistical"):
+            raise ValueError(f"margin must be 'worst_case' or 'statistical', got {margin!r}")
+        det = float(err.max().item()) if margin == "worst_case" else None       # K floats: a small read-back
+        ids, sc, cnt, _ = kernels.search_batched(shadow, cen, dim, norms, None, -1, rows, 1, margin_sigmas=margin_sigmas,
+                                                 det_row_err=det)
     else:
         ids, sc, cnt = kernels.search_exact(cen, dim, norms, None, rows, 1, _lib.COSINE)
     return ids[:, 0], sc[:, 0]

@@ -508,3 +508,131 @@ extern "C" int lz_connected_components(const int32_t* src, const int32_t* dst, i
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
+
+// ---- components the way the reference's traversal forms them ----------------------------------
+// BufferGraph.get_connected_components (core/buffer_graph.py:99-120) is NOT plain undirected connectivity: it visits
+// the nodes in dict order, and from a node it only follows the edges of the shard that node lives in
+// (buffer_graph.py:72-77 -> memory_shard.py:54-62).  An edge whose other endpoint lives elsewhere (a cross-shard
+// link, an id that is not resident) can therefore be walked from one end only, and the component such a target
+// lands in depends on the visiting order.  What the DFS computes is:  label(v) = the SMALLEST index among the
+// nodes that can reach v  (indices = visiting order).  Proof sketch: an unvisited node reachable from the current
+// root is reachable through unvisited nodes only (a visited node on the path would have pulled it in earlier),
+// so a root takes exactly the unvisited part of its reachable set, and the least ancestor of v is always a root.
+//
+// Device form: union-find over the two-way edges (every node of such a component reaches every other), then
+// min-label propagation along the one-way edges between those components until nothing changes.
+namespace {
+__global__ void __launch_bounds__(kThreads) edge_global_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                               const float* __restrict__ w, int64_t n, const int32_t* __restrict__ slot_global,
+                                                               const uint8_t* __restrict__ slot_resident, int n_slots, double min_weight,
+                                                               int32_t* __restrict__ o_src, int32_t* __restrict__ o_dst,
+                                                               uint8_t* __restrict__ o_walk) {
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < n; e += (int64_t)gridDim.x * kThreads) {
+        const int a = src[e], b = dst[e];
+        const bool ok = a >= 0 && b >= 0 && a < n_slots && b < n_slots && (w == nullptr || (double)w[e] >= min_weight);
+        o_src[e] = ok ? slot_global[a] : -1;
+        o_dst[e] = ok ? slot_global[b] : -1;
+        o_walk[e] = ok ? (uint8_t)((slot_resident[a] ? 1 : 0) | (slot_resident[b] ? 2 : 0)) : (uint8_t)0;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) reach_hook_kernel(const int32_t* __restrict__ src, const int32_t* __restrict__ dst,
+                                                              const uint8_t* __restrict__ walk, int64_t n_edges, int n_nodes,
+                                                              int* parent, int2* __restrict__ list, int* list_n) {
+    for (int64_t e = (int64_t)blockIdx.x * kThreads + threadIdx.x; e < n_edges; e += (int64_t)gridDim.x * kThreads) {
+        int u = src[e], v = dst[e];
+        const int wk = walk ? walk[e] : 3;
+        if (wk == 0 || u < 0 || v < 0 || u >= n_nodes || v >= n_nodes || u == v) continue;
+        if (wk != 3) {                                             // one-way: remember it as (from, to)
+            list[atomicAdd(list_n, 1)] = wk == 1 ? make_int2(u, v) : make_int2(v, u);
+            continue;
+        }
+        while (true) {
+            u = cc_find(parent, u);
+            v = cc_find(parent, v);
+            if (u == v) break;
+            const int hi = u > v ? u : v, lo = u > v ? v : u;
+            if (atomicCAS(&parent[hi], hi, lo) == hi) break;
+        }
+    }
+}
+
+__device__ __forceinline__ int ld_cg(const int* p) {
+    int v;
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+// One CTA: L[root] = min(L[root], L[root of a one-way predecessor]) until a whole sweep changes nothing.  One-way
+// edges are the cross-shard links (a handful per new memory), so a single CTA sweeping the list is ample.
+__global__ void __launch_bounds__(1024) reach_propagate_kernel(const int2* __restrict__ list, const int* __restrict__ list_n,
+                                                               const int* __restrict__ root, int* L) {
+    const int n = *list_n;
+    while (true) {
+        int changed = 0;
+        for (int i = threadIdx.x; i < n; i += 1024) {
+            const int2 e = list[i];
+            const int lu = ld_cg(L + root[e.x]), rv = root[e.y];
+            if (lu < ld_cg(L + rv)) { atomicMin(L + rv, lu); changed = 1; }
+        }
+        if (!__syncthreads_or(changed)) break;
+    }
+}
+
+__global__ void __launch_bounds__(kThreads) reach_apply_kernel(int* labels, const int* __restrict__ L, int n) {
+    for (int i = blockIdx.x * kThreads + threadIdx.x; i < n; i += gridDim.x * kThreads) labels[i] = L[labels[i]];
+}
+}  // namespace
+
+extern "C" int lz_edge_endpoints_to_global(const int32_t* src, const int32_t* dst, const float* weight, int64_t n,
+                                           const int32_t* slot_global, const uint8_t* slot_resident, int32_t n_slots,
+                                           double min_weight, int32_t* out_src, int32_t* out_dst, uint8_t* out_walk,
+                                           void* stream) {
+    if (n <= 0) return LZ_OK;
+    LZ_REQUIRE(src && dst && slot_global && slot_resident && out_src && out_dst && out_walk,
+               "lz_edge_endpoints_to_global: NULL pointer");
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    int64_t b = (n + kThreads - 1) / kThreads;
+    if (b > (int64_t)sms * 16) b = (int64_t)sms * 16;
+    edge_global_kernel<<<(unsigned)b, kThreads, 0, (cudaStream_t)stream>>>(src, dst, weight, n, slot_global, slot_resident,
+                                                                           n_slots, min_weight, out_src, out_dst, out_walk);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
+extern "C" size_t lz_reach_components_scratch_bytes(int64_t n_edges, int32_t n_nodes) {
+    const size_t nodes = ((size_t)(n_nodes > 0 ? n_nodes : 0) * 4 + 255) & ~(size_t)255;
+    return nodes + 256 + (size_t)(n_edges > 0 ? n_edges : 0) * 8;
+}
+
+extern "C" int lz_reach_components(const int32_t* src, const int32_t* dst, const uint8_t* walk, int64_t n_edges,
+                                   int32_t n_nodes, void* scratch, size_t scratch_bytes, int32_t* labels, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n_nodes <= 0) return LZ_OK;
+    LZ_REQUIRE(labels != nullptr && scratch != nullptr && (n_edges == 0 || (src && dst)), "lz_reach_components: NULL pointer");
+    LZ_REQUIRE(n_edges >= 0 && n_edges < (1ll << 31), "lz_reach_components: n_edges=%lld", (long long)n_edges);
+    const size_t need = lz_reach_components_scratch_bytes(n_edges, n_nodes);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_reach_components: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    auto blocks = [&](int64_t n) { int64_t b = (n + kThreads - 1) / kThreads; return (unsigned)(b < 1 ? 1 : (b > sms * 16 ? sms * 16 : b)); };
+    const size_t nodes_bytes = ((size_t)n_nodes * 4 + 255) & ~(size_t)255;
+    int* L = (int*)scratch;
+    int* list_n = (int*)((unsigned char*)scratch + nodes_bytes);
+    int2* list = (int2*)((unsigned char*)scratch + nodes_bytes + 256);
+    LZ_CUDA(cudaMemsetAsync(list_n, 0, 4, st));
+    cc_init_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(labels, n_nodes);
+    cc_init_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(L, n_nodes);
+    if (n_edges > 0) reach_hook_kernel<<<blocks(n_edges), kThreads, 0, st>>>(src, dst, walk, n_edges, n_nodes, labels, list, list_n);
+    cc_flatten_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(labels, n_nodes);
+    if (n_edges > 0 && walk != nullptr) {
+        reach_propagate_kernel<<<1, 1024, 0, st>>>(list, list_n, labels, L);
+        reach_apply_kernel<<<blocks(n_nodes), kThreads, 0, st>>>(labels, L, n_nodes);
+    }
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}

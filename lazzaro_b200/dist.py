@@ -166,3 +166,41 @@ class _PendingSearch:
         """Waits for the search and returns host (ids int64 [B,k], scores float64 [B,k], counts int32 [B])."""
         self._done.synchronize()
         return tuple(b.numpy().copy() for b in self._bufs)
+
+
+PARITY_CASES = ((1, 10), (3, 100), (64, 10), (300, 7))     # (batch, k): exact-scan path and tensor-core path
+
+
+def parity_check(n: int = 300_000, dim: int = 128, cases=PARITY_CASES, group=None):
+    """Run on every rank of an initialised NCCL job (one rank per GPU): builds the SAME n x dim rows on each rank,
+    gives rank r the r-th slab, and checks that the sharded search (local search with id_base, one packed
+    all-gather, strided merge) returns bit for bit what a single-GPU lz_search_exact over all rows returns —
+    ids, float64 scores and counts, through the device API and through the pipelined host API.  Queries are
+    drawn near rows of the whole matrix, so true neighbours sit on every rank.
+    Returns a list of {"batch", "k", "ok"} (identical on every rank: the verdicts are all-reduced)."""
+    from . import _lib, kernels as K, synth
+    from .store import B200Store
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    rows, _ = synth.clustered_rows_device(n, dim, 32, dev)          # same seed on every rank: same rows
+    lo, hi = even_slabs(n, world)[rank]
+    st = B200Store(device=str(dev))
+    st.adopt_rows(rows[lo:hi].contiguous(), id_prefix="r")
+    ss = ShardedSearch(st, row_offset=lo, world=world, group=group)
+    norms = K.row_norms(rows)
+    out = []
+    for B, k in cases:
+        q = synth.queries_near_rows_device(rows, B, seed=synth.SEED_QUERY + B)
+        ids, sc, cnt = ss.search_device(q, k)
+        want_ids, want_sc, want_cnt = K.search_exact(rows, dim, norms, None, q, k, _lib.COSINE)
+        good = bool((ids == want_ids).all()) and bool((sc == want_sc).all()) and bool((cnt == want_cnt).all())
+        h = ss.submit_host(q.cpu().numpy(), k).result()
+        good = good and np.array_equal(h[0], want_ids.cpu().numpy())
+        if B >= 2 * world:                                         # the answers really are spread over the ranks
+            owners = torch.bincount((want_ids[want_ids >= 0] // max(1, n // world)).clamp(max=world - 1), minlength=world)
+            good = good and bool((owners > 0).all())
+        flag = torch.tensor([int(good)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        out.append({"batch": B, "k": k, "ok": bool(int(flag))})
+    st.close()
+    return out

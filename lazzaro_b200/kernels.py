@@ -234,6 +234,33 @@ def connected_components(src: torch.Tensor, dst: torch.Tensor, n_edges: int, n_n
     return labels
 
 
+def edge_endpoints_to_global(src, dst, weight, n: int, slot_global: torch.Tensor, slot_resident: torch.Tensor,
+                             out_src: torch.Tensor, out_dst: torch.Tensor, out_walk: torch.Tensor, min_weight: float = 0.0):
+    """One shard's edge endpoints as global node indices + walk flags (lz_edge_endpoints_to_global); outputs are
+    caller-provided slices of the concatenated arrays."""
+    dev = _dev(slot_global)
+    assert slot_global.dtype == torch.int32 and slot_resident.dtype == torch.uint8 and out_walk.dtype == torch.uint8
+    assert out_src.dtype == torch.int32 and out_dst.dtype == torch.int32 and out_src.numel() >= n
+    with torch.cuda.device(dev):
+        check(_lib.load().lz_edge_endpoints_to_global(ptr(src), ptr(dst), ptr(weight), int(n), ptr(slot_global), ptr(slot_resident),
+                                                      slot_global.numel(), float(min_weight), ptr(out_src), ptr(out_dst),
+                                                      ptr(out_walk), stream_ptr(dev)), "lz_edge_endpoints_to_global")
+
+
+def reach_components(src: torch.Tensor, dst: torch.Tensor, walk: Optional[torch.Tensor], n_edges: int, n_nodes: int) -> torch.Tensor:
+    """int32 [n_nodes]: labels[v] = smallest index among the nodes that can reach v under the walk flags
+    (lz_reach_components) — the reference traversal's components when indices follow its visiting order."""
+    dev = _dev(src)
+    lib = _lib.load()
+    labels = torch.empty(n_nodes, dtype=torch.int32, device=dev)
+    nbytes = int(lib.lz_reach_components_scratch_bytes(int(n_edges), int(n_nodes)))
+    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.lz_reach_components(ptr(src), ptr(dst), ptr(walk), int(n_edges), int(n_nodes), ptr(scratch), nbytes,
+                                      ptr(labels), stream_ptr(dev)), "lz_reach_components")
+    return labels
+
+
 def evict_lowest(salience: torch.Tensor, access_count: torch.Tensor, last_accessed: torch.Tensor, now: float, k: int,
                  skip: Optional[torch.Tensor] = None, want_all: bool = False):
     """The k least important nodes (lz_evict_lowest): (idx int64 [count], importance float64 [count]) in

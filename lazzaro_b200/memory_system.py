@@ -99,32 +99,50 @@ class BufferGraph(_DeviceBufferGraph):
             node.salience = min(1.0, node.salience + 0.05)
 
     def get_connected_components(self) -> List[Set[str]]:
-        """buffer_graph.py:99-120 (iterative here; neighbours searched inside the node's own shard at any
-        weight).  Host-side: the device CSR version is SURVEY §8f, next."""
-        adj: Dict[str, Set[str]] = defaultdict(set)
+        """buffer_graph.py:99-120 on the device (lz_reach_components): one launch sequence over the concatenated
+        shard edge tables, no host traversal.
+
+        Node indices follow the reference's visiting order (`self.nodes`: super-nodes, then the shards' nodes in
+        dict order; ids that appear only as edge endpoints come last).  The reference follows an edge from a node
+        only if the edge sits in the shard the node lives in (buffer_graph.py:72-77), so every edge gets walk
+        flags from the residency of its endpoints IN ITS OWN SHARD: both resident = two-way; a cross-shard link or
+        an endpoint that is not resident = one-way, away from the resident end; the kernel then assigns each node
+        the smallest index that can reach it, which is the root the reference's DFS gives it.  Components come
+        back in the reference's order (by root)."""
+        index: Dict[str, int] = {}
+        for nid in self.nodes:                                   # visiting order of buffer_graph.py:114
+            index.setdefault(nid, len(index))
+        n_resident = len(index)
+        plan, total = [], 0
         for shard in self.shards.values():
-            for (src, tgt), e in shard.edges.items():
-                if e.weight >= 0.0:
-                    if src in shard.nodes:
-                        adj[src].add(tgt)
-                    if tgt in shard.nodes:
-                        adj[tgt].add(src)
-        seen: Set[str] = set()
-        comps: List[Set[str]] = []
-        for nid in self.nodes:
-            if nid in seen:
+            shard._flush()
+            if shard._table.n == 0:
                 continue
-            comp, stack = set(), [nid]
-            seen.add(nid)
-            while stack:
-                cur = stack.pop()
-                comp.add(cur)
-                for nb in adj.get(cur, ()):
-                    if nb not in seen:
-                        seen.add(nb)
-                        stack.append(nb)
-            comps.append(comp)
-        return comps
+            for name in shard._names:                            # edge-only ids: indexed after every resident node
+                index.setdefault(name, len(index))
+            plan.append((shard, total))
+            total += shard._table.n
+        names = list(index)
+        if not names:
+            return []
+        if total == 0:
+            return [{nid} for nid in names[:n_resident]]
+        dev = plan[0][0]._table.device
+        gsrc = torch.empty(total, dtype=torch.int32, device=dev)
+        gdst = torch.empty(total, dtype=torch.int32, device=dev)
+        walk = torch.empty(total, dtype=torch.uint8, device=dev)
+        for shard, off in plan:
+            t = shard._table
+            slot_global = torch.tensor([index[nm] for nm in shard._names], dtype=torch.int32).to(dev, non_blocking=True)
+            resident = torch.tensor([1 if nm in shard.nodes else 0 for nm in shard._names], dtype=torch.uint8).to(dev, non_blocking=True)
+            kernels.edge_endpoints_to_global(t.src, t.dst, t.weight, t.n, slot_global, resident,
+                                             gsrc[off:off + t.n], gdst[off:off + t.n], walk[off:off + t.n], min_weight=0.0)
+        labels = kernels.reach_components(gsrc, gdst, walk, total, len(names)).cpu().numpy()
+        groups: Dict[int, Set[str]] = {}
+        for i, lab in enumerate(labels.tolist()):
+            if i < n_resident or lab != i:                        # an edge-only id nobody reaches is not a node
+                groups.setdefault(lab, set()).add(names[i])
+        return [groups[k] for k in sorted(groups)]
 
 
 class MemorySystem:
@@ -462,8 +480,23 @@ class MemorySystem:
                 ids.append(nid)
         if not embs:
             return {}
-        links = consolidate.link_candidates(self.store, np.asarray(embs, np.float32), self.user_id)
-        return dict(zip(ids, links))
+        # The reference ranks only resident non-super nodes (memory_system.py:842-847) and takes the best 3 of THOSE;
+        # the store also holds the super-nodes' centroid rows (written by _save_to_persistence), which are often among
+        # a new memory's nearest rows.  So ask for 3 + (number of super-nodes) candidates, drop super-nodes and rows
+        # that are not resident, and keep the first 3 — the same three the reference finds.
+        m = min(_lib.MAX_K, consolidate.LINK_TOP + len(self.super_nodes))
+        links = consolidate.link_candidates(self.store, np.asarray(embs, np.float32), self.user_id, m=m)
+        out = {}
+        for nid, lst in zip(ids, links):
+            keep = []
+            for cand in lst:
+                node = self.buffer.get_node(cand[0])
+                if node is not None and not node.is_super_node:
+                    keep.append(cand)
+                    if len(keep) == consolidate.LINK_TOP:
+                        break
+            out[nid] = keep
+        return out
 
     def _apply_cross_links(self, new_nodes, cross):
         """memory_system.py:866-889: skip a link whose edge exists in either direction in any shard; the
@@ -502,9 +535,10 @@ class MemorySystem:
             return
         new_set = {nid for nid, _ in new_nodes}
         embs = [self.buffer.get_node(nid).embedding for nid, _ in new_nodes]
-        k = min(_lib.MAX_K, 3 + len(new_set))
+        k = min(_lib.MAX_K, 3 + len(new_set) + len(self.super_nodes))
         links = consolidate.link_candidates(self.store, np.asarray(embs, np.float32), self.user_id, m=k)
-        cross = {nid: [l for l in lst if l[0] not in new_set][:3] for (nid, _), lst in zip(new_nodes, links)}
+        keep = lambda c: c[0] not in new_set and (lambda n: n is not None and not n.is_super_node)(self.buffer.get_node(c[0]))
+        cross = {nid: [l for l in lst if keep(l)][:3] for (nid, _), lst in zip(new_nodes, links)}
         self._apply_cross_links(new_nodes, cross)
 
     def _create_super_nodes_for_shard(self, shard_key: str):
@@ -624,6 +658,16 @@ class MemorySystem:
                 out.append(rid)
                 seen.add(rid)
         return out[:5]
+
+    def save_state(self, filename: str = "memory_state.json") -> str:
+        """memory_system.py:1216-1239 (same JSON layout; lazzaro_b200/persist.py)."""
+        from . import persist
+        return persist.save_state(self, filename)
+
+    def load_state(self, filename: str = "memory_state.json") -> str:
+        """memory_system.py:1241-1273."""
+        from . import persist
+        return persist.load_state(self, filename)
 
     def close(self):
         self.store.close()

@@ -1,7 +1,7 @@
 """Import / export of the store's contents in the reference's table layout.
 
 The reference persists three LanceDB tables whose Arrow schemas are fixed in core/vector_store.py:33-85
-(`nodes`, `edges`, `user_profile`).  LanceDB itself is not installed here, but its tables are Arrow tables:
+(`nodes`, `edges`, `profiles`).  LanceDB itself is not installed here, but its tables are Arrow tables:
 what this module writes (Arrow IPC files, or Parquet) has exactly those schemas — same field names, order and
 types, `vector` as FixedSizeList<float32>[dim], `child_ids` / `metadata` as JSON strings — so a site that has
 lancedb can hand them straight to `db.create_table(name, data=table)`, and `table.to_arrow()` of an existing
@@ -23,7 +23,8 @@ import torch
 
 from .store import B200Store
 
-NODES, EDGES, PROFILES = "nodes", "edges", "user_profile"          # vector_store.py:21-23 table names
+NODES, EDGES, PROFILES = "nodes", "edges", "profiles"              # vector_store.py:20-22 table names
+_OLD_PROFILES = "user_profile"                                      # name used by dumps this module wrote before; still read
 
 
 def node_schema(dim: int = 1536) -> pa.Schema:
@@ -126,7 +127,7 @@ def import_tables(tables: Dict[str, pa.Table], store: Optional[B200Store] = None
             by_user.setdefault(e.pop("user_id"), []).append(e)
         for u, es in by_user.items():
             st.add_edges(es, user_id=u)
-    profiles = tables.get(PROFILES)
+    profiles = tables.get(PROFILES, tables.get(_OLD_PROFILES))
     if profiles is not None:
         for p in profiles.to_pylist():
             st.save_profile(json.loads(p["data"]), user_id=p["user_id"])
@@ -134,7 +135,7 @@ def import_tables(tables: Dict[str, pa.Table], store: Optional[B200Store] = None
 
 
 def save(store: B200Store, directory: str, fmt: str = "arrow") -> Dict[str, str]:
-    """Writes `<directory>/{nodes,edges,user_profile}.{arrow|parquet}`; returns the paths."""
+    """Writes `<directory>/{nodes,edges,profiles}.{arrow|parquet}`; returns the paths."""
     if fmt not in ("arrow", "parquet"):
         raise ValueError("fmt must be 'arrow' or 'parquet'")
     os.makedirs(directory, exist_ok=True)
@@ -153,8 +154,74 @@ def save(store: B200Store, directory: str, fmt: str = "arrow") -> Dict[str, str]
 def load(directory: str, fmt: str = "arrow", **store_kwargs: Any) -> B200Store:
     """Reads what `save` wrote (or files of the same names and schemas) into a new store."""
     tables = {}
-    for name in (NODES, EDGES, PROFILES):
+    for name in (NODES, EDGES, PROFILES, _OLD_PROFILES):
         path = os.path.join(directory, f"{name}.{fmt}")
         if os.path.exists(path):
             tables[name] = ipc.open_file(path).read_all() if fmt == "arrow" else pq.read_table(path)
     return import_tables(tables, **store_kwargs)
+
+
+# ---- the JSON graph state (memory_system.py:1216-1273) ------------------------------------------------------
+
+def state_dict(ms) -> Dict[str, Any]:
+    """What the reference's `save_state` serialises (memory_system.py:1217-1237): per shard the nodes and edges as
+    `asdict` dictionaries (models/graph.py:58-60, 102-104), the super-nodes, the profile, the counters and five
+    settings.  `ms` is a lazzaro_b200.memory_system.MemorySystem; edge weights are read back from HBM."""
+    node = lambda n: {"id": n.id, "content": n.content, "embedding": list(n.embedding), "type": n.type,
+                      "timestamp": n.timestamp, "access_count": n.access_count, "last_accessed": n.last_accessed,
+                      "salience": n.salience, "is_super_node": n.is_super_node, "child_ids": list(n.child_ids),
+                      "parent_id": n.parent_id, "shard_key": n.shard_key}
+    edge = lambda e: {"source": e.source, "target": e.target, "weight": e.weight, "edge_type": e.edge_type,
+                      "co_occurrence": e.co_occurrence, "last_updated": e.last_updated}
+    profile = ms.profile if isinstance(ms.profile, dict) and "data" in ms.profile else {"data": ms.profile or {}, "last_updated": 0.0}
+    return {
+        "shards": {k: {"nodes": [node(n) for n in v.nodes.values()], "edges": [edge(e) for e in v.edges.values()]}
+                   for k, v in ms.shards.items()},
+        "super_nodes": [node(n) for n in ms.super_nodes.values()],
+        "profile": profile,
+        "node_counter": ms.node_counter,
+        "conversation_count": ms.conversation_count,
+        "settings": {"auto_consolidate": ms.auto_consolidate, "consolidate_every": ms.consolidate_every,
+                     "auto_prune": ms.auto_prune, "prune_threshold": ms.prune_threshold,
+                     "max_buffer_size": ms.max_buffer_size},
+    }
+
+
+def save_state(ms, filename: str = "memory_state.json") -> str:
+    """memory_system.py:1216-1239: same file layout, so either implementation reads the other's file."""
+    with open(filename, "w") as f:
+        json.dump(state_dict(ms), f, indent=2)
+    return f"✓ State saved to {filename}"
+
+
+def load_state(ms, filename: str = "memory_state.json") -> str:
+    """memory_system.py:1241-1273: rebuilds shards (nodes, then edges through add_edge, so a repeated key is
+    reinforced exactly as the reference's loader does), super-nodes, profile, counters and settings.  The edge
+    tables are uploaded to HBM shard by shard in one batch each."""
+    from .graph import Edge, MemoryShard, Node
+    from .memory_system import BufferGraph
+    try:
+        with open(filename, "r") as f:
+            state = json.load(f)
+    except FileNotFoundError:
+        return f"⚠ File {filename} not found"
+    nf, ef = Node.__dataclass_fields__, Edge.__dataclass_fields__
+    ms.shards = {}
+    for key, data in state.get("shards", {}).items():
+        shard = MemoryShard(key, device=str(ms.store.device))
+        for nd in data.get("nodes", []):
+            shard.add_node(Node(**{k: v for k, v in nd.items() if k in nf}))
+        shard.add_edges([Edge(**{k: v for k, v in ed.items() if k in ef}) for ed in data.get("edges", [])])
+        ms.shards[key] = shard
+    ms.super_nodes = {n["id"]: Node(**{k: v for k, v in n.items() if k in nf}) for n in state.get("super_nodes", [])}
+    ms.buffer = BufferGraph(ms.shards, ms.super_nodes)
+    ms.buffer._device = str(ms.store.device)
+    prof = state.get("profile", {})
+    if prof:
+        ms.profile = {"data": prof.get("data", {}), "last_updated": prof.get("last_updated", 0.0)}
+    ms.node_counter = state.get("node_counter", 0)
+    ms.conversation_count = state.get("conversation_count", 0)
+    for key, val in state.get("settings", {}).items():
+        if hasattr(ms, key):
+            setattr(ms, key, val)
+    return f"✓ State loaded from {filename}"

@@ -32,6 +32,42 @@ def _round_up(v: int, m: int) -> int:
     return (v + m - 1) // m * m
 
 
+class _Shadow:
+    """The fp16 copy of the rows that the tensor-core pass reads, for ONE metric (cosine: normalised rows; l2: raw
+    rows + the norm-term columns), kept up to date lazily, with what the certification margin needs: the largest
+    rounding-error norm of any shadow row (deterministic margin) and the largest row norm (L2 margins)."""
+
+    def __init__(self, metric: int):
+        self.metric = metric
+        self.t: Optional[torch.Tensor] = None        # fp16 [capacity, dim_p (+ 8)]
+        self.err: Optional[torch.Tensor] = None      # float32 [capacity] per-row rounding-error norm
+        self.n = 0                                    # rows that are up to date
+        self.max_err = 0.0
+        self.max_norm = 0.0
+
+    def reset(self):
+        self.n, self.max_err, self.max_norm = 0, 0.0, 0.0
+
+    def ensure(self, store: "B200Store"):
+        cap = store._rows.shape[0]
+        if self.t is None or self.t.shape[0] != cap:
+            t = torch.empty((cap, kernels.shadow_dim(store._dim_p, self.metric)), dtype=torch.float16, device=store.device)
+            err = torch.empty(cap, dtype=torch.float32, device=store.device)
+            if self.t is not None and self.n:
+                t[:self.n] = self.t[:self.n]
+                err[:self.n] = self.err[:self.n]
+            self.t, self.err = t, err
+        if self.n < store._n:
+            a, b = self.n, store._n
+            kernels.rows_to_shadow(store._rows[a:b], store._dim_p, store._norms[a:b], out=self.t[a:b], metric=self.metric,
+                                   row_err=self.err[a:b])
+            # row side of the margins: the largest row norm (L2) and the largest rounding-error norm of any shadow row
+            # (deleted rows included — upper bounds are all that is needed); one small read-back per refresh
+            self.max_norm = max(self.max_norm, float(store._norms[a:b].max().item()))
+            self.max_err = max(self.max_err, float(self.err[a:b].max().item()))
+            self.n = b
+
+
 class B200Store:
     def __init__(self, db_dir: str = "db", dim: Optional[int] = None, metric: str = "cosine",
                  device: Optional[str] = None, capacity: int = 4096, batched_search: str = "auto"):
@@ -80,11 +116,9 @@ class B200Store:
         # bit-exact ids); "statistical" = margin_sigmas standard deviations under independent rounding errors
         # (narrower, fewer fallbacks, but not a proof — see DESIGN.md §4)
         self.margin = "worst_case"
-        self._row_err: Optional[torch.Tensor] = None  # float32 [capacity] rounding-error norm of each shadow row
-        self._max_err = 0.0
-        self._shadow: Optional[torch.Tensor] = None   # bf16 [capacity, dim_p] normalised copy of the rows
-        self._shadow_n = 0                            # rows of the shadow that are up to date
-        self._max_norm = 0.0                          # largest row norm seen by the shadow (L2 margin)
+        # fp16 shadows by metric, built on first use: the store's own metric, and cosine on an l2 store when the
+        # consolidation code asks for cosine neighbours (memory_system.py:858-867 ranks by cosine whatever the store does)
+        self._shadows: Dict[int, _Shadow] = {}
         self._bscratch: Optional[torch.Tensor] = None
         self.last_certified: Optional[torch.Tensor] = None
         self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
@@ -114,31 +148,19 @@ class B200Store:
         self._rows, self._norms, self._tags = rows, norms, tags
         self._gen += 1
         self._graphs.clear()                   # captured graphs hold the old columns' addresses
-        if self._shadow is not None:
-            shadow = torch.empty((cap, self._shadow.shape[1]), dtype=torch.float16, device=self.device)
-            shadow[:self._shadow_n] = self._shadow[:self._shadow_n]
-            self._shadow = shadow
-            self._row_err = torch.empty(cap, dtype=torch.float32, device=self.device)
 
-    def _ensure_shadow(self):
-        """Brings the normalised bf16 copy of the rows (read by the tensor-core pass) up to date."""
-        if self._shadow is None:
-            self._shadow = torch.empty((self._rows.shape[0], kernels.shadow_dim(self._dim_p, self._metric)),
-                                       dtype=torch.float16, device=self.device)
-            self._row_err = torch.empty(self._rows.shape[0], dtype=torch.float32, device=self.device)
-            self._shadow_n = 0
-            self._max_norm = 0.0
-            self._max_err = 0.0
-        if self._shadow_n < self._n:
-            a, b = self._shadow_n, self._n
-            kernels.rows_to_shadow(self._rows[a:b], self._dim_p, self._norms[a:b], out=self._shadow[a:b], metric=self._metric,
-                                 row_err=self._row_err[a:b])
-            if self._metric == _lib.L2:                 # the L2 error margin scales with the largest row norm
-                self._max_norm = max(self._max_norm, float(self._norms[a:b].max().item()))
-            # row side of the deterministic margin: the largest rounding-error norm of any shadow row (deleted rows
-            # included — an upper bound is all that is needed)
-            self._max_err = max(self._max_err, float(self._row_err[a:b].max().item()))
-            self._shadow_n = b
+    def _shadow_for(self, metric: int) -> _Shadow:
+        """The up-to-date fp16 shadow for `metric` (created on first use)."""
+        sh = self._shadows.get(metric)
+        if sh is None:
+            sh = self._shadows[metric] = _Shadow(metric)
+        sh.ensure(self)
+        return sh
+
+    @property
+    def _shadow(self) -> Optional[torch.Tensor]:
+        sh = self._shadows.get(self._metric)
+        return None if sh is None else sh.t
 
     def _reserve(self, extra: int):
         need = self._n + extra
@@ -433,12 +455,11 @@ class B200Store:
             torch.cuda.current_stream().synchronize()
         return host_views
 
-    def _det_row_err(self) -> Optional[float]:
-        if self.margin == "worst_case":
-            return self._max_err
-        if self.margin != "statistical":
-            raise ValueError(f"margin must be 'worst_case' or 'statistical', got {self.margin!r}")
-        return None
+    @staticmethod
+    def _check_margin(margin: str) -> str:
+        if margin not in ("worst_case", "statistical"):
+            raise ValueError(f"margin must be 'worst_case' or 'statistical', got {margin!r}")
+        return margin
 
     def _takes_batched_path(self, B: int, k: int, span: int) -> bool:
         return (k <= _lib.BATCHED_MAX_K and
@@ -455,10 +476,13 @@ class B200Store:
         return max(16, int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks)))
 
     def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0,
-                      row_range=None, out=None, _own=None):
+                      row_range=None, out=None, _own=None, metric: Optional[str] = None, margin: Optional[str] = None):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
-        tensors, nothing synchronised.  The exact fp64 scan over the user's row span.
-        `_own` (internal): scratch / group tags owned by a captured CUDA graph instead of the store's shared ones."""
+        tensors, nothing synchronised.  Small batches: the exact fp64 scan over the user's row span; larger
+        ones: the tensor-core path (same answer).
+        `metric`  rank by "cosine" / "l2" instead of the store's own metric (a second fp16 shadow is built on first use)
+        `margin`  certification margin of the tensor-core path for this call (default: the store's `margin`)
+        `_own`    (internal) scratch / group tags owned by a captured CUDA graph instead of the store's shared ones."""
         u = self._user(user) if isinstance(user, str) else user
         lo, hi = self._span[u]
         if row_range is not None:                      # e.g. one semantic shard's contiguous rows
@@ -467,18 +491,20 @@ class B200Store:
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
         tags = None if single_user else self._tags
         B = queries.shape[0]
+        mcode = self._metric if metric is None else _lib.METRICS[metric]
         batched = self._takes_batched_path(B, k, hi - lo)
         if batched:
-            self._ensure_shadow()
+            sh = self._shadow_for(mcode)
             need = int(_lib.load().lz_search_batched_scratch_bytes(hi - lo, B, k, self._dim_p))
             if self._bscratch is None or self._bscratch.numel() < need:
                 self._bscratch = torch.empty(need, dtype=torch.uint8, device=self.device)
-            ids, sc, cnt, cert = kernels.search_batched(self._shadow, self._rows, self._dim_p, self._norms, tags,
+            det = sh.max_err if self._check_margin(margin or self.margin) == "worst_case" else None
+            ids, sc, cnt, cert = kernels.search_batched(sh.t, self._rows, self._dim_p, self._norms, tags,
                                                         -1 if tags is None else u, queries, k, row_range=(lo, hi),
                                                         margin_sigmas=self.margin_sigmas, id_base=id_base,
                                                         scratch=self._bscratch, n_rows_total=self._n,
-                                                        metric=self._metric, max_row_norm=self._max_norm, out=out,
-                                                        det_row_err=self._det_row_err())
+                                                        metric=mcode, max_row_norm=sh.max_norm, out=out,
+                                                        det_row_err=det)
             self.last_certified = cert
             return ids, sc, cnt
         gs, n_groups = self._exact_groups(B)
@@ -503,7 +529,7 @@ class B200Store:
             if self._scratch is None or self._scratch.numel() < need:
                 self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
             scratch = self._scratch
-        return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, self._metric,
+        return kernels.search_exact(self._rows, self._dim_p, self._norms, tags, queries, k, mcode,
                                     row_range=(lo, hi), group_tag=gtag, group_size=gs, n_chunks=n_chunks,
                                     scratch=scratch, id_base=id_base, out=out)
 
@@ -631,9 +657,8 @@ class B200Store:
         for name in ("_rows", "_norms", "_tags"):
             t = getattr(self, name)
             t[:m] = t.index_select(0, idx)
-        if self._shadow is not None:
-            self._shadow_n = 0                         # rebuilt lazily by the next batched search
-            self._max_err = self._max_norm = 0.0
+        for sh in self._shadows.values():
+            sh.reset()                                 # rebuilt lazily by the next batched search
         remap = {int(old): new for new, old in enumerate(live.tolist())}
         self._row_id = {remap[r]: v for r, v in self._row_id.items() if r in remap}
         self._row_meta = {remap[r]: v for r, v in self._row_meta.items() if r in remap}
@@ -717,7 +742,8 @@ class B200Store:
 
     def close(self):                                                  # vector_store.py:235-244
         with self._lock:
-            self._rows = self._norms = self._tags = self._scratch = self._shadow = self._bscratch = None
+            self._rows = self._norms = self._tags = self._scratch = self._bscratch = None
+            self._shadows.clear()
             self._pin.clear()
             self._io.clear()
             self._graphs.clear()

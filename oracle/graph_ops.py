@@ -145,3 +145,68 @@ def neighbors(src, dst, weight, node: int, min_weight: float = 0.3):
         elif t == node and w >= min_weight:
             out.append(s)
     return out
+
+
+# --- connected components as the reference traverses them ------------------------------------------
+
+def reference_components(super_ids, nodes, edges):
+    """core/buffer_graph.py:99-120 restated: `nodes` = [(id, shard_key)] in insertion order, `edges` =
+    [(source, target, weight)] in insertion order (an edge is stored in the shard of its SOURCE node, else in
+    "default" if that shard exists — buffer_graph.py:51-61; a repeated key is reinforced, memory_shard.py:42-52).
+    Visiting order = super-nodes, then shards in creation order with their nodes in insertion order
+    (buffer_graph.py:28-34); from a node only the edges of ITS shard are followed, at weight >= 0.0
+    (buffer_graph.py:72-77, 110).  Returns the list of components (sets) in visiting order."""
+    shard_nodes, shard_edges = {}, {}
+    for nid, key in nodes:
+        shard_nodes.setdefault(key, []).append(nid)
+        shard_edges.setdefault(key, {})
+    home = {nid: key for nid, key in nodes}
+    for s, t, w in edges:
+        key = home.get(s, "default" if "default" in shard_nodes else None)
+        if key is None:
+            continue
+        d = shard_edges[key]
+        d[(s, t)] = min(1.0, d[(s, t)] + 0.1) if (s, t) in d else w
+    def nbrs(nid):
+        if nid not in home:
+            return []
+        out = []
+        for (s, t), w in shard_edges[home[nid]].items():
+            if s == nid and w >= 0.0:
+                out.append(t)
+            elif t == nid and w >= 0.0:
+                out.append(s)
+        return out
+    order = list(super_ids) + [nid for key in shard_nodes for nid in shard_nodes[key]]
+    seen, comps = set(), []
+    for root in order:
+        if root in seen:
+            continue
+        comp, stack = set(), [root]
+        seen.add(root)
+        while stack:                                   # iterative DFS: same visited sets as the recursive one
+            cur = stack.pop()
+            comp.add(cur)
+            for nb in nbrs(cur):
+                if nb not in seen:
+                    seen.add(nb)
+                    stack.append(nb)
+        comps.append(comp)
+    return comps
+
+
+def min_ancestor_labels(n_nodes: int, src, dst, walk):
+    """What lz_reach_components computes, by plain fixed-point iteration: labels[v] = the smallest index among the
+    nodes that can reach v; walk bit 0 = src->dst allowed, bit 1 = dst->src allowed."""
+    lab = np.arange(n_nodes, dtype=np.int64)
+    changed = True
+    while changed:
+        changed = False
+        for s, t, w in zip(src, dst, walk):
+            if s < 0 or t < 0:
+                continue
+            if w & 1 and lab[s] < lab[t]:
+                lab[t] = lab[s]; changed = True
+            if w & 2 and lab[t] < lab[s]:
+                lab[s] = lab[t]; changed = True
+    return lab

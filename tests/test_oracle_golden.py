@@ -193,3 +193,55 @@ def test_neighbors_match_reference(golden_next):
     for mw, want in lists.items():
         for node in range(0, int(g["nb_n"]), 3):
             assert graph_ops.neighbors(g["nb_src"], g["nb_dst"], g["nb_w"], node, float(mw)) == want[node]
+
+
+def _components_case_arrays(case):
+    """Global indices in the reference's visiting order + per-edge walk flags, as BufferGraph.get_connected_components
+    of the device mirror derives them (residency of each endpoint in the edge's own shard)."""
+    supers, nodes, edges = case["supers"], case["nodes"], case["edges"]
+    shards = {}
+    for nid, key in nodes:
+        shards.setdefault(key, []).append(nid)
+    home = {nid: key for nid, key in nodes}
+    index = {}
+    for nid in list(supers) + [nid for key in shards for nid in shards[key]]:
+        index.setdefault(nid, len(index))
+    n_res = len(index)
+    seen, src, dst, walk = set(), [], [], []
+    for s, t, w in edges:
+        key = home.get(s, "default" if "default" in shards else None)
+        if key is None or (key, s, t) in seen:
+            continue
+        seen.add((key, s, t))
+        for x in (s, t):
+            index.setdefault(x, len(index))
+        src.append(index[s]); dst.append(index[t])
+        walk.append((1 if home.get(s) == key else 0) | (2 if home.get(t) == key else 0))
+    return index, n_res, np.array(src), np.array(dst), np.array(walk)
+
+
+def test_components_oracle_and_min_ancestor_form_match_reference():
+    """buffer_graph.py:99-120 recorded from the reference on graphs with cross-shard, dangling and super-node edges
+    (tests/golden/make_golden_r2.py): the oracle's DFS restatement reproduces it, and so does the order-free
+    formulation the CUDA kernel implements (label = smallest index that can reach the node)."""
+    import json
+    import os
+    from oracle import graph_ops
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_r2.npz"))
+    cases = json.loads(str(g["comps"]))
+    order_dependent = 0
+    for case in cases:
+        want = [sorted(c) for c in case["components"]]
+        got = [sorted(c) for c in graph_ops.reference_components(case["supers"], case["nodes"], case["edges"])]
+        assert got == want
+        index, n_res, src, dst, walk = _components_case_arrays(case)
+        lab = graph_ops.min_ancestor_labels(len(index), src, dst, walk)
+        names = list(index)
+        groups = {}
+        for i, l in enumerate(lab.tolist()):
+            if i < n_res or l != i:
+                groups.setdefault(l, []).append(names[i])
+        assert [sorted(groups[k]) for k in sorted(groups)] == want
+        undirected = graph_ops.min_ancestor_labels(len(index), src, dst, np.where(walk > 0, 3, 0))
+        order_dependent += int(len(set(undirected[:n_res].tolist())) != len([c for c in want]))
+    assert order_dependent >= 2, "the fixture should include graphs where one-way edges change the components"
