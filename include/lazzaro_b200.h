@@ -151,6 +151,45 @@ int lz_search_batched(const void* shadow, const float* rows, int64_t ld, int dim
                       int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                       void* stream);
 
+/* Exhaustive float64 top-k of query q over the UNION of n_ranges row ranges [range_lo[q*n_ranges + j],
+ * range_hi[q*n_ranges + j]) (device int64 arrays; an empty range contributes nothing; ranges of one query must not
+ * overlap) — the member scan of a two-level search whose probed shards differ per query, one pass, no merge of
+ * per-range results by the caller.  chunks_per_range CTAs share each range.  Scratch:
+ * lz_search_exact_scratch_bytes(n_queries, k, n_ranges * chunks_per_range).  Other arguments as lz_search_exact. */
+int lz_search_exact_ranges(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
+                           const int64_t* range_lo, const int64_t* range_hi, int n_ranges, int64_t n_rows_total,
+                           const float* queries, int64_t q_ld, int n_queries, int k, int metric,
+                           int chunks_per_range, int64_t id_base, void* scratch, size_t scratch_bytes,
+                           int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
+
+/* ---- two-level semantic-shard search on the tensor cores (north_star (1); the reference's level 1 is the cosine of
+ *      the query against every super-node centroid, core/memory_system.py:464-470) ---------------------------------
+ *
+ * Rows are stored shard by shard: shard s = rows [shard_offsets[s], shard_offsets[s+1]).  Level 1 scores the query batch
+ * against the shard centroids (lz_search_batched over the centroid table, k = nprobe: cosine, exact, ties to the lower
+ * shard index).  Level 2 scores each query against the member rows of its nprobe shards only: the (query, shard) pairs
+ * are grouped by shard on the device, the queries of a shard are copied next to each other into a permuted query
+ * array, and the same tcgen05/TMA GEMM + fused candidate epilogue runs over a work list of (128-query tile, shard
+ * slice) items; float64 rescoring, top-k with the id tie-break and certification as in lz_search_batched; queries
+ * that fail certification are answered by the exact scan of exactly their probed shards (lz_search_exact_ranges).
+ * The result is the exact top-k over the union of the probed shards (oracle/flat_search.py two_level_topk);
+ * nprobe >= n_shards visits everything and equals lz_search_batched bit for bit.  nprobe < n_shards is an
+ * APPROXIMATION of the flat search — report it with recall, never as parity.
+ *   cen_shadow / centroids / cen_norms   centroid table [n_shards, dim]: lz_rows_to_shadow(LZ_COSINE) copy, float32 rows
+ *                 (lz_segment_mean, cast to float32), lz_row_norms; cen_det_row_err: max row_err of that shadow, or < 0
+ *                 for the statistical margin at level 1
+ *   shard_offsets device int64 [n_shards + 1];  k <= LZ_BATCHED_MAX_K;  nprobe <= LZ_MAX_K (clamped to n_shards)
+ *   out_probe     optional int64 [n_queries, nprobe]: the shards each query visited, best first
+ * margin_sigmas, metric, max_row_norm, det_row_err, id_base, outputs: as lz_search_batched (for the member pass). */
+size_t lz_search_two_level_scratch_bytes(int n_shards, int n_queries, int k, int nprobe, int dim);
+int lz_search_two_level(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
+                        int64_t n_rows_total, const int64_t* shard_offsets, int n_shards,
+                        const void* cen_shadow, const float* centroids, int64_t cen_ld, const double* cen_norms,
+                        double cen_det_row_err, const float* queries, int64_t q_ld, int n_queries, int k, int nprobe,
+                        double margin_sigmas, int metric, double max_row_norm, double det_row_err, int64_t id_base,
+                        void* scratch, size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
+                        int32_t* out_certified, int64_t* out_probe, void* stream);
+
 /* Merge `n_lists` per-partition top-k lists per query into one (the all-gather merge of the
  * multi-GPU search; ids are global row ids).  in_ids int64 [n_lists, n_queries, k] (-1 = empty
  * slot), in_scores float64 same shape; outputs as lz_search_exact.  Uses no scratch. */

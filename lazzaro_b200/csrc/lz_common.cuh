@@ -31,7 +31,7 @@ void lz_set_error(const char* fmt, ...);
         }                                                                                     \
     } while (0)
 
-int lz_sm_count();
+int lz_sm_count();   // SM count of the current device (cached per device), <= 0 on failure
 
 // lz_search_exact with an optional device-side work list: int32 indices of the queries to answer (the
 // others' outputs are left untouched) and their count.  Used by the batched search to re-run only the
@@ -41,7 +41,7 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
                          const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
                          int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
                          size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
-                         const int32_t* work_list, const int32_t* work_count, void* stream);   // SM count of the current device (cached per device), <= 0 on failure
+                         const int32_t* work_list, const int32_t* work_count, void* stream, int n_ranges = 1);
 
 // ---- device helpers ----------------------------------------------------------------------------
 

@@ -216,7 +216,44 @@ struct GemmParams {
     u32* gthr;          // [n_queries] best threshold any CTA has reached for the query (ord32 key, 0 = none)
     const double* top1_eps;   // top-1 against a tiny table only (else null): per-query eps; the threshold then
                               // follows the running best group at a distance of 3 eps (see scan_chunk)
+    // Grouped mode (two-level search; items != null): the work is a device-built list of (q-tile of the PERMUTED
+    // query array, row range of one shard slice) items instead of the (q-group, slice) grid; cs == 1.
+    const int4* items;        // [*n_items_dev] x = q-tile, y = first row, z = end row (of the shard slice)
+    const int* n_items_dev;
+    const int32_t* qmap;      // [perm rows] real query index of a permuted query row, -1 = padding
 };
+
+// What one CTA works on: a q-tile against rows tiles row_begin, row_begin + stride, ... (n_tiles of them); rows at or
+// beyond row_end are not candidates; its candidate slots are slot_base + lane.
+struct WorkItem {
+    int qt, n_tiles;
+    int64_t row_begin, row_end, stride;
+    size_t slot_base;
+};
+
+__device__ __forceinline__ WorkItem decode_item(const GemmParams& p, int item, int rank) {
+    WorkItem w;
+    if (p.items != nullptr) {
+        const int4 it = p.items[item];
+        w.qt = it.x;
+        w.row_begin = it.y;
+        w.row_end = it.z;
+        w.stride = BN;
+        w.n_tiles = (it.z - it.y + BN - 1) / BN;
+        w.slot_base = (size_t)item * BM;
+    } else {
+        const int sl = item / p.n_qgroups;
+        w.qt = (item % p.n_qgroups) * p.cs + rank;
+        const int t0 = sl * p.tiles_per_slice;
+        const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
+        w.stride = (int64_t)p.tile_mul * BN;
+        w.row_begin = p.row_lo + (int64_t)t0 * w.stride;
+        w.row_end = p.row_hi;
+        w.n_tiles = t1 - t0;
+        w.slot_base = ((size_t)sl * p.n_qgroups * p.cs + w.qt) * BM;
+    }
+    return w;
+}
 
 // Warp-cooperative compaction of the candidate buffers of the lanes in `need` (each over kp entries):
 // the warp loads one lane's buffer into registers (EPL keys per lane), finds the kp-th largest coarse
@@ -289,7 +326,7 @@ __device__ __forceinline__ void warp_select(unsigned need, u64* my_buf, int& cou
 // One TMEM chunk (32 consecutive rows of this thread's query): reduce each group of kSub rows to its best
 // coarse score and append the groups that beat the query's threshold.
 template <int EPL>
-__device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_first, const GemmParams& p, u64* buf,
+__device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_first, int64_t row_hi, const GemmParams& p, u64* buf,
                                            int& count, float& thr, float slack, int q, int lane) {
     float g[32 / kSub];
 #pragma unroll
@@ -306,7 +343,7 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
     // the threshold trails the running best by 3 eps — a handful of candidates per query instead of all of them,
     // and the final threshold T = c_1 - 3 eps certifies by construction (exact best >= c_1 - eps > T + eps).
     // Chunks reaching past the range are left out: their rows are not candidates.
-    if (row_first + 32 <= p.row_hi) thr = fmaxf(thr, m - slack);
+    if (row_first + 32 <= row_hi) thr = fmaxf(thr, m - slack);
     const bool top1 = slack != INFINITY;                          // single-row candidates
     if (m > thr) {
         if (top1) {
@@ -319,7 +356,7 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
                     for (int i = 0; i < kSub; ++i) {
                         const float val = __uint_as_float(v[j * kSub + i]);
                         const int64_t r = row_first + j * kSub + i;
-                        if (val > thr && r < p.row_hi) buf[count++] = ((u64)ord32(val) << 32) | (u64)(0xffffffffu - (u32)r);
+                        if (val > thr && r < row_hi) buf[count++] = ((u64)ord32(val) << 32) | (u64)(0xffffffffu - (u32)r);
                     }
                 }
             }
@@ -327,14 +364,14 @@ __device__ __forceinline__ void scan_chunk(const uint32_t (&v)[32], int64_t row_
 #pragma unroll
             for (int j = 0; j < 32 / kSub; ++j) {
                 const int64_t r0 = row_first + j * kSub;
-                if (g[j] > thr && r0 < p.row_hi) buf[count++] = ((u64)ord32(g[j]) << 32) | (u64)(0xffffffffu - (u32)r0);
+                if (g[j] > thr && r0 < row_hi) buf[count++] = ((u64)ord32(g[j]) << 32) | (u64)(0xffffffffu - (u32)r0);
             }
         }
     }
     const unsigned need = __ballot_sync(0xffffffffu, count > p.cap - (top1 ? 32 : 32 / kSub));
     if (need) {
         warp_select<EPL>(need, buf, count, thr, p.kp, lane);
-        if ((need >> lane) & 1u) atomicMax(p.gthr + q, ord32(thr));
+        if (((need >> lane) & 1u) && q >= 0) atomicMax(p.gthr + q, ord32(thr));
     }
 }
 
@@ -365,7 +402,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     const int cs = p.cs;
     const int rank = cs > 1 ? (int)cluster_rank() : 0;
     const uint16_t mc_mask = (uint16_t)((1u << cs) - 1u);
-    const int n_items = p.n_qgroups * p.n_slices;
+    const int n_items = p.items != nullptr ? *p.n_items_dev : p.n_qgroups * p.n_slices;
     const int cluster_id = blockIdx.x / cs, n_clusters = gridDim.x / cs;
 
     if (threadIdx.x == 0) {
@@ -388,11 +425,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             uint32_t stage = 0, phase = 0;
             const int slice_rows = BN / cs;
             for (int item = cluster_id; item < n_items; item += n_clusters) {
-                const int qt = (item % p.n_qgroups) * cs + rank, sl = item / p.n_qgroups;
-                const int t0 = sl * p.tiles_per_slice;
-                const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
-                for (int t = t0; t < t1; ++t) {
-                    const int row0 = (int)(p.row_lo + (int64_t)t * p.tile_mul * BN);
+                const WorkItem w = decode_item(p, item, rank);
+                const int qt = w.qt;
+                for (int t = 0; t < w.n_tiles; ++t) {
+                    const int row0 = (int)(w.row_begin + (int64_t)t * w.stride);
                     for (int kb = 0; kb < p.kblocks; ++kb) {
                         { LZ_T0 mbar_wait(&empty[stage], phase ^ 1); LZ_ACC(4) }   // all cs consumers have released the stage
                         unsigned char* st = tiles + stage * STAGE_BYTES;
@@ -415,10 +451,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             constexpr uint32_t idesc = idesc_f16_f32(BM, BN);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (int item = cluster_id; item < n_items; item += n_clusters) {
-                const int sl = item / p.n_qgroups;
-                const int t0 = sl * p.tiles_per_slice;
-                const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
-                for (int t = t0; t < t1; ++t) {
+                const WorkItem w = decode_item(p, item, rank);
+                for (int t = 0; t < w.n_tiles; ++t) {
                     { LZ_T0 mbar_wait(&tempty[acc], acc_phase ^ 1); LZ_ACC(2) }   // epilogue has drained this accumulator
                     tc_fence_after();
                     const uint32_t d = tmem_base + acc * BN;
@@ -448,18 +482,18 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         const int qlane = quarter * 32 + lane;
         uint32_t acc = 0, acc_phase = 0;
         for (int item = cluster_id; item < n_items; item += n_clusters) {
-            const int qt = (item % p.n_qgroups) * cs + rank, sl = item / p.n_qgroups;
-            const int t0 = sl * p.tiles_per_slice;
-            const int t1 = min(p.n_tiles, t0 + p.tiles_per_slice);
-            const size_t slot0 = ((size_t)sl * p.n_qgroups * cs + qt) * BM + qlane;   // [slice][q-tile][query lane]
+            const WorkItem w = decode_item(p, item, rank);
+            const size_t slot0 = w.slot_base + qlane;   // flat: [slice][q-tile][query lane]; grouped: [item][query lane]
             u64* buf = p.cand + slot0 * p.cap;
-            const int q = qt * BM + qlane;
-            const bool valid = q < p.n_queries;
+            // grouped mode: the lane's row of the permuted query array stands for real query qmap[...] (thresholds are
+            // shared between all items of the REAL query, whichever shard they scan)
+            const int q = p.qmap != nullptr ? p.qmap[w.qt * BM + qlane] : (w.qt * BM + qlane < p.n_queries ? w.qt * BM + qlane : -1);
+            const bool valid = q >= 0;
             int count = 0;
             float thr = valid ? -INFINITY : INFINITY;
             const float slack = (p.top1_eps != nullptr && valid) ? fmaxf(3.0f * (float)p.top1_eps[q], 1e-30f) : INFINITY;
-            for (int t = t0; t < t1; ++t) {
-                const int64_t row0 = p.row_lo + (int64_t)t * p.tile_mul * BN;
+            for (int t = 0; t < w.n_tiles; ++t) {
+                const int64_t row0 = w.row_begin + (int64_t)t * w.stride;
                 if (valid) {
                     // adopt the best threshold any CTA working on this query has reached: a row below some
                     // CTA's kp-th best coarse score cannot be among the kp best overall
@@ -482,10 +516,10 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 for (int c = 0; c < BN / 32; c += 2) {
                     tmem_ld_wait();
                     tmem_ld32(tacc + (c + 1) * 32, vb);
-                    scan_chunk<EPL>(va, row0 + c * 32, p, buf, count, thr, slack, q, lane);
+                    scan_chunk<EPL>(va, row0 + c * 32, w.row_end, p, buf, count, thr, slack, q, lane);
                     tmem_ld_wait();
                     if (c + 2 < BN / 32) tmem_ld32(tacc + (c + 2) * 32, va);
-                    scan_chunk<EPL>(vb, row0 + (c + 1) * 32, p, buf, count, thr, slack, q, lane);
+                    scan_chunk<EPL>(vb, row0 + (c + 1) * 32, w.row_end, p, buf, count, thr, slack, q, lane);
                 }
                 tc_fence_before();
                 __syncwarp();
@@ -529,7 +563,17 @@ struct SelectParams {
     int32_t* fb_list; int32_t* fb_count;     // queries that failed certification, for the exact fallback
     const u32* gthr;                         // [n_queries] best threshold any CTA reached (lower bound of the kp-th best)
     int metric;                              // LZ_COSINE, or LZ_L2 (coarse key = x.q - |x|^2/2 = -(d - |q|^2)/2)
+    // grouped (two-level) mode, probe != null: a query's candidates sit in the items of its probed shards
+    const int64_t* probe;                    // [n_queries][nprobe] shard of each probe (-1 = none)
+    const int32_t* pair_row;                 // [n_queries][nprobe] the pair's row in the permuted query array
+    const int32_t* item_base;                // [n_shards] first item of a shard
+    const int32_t* qt_base;                  // [n_shards] first permuted q-tile of a shard
+    const int32_t* nsl;                      // [n_shards] row slices (items) per q-tile of a shard
+    const int64_t* shard_off;                // [n_shards + 1]
+    int nprobe, n_shards;
 };
+
+constexpr int kMaxSlices = 1024;             // candidate sources (slices) per query the exact pass can index
 
 __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -554,11 +598,55 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
     // round are independent (a slice-by-slice loop is one dependent round trip per slice).
     __shared__ float s_tw[kSelThreads / 32];
     __shared__ int s_nw[kSelThreads / 32];
+    __shared__ int s_ps[kSelThreads / 32];
+    __shared__ int s_slot[kMaxSlices];        // the (item, lane) slots that hold this query's candidates
+    __shared__ int s_off[kMaxSlices + 1];
+    __shared__ int s_nsrc;
+    // 0. where this query's candidates are: flat mode — slot (slice, q-tile, lane) of every slice; grouped mode — the
+    // items of the probed shards (slices of that shard for the q-tile the pair was placed in), laid end to end
+    if (p.probe != nullptr) {
+        const int per = (p.nprobe + kSelThreads - 1) / kSelThreads;
+        const int j0 = min(p.nprobe, tid * per), j1 = min(p.nprobe, j0 + per);
+        int mine = 0;
+        for (int j = j0; j < j1; ++j) {
+            const int64_t sh = p.probe[(size_t)q * p.nprobe + j];
+            mine += sh >= 0 ? p.nsl[sh] : 0;
+        }
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_ps[warp] = incl;
+        __syncthreads();
+        int run = incl - mine;
+#pragma unroll
+        for (int w = 0; w < kSelThreads / 32; ++w) if (w < warp) run += s_ps[w];
+        for (int j = j0; j < j1; ++j) {
+            const int64_t sh = p.probe[(size_t)q * p.nprobe + j];
+            if (sh < 0) continue;
+            const int pr = p.pair_row[(size_t)q * p.nprobe + j];
+            const int n = p.nsl[sh];
+            const int first = p.item_base[sh] + (pr / BM - p.qt_base[sh]) * n;
+            for (int i = 0; i < n; ++i)
+                if (run + i < kMaxSlices) s_slot[run + i] = (first + i) * BM + pr % BM;
+            run += n;
+        }
+        if (tid == kSelThreads - 1) s_nsrc = min(run, kMaxSlices);     // the host sized the items so that this fits
+        __syncthreads();
+    } else {
+        for (int sl = tid; sl < min(p.n_slices, kMaxSlices); sl += kSelThreads)
+            s_slot[sl] = (int)(((size_t)sl * p.n_qtiles_pad + qt) * BM + ql);
+        if (tid == 0) s_nsrc = p.n_slices;
+        __syncthreads();
+    }
+    const int n_src = s_nsrc;
     {
         float t_loc = -INFINITY;
         int n_loc = 0;
-        for (int sl = tid; sl < p.n_slices; sl += kSelThreads) {
-            const size_t slot = ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
+        for (int sl = tid; sl < n_src; sl += kSelThreads) {
+            const size_t slot = n_src <= kMaxSlices ? (size_t)s_slot[sl] : ((size_t)sl * p.n_qtiles_pad + qt) * BM + ql;
             t_loc = fmaxf(t_loc, p.cand_thr[slot]);
             n_loc += p.cand_cnt[slot];
         }
@@ -574,17 +662,15 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
     int total = 0;
 #pragma unroll
     for (int w = 0; w < kSelThreads / 32; ++w) { T = fmaxf(T, s_tw[w]); total += s_nw[w]; }
-    constexpr int kMaxSlices = 1024;
-    __shared__ int s_off[kMaxSlices + 1];
-    if (p.n_slices <= kMaxSlices) {
+    if (n_src <= kMaxSlices) {
         // With shared thresholds most slices leave only a few entries: lay the slices' counts end to end (block
         // scan) and walk the ENTRIES, 512 per round — not the n_slices * kp slots, most of them empty, each of
         // which cost a dependent count-then-entry round trip.
-        const int per = (p.n_slices + kSelThreads - 1) / kSelThreads;
-        const int c0 = min(p.n_slices, tid * per), c1 = min(p.n_slices, c0 + per);
+        const int per = (n_src + kSelThreads - 1) / kSelThreads;
+        const int c0 = min(n_src, tid * per), c1 = min(n_src, c0 + per);
         int mine = 0;
         for (int sl = c0; sl < c1; ++sl) {
-            const int c = p.cand_cnt[((size_t)sl * p.n_qtiles_pad + qt) * BM + ql];
+            const int c = p.cand_cnt[s_slot[sl]];
             s_off[sl + 1] = c;
             mine += c;
         }
@@ -594,7 +680,7 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
             const int t = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += t;
         }
-        __shared__ int s_ps[kSelThreads / 32];
+        __syncthreads();                                   // s_ps may still be read by the source layout above
         if (lane == 31) s_ps[warp] = incl;
         __syncthreads();
         int run = incl - mine;
@@ -603,19 +689,18 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
         for (int sl = c0; sl < c1; ++sl) { const int c = s_off[sl + 1]; s_off[sl + 1] = run + c; run += c; }
         if (tid == 0) s_off[0] = 0;
         __syncthreads();
-        const int Q = s_off[p.n_slices];
+        const int Q = s_off[n_src];
         for (int base = 0; base < Q; base += 2 * kSelThreads) {
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int t = base + h * kSelThreads + tid;
                 if (t < Q) {
-                    int lo = 0, hi = p.n_slices - 1;                            // slice with s_off[sl] <= t < s_off[sl+1]
+                    int lo = 0, hi = n_src - 1;                                 // slice with s_off[sl] <= t < s_off[sl+1]
                     while (lo < hi) {
                         const int mid = (lo + hi + 1) >> 1;
                         if (s_off[mid] <= t) lo = mid; else hi = mid - 1;
                     }
-                    const size_t slot = ((size_t)lo * p.n_qtiles_pad + qt) * BM + ql;
-                    const u64 kk = p.cand[slot * p.cap + (t - s_off[lo])];
+                    const u64 kk = p.cand[(size_t)s_slot[lo] * p.cap + (t - s_off[lo])];
                     lz_sel_push(&sa, kk >> 32, 0xffffffffu - (u32)kk);
                 }
             }
@@ -643,6 +728,23 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
     lz_sel_compact<kSelThreads>(&sa);
     int m = min(sa.count, p.kp);
     if (total > p.kp && sa.count >= p.kp) T = fmaxf(T, unord32((u32)key_a[p.kp - 1]));
+    // Each surviving group's rows are eligible up to the end of ITS range: the scanned range (flat), or the shard the
+    // group lies in (grouped: a binary search of the shard offsets).  Kept in the upper half of the group's key word.
+    __syncthreads();
+    for (int j = tid; j < m; j += kSelThreads) {
+        u64 hi_row = (u64)p.row_hi;
+        if (p.probe != nullptr) {
+            int lo = 0, hi = p.n_shards - 1;                                    // shard with off[s] <= row < off[s+1]
+            const int64_t r = (int64_t)id_a[j];
+            while (lo < hi) {
+                const int mid = (lo + hi + 1) >> 1;
+                if (p.shard_off[mid] <= r) lo = mid; else hi = mid - 1;
+            }
+            hi_row = (u64)p.shard_off[lo + 1];
+        }
+        key_a[j] = (key_a[j] & 0xffffffffull) | (hi_row << 32);
+    }
+    __syncthreads();
     // Prune before rescoring: the k best groups lying wholly inside the range each hold an eligible row with
     // coarse >= c_k (the k-th such group's key), i.e. k rows with exact >= c_k - eps; a group whose best
     // coarse is below c_k - 2 eps holds only rows with exact < c_k - eps and cannot reach the top-k.
@@ -653,7 +755,7 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
         if (p.tags == nullptr) {
             int full = 0;
             for (int j = 0; j < m; ++j) {
-                if ((int64_t)id_a[j] + p.sub <= p.row_hi && ++full == p.k) {
+                if ((int64_t)id_a[j] + p.sub <= (int64_t)(key_a[j] >> 32) && ++full == p.k) {
                     const float cutoff = unord32((u32)key_a[j]) - 2.0f * (float)p.eps[q];
                     keep = j + 1;
                     while (keep < m && unord32((u32)key_a[keep]) >= cutoff) ++keep;
@@ -693,7 +795,7 @@ __global__ void __launch_bounds__(kSelThreads, 2) select_rescore_kernel(SelectPa
             for (int h = 0; h < kRow; ++h) {
                 const int pi = base + (it * kRow + h) * kW + warp;
                 row[h] = pi < n_pairs ? (int64_t)id_a[pi / p.sub] + pi % p.sub : -1;
-                bool ok = row[h] >= 0 && row[h] < p.row_hi;
+                bool ok = row[h] >= 0 && row[h] < (int64_t)(key_a[pi / p.sub] >> 32);
                 if (ok && p.tags) {
                     const int tg = p.tags[row[h]];
                     ok = tg >= 0 && (p.want_tag < 0 || tg == p.want_tag);
@@ -1155,6 +1257,134 @@ __global__ void __launch_bounds__(kSelThreads) seed_threshold_kernel(SelectParam
     if (tid == 0 && sa.count >= p.kp) gthr[q] = (u32)key_a[p.kp - 1];
 }
 
+// ---- two-level search: grouping the (query, probed shard) pairs by shard -----------------------------------------------
+// Level 1 leaves probe[q][j] = the j-th best shard of query q.  The member pass runs the same GEMM kernel over a work
+// list: the queries that probe shard s are copied next to each other into a PERMUTED query array (padded to whole
+// q-tiles of 128 per shard), and an item is (one such q-tile, one slice of the shard's rows).  Everything below is
+// built on the device, so the search never waits for the host.
+struct GroupParams {
+    const int64_t* probe; int n_queries, nprobe, n_shards;
+    const int64_t* shard_off;
+    int32_t* cnt;         // [n_shards] pairs per shard, then reused as the scatter cursor
+    int32_t* qt_base;     // [n_shards] first permuted q-tile of the shard
+    int32_t* n_qt;        // [n_shards]
+    int32_t* nsl;         // [n_shards] slices per q-tile
+    int32_t* item_base;   // [n_shards]
+    int32_t* pair_row;    // [n_queries * nprobe]
+    int32_t* qmap;        // [max_ptiles * BM], pre-set to -1
+    int64_t* range_lo;    // [n_queries * nprobe] the pair's row range (for the exact fallback)
+    int64_t* range_hi;
+    int4* items; int* n_items; int max_items, max_ptiles, grid, max_nsl;
+};
+
+__global__ void __launch_bounds__(256) group_count_kernel(GroupParams g) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= g.n_queries * g.nprobe) return;
+    const int64_t sh = g.probe[i];
+    const bool ok = sh >= 0 && sh < g.n_shards;
+    g.range_lo[i] = ok ? g.shard_off[sh] : 0;
+    g.range_hi[i] = ok ? g.shard_off[sh + 1] : 0;
+    if (ok) atomicAdd(&g.cnt[sh], 1);
+}
+
+// One CTA: per shard the number of q-tiles and row tiles, the tiles-per-item T that makes ~3 items per CTA of the GEMM
+// grid (and keeps a query's candidate sources within what the exact pass indexes), the prefix sums, the item list.
+__global__ void __launch_bounds__(1024) group_layout_kernel(GroupParams g) {
+    __shared__ long long s_red[32];
+    __shared__ int s_scan[2][32];
+    __shared__ int s_T;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int per = (g.n_shards + 1023) / 1024;
+    const int s0 = min(g.n_shards, tid * per), s1 = min(g.n_shards, s0 + per);
+    long long work = 0;
+    int max_rt = 0;
+    for (int s = s0; s < s1; ++s) {
+        const int nq = (g.cnt[s] + BM - 1) / BM;
+        const int rt = (int)((g.shard_off[s + 1] - g.shard_off[s] + BN - 1) / BN);
+        g.n_qt[s] = nq;
+        work += (long long)nq * rt;
+        if (nq > 0) max_rt = max(max_rt, rt);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        work += __shfl_xor_sync(0xffffffffu, work, o);
+        max_rt = max(max_rt, __shfl_xor_sync(0xffffffffu, max_rt, o));
+    }
+    if (lane == 0) { s_red[warp] = work; s_scan[0][warp] = max_rt; }
+    __syncthreads();
+    if (tid == 0) {
+        long long w = 0;
+        int mr = 0;
+        for (int i = 0; i < 32; ++i) { w += s_red[i]; mr = max(mr, s_scan[0][i]); }
+        long long T = (w + 3ll * g.grid - 1) / (3ll * g.grid);               // ~3 items per CTA
+        const long long t_min = (mr + g.max_nsl - 1) / g.max_nsl;            // at most max_nsl slices per q-tile
+        if (T < t_min) T = t_min;
+        if (T < 1) T = 1;
+        s_T = (int)T;
+    }
+    __syncthreads();
+    const int T = s_T;
+    int qt_sum = 0, it_sum = 0;
+    for (int s = s0; s < s1; ++s) {
+        const int rt = (int)((g.shard_off[s + 1] - g.shard_off[s] + BN - 1) / BN);
+        const int n = g.n_qt[s] > 0 ? (rt + T - 1) / T : 0;
+        g.nsl[s] = n;
+        qt_sum += g.n_qt[s];
+        it_sum += g.n_qt[s] * n;
+    }
+    int qi = qt_sum, ii = it_sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int a = __shfl_up_sync(0xffffffffu, qi, o), b = __shfl_up_sync(0xffffffffu, ii, o);
+        if (lane >= o) { qi += a; ii += b; }
+    }
+    __syncthreads();
+    if (lane == 31) { s_scan[0][warp] = qi; s_scan[1][warp] = ii; }
+    __syncthreads();
+    int q_run = qi - qt_sum, i_run = ii - it_sum;
+    for (int w = 0; w < warp; ++w) { q_run += s_scan[0][w]; i_run += s_scan[1][w]; }
+    for (int s = s0; s < s1; ++s) {
+        g.qt_base[s] = q_run;
+        g.item_base[s] = i_run;
+        const int64_t lo = g.shard_off[s], hi = g.shard_off[s + 1];
+        for (int qt = 0; qt < g.n_qt[s]; ++qt)
+            for (int sl = 0; sl < g.nsl[s]; ++sl) {
+                const int item = i_run + qt * g.nsl[s] + sl;
+                const int64_t rb = lo + (int64_t)sl * T * BN;
+                const int64_t re = min(hi, rb + (int64_t)T * BN);
+                if (item < g.max_items) g.items[item] = make_int4(q_run + qt, (int)rb, (int)re, s);
+            }
+        q_run += g.n_qt[s];
+        i_run += g.n_qt[s] * g.nsl[s];
+        g.cnt[s] = 0;                                                       // becomes the scatter cursor
+    }
+    if (tid == 1023) *g.n_items = min(i_run, g.max_items);                  // the last thread holds the totals
+}
+
+__global__ void __launch_bounds__(256) group_scatter_kernel(GroupParams g) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= g.n_queries * g.nprobe) return;
+    const int64_t sh = g.probe[i];
+    int row = -1;
+    if (sh >= 0 && sh < g.n_shards) {
+        row = g.qt_base[sh] * BM + atomicAdd(&g.cnt[sh], 1);
+        if (row < g.max_ptiles * BM) g.qmap[row] = i / g.nprobe; else row = -1;
+    }
+    g.pair_row[i] = row;
+}
+
+// one warp per row of the permuted query array: copy the real query's fp16 row (zeros for padding rows)
+__global__ void __launch_bounds__(256) group_gather_kernel(const __half* __restrict__ q16, int dim_s, const int32_t* __restrict__ qmap,
+                                                           int n_rows, __half* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const int r = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (r >= n_rows) return;
+    const int q = qmap[r];
+    const uint4* src = reinterpret_cast<const uint4*>(q16 + (size_t)(q < 0 ? 0 : q) * dim_s);
+    uint4* dst = reinterpret_cast<uint4*>(out + (size_t)r * dim_s);
+    for (int e = lane; e < dim_s / 8; e += 32) dst[e] = q >= 0 ? src[e] : make_uint4(0u, 0u, 0u, 0u);
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -1401,7 +1631,7 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
         CUtensorMap tq, tx;
         if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
         if (int rc = make_tmap(&tx, shadow, n_rows_total, dim_s, BN / pl.cs)) return rc;
-        GemmParams g;
+        GemmParams g = {};
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
         g.tiles_per_slice = pl.tiles_per_slice; g.n_tiles = pl.n_tiles; g.kblocks = (dim_s + BK - 1) / BK;
         g.cs = pl.cs; g.n_qgroups = pl.n_qgroups; g.tile_mul = 1;
@@ -1451,7 +1681,7 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
         LZ_CUDA(cudaMemsetAsync(s + L.cand_thr, 0xff, items * BM * 4, st));     // NaN: ignored by fmaxf
     }
 
-    SelectParams sp;
+    SelectParams sp = {};
     sp.rows = rows; sp.ld = ld; sp.dim = dim; sp.norms = norms; sp.queries = queries; sp.q_ld = q_ld; sp.eps = eps;
     sp.tags = tags; sp.want_tag = want_tag; sp.row_lo = row_lo; sp.row_hi = row_hi;
     sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
@@ -1477,4 +1707,192 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, nullptr, nullptr, tags ? gtag : nullptr, queries, q_ld,
                                 n_queries, 1, k, metric, pl.fb_chunks, id_base, s + L.fallback,
                                 L.total - L.fallback, out_ids, out_scores, out_counts, fb_list, fb_count, stream);
+}
+
+// ---- two-level search (north_star (1); the reference's level 1 is core/memory_system.py:464-470) ---------------------
+namespace {
+struct TwoLevelLayout {
+    size_t l1, probe_ids, probe_sc, probe_cnt, shard_i32, pair_row, qmap, range_lo, range_hi, items, n_items,
+           q16, qperm, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
+    int max_ptiles, max_items, kp, cap, grid, fb_cps, max_nsl;
+    size_t l1_bytes, fb_bytes;
+    bool l1_batched;
+};
+
+int two_level_layout(int n_shards, int n_queries, int k, int nprobe, int dim, TwoLevelLayout* L) {
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
+    const int64_t pairs = (int64_t)n_queries * nprobe;
+    L->grid = sms;
+    L->max_ptiles = (int)((pairs + BM - 1) / BM + (pairs < n_shards ? pairs : n_shards));
+    L->max_items = 3 * L->grid + L->max_ptiles;
+    L->max_nsl = kMaxSlices / nprobe < 1 ? 1 : kMaxSlices / nprobe;
+    L->kp = k <= 3 ? 32 : (k <= 16 ? 128 : (k <= 48 ? 256 : 512));
+    L->cap = 2 * L->kp;
+    L->l1_batched = nprobe <= LZ_BATCHED_MAX_K && n_queries >= 8;
+    L->l1_bytes = L->l1_batched ? lz_search_batched_scratch_bytes(n_shards, n_queries, nprobe, dim)
+                                : lz_search_exact_scratch_bytes(n_queries, nprobe, lz_search_exact_default_chunks(n_shards, (n_queries + 3) / 4));
+    L->fb_cps = (2 * sms) / nprobe < 1 ? 1 : (2 * sms) / nprobe;
+    L->fb_bytes = lz_search_exact_scratch_bytes(n_queries, k, nprobe * L->fb_cps);
+    L->l1 = take(L->l1_bytes);
+    L->probe_ids = take((size_t)pairs * 8);
+    L->probe_sc = take((size_t)pairs * 8);
+    L->probe_cnt = take((size_t)n_queries * 4);
+    L->shard_i32 = take((size_t)n_shards * 4 * 5);                 // cnt, qt_base, n_qt, nsl, item_base
+    L->pair_row = take((size_t)pairs * 4);
+    L->qmap = take((size_t)L->max_ptiles * BM * 4);
+    L->range_lo = take((size_t)pairs * 8);
+    L->range_hi = take((size_t)pairs * 8);
+    L->items = take((size_t)L->max_items * 16);
+    L->n_items = take(4);
+    L->q16 = take((size_t)n_queries * (dim + 8) * 2);
+    L->qperm = take((size_t)L->max_ptiles * BM * (dim + 8) * 2);
+    L->eps = take((size_t)n_queries * 8);
+    L->gtag = take((size_t)n_queries * 4);
+    L->gthr = take((size_t)n_queries * 4);
+    L->fb_list = take((size_t)n_queries * 4);
+    L->fb_count = take(4);
+    L->cand = take((size_t)L->max_items * BM * L->cap * 8);
+    L->cand_cnt = take((size_t)L->max_items * BM * 4);
+    L->cand_thr = take((size_t)L->max_items * BM * 4);
+    L->certified = take((size_t)n_queries * 4);
+    L->fallback = take(L->fb_bytes);
+    L->total = off;
+    return LZ_OK;
+}
+}  // namespace
+
+extern "C" size_t lz_search_two_level_scratch_bytes(int n_shards, int n_queries, int k, int nprobe, int dim) {
+    if (n_shards <= 0 || n_queries <= 0 || k <= 0 || nprobe <= 0) return 0;
+    if (nprobe > n_shards) nprobe = n_shards;
+    TwoLevelLayout L;
+    if (two_level_layout(n_shards, n_queries, k, nprobe, dim, &L)) return 0;
+    return L.total;
+}
+
+extern "C" int lz_search_two_level(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
+                                   int64_t n_rows_total, const int64_t* shard_offsets, int n_shards,
+                                   const void* cen_shadow, const float* centroids, int64_t cen_ld, const double* cen_norms,
+                                   double cen_det_row_err, const float* queries, int64_t q_ld, int n_queries, int k,
+                                   int nprobe, double margin_sigmas, int metric, double max_row_norm, double det_row_err,
+                                   int64_t id_base, void* scratch, size_t scratch_bytes, int64_t* out_ids,
+                                   double* out_scores, int32_t* out_counts, int32_t* out_certified, int64_t* out_probe,
+                                   void* stream) {
+    if (n_queries <= 0) return LZ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(shadow && rows && norms && shard_offsets && cen_shadow && centroids && cen_norms && queries && scratch &&
+               out_ids && out_scores && out_counts, "lz_search_two_level: NULL pointer");
+    LZ_REQUIRE(dim > 0 && dim % 8 == 0 && ld >= dim && ld % 4 == 0 && cen_ld >= dim && cen_ld % 4 == 0,
+               "lz_search_two_level: dim=%d must be a multiple of 8", dim);
+    LZ_REQUIRE(q_ld >= dim && q_ld % 4 == 0 && ((uintptr_t)queries & 15) == 0,
+               "lz_search_two_level: queries must be 16-byte aligned with q_ld >= dim, q_ld %% 4 == 0");
+    LZ_REQUIRE(k >= 1 && k <= LZ_BATCHED_MAX_K, "lz_search_two_level: k=%d outside 1..%d", k, LZ_BATCHED_MAX_K);
+    LZ_REQUIRE(n_shards >= 1 && nprobe >= 1 && nprobe <= LZ_MAX_K, "lz_search_two_level: n_shards=%d nprobe=%d", n_shards, nprobe);
+    LZ_REQUIRE(n_rows_total >= 0 && n_rows_total <= 0x7fffff00LL, "lz_search_two_level: bad row count %lld", (long long)n_rows_total);
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_two_level: unknown metric %d", metric);
+    LZ_REQUIRE(margin_sigmas > 0.0, "lz_search_two_level: margin_sigmas must be positive");
+    if (int rc = require_local_device_memory(shadow, "lz_search_two_level: shadow")) return rc;
+    if (nprobe > n_shards) nprobe = n_shards;
+    TwoLevelLayout L;
+    if (int rc = two_level_layout(n_shards, n_queries, k, nprobe, dim, &L)) return rc;
+    if (scratch_bytes < L.total) {
+        lz_set_error("lz_search_two_level: scratch has %zu bytes, needs %zu", scratch_bytes, L.total);
+        return LZ_ERR_SCRATCH;
+    }
+    unsigned char* s = (unsigned char*)scratch;
+    int64_t* probe = (int64_t*)(s + L.probe_ids);
+    const int dim_s = metric == LZ_L2 ? dim + 8 : dim;
+
+    // level 1: the nprobe best shards of every query by cosine against the shard centroids (memory_system.py:466-470)
+    if (L.l1_batched) {
+        if (int rc = lz_search_batched(cen_shadow, centroids, cen_ld, dim, cen_norms, nullptr, -1, n_shards, 0, n_shards, queries,
+                                       q_ld, n_queries, nprobe, margin_sigmas, LZ_COSINE, 0.0, cen_det_row_err, 0, s + L.l1,
+                                       L.l1_bytes, probe, (double*)(s + L.probe_sc), (int32_t*)(s + L.probe_cnt), nullptr, stream))
+            return rc;
+    } else {
+        const int gs = n_queries >= 4 ? 4 : (n_queries >= 2 ? 2 : 1);
+        if (int rc = lz_search_exact(centroids, cen_ld, dim, cen_norms, nullptr, 0, n_shards, nullptr, nullptr, nullptr, queries, q_ld,
+                                     n_queries, gs, nprobe, LZ_COSINE, lz_search_exact_default_chunks(n_shards, (n_queries + gs - 1) / gs),
+                                     0, s + L.l1, L.l1_bytes, probe, (double*)(s + L.probe_sc), (int32_t*)(s + L.probe_cnt), stream))
+            return rc;
+    }
+    if (out_probe) LZ_CUDA(cudaMemcpyAsync(out_probe, probe, (size_t)n_queries * nprobe * 8, cudaMemcpyDeviceToDevice, st));
+
+    // group the (query, shard) pairs by shard; build the permuted query array and the item list
+    GroupParams g;
+    g.probe = probe; g.n_queries = n_queries; g.nprobe = nprobe; g.n_shards = n_shards; g.shard_off = shard_offsets;
+    int32_t* si = (int32_t*)(s + L.shard_i32);
+    g.cnt = si; g.qt_base = si + n_shards; g.n_qt = si + 2 * (size_t)n_shards; g.nsl = si + 3 * (size_t)n_shards;
+    g.item_base = si + 4 * (size_t)n_shards;
+    g.pair_row = (int32_t*)(s + L.pair_row); g.qmap = (int32_t*)(s + L.qmap);
+    g.range_lo = (int64_t*)(s + L.range_lo); g.range_hi = (int64_t*)(s + L.range_hi);
+    g.items = (int4*)(s + L.items); g.n_items = (int*)(s + L.n_items);
+    g.max_items = L.max_items; g.max_ptiles = L.max_ptiles; g.grid = L.grid; g.max_nsl = L.max_nsl;
+    const int pairs = n_queries * nprobe;
+    LZ_CUDA(cudaMemsetAsync(g.cnt, 0, (size_t)n_shards * 4, st));
+    LZ_CUDA(cudaMemsetAsync(g.qmap, 0xff, (size_t)L.max_ptiles * BM * 4, st));
+    group_count_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(g);
+    group_layout_kernel<<<1, 1024, 0, st>>>(g);
+    group_scatter_kernel<<<(pairs + 255) / 256, 256, 0, st>>>(g);
+    LZ_CUDA(cudaGetLastError());
+
+    __half* q16 = (__half*)(s + L.q16);
+    __half* qperm = (__half*)(s + L.qperm);
+    double* eps = (double*)(s + L.eps);
+    u32* gthr = (u32*)(s + L.gthr);
+    int32_t* fb_list = (int32_t*)(s + L.fb_list);
+    int32_t* fb_count = (int32_t*)(s + L.fb_count);
+    int32_t* cert = out_certified ? out_certified : (int32_t*)(s + L.certified);
+    queries_to_shadow_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, (int32_t*)(s + L.gtag),
+                                                                  gthr, fb_count, -1, margin_sigmas, metric, max_row_norm, det_row_err);
+    const int perm_rows = L.max_ptiles * BM;
+    group_gather_kernel<<<(perm_rows + 7) / 8, 256, 0, st>>>(q16, dim_s, g.qmap, perm_rows, qperm);
+    LZ_CUDA(cudaGetLastError());
+
+    // level 2: the member rows of the probed shards — the same tcgen05 GEMM + candidate epilogue, over the item list
+    CUtensorMap tq, tx;
+    if (int rc = make_tmap(&tq, qperm, perm_rows, dim_s, BM)) return rc;
+    if (int rc = make_tmap(&tx, shadow, n_rows_total, dim_s, BN)) return rc;
+    GemmParams gp = {};
+    gp.n_queries = n_queries; gp.kblocks = (dim_s + BK - 1) / BK; gp.cs = 1; gp.n_qgroups = 1; gp.tile_mul = 1;
+    gp.kp = L.kp; gp.cap = L.cap; gp.tags = nullptr; gp.want_tag = -1; gp.gthr = gthr; gp.top1_eps = nullptr;
+    gp.cand = (u64*)(s + L.cand); gp.cand_cnt = (int32_t*)(s + L.cand_cnt); gp.cand_thr = (float*)(s + L.cand_thr);
+    gp.items = g.items; gp.n_items_dev = g.n_items; gp.qmap = g.qmap;
+    auto kern = L.kp == 32 ? gemm_topk_kernel<2> : L.kp == 128 ? gemm_topk_kernel<8>
+                : L.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>;
+    LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGemmSmem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)L.grid);
+    cfg.blockDim = dim3(kGemmThreads);
+    cfg.dynamicSmemBytes = kGemmSmem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, gp));
+
+    SelectParams sp = {};
+    sp.rows = rows; sp.ld = ld; sp.dim = dim; sp.norms = norms; sp.queries = queries; sp.q_ld = q_ld; sp.eps = eps;
+    sp.tags = nullptr; sp.want_tag = -1; sp.row_lo = 0; sp.row_hi = n_rows_total;
+    sp.cand = gp.cand; sp.cand_cnt = gp.cand_cnt; sp.cand_thr = gp.cand_thr;
+    sp.n_qtiles_pad = 0; sp.n_slices = 0; sp.kp = L.kp; sp.cap = L.cap; sp.k = k;
+    sp.cap_a = lz_next_pow2(2 * L.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
+    sp.id_base = id_base; sp.sub = kSub;
+    sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
+    sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
+    sp.probe = probe; sp.pair_row = g.pair_row; sp.item_base = g.item_base; sp.qt_base = g.qt_base; sp.nsl = g.nsl;
+    sp.shard_off = shard_offsets; sp.nprobe = nprobe; sp.n_shards = n_shards;
+    const size_t ssmem = (size_t)(sp.cap_a + sp.cap_b) * 12;
+    LZ_CUDA(cudaFuncSetAttribute(select_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssmem));
+    select_rescore_kernel<<<n_queries, kSelThreads, ssmem, st>>>(sp);
+    LZ_CUDA(cudaGetLastError());
+
+    // queries that could not be certified: exact float64 scan of exactly their probed shards (a no-op launch when none)
+    return lz_search_exact_impl(rows, ld, dim, norms, nullptr, 0, n_rows_total, g.range_lo, g.range_hi, nullptr, queries, q_ld,
+                                n_queries, 1, k, metric, nprobe * L.fb_cps, id_base, s + L.fallback, L.fb_bytes, out_ids, out_scores,
+                                out_counts, fb_list, fb_count, stream, nprobe);
 }

@@ -50,6 +50,8 @@ struct ScanParams {
     u64* part_key; u32* part_id; int32_t* part_cnt;
     const int32_t* work_list;   // optional: indices of the queries to answer (group_size 1); others untouched
     const int32_t* work_count;  // device count of work_list entries
+    int n_ranges;               // > 1: group g scans the n_ranges ranges [group_lo[g*n_ranges + j], group_hi[...]) (the probed
+                                // shards of a two-level search); n_chunks is a multiple of n_ranges, chunk c works on range c / per
 };
 
 template <int QB, int METRIC>
@@ -90,12 +92,14 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
     }
     __syncthreads();
 
-    int64_t lo = p.group_lo ? p.group_lo[g] : p.row_lo;
-    int64_t hi = p.group_hi ? p.group_hi[g] : p.row_hi;
+    const int per_range = p.n_ranges > 1 ? p.n_chunks / p.n_ranges : p.n_chunks;       // chunks that share one range
+    const size_t ri = p.n_ranges > 1 ? (size_t)g * p.n_ranges + c / per_range : (size_t)g;
+    int64_t lo = p.group_lo ? p.group_lo[ri] : p.row_lo;
+    int64_t hi = p.group_hi ? p.group_hi[ri] : p.row_hi;
     if (hi < lo) hi = lo;
     const int want_tag = p.group_tag ? p.group_tag[g] : -1;
-    const int64_t len = (hi - lo + p.n_chunks - 1) / p.n_chunks;
-    const int64_t cta_lo = lo + (int64_t)c * len;
+    const int64_t len = (hi - lo + per_range - 1) / per_range;
+    const int64_t cta_lo = lo + (int64_t)(c % per_range) * len;
     const int64_t cta_hi = min(hi, cta_lo + len);
 
     for (int64_t base = cta_lo; base < cta_hi; base += kChunkRows) {
@@ -488,9 +492,11 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
                          const int32_t* group_tag, const float* queries, int64_t q_ld, int n_queries,
                          int group_size, int k, int metric, int n_chunks, int64_t id_base, void* scratch,
                          size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
-                         const int32_t* work_list, const int32_t* work_count, void* stream) {
+                         const int32_t* work_list, const int32_t* work_count, void* stream, int n_ranges) {
     if (n_queries <= 0) return LZ_OK;
     if (int rc = check_rows("lz_search_exact", rows, ld, dim)) return rc;
+    LZ_REQUIRE(n_ranges >= 1 && (n_ranges == 1 || (group_lo != nullptr && n_chunks % n_ranges == 0)),
+               "lz_search_exact: n_ranges=%d needs per-group ranges and n_chunks (%d) a multiple of it", n_ranges, n_chunks);
     LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_exact: unknown metric %d", metric);
     LZ_REQUIRE(metric == LZ_L2 || norms != nullptr, "lz_search_exact: cosine needs norms");
     LZ_REQUIRE(k >= 1 && k <= LZ_MAX_K, "lz_search_exact: k=%d outside 1..%d", k, LZ_MAX_K);
@@ -516,7 +522,7 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     p.row_lo = row_lo; p.row_hi = row_hi; p.group_lo = group_lo; p.group_hi = group_hi; p.group_tag = group_tag;
     p.queries = queries; p.q_ld = q_ld; p.n_queries = n_queries;
     p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows);
-    p.work_list = work_list; p.work_count = work_count;
+    p.work_list = work_list; p.work_count = work_count; p.n_ranges = n_ranges;
     unsigned char* s = (unsigned char*)scratch;
     p.part_key = (u64*)s;
     p.part_id = (u32*)(s + slots * k * sizeof(u64));
@@ -550,7 +556,18 @@ extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const dou
                                void* stream) {
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, group_lo, group_hi, group_tag, queries,
                                 q_ld, n_queries, group_size, k, metric, n_chunks, id_base, scratch, scratch_bytes,
-                                out_ids, out_scores, out_counts, nullptr, nullptr, stream);
+                                out_ids, out_scores, out_counts, nullptr, nullptr, stream, 1);
+}
+
+extern "C" int lz_search_exact_ranges(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
+                                      const int64_t* range_lo, const int64_t* range_hi, int n_ranges, int64_t n_rows_total,
+                                      const float* queries, int64_t q_ld, int n_queries, int k, int metric,
+                                      int chunks_per_range, int64_t id_base, void* scratch, size_t scratch_bytes,
+                                      int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream) {
+    LZ_REQUIRE(n_ranges >= 1 && chunks_per_range >= 1 && range_lo && range_hi, "lz_search_exact_ranges: bad ranges");
+    return lz_search_exact_impl(rows, ld, dim, norms, tags, 0, n_rows_total, range_lo, range_hi, nullptr, queries,
+                                q_ld, n_queries, 1, k, metric, n_ranges * chunks_per_range, id_base, scratch, scratch_bytes,
+                                out_ids, out_scores, out_counts, nullptr, nullptr, stream, n_ranges);
 }
 
 extern "C" int lz_merge_topk(const int64_t* in_ids, const double* in_scores, int n_lists, int n_queries, int k,

@@ -212,6 +212,67 @@ def search_batched(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: to
     return ids, scores, counts, cert
 
 
+def search_exact_ranges(rows: torch.Tensor, dim: int, norms: Optional[torch.Tensor], queries: torch.Tensor,
+                        range_lo: torch.Tensor, range_hi: torch.Tensor, k: int, metric: int = _lib.COSINE,
+                        n_rows_total: Optional[int] = None, chunks_per_range: Optional[int] = None, id_base: int = 0):
+    """Exact float64 top-k of query q over the union of the row ranges [range_lo[q, j], range_hi[q, j]) (int64 [B, R] on the
+    device) — lz_search_exact_ranges.  Returns (ids, scores, counts)."""
+    dev = _dev(rows)
+    assert range_lo.dtype == torch.int64 and range_hi.dtype == torch.int64 and range_lo.is_contiguous() and range_hi.is_contiguous()
+    B, R = range_lo.shape
+    assert queries.shape[0] == B and queries.dtype == torch.float32 and queries.stride(1) == 1
+    lib = _lib.load()
+    n_total = rows.shape[0] if n_rows_total is None else n_rows_total
+    with torch.cuda.device(dev):
+        if chunks_per_range is None:
+            sms = torch.cuda.get_device_properties(dev).multi_processor_count
+            chunks_per_range = max(1, (2 * sms) // max(1, B * R))
+        need = int(lib.lz_search_exact_scratch_bytes(B, k, R * chunks_per_range))
+        scratch = torch.empty(max(need, 16), dtype=torch.uint8, device=dev)
+        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+        scores = torch.empty((B, k), dtype=torch.float64, device=dev)
+        counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        check(lib.lz_search_exact_ranges(ptr(rows), rows.stride(0), dim, ptr(norms), None, ptr(range_lo), ptr(range_hi), R,
+                                         int(n_total), ptr(queries), queries.stride(0), B, k, int(metric), int(chunks_per_range),
+                                         int(id_base), ptr(scratch), scratch.numel(), ptr(ids), ptr(scores), ptr(counts),
+                                         stream_ptr(dev)), "lz_search_exact_ranges")
+    return ids, scores, counts
+
+
+def search_two_level(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: torch.Tensor, n_rows_total: int,
+                     shard_offsets: torch.Tensor, cen_shadow: torch.Tensor, centroids: torch.Tensor, cen_norms: torch.Tensor,
+                     queries: torch.Tensor, k: int, nprobe: int, metric: int = _lib.COSINE, margin_sigmas: float = 4.0,
+                     max_row_norm: float = 0.0, det_row_err: Optional[float] = None, cen_det_row_err: Optional[float] = None,
+                     id_base: int = 0, scratch: Optional[torch.Tensor] = None, want_probe: bool = False):
+    """Two-level search on the tensor cores (lz_search_two_level): centroid routing, then the member rows of the nprobe
+    best shards per query.  Returns (ids int64 [B,k], scores float64 [B,k], counts int32 [B], certified int32 [B],
+    probe int64 [B,nprobe] or None)."""
+    dev = _dev(rows)
+    assert shadow.dtype == torch.float16 and cen_shadow.dtype == torch.float16 and shard_offsets.dtype == torch.int64
+    assert centroids.dtype == torch.float32 and centroids.stride(1) == 1 and cen_norms.dtype == torch.float64
+    assert queries.dtype == torch.float32 and queries.stride(1) == 1 and rows.stride(1) == 1
+    B, S = queries.shape[0], shard_offsets.numel() - 1
+    P = max(1, min(int(nprobe), S))
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        need = int(lib.lz_search_two_level_scratch_bytes(S, B, k, P, dim))
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+        scores = torch.empty((B, k), dtype=torch.float64, device=dev)
+        counts = torch.empty((B,), dtype=torch.int32, device=dev)
+        cert = torch.empty((B,), dtype=torch.int32, device=dev)
+        probe = torch.empty((B, P), dtype=torch.int64, device=dev) if want_probe else None
+        check(lib.lz_search_two_level(ptr(shadow), ptr(rows), rows.stride(0), dim, ptr(norms), int(n_rows_total), ptr(shard_offsets), S,
+                                      ptr(cen_shadow), ptr(centroids), centroids.stride(0), ptr(cen_norms),
+                                      -1.0 if cen_det_row_err is None else float(cen_det_row_err),
+                                      ptr(queries), queries.stride(0), B, k, P, float(margin_sigmas), int(metric), float(max_row_norm),
+                                      -1.0 if det_row_err is None else float(det_row_err), int(id_base),
+                                      ptr(scratch), scratch.numel(), ptr(ids), ptr(scores), ptr(counts), ptr(cert), ptr(probe),
+                                      stream_ptr(dev)), "lz_search_two_level")
+    return ids, scores, counts, cert, probe, scratch
+
+
 def segment_mean(rows: torch.Tensor, dim: int, seg_offsets: torch.Tensor, order: Optional[torch.Tensor] = None) -> torch.Tensor:
     """float64 [n_segments, dim] means of row groups (lz_segment_mean)."""
     dev = _dev(rows)

@@ -580,35 +580,61 @@ class B200Store:
     def set_shards(self, shard_offsets: Sequence[int]):
         """Declare the semantic-shard layout of the rows: shard s is the contiguous row range
         shard_offsets[s]:shard_offsets[s+1] (rows are stored shard by shard).  Computes one centroid per
-        shard = mean of its member rows (memory_system.py:916-917) for the two-level search."""
+        shard = mean of its member rows (memory_system.py:916-917) and the centroid table's norms and fp16 shadow
+        for the two-level search."""
         with self._lock:
             off = torch.as_tensor(np.asarray(shard_offsets, dtype=np.int64)).to(self.device)
             assert int(off[-1]) <= self._n and int(off[0]) >= 0
             cen = kernels.segment_mean(self._rows, self._dim_p, off).to(torch.float32).contiguous()
             self._shard_off, self._shard_off_host = off, np.asarray(shard_offsets, dtype=np.int64)
             self._centroids, self._centroid_norms = cen, kernels.row_norms(cen)
+            err = torch.empty(cen.shape[0], dtype=torch.float32, device=self.device)
+            self._centroid_shadow = kernels.rows_to_shadow(cen, self._dim_p, self._centroid_norms, row_err=err)
+            self._centroid_err = float(err.max().item())
+            self._tl_scratch = None
+
+    def search_two_level_device(self, queries: torch.Tensor, k: int, nprobe: Optional[int] = None, margin: Optional[str] = None,
+                                want_probe: bool = False):
+        """Two-level search, device in / device out, nothing synchronised: queries float32 [B, dim_p] ->
+        (ids, scores, counts[, probe]).  Level 1 always ranks the shards by cosine against their centroids
+        (memory_system.py:466-470); level 2 ranks the member rows of the `nprobe` best shards by the store's metric.
+        Batches take the tensor-core path (lz_search_two_level: centroid GEMM, then a grouped member GEMM over the
+        probed shards); fewer than 8 queries take the exact float64 kernels (centroid scan, then ONE multi-range member
+        scan, lz_search_exact_ranges).  Both return the exact top-k over the union of the probed shards."""
+        S = int(self._centroids.shape[0])
+        P = S if nprobe is None else max(1, min(int(nprobe), S))
+        B = queries.shape[0]
+        if self._takes_batched_path(B, k, self._n):
+            sh = self._shadow_for(self._metric)
+            worst = self._check_margin(margin or self.margin) == "worst_case"
+            ids, sc, cnt, cert, probe, self._tl_scratch = kernels.search_two_level(
+                sh.t, self._rows, self._dim_p, self._norms, self._n, self._shard_off, self._centroid_shadow, self._centroids,
+                self._centroid_norms, queries, k, P, metric=self._metric, margin_sigmas=self.margin_sigmas,
+                max_row_norm=sh.max_norm, det_row_err=sh.max_err if worst else None,
+                cen_det_row_err=self._centroid_err if worst else None, scratch=self._tl_scratch, want_probe=want_probe)
+            self.last_certified = cert
+        else:
+            probe, _, _ = kernels.search_exact(self._centroids, self._dim_p, self._centroid_norms, None, queries, P, _lib.COSINE)
+            pc = probe.clamp(min=0)
+            lo = torch.where(probe >= 0, self._shard_off[:-1][pc], torch.zeros_like(probe)).contiguous()
+            hi = torch.where(probe >= 0, self._shard_off[1:][pc], torch.zeros_like(probe)).contiguous()
+            ids, sc, cnt = kernels.search_exact_ranges(self._rows, self._dim_p, self._norms, queries, lo, hi, k, self._metric,
+                                                       n_rows_total=self._n)
+        return (ids, sc, cnt, probe) if want_probe else (ids, sc, cnt)
 
     def search_two_level(self, queries, limit: int = 5, nprobe: Optional[int] = None, return_rows: bool = False):
         """Two-level cosine search (north_star (1); the reference's level 1 is memory_system.py:464-470):
         score the queries against the shard centroids, then search only the `nprobe` best shards' member
-        rows and merge.  nprobe = None or >= the number of shards visits every shard and equals the flat
+        rows.  nprobe = None or >= the number of shards visits every shard and equals the flat
         search (the parity mode); smaller nprobe is approximate — callers report recall."""
         with self._lock:
+            if len(self._user_names) != 1 or self._live[0] != self._n:
+                raise RuntimeError("two-level search serves single-tenant stores without deleted rows")
             q = np.ascontiguousarray(queries, dtype=np.float32)
             qd = self._to_device(q)
-            B, S = q.shape[0], self._centroids.shape[0]
-            p = S if nprobe is None else max(1, min(int(nprobe), S))
+            B = q.shape[0]
             k = self._check_limit(limit, 0)
-            probe, _, _ = kernels.search_exact(self._centroids, self._dim_p, self._centroid_norms, None, qd, p, _lib.COSINE)
-            lo = self._shard_off[:-1][probe.clamp(min=0)].T.contiguous().reshape(-1)       # [p*B] list-major
-            hi = self._shard_off[1:][probe.clamp(min=0)].T.contiguous().reshape(-1)
-            vq = qd.repeat(p, 1)
-            n_chunks = kernels.default_chunks(int((self._shard_off_host[1:] - self._shard_off_host[:-1]).max()), p * B, self.device)
-            tag = torch.full((p * B,), -1, dtype=torch.int32, device=self.device)
-            ids, sc, cnt = kernels.search_exact(self._rows, self._dim_p, self._norms, self._tags, vq, k, self._metric,
-                                                row_range=(0, self._n), group_lo=lo, group_hi=hi, group_tag=tag,
-                                                group_size=1, n_chunks=n_chunks)
-            ids, sc, cnt = kernels.merge_topk(ids.view(p, B, k), sc.view(p, B, k), self._metric)
+            ids, sc, cnt = self.search_two_level_device(qd, k, nprobe)
             torch.cuda.current_stream(self.device).synchronize()
             if return_rows:
                 return ids, sc, cnt

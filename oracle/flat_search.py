@@ -145,3 +145,31 @@ def fast_topk_f32(rows: np.ndarray, queries: np.ndarray, k: int, metric: str = "
             best_s, best_i = np.take_along_axis(best_s, o, 1), np.take_along_axis(best_i, o, 1)
     o = np.argsort(-best_s, axis=1, kind="stable")[:, :k]
     return np.take_along_axis(best_i, o, 1), np.take_along_axis(best_s, o, 1)
+
+
+def two_level_topk(rows, shard_offsets, queries, k, nprobe, metric="cosine"):
+    """Two-level search, restated exactly (north_star (1); level 1 = core/memory_system.py:464-470):
+    centroid of a shard = float64 mean of its float32 member rows (memory_system.py:916-917), kept as float32;
+    level 1 ranks the shards by cosine(query, centroid), best first, ties by lower shard index, and keeps `nprobe`;
+    level 2 is the exhaustive top-k (`metric`, ties by row index) over the rows of exactly those shards.
+    Returns (ids [B,k] int64 padded with -1, scores [B,k] float64, probed shards [B,nprobe] int64)."""
+    rows = np.ascontiguousarray(rows, dtype=np.float32)
+    off = np.asarray(shard_offsets, dtype=np.int64)
+    S = off.size - 1
+    cen = np.stack([rows[off[s]:off[s + 1]].astype(np.float64).mean(axis=0) if off[s + 1] > off[s] else np.zeros(rows.shape[1])
+                    for s in range(S)]).astype(np.float32)
+    queries = np.atleast_2d(np.asarray(queries, dtype=np.float32))
+    p = min(nprobe, S)
+    ids = np.full((queries.shape[0], k), -1, dtype=np.int64)
+    sc = np.full((queries.shape[0], k), np.nan, dtype=np.float64)
+    probes = np.full((queries.shape[0], p), -1, dtype=np.int64)
+    for b, q in enumerate(queries):
+        ps, _ = flat_topk(cen, q, p, "cosine")
+        probes[b, :ps.size] = ps
+        mask = np.zeros(rows.shape[0], dtype=bool)
+        for s in ps:
+            mask[off[s]:off[s + 1]] = True
+        i, v = flat_topk(rows, q, k, metric, mask)
+        ids[b, :i.size] = i
+        sc[b, :v.size] = v
+    return ids, sc, probes
