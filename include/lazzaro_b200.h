@@ -190,6 +190,27 @@ int lz_search_two_level(const void* shadow, const float* rows, int64_t ld, int d
                         void* scratch, size_t scratch_bytes, int64_t* out_ids, double* out_scores, int32_t* out_counts,
                         int32_t* out_certified, int64_t* out_probe, void* stream);
 
+/* ---- shard (re)assignment: nearest centroid of every row (north_star (2); the reference has no k-means — its only
+ *      centroid arithmetic is the super-node mean of core/memory_system.py:916-917 — so the rule is fixed here:
+ *      argmax over the table of cosine(row, table row), ties to the LOWEST table index) --------------------------------
+ *
+ * The rows are the query side of the contraction, the (tiny) centroid table the scanned side: the same GEMM in its
+ * top-1 mode (candidates = single table rows within 3 eps of the running best), then every row is scored in float64
+ * against its surviving candidates from a per-CTA shared-memory cache of the table rows its block needs.
+ *   table_shadow / table / table_norms   centroid table [n_table, dim] (n_table <= 2048 for the cached kernel; larger tables
+ *                 take the generic top-1 path): lz_rows_to_shadow(LZ_COSINE), float32 rows, lz_row_norms
+ *   table_det_row_err   max row_err of table_shadow (deterministic margin) or < 0 (statistical, margin_sigmas)
+ *   row_shadow, row_err optional: the rows' OWN fp16 cosine shadow and rounding-error norms (a resident store already
+ *                 holds both) — the conversion pass over the rows is then skipped (needs table_det_row_err >= 0)
+ *   out_idx int64 [n_rows], out_cos float64 [n_rows], out_counts int32 [n_rows] (0 only when the table is empty or all
+ *   scores are NaN), out_certified optional int32 [n_rows].  Scratch: lz_assign_nearest_scratch_bytes(...). */
+size_t lz_assign_nearest_scratch_bytes(int n_table, int64_t n_rows, int dim, int have_row_shadow);
+int lz_assign_nearest(const void* table_shadow, const float* table, int64_t table_ld, int dim, const double* table_norms,
+                      int n_table, double table_det_row_err, const float* rows, int64_t ld, int64_t n_rows,
+                      const void* row_shadow, const float* row_err, double margin_sigmas, void* scratch,
+                      size_t scratch_bytes, int64_t* out_idx, double* out_cos, int32_t* out_counts,
+                      int32_t* out_certified, void* stream);
+
 /* Merge `n_lists` per-partition top-k lists per query into one (the all-gather merge of the
  * multi-GPU search; ids are global row ids).  in_ids int64 [n_lists, n_queries, k] (-1 = empty
  * slot), in_scores float64 same shape; outputs as lz_search_exact.  Uses no scratch. */
@@ -219,6 +240,14 @@ int lz_score_pairs(const float* rows, int64_t ld, int dim, const double* norms,
  *   seg_offsets  int64 [n_segments + 1];  out_means float64 [n_segments, dim] */
 int lz_segment_mean(const float* rows, int64_t ld, int dim, const int64_t* order, const int64_t* seg_offsets,
                     int n_segments, double* out_means, void* stream);
+
+/* Member lists of an assignment: a STABLE counting sort of the row indices 0..n-1 by labels[i] (int64, entries outside
+ * [0, n_labels) are left out), so that lz_segment_mean(order = out_order, seg_offsets = out_offsets) sums every centroid's
+ * members in ascending row order (deterministic).  n_labels <= 16384.  out_order int64 [n] (first out_offsets[n_labels]
+ * entries valid), out_offsets int64 [n_labels + 1].  No reference counterpart (the reference has no k-means). */
+size_t lz_group_by_label_scratch_bytes(int64_t n, int n_labels);
+int lz_group_by_label(const int64_t* labels, int64_t n, int n_labels, void* scratch, size_t scratch_bytes,
+                      int64_t* out_order, int64_t* out_offsets, void* stream);
 
 /* ---- biological decay and pruning (stands behind MemoryShard.apply_temporal_decay and
  *      MemoryShard.prune_weak_edges, core/memory_shard.py:64-84; fan-out core/buffer_graph.py:87-97) */

@@ -37,9 +37,13 @@ SIGNATURES = {
     "lz_search_two_level_scratch_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),
     "lz_search_two_level": (_i32, [_p, _p, _i64, _i32, _p, _i64, _p, _i32, _p, _p, _i64, _p, _f64, _p, _i64, _i32, _i32, _i32,
                                    _f64, _i32, _f64, _f64, _i64, _p, _sz, _p, _p, _p, _p, _p, _p]),
+    "lz_assign_nearest_scratch_bytes": (_sz, [_i32, _i64, _i32, _i32]),
+    "lz_assign_nearest": (_i32, [_p, _p, _i64, _i32, _p, _i32, _f64, _p, _i64, _i64, _p, _p, _f64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_merge_topk_strided": (_i32, [_p, _p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),
+    "lz_group_by_label_scratch_bytes": (_sz, [_i64, _i32]),
+    "lz_group_by_label": (_i32, [_p, _i64, _i32, _p, _sz, _p, _p, _p]),
     "lz_segment_mean": (_i32, [_p, _i64, _i32, _p, _p, _i32, _p, _p]),
     "lz_edge_decay_prune_scratch_bytes": (_sz, [_i64]),
     "lz_edge_decay_prune": (_i32, [_p, _p, _p, _p, _i64, _f64, _f64, _p, _p, _p, _p, _p, _p, _sz, _p]),

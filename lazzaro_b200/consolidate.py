@@ -91,40 +91,55 @@ def link_candidates(store, new_emb, user_id: str = "default", m: int = LINK_TOP,
         return out
 
 
+def _centroid_table(centroids: torch.Tensor, margin: str):
+    if margin not in ("worst_case", "statistical"):
+        raise ValueError(f"margin must be 'worst_case' or 'statistical', got {margin!r}")
+    cen = centroids.contiguous()
+    norms = kernels.row_norms(cen)
+    err = torch.empty(cen.shape[0], dtype=torch.float32, device=cen.device)
+    shadow = kernels.rows_to_shadow(cen, cen.shape[1], norms, row_err=err)
+    det = float(err.max().item()) if margin == "worst_case" else None       # K floats: a small read-back
+    return cen, norms, shadow, det
+
+
 def assign_to_centroids(rows: torch.Tensor, centroids: torch.Tensor, margin_sigmas: float = 4.0, margin: str = MARGIN):
     """argmax_c cosine(row, centroid_c) for float32 CUDA tensors rows [n, dim], centroids [K, dim]
     (dim % 8 == 0).  Returns (index int64 [n], cosine float64 [n]) on the device; ties go to the lowest
     centroid index.  Rows are the query side of the contraction, centroids the scanned side."""
     assert rows.is_cuda and centroids.is_cuda and rows.dtype == torch.float32 and centroids.dtype == torch.float32
     dim = rows.shape[1]
-    cen = centroids.contiguous()
-    norms = kernels.row_norms(cen)
     n = rows.shape[0]
     if n >= 8 and dim % 8 == 0:
-        err = torch.empty(cen.shape[0], dtype=torch.float32, device=cen.device)
-        shadow = kernels.rows_to_shadow(cen, dim, norms, row_err=err)
-        if margin not in ("worst_case", "statistical"):
-            raise ValueError(f"margin must be 'worst_case' or 'statistical', got {margin!r}")
-        det = float(err.max().item()) if margin == "worst_case" else None       # K floats: a small read-back
-        ids, sc, cnt, _ = kernels.search_batched(shadow, cen, dim, norms, None, -1, rows, 1, margin_sigmas=margin_sigmas,
-                                                 det_row_err=det)
-    else:
-        ids, sc, cnt = kernels.search_exact(cen, dim, norms, None, rows, 1, _lib.COSINE)
+        cen, norms, shadow, det = _centroid_table(centroids, margin)
+        idx, cos, _ = kernels.assign_nearest(shadow, cen, norms, rows, dim, table_det_row_err=det, margin_sigmas=margin_sigmas)
+        return idx, cos
+    cen = centroids.contiguous()
+    ids, sc, cnt = kernels.search_exact(cen, dim, kernels.row_norms(cen), None, rows, 1, _lib.COSINE)
     return ids[:, 0], sc[:, 0]
+
+
+def assign_store_rows(store, centroids: torch.Tensor, row_range: Optional[Tuple[int, int]] = None, margin_sigmas: float = 4.0):
+    """Shard reassignment of rows RESIDENT in a store: the same argmax, with the store's own fp16 cosine shadow and
+    per-row rounding-error norms as the query side, so no conversion pass over the rows is needed (deterministic
+    margin).  Returns (index int64 [n], cosine float64 [n]) for rows row_range (default: all rows)."""
+    with store._lock:
+        sh = store._shadow_for(_lib.COSINE)
+        lo, hi = (0, store.n_rows) if row_range is None else (int(row_range[0]), int(row_range[1]))
+        cen, norms, shadow, det = _centroid_table(centroids, "worst_case")
+        idx, cos, _ = kernels.assign_nearest(shadow, cen, norms, store._rows[lo:hi], store._dim_p, table_det_row_err=det,
+                                             row_shadow=sh.t[lo:hi], row_err=sh.err[lo:hi], margin_sigmas=margin_sigmas)
+        return idx, cos
 
 
 def centroid_means(rows: torch.Tensor, assign: Optional[torch.Tensor] = None, n_centroids: Optional[int] = None,
                    seg_offsets: Optional[torch.Tensor] = None) -> torch.Tensor:
     """float64 [K, dim] arithmetic means (memory_system.py:916-917).  Either `seg_offsets` (int64 [K+1],
     members of centroid c are the contiguous rows seg_offsets[c]:seg_offsets[c+1] — rows stored shard by
-    shard) or `assign` (int64 [n] centroid of each row).  With `assign`, member lists are formed by a
-    stable sort of the assignment (torch, index plumbing only); the summation is lz_segment_mean."""
+    shard) or `assign` (int64 [n] centroid of each row, n_centroids <= 16384).  With `assign`, the member lists come
+    from a stable counting sort on the device (lz_group_by_label); the summation is lz_segment_mean."""
     dim = rows.shape[1]
     if seg_offsets is not None:
         return kernels.segment_mean(rows, dim, seg_offsets.to(torch.int64))
     assert assign is not None and n_centroids is not None
-    order = torch.argsort(assign, stable=True)
-    counts = torch.bincount(assign, minlength=n_centroids)
-    seg = torch.zeros(n_centroids + 1, dtype=torch.int64, device=rows.device)
-    seg[1:] = torch.cumsum(counts, 0)
+    order, seg = kernels.group_by_label(assign.contiguous(), n_centroids)
     return kernels.segment_mean(rows, dim, seg, order)

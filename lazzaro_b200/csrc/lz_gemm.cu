@@ -1222,6 +1222,229 @@ __global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParam
     }
 }
 
+// Top-1 against a tiny table, any number of surviving candidates per query.  The kernel above handles queries with ONE
+// surviving row; everything else used to fall to a warp per query reading its candidate rows from L2 — as many bytes
+// again per candidate as the query itself, which made nearly coincident centroids (the normal k-means shape, k above
+// the number of clusters) 5-10x slower than separated ones.  Here a CTA takes kMultiQ consecutive queries, collects
+// every query's surviving rows (up to kMultiLive), stages the DISTINCT table rows the block needs in shared memory
+// (rows of one block mostly share their candidates: the store keeps rows shard by shard), and a warp then holds one
+// query in registers as float64 and scores it against each of its candidates from shared memory: the query is read
+// from HBM once, a candidate costs dim*4 bytes of shared-memory traffic.  When a block needs more distinct table rows
+// than fit, they are staged in rounds and a query is re-read in the rounds that hold some of its candidates.
+// Summation order per pair is the exact scan's, so scores are bit-identical to it.
+constexpr int kMultiQ = 1024;            // queries per CTA
+constexpr int kMultiLive = 16;           // surviving candidates kept per query (more: the direct path)
+constexpr int kMultiThreads = 512;
+constexpr int kMultiTable = kBucketGroups * kSub;     // table rows the bitmap covers (2048)
+
+template <int NSEG, int METRIC>
+__global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParams p, int n_queries, int cache_rows) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int kStride = NSEG * 128;                                                // floats per cached row, zero padded
+    float* s_rows = reinterpret_cast<float*>(smem);                                    // [cache_rows][kStride]
+    double* s_cnorm = reinterpret_cast<double*>(s_rows + (size_t)cache_rows * kStride); // [cache_rows]
+    u64* s_bkey = reinterpret_cast<u64*>(s_cnorm + cache_rows);                         // [kMultiQ] best exact key so far
+    float* s_T = reinterpret_cast<float*>(s_bkey + kMultiQ);                            // [kMultiQ]
+    u32* s_bid = reinterpret_cast<u32*>(s_T + kMultiQ);                                 // [kMultiQ]
+    unsigned short* s_list = reinterpret_cast<unsigned short*>(s_bid + kMultiQ);        // [kMultiQ][kMultiLive] table row - row_lo
+    signed char* s_nlive = reinterpret_cast<signed char*>(s_list + (size_t)kMultiQ * kMultiLive);   // [kMultiQ], -1 = direct path
+    __shared__ u32 s_bits[kMultiTable / 32];
+    __shared__ int s_pref[kMultiTable / 32 + 1];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kMultiThreads / 32;
+    const int q0 = blockIdx.x * kMultiQ;
+    const int nq = min(kMultiQ, n_queries - q0);
+    for (int i = tid; i < kMultiTable / 32; i += kMultiThreads) s_bits[i] = 0u;
+    __syncthreads();
+    // A. one thread per query: best coarse candidate, the rows within 2 eps of it, the block's bitmap of needed rows
+    for (int i = tid; i < nq; i += kMultiThreads) {
+        const int q = q0 + i;                                                 // n_slices == 1: slot == query
+        const int cnt = p.cand_cnt[q];
+        const u64* src = p.cand + (size_t)q * p.cap;
+        u64 best = 0ull;
+        for (int j = 0; j < cnt; ++j) {
+            const u64 kk = src[j];
+            best = kk > best ? kk : best;
+        }
+        int n_live = 0;
+        if (best != 0ull) {
+            const float cutoff = unord32((u32)(best >> 32)) - 2.0f * (float)p.eps[q];
+            for (int j = 0; j < cnt; ++j) {
+                const u64 kk = src[j];
+                if (unord32((u32)(kk >> 32)) >= cutoff) {
+                    const u32 rel = (0xffffffffu - (u32)kk) - (u32)p.row_lo;
+                    if (n_live < kMultiLive && rel < (u32)kMultiTable) s_list[i * kMultiLive + n_live] = (unsigned short)rel;
+                    else n_live = kMultiLive + 64;                            // too many (or out of the bitmap): direct path
+                    ++n_live;
+                }
+            }
+        }
+        if (n_live > kMultiLive) n_live = -1;
+        s_nlive[i] = (signed char)n_live;
+        for (int j = 0; j < n_live; ++j) {
+            const int rel = s_list[i * kMultiLive + j];
+            atomicOr(&s_bits[rel >> 5], 1u << (rel & 31));
+        }
+        s_T[i] = p.cand_thr[q];
+        s_bkey[i] = 0ull;
+        s_bid[i] = 0xffffffffu;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0;
+        for (int w = 0; w < kMultiTable / 32; ++w) { s_pref[w] = run; run += __popc(s_bits[w]); }
+        s_pref[kMultiTable / 32] = run;
+    }
+    __syncthreads();
+    const int n_distinct = s_pref[kMultiTable / 32];
+    const int n4 = p.dim / 4;
+    for (int r0 = 0; r0 < n_distinct; r0 += cache_rows) {
+        const int r1 = min(n_distinct, r0 + cache_rows);
+        __syncthreads();                                                       // the previous round's readers are done
+        // stage the table rows with rank [r0, r1): warp w takes slots w, w + kWarps, ...
+        for (int slot = warp; slot < r1 - r0; slot += kWarps) {
+            const int want = r0 + slot;                                        // rank of the row to fetch
+            int w = 0;                                                         // word with s_pref[w] <= want < s_pref[w+1]
+            {
+                int lo = 0, hi = kMultiTable / 32 - 1;
+                while (lo < hi) {
+                    const int mid = (lo + hi + 1) >> 1;
+                    if (s_pref[mid] <= want) lo = mid; else hi = mid - 1;
+                }
+                w = lo;
+            }
+            u32 bits = s_bits[w];
+            for (int skip = want - s_pref[w]; skip > 0; --skip) bits &= bits - 1;
+            const int rel = w * 32 + __ffs(bits) - 1;
+            const float* src = p.rows + (p.row_lo + rel) * p.ld;
+            for (int e = lane; e < kStride / 4; e += 32)
+                reinterpret_cast<float4*>(s_rows + (size_t)slot * kStride)[e] =
+                    e < n4 ? lz_ldg_stream(src + e * 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+            if (lane == 0) s_cnorm[slot] = METRIC == LZ_COSINE ? p.norms[p.row_lo + rel] : 0.0;
+        }
+        __syncthreads();
+        // every warp walks the block's queries; a query with candidates in this round is loaded once as float64
+        for (int i = warp; i < nq; i += kWarps) {
+            const int nl = s_nlive[i];
+            if (nl <= 0) continue;                                             // warp-uniform
+            int slots[kMultiLive];
+            int n_here = 0;
+#pragma unroll
+            for (int j = 0; j < kMultiLive; ++j) {
+                if (j < nl) {
+                    const int rel = s_list[i * kMultiLive + j];
+                    const int rank = s_pref[rel >> 5] + __popc(s_bits[rel >> 5] & ((1u << (rel & 31)) - 1u));
+                    if (rank >= r0 && rank < r1) slots[n_here++] = (rank - r0) | (rel << 16);
+                }
+            }
+            if (n_here == 0) continue;
+            const float* qp = p.queries + (int64_t)(q0 + i) * p.q_ld;
+            double qd[NSEG][4];
+            double qs = 0.0;
+#pragma unroll
+            for (int sg = 0; sg < NSEG; ++sg) {
+                const int e = lane * 4 + 128 * sg;
+                const float4 v = e < p.dim ? lz_ldg_stream(qp + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+                qd[sg][0] = v.x; qd[sg][1] = v.y; qd[sg][2] = v.z; qd[sg][3] = v.w;
+            }
+#pragma unroll
+            for (int sg = 0; sg < NSEG; ++sg)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) qs = fma(qd[sg][c], qd[sg][c], qs);
+            const double qn = sqrt(lz_warp_sum(qs));
+            u64 bkey = s_bkey[i];
+            u32 bid = s_bid[i];
+            // four candidates at a time: four independent accumulation chains (each in the exact scan's order) keep the
+            // float64 pipe busy; a lone chain of dim/32 dependent DFMAs per pair left the warp waiting on its own latency
+            constexpr int kAt = 4;
+            for (int j0 = 0; j0 < n_here; j0 += kAt) {
+                const float* xr[kAt];
+                int slot[kAt], rel[kAt];
+#pragma unroll
+                for (int c = 0; c < kAt; ++c) {
+                    const int sv = slots[min(j0 + c, n_here - 1)];
+                    slot[c] = sv & 0xffff;
+                    rel[c] = sv >> 16;
+                    xr[c] = s_rows + (size_t)slot[c] * kStride + lane * 4;
+                }
+                double acc[kAt];
+#pragma unroll
+                for (int c = 0; c < kAt; ++c) acc[c] = 0.0;
+#pragma unroll
+                for (int sg = 0; sg < NSEG; ++sg) {
+                    float4 x[kAt];
+#pragma unroll
+                    for (int c = 0; c < kAt; ++c) x[c] = *reinterpret_cast<const float4*>(xr[c] + 128 * sg);
+#pragma unroll
+                    for (int c = 0; c < kAt; ++c) {
+                        if (METRIC == LZ_COSINE) {
+                            acc[c] = fma((double)x[c].x, qd[sg][0], acc[c]); acc[c] = fma((double)x[c].y, qd[sg][1], acc[c]);
+                            acc[c] = fma((double)x[c].z, qd[sg][2], acc[c]); acc[c] = fma((double)x[c].w, qd[sg][3], acc[c]);
+                        } else {
+                            const double d0 = (double)x[c].x - qd[sg][0], d1 = (double)x[c].y - qd[sg][1];
+                            const double d2 = (double)x[c].z - qd[sg][2], d3 = (double)x[c].w - qd[sg][3];
+                            acc[c] = fma(d0, d0, acc[c]); acc[c] = fma(d1, d1, acc[c]);
+                            acc[c] = fma(d2, d2, acc[c]); acc[c] = fma(d3, d3, acc[c]);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+                    for (int c = 0; c < kAt; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+#pragma unroll
+                for (int c = 0; c < kAt; ++c) {
+                    if (j0 + c >= n_here) break;                               // warp-uniform
+                    double sc;
+                    if (METRIC == LZ_COSINE) {
+                        const double den = s_cnorm[slot[c]] * qn;
+                        sc = den > 0.0 ? acc[c] / den : 0.0;
+                        sc += 0.0;
+                    } else {
+                        sc = 0.0 - acc[c];
+                    }
+                    if (sc == sc) {
+                        const u64 key = lz_ord(sc);
+                        const u32 id = (u32)(p.row_lo + rel[c]);
+                        if (lz_better(key, id, bkey, bid)) { bkey = key; bid = id; }
+                    }
+                }
+            }
+            if (lane == 0) { s_bkey[i] = bkey; s_bid[i] = bid; }
+        }
+    }
+    __syncthreads();
+    // results + certification: every row dropped by the coarse pass had coarse <= T = c_1 - 3 eps
+    for (int i = tid; i < nq; i += kMultiThreads) {
+        if (s_nlive[i] < 0) continue;
+        const int q = q0 + i;
+        const bool has = s_bkey[i] != 0ull;
+        const double v = has ? lz_unord(s_bkey[i]) : 0.0;
+        p.out_ids[q] = has ? (int64_t)s_bid[i] + p.id_base : -1;
+        p.out_scores[q] = has ? (METRIC == LZ_COSINE ? v : 0.0 - v) : __longlong_as_double(0x7ff8000000000000ll);
+        p.out_counts[q] = has ? 1 : 0;
+        const float T = s_T[i];
+        bool cert = T == -INFINITY;
+        if (!cert && has) {
+            double e_coarse = v;
+            if (METRIC != LZ_COSINE) {                                          // -(d - |q|^2)/2 needs |q|^2
+                const float* qp = p.queries + (int64_t)q * p.q_ld;
+                double qq = 0.0;
+                for (int e = 0; e < p.dim; ++e) qq = fma((double)qp[e], (double)qp[e], qq);
+                e_coarse = 0.5 * (v + qq);
+            }
+            cert = e_coarse > (double)T + p.eps[q];
+        }
+        p.certified[q] = cert ? 1 : 0;
+        if (!cert) p.fb_list[atomicAdd(p.fb_count, 1)] = q;
+    }
+    __syncthreads();
+    for (int i = warp; i < nq; i += kWarps) {
+        if (s_nlive[i] >= 0) continue;                                        // warp-uniform
+        small_direct_call(p, q0 + i, lane);                                   // rare: more than kMultiLive survivors
+    }
+}
+
 // Threshold seeding: the coarse pass is first run over a strided sample of the rows tiles (64 tiles, one per
 // item, so nothing is compacted); here each query's kp-th best sampled group key becomes its starting
 // threshold.  The kp-th best of a subset can only be lower than the kp-th best of all groups, so the seed is
@@ -1515,12 +1738,12 @@ struct ScratchLayout {
     size_t q16, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
 };
 
-ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim) {
+ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim, bool with_q16 = true) {
     ScratchLayout L;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
     const size_t items = (size_t)pl.n_qgroups * pl.cs * (pl.n_slices > 64 ? pl.n_slices : 64);
-    L.q16 = take((size_t)n_queries * (dim + 8) * 2);
+    L.q16 = take(with_q16 ? (size_t)n_queries * (dim + 8) * 2 : 0);
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
     L.gthr = take((size_t)n_queries * 4);
@@ -1574,6 +1797,31 @@ extern "C" size_t lz_search_batched_scratch_bytes(int64_t n_rows, int n_queries,
     return layout(pl, n_queries, k, dim).total;
 }
 
+namespace {
+// eps[q] for queries whose fp16 shadow already exists (rows of a resident store used as the query side): the
+// deterministic margin from the row-side bound and the query's own measured rounding-error norm.
+__global__ void __launch_bounds__(256) queries_eps_kernel(const float* __restrict__ q_err, int n, int dim, double det_row_err,
+                                                          double* __restrict__ eps, int32_t* __restrict__ gtag, u32* __restrict__ gthr,
+                                                          int32_t* __restrict__ fb_count, int want_tag) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i == 0) *fb_count = 0;
+    if (i >= n) return;
+    const double dq = (double)q_err[i];
+    const double ev = det_row_err + dq + det_row_err * dq + (double)dim * 1.1920928955078125e-7 * 1.01 + 1e-9;
+    eps[i] = ev == ev ? ev : INFINITY;
+    gtag[i] = want_tag;
+    gthr[i] = 0u;
+}
+
+int search_batched_core(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
+                        const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
+                        int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
+                        double margin_sigmas, int metric, double max_row_norm, double det_row_err,
+                        int64_t id_base, void* scratch, size_t scratch_bytes,
+                        int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
+                        void* stream, const void* query_shadow, const float* query_err);
+}  // namespace
+
 extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
                                  const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
                                  int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
@@ -1581,6 +1829,40 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
                                  int64_t id_base, void* scratch, size_t scratch_bytes,
                                  int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                                  void* stream) {
+    return search_batched_core(shadow, rows, ld, dim, norms, tags, want_tag, n_rows_total, row_lo, row_hi, queries, q_ld,
+                               n_queries, k, margin_sigmas, metric, max_row_norm, det_row_err, id_base, scratch, scratch_bytes,
+                               out_ids, out_scores, out_counts, out_certified, stream, nullptr, nullptr);
+}
+
+extern "C" size_t lz_assign_nearest_scratch_bytes(int n_table, int64_t n_rows, int dim, int have_row_shadow) {
+    if (n_table <= 0 || n_rows <= 0 || n_rows > 0x7fffffffLL) return 0;
+    Plan pl;
+    if (make_plan(n_table, (int)n_rows, 1, &pl)) return 0;
+    return layout(pl, (int)n_rows, 1, dim, have_row_shadow == 0).total;
+}
+
+extern "C" int lz_assign_nearest(const void* table_shadow, const float* table, int64_t table_ld, int dim,
+                                 const double* table_norms, int n_table, double table_det_row_err,
+                                 const float* rows, int64_t ld, int64_t n_rows, const void* row_shadow, const float* row_err,
+                                 double margin_sigmas, void* scratch, size_t scratch_bytes, int64_t* out_idx,
+                                 double* out_cos, int32_t* out_counts, int32_t* out_certified, void* stream) {
+    LZ_REQUIRE(n_rows >= 0 && n_rows <= 0x7fffffffLL, "lz_assign_nearest: n_rows=%lld", (long long)n_rows);
+    LZ_REQUIRE((row_shadow == nullptr) == (row_err == nullptr), "lz_assign_nearest: row_shadow and row_err come together");
+    LZ_REQUIRE(row_shadow == nullptr || table_det_row_err >= 0.0,
+               "lz_assign_nearest: a resident row shadow needs the deterministic margin (table_det_row_err >= 0)");
+    return search_batched_core(table_shadow, table, table_ld, dim, table_norms, nullptr, -1, n_table, 0, n_table, rows, ld,
+                               (int)n_rows, 1, margin_sigmas, LZ_COSINE, 0.0, table_det_row_err, 0, scratch, scratch_bytes,
+                               out_idx, out_cos, out_counts, out_certified, stream, row_shadow, row_err);
+}
+
+namespace {
+int search_batched_core(const void* shadow, const float* rows, int64_t ld, int dim, const double* norms,
+                        const int32_t* tags, int want_tag, int64_t n_rows_total, int64_t row_lo,
+                        int64_t row_hi, const float* queries, int64_t q_ld, int n_queries, int k,
+                        double margin_sigmas, int metric, double max_row_norm, double det_row_err,
+                        int64_t id_base, void* scratch, size_t scratch_bytes,
+                        int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
+                        void* stream, const void* query_shadow, const float* query_err) {
     if (n_queries <= 0) return LZ_OK;
     cudaStream_t st = (cudaStream_t)stream;
     LZ_REQUIRE(shadow && rows && norms && queries && scratch && out_ids && out_scores && out_counts,
@@ -1601,7 +1883,7 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
     const int dim_s = metric == LZ_L2 ? dim + 8 : dim;         // columns of the shadow (and K of the contraction)
     Plan pl;
     if (int rc = make_plan(row_hi - row_lo, n_queries, k, &pl)) return rc;
-    const ScratchLayout L = layout(pl, n_queries, k, dim);
+    const ScratchLayout L = layout(pl, n_queries, k, dim, query_shadow == nullptr);
     if (scratch_bytes < L.total) {
         lz_set_error("lz_search_batched: scratch has %zu bytes, needs %zu", scratch_bytes, L.total);
         return LZ_ERR_SCRATCH;
@@ -1615,9 +1897,17 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
     u32* gthr = (u32*)(s + L.gthr);
     int32_t* fb_list = (int32_t*)(s + L.fb_list);
     int32_t* fb_count = (int32_t*)(s + L.fb_count);
-    queries_to_shadow_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
-                                                                fb_count, want_tag, margin_sigmas, metric, max_row_norm,
-                                                                det_row_err);
+    if (query_shadow != nullptr) {
+        // the query side already has its fp16 shadow (rows of a resident store): no conversion pass over the queries
+        if (int rc = require_local_device_memory(query_shadow, "lz_assign_nearest: row_shadow")) return rc;
+        q16 = (__half*)const_cast<void*>(query_shadow);
+        queries_eps_kernel<<<(n_queries + 255) / 256, 256, 0, st>>>(query_err, n_queries, dim, det_row_err, eps, gtag, gthr,
+                                                                    fb_count, want_tag);
+    } else {
+        queries_to_shadow_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
+                                                                    fb_count, want_tag, margin_sigmas, metric, max_row_norm,
+                                                                    det_row_err);
+    }
     LZ_CUDA(cudaGetLastError());
 
     // top-1 against a tiny table (shard reassignment): trailing threshold in the coarse pass, bucketed exact pass
@@ -1691,7 +1981,22 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
     sp.id_base = id_base; sp.sub = tiny_top1 ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
-    if (tiny_top1) {
+    if (tiny_top1 && dim <= 1024 && env_int("LZ_ASSIGN_OLD", 0) == 0) {
+        // per-CTA fixed part of the shared memory, then as many cached table rows as fit (at most 64)
+        const size_t fixed = (size_t)kMultiQ * (8 + 4 + 4 + 2 * kMultiLive + 1) + 64;
+        const int nseg0 = (dim + 127) / 128, nseg = nseg0 <= 2 ? 2 : nseg0 <= 4 ? 4 : nseg0 <= 6 ? 6 : 8;
+        const size_t row_bytes = (size_t)nseg * 512 + 8;
+        int cache_rows = (int)((200 * 1024 - fixed) / row_bytes);
+        if (cache_rows > 64) cache_rows = 64;
+        const size_t msmem = fixed + (size_t)cache_rows * row_bytes;
+        auto mk = metric == LZ_COSINE
+                      ? (nseg == 2 ? assign_multi_kernel<2, LZ_COSINE> : nseg == 4 ? assign_multi_kernel<4, LZ_COSINE>
+                         : nseg == 6 ? assign_multi_kernel<6, LZ_COSINE> : assign_multi_kernel<8, LZ_COSINE>)
+                      : (nseg == 2 ? assign_multi_kernel<2, LZ_L2> : nseg == 4 ? assign_multi_kernel<4, LZ_L2>
+                         : nseg == 6 ? assign_multi_kernel<6, LZ_L2> : assign_multi_kernel<8, LZ_L2>);
+        LZ_CUDA(cudaFuncSetAttribute(mk, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)msmem));
+        mk<<<(n_queries + kMultiQ - 1) / kMultiQ, kMultiThreads, msmem, st>>>(sp, n_queries, cache_rows);
+    } else if (tiny_top1) {
         LZ_CUDA(cudaFuncSetAttribute(assign_rescore_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rows_smem));
         assign_rescore_kernel<<<(n_queries + kBucketQ - 1) / kBucketQ, kSelThreads, rows_smem, st>>>(sp, n_queries);
     } else if (k <= kSmallK) {
@@ -1708,6 +2013,8 @@ extern "C" int lz_search_batched(const void* shadow, const float* rows, int64_t 
                                 n_queries, 1, k, metric, pl.fb_chunks, id_base, s + L.fallback,
                                 L.total - L.fallback, out_ids, out_scores, out_counts, fb_list, fb_count, stream);
 }
+}  // namespace
+
 
 // ---- two-level search (north_star (1); the reference's level 1 is core/memory_system.py:464-470) ---------------------
 namespace {

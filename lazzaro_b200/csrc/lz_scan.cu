@@ -668,6 +668,127 @@ extern "C" int lz_segment_mean(const float* rows, int64_t ld, int dim, const int
     return LZ_OK;
 }
 
+// ---- grouping rows by label: the member lists of a k-means style (re)assignment ------------------------------------
+// A STABLE counting sort of the row indices by label (labels < n_labels <= kGroupMaxLabels), so that lz_segment_mean
+// sums every centroid's members in ascending row order — a fixed order, hence the same bits on every run.  Three
+// launches, no CTA waits on another: per-tile label histograms; per label an exclusive scan over the tiles (+ the label
+// offsets); per tile the scatter, ranking equal labels in row order (rounds of 256 rows, warps admitted in order,
+// __match_any inside a warp).
+namespace {
+constexpr int kGroupTile = 2048;
+constexpr int kGroupMaxLabels = 16384;
+
+template <bool SCATTER>
+__global__ void __launch_bounds__(kThreads) group_by_label_kernel(const int64_t* __restrict__ labels, int64_t n, int n_labels,
+                                                                  int32_t* __restrict__ tile_hist,     // [n_tiles][n_labels]
+                                                                  int64_t* __restrict__ order) {
+    extern __shared__ int s_cnt[];                                            // [n_labels] running count / base
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t base = (int64_t)blockIdx.x * kGroupTile;
+    int32_t* hist = tile_hist + (size_t)blockIdx.x * n_labels;
+    for (int l = tid; l < n_labels; l += kThreads) s_cnt[l] = SCATTER ? hist[l] : 0;     // scatter: where the tile's first row of label l goes
+    __syncthreads();
+    for (int r = 0; r < kGroupTile / kThreads; ++r) {
+        const int64_t i = base + (int64_t)r * kThreads + tid;
+        const int64_t lab64 = i < n ? labels[i] : -1;
+        const int lab = (lab64 >= 0 && lab64 < n_labels) ? (int)lab64 : -1;
+        const unsigned peers = __match_any_sync(0xffffffffu, lab);
+        const int rank = __popc(peers & ((1u << lane) - 1u));
+        const bool leader = rank == 0;
+        int at = 0;
+        for (int w = 0; w < kThreads / 32; ++w) {                             // warps in order: rows keep their order within a label
+            if (warp == w && lab >= 0 && leader) {
+                at = s_cnt[lab];
+                s_cnt[lab] = at + __popc(peers);
+            }
+            __syncthreads();
+        }
+        if (SCATTER && lab >= 0) {
+            at = __shfl_sync(peers, at, __ffs(peers) - 1);
+            order[at + rank] = i;
+        }
+    }
+    if (!SCATTER) {
+        __syncthreads();
+        for (int l = tid; l < n_labels; l += kThreads) hist[l] = s_cnt[l];
+    }
+}
+
+// per label: counts of the tiles -> exclusive positions (label offset + tiles before), in place; seg[l] = label offsets
+__global__ void __launch_bounds__(kThreads) group_scan_kernel(int32_t* __restrict__ tile_hist, int n_tiles, int n_labels,
+                                                              int64_t* __restrict__ seg) {
+    __shared__ long long s_warp[kThreads / 32];
+    __shared__ long long s_carry;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    // pass 1: total per label, block-wide exclusive scan over the labels in chunks of 256
+    for (int l0 = 0; l0 < n_labels; l0 += kThreads) {
+        const int l = l0 + tid;
+        long long tot = 0;
+        if (l < n_labels)
+            for (int t = 0; t < n_tiles; ++t) tot += tile_hist[(size_t)t * n_labels + l];
+        long long incl = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const long long v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        long long off = s_carry + incl - tot;
+        for (int w = 0; w < warp; ++w) off += s_warp[w];
+        if (l < n_labels) {
+            seg[l] = off;
+            long long run = off;
+            for (int t = 0; t < n_tiles; ++t) {
+                const int c = tile_hist[(size_t)t * n_labels + l];
+                tile_hist[(size_t)t * n_labels + l] = (int32_t)run;
+                run += c;
+            }
+        }
+        __syncthreads();
+        if (tid == kThreads - 1) s_carry = off + tot;
+        __syncthreads();
+    }
+    if (tid == 0) seg[n_labels] = s_carry;
+}
+}  // namespace
+
+extern "C" size_t lz_group_by_label_scratch_bytes(int64_t n, int n_labels) {
+    if (n <= 0 || n_labels <= 0) return 256;
+    const int64_t tiles = (n + kGroupTile - 1) / kGroupTile;
+    return (size_t)(((size_t)tiles * n_labels * 4 + 255) & ~(size_t)255);
+}
+
+extern "C" int lz_group_by_label(const int64_t* labels, int64_t n, int n_labels, void* scratch, size_t scratch_bytes,
+                                 int64_t* out_order, int64_t* out_offsets, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    LZ_REQUIRE(n_labels >= 1 && n_labels <= kGroupMaxLabels, "lz_group_by_label: n_labels=%d outside 1..%d", n_labels, kGroupMaxLabels);
+    LZ_REQUIRE(out_offsets != nullptr, "lz_group_by_label: NULL output");
+    if (n <= 0) {
+        LZ_CUDA(cudaMemsetAsync(out_offsets, 0, (size_t)(n_labels + 1) * 8, st));
+        return LZ_OK;
+    }
+    LZ_REQUIRE(labels && out_order && scratch, "lz_group_by_label: NULL pointer");
+    LZ_REQUIRE(n < (1ll << 31), "lz_group_by_label: n too large");
+    const size_t need = lz_group_by_label_scratch_bytes(n, n_labels);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_group_by_label: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    const int tiles = (int)((n + kGroupTile - 1) / kGroupTile);
+    const size_t smem = (size_t)n_labels * 4;
+    LZ_CUDA(cudaFuncSetAttribute(group_by_label_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    LZ_CUDA(cudaFuncSetAttribute(group_by_label_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int32_t* hist = (int32_t*)scratch;
+    group_by_label_kernel<false><<<tiles, kThreads, smem, st>>>(labels, n, n_labels, hist, nullptr);
+    group_scan_kernel<<<1, kThreads, 0, st>>>(hist, tiles, n_labels, out_offsets);
+    group_by_label_kernel<true><<<tiles, kThreads, smem, st>>>(labels, n, n_labels, hist, out_order);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
 // ---- importance scoring + lowest-k selection (buffer-limit eviction) ---------------------------------------
 // Stands behind MemorySystem._enforce_buffer_limit (core/memory_system.py:535-578):
 //   days_old   = (now - last_accessed) / 86400

@@ -273,6 +273,52 @@ def search_two_level(shadow: torch.Tensor, rows: torch.Tensor, dim: int, norms: 
     return ids, scores, counts, cert, probe, scratch
 
 
+def assign_nearest(table_shadow: torch.Tensor, table: torch.Tensor, table_norms: torch.Tensor, rows: torch.Tensor, dim: int,
+                   table_det_row_err: Optional[float] = None, row_shadow: Optional[torch.Tensor] = None,
+                   row_err: Optional[torch.Tensor] = None, margin_sigmas: float = 4.0, scratch: Optional[torch.Tensor] = None):
+    """Nearest table row (centroid) of every row by cosine, ties to the lowest table index (lz_assign_nearest).
+    Returns (idx int64 [n], cos float64 [n], certified int32 [n])."""
+    dev = _dev(rows)
+    assert table_shadow.dtype == torch.float16 and table.dtype == torch.float32 and rows.dtype == torch.float32
+    assert rows.stride(1) == 1 and table.stride(1) == 1
+    n, K = rows.shape[0], table.shape[0]
+    if row_shadow is not None:
+        assert row_shadow.dtype == torch.float16 and row_shadow.is_contiguous() and row_shadow.shape == (n, dim)
+        assert row_err is not None and row_err.dtype == torch.float32 and row_err.numel() >= n
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        need = int(lib.lz_assign_nearest_scratch_bytes(K, n, dim, int(row_shadow is not None)))
+        if scratch is None or scratch.numel() < need:
+            scratch = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        idx = torch.empty(n, dtype=torch.int64, device=dev)
+        cos = torch.empty(n, dtype=torch.float64, device=dev)
+        cnt = torch.empty(n, dtype=torch.int32, device=dev)
+        cert = torch.empty(n, dtype=torch.int32, device=dev)
+        check(lib.lz_assign_nearest(ptr(table_shadow), ptr(table), table.stride(0), dim, ptr(table_norms), K,
+                                    -1.0 if table_det_row_err is None else float(table_det_row_err),
+                                    ptr(rows), rows.stride(0), n, ptr(row_shadow), ptr(row_err), float(margin_sigmas),
+                                    ptr(scratch), scratch.numel(), ptr(idx), ptr(cos), ptr(cnt), ptr(cert), stream_ptr(dev)),
+              "lz_assign_nearest")
+    return idx, cos, cert
+
+
+def group_by_label(labels: torch.Tensor, n_labels: int):
+    """(order int64 [n], seg_offsets int64 [n_labels + 1]): row indices grouped by label, ascending inside a label
+    (lz_group_by_label, a stable counting sort)."""
+    dev = _dev(labels)
+    assert labels.dtype == torch.int64 and labels.is_contiguous()
+    n = labels.numel()
+    lib = _lib.load()
+    order = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    seg = torch.empty(n_labels + 1, dtype=torch.int64, device=dev)
+    nbytes = int(lib.lz_group_by_label_scratch_bytes(n, n_labels))
+    scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.lz_group_by_label(ptr(labels), n, int(n_labels), ptr(scratch), nbytes, ptr(order), ptr(seg), stream_ptr(dev)),
+              "lz_group_by_label")
+    return order, seg
+
+
 def segment_mean(rows: torch.Tensor, dim: int, seg_offsets: torch.Tensor, order: Optional[torch.Tensor] = None) -> torch.Tensor:
     """float64 [n_segments, dim] means of row groups (lz_segment_mean)."""
     dev = _dev(rows)

@@ -11,13 +11,35 @@ rows, shard = synth.clustered_rows_device(n, dim, 102 if slab else kc, "cuda")
 seg = torch.linspace(0, n, kc + 1, device="cuda").long() if slab else \
     torch.searchsorted(shard.long().contiguous(), torch.arange(kc + 1, device="cuda"))
 cen32 = consolidate.centroid_means(rows, seg_offsets=seg).float().contiguous()
+for margin in ("worst_case", "statistical"):
+    for _ in range(2):
+        idx, cos = consolidate.assign_to_centroids(rows, cen32, margin=margin)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        idx, cos = consolidate.assign_to_centroids(rows, cen32, margin=margin)
+    e1.record(); torch.cuda.synchronize()
+    print(margin, "ms", e0.elapsed_time(e1) / 3, "own-slab fraction" if slab else "own-shard fraction",
+          (idx == (torch.arange(n, device="cuda") * kc // n if slab else shard.long())).float().mean().item(), flush=True)
+
+from lazzaro_b200.store import B200Store
+st = B200Store(); st.adopt_rows(rows)
+st._shadow_for(0)
 for _ in range(2):
-    idx, cos = consolidate.assign_to_centroids(rows, cen32)
+    idx2, cos2 = consolidate.assign_store_rows(st, cen32)
 torch.cuda.synchronize()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(3):
-    idx, cos = consolidate.assign_to_centroids(rows, cen32)
+    idx2, cos2 = consolidate.assign_store_rows(st, cen32)
 e1.record(); torch.cuda.synchronize()
-print("ms", e0.elapsed_time(e1) / 3, "own-slab fraction" if slab else "own-shard fraction",
-      (idx == (torch.arange(n, device="cuda") * kc // n if slab else shard.long())).float().mean().item())
+print("resident rows (store shadow as the query side) ms", e0.elapsed_time(e1) / 3, "same answer", bool(torch.equal(idx2, idx)), flush=True)
+for _ in range(2):
+    m = consolidate.centroid_means(rows, assign=idx, n_centroids=kc)
+torch.cuda.synchronize()
+e0.record()
+for _ in range(3):
+    m = consolidate.centroid_means(rows, assign=idx, n_centroids=kc)
+e1.record(); torch.cuda.synchronize()
+print("centroid update from an arbitrary assignment ms", e0.elapsed_time(e1) / 3, flush=True)

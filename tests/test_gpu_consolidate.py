@@ -138,3 +138,65 @@ def test_cfg3_size_dedup_and_reassignment():
     assert (cos > 0.9).all()
     means = consolidate.centroid_means(rows, assign=idx, n_centroids=kc)
     assert torch.allclose(means[5], rows[idx == 5].double().mean(0), rtol=1e-11, atol=1e-14)
+
+
+@pytest.mark.parametrize("margin", ["worst_case", "statistical"])
+@pytest.mark.parametrize("order", ["clustered", "shuffled"])
+def test_assign_with_nearly_coincident_centroids(margin, order):
+    """k-means with k above the number of clusters: ~10 centroids per true cluster, nearly coincident (means of equal
+    slabs of the rows), so a row sees many centroids inside the rescoring window — the multi-candidate kernel.  Rows
+    stored cluster by cluster (the store's layout: a block shares its candidates) and shuffled (every block needs far
+    more table rows than its cache holds: staged in rounds).  Exact ties (duplicated centroids) go to the lowest index."""
+    from lazzaro_b200 import consolidate, synth
+    n, dim, clusters, K = 24000, 96, 12, 120
+    rows_np, _ = synth.clustered_rows(n, dim, clusters, seed=5)
+    seg = np.linspace(0, n, K + 1).astype(np.int64)
+    cen_np = np.stack([rows_np[a:b].astype(np.float64).mean(0) for a, b in zip(seg[:-1], seg[1:])]).astype(np.float32)
+    cen_np[7] = cen_np[3]                                                # exact duplicates: index 3 must win
+    cen_np[55] = cen_np[51]
+    if order == "shuffled":
+        rows_np = rows_np[np.random.default_rng(1).permutation(n)]
+    rows, cen = torch.as_tensor(rows_np).cuda(), torch.as_tensor(cen_np).cuda()
+    idx, cos = consolidate.assign_to_centroids(rows, cen, margin=margin)
+    want_idx, want_cos = graph_ops.assign_to_centroids(rows_np, cen_np)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want_idx)
+    np.testing.assert_allclose(cos.cpu().numpy(), want_cos, rtol=1e-12)
+    assert not (idx == 7).any() and not (idx == 55).any()
+    # the window really holds several centroids per row on this data
+    sims = graph_ops.cosine_matrix(rows_np[:200], cen_np)
+    assert np.median((sims >= sims.max(1, keepdims=True) - 1e-3).sum(1)) >= 2
+
+
+@pytest.mark.parametrize("n,K", [(1, 1), (5000, 7), (100_003, 1024), (70_000, 16384), (4096, 3)])
+def test_group_by_label_is_a_stable_counting_sort(n, K):
+    from lazzaro_b200 import kernels as Kn
+    g = torch.Generator(device="cuda"); g.manual_seed(n)
+    labels = torch.randint(0, K, (n,), generator=g, device="cuda", dtype=torch.int64)
+    if n > 10:
+        labels[3] = -1                     # out-of-range labels are left out
+        labels[7] = K
+    order, seg = Kn.group_by_label(labels, K)
+    ok = (labels >= 0) & (labels < K)
+    idx = torch.nonzero(ok).flatten()
+    want = idx[torch.argsort(labels[idx], stable=True)]
+    assert torch.equal(order[: want.numel()], want)
+    counts = torch.bincount(labels[idx], minlength=K)
+    assert torch.equal(seg[1:] - seg[:-1], counts) and int(seg[0]) == 0
+
+
+def test_assign_rows_resident_in_a_store_matches_the_plain_call():
+    """The store's own fp16 shadow and rounding-error norms as the query side (no conversion pass): same assignment."""
+    from lazzaro_b200 import consolidate, synth
+    from lazzaro_b200.store import B200Store
+    rows_np, _ = synth.clustered_rows(20000, 128, 10, seed=2)
+    rows_np *= np.linspace(0.5, 2.0, 20000, dtype=np.float32)[:, None]
+    cen_np = np.stack([rows_np[a:a + 200].astype(np.float64).mean(0) for a in range(0, 20000, 200)]).astype(np.float32)
+    st = B200Store(metric="l2")                                       # an l2 store builds its cosine shadow on demand
+    st.add_rows(rows_np)
+    cen = torch.as_tensor(cen_np).cuda()
+    idx, cos = consolidate.assign_store_rows(st, cen)
+    want_idx, want_cos = graph_ops.assign_to_centroids(rows_np, cen_np)
+    np.testing.assert_array_equal(idx.cpu().numpy(), want_idx)
+    np.testing.assert_allclose(cos.cpu().numpy(), want_cos, rtol=1e-12)
+    idx2, cos2 = consolidate.assign_store_rows(st, cen, row_range=(5000, 12000))
+    assert torch.equal(idx2, idx[5000:12000]) and torch.equal(cos2, cos[5000:12000])
