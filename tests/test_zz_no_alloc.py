@@ -76,3 +76,30 @@ def test_no_alloc_rejects_oversize_and_handles_empty():
                                          C.c_void_p(kept.data_ptr()), None)
     torch.cuda.synchronize()
     assert rc == 0 and int(kept.item()) == 0
+
+
+def test_no_alloc_in_place_and_against_the_oracle():
+    """The mode this entry point's single-pass kernel exists for: outputs aliasing the inputs (compaction in place, as a
+    binding that owns one copy of the edge columns would call it) — checked directly against the numpy oracle
+    (oracle/graph_ops.py decay_prune_edges, memory_shard.py:64-84), not only against the scratch-taking entry point."""
+    from lazzaro_b200 import _lib
+    from oracle import graph_ops
+    lib = _lib.load()
+    for n, seed, factor, thr in [(900_001, 303, 0.99, 0.5), (5_000, 404, 1.0, 0.25)]:
+        cols = _cols(n, seed)
+        host = [c.cpu().numpy() for c in cols]
+        ws, wd, ww, wc, pruned = graph_ops.decay_prune_edges(*host, factor, thr)
+        k_out, out = _no_alloc(cols, n, factor, thr)                        # out of place first
+        work = [c.clone() for c in cols]
+        kept = torch.full((1,), -7, dtype=torch.int64, device="cuda")
+        p = lambda t: C.c_void_p(t.data_ptr())
+        rc = lib.lz_edge_decay_prune_noalloc(p(work[0]), p(work[1]), p(work[2]), p(work[3]), n, factor, thr,
+                                             p(work[0]), p(work[1]), p(work[2]), p(work[3]), p(kept),
+                                             C.c_void_p(torch.cuda.current_stream().cuda_stream))
+        _lib.check(rc, "lz_edge_decay_prune_noalloc (in place)")
+        torch.cuda.synchronize()
+        k = int(kept.item())
+        assert k == k_out == n - pruned == ws.shape[0]
+        for got, alias, want in zip(out, work, (ws, wd, ww, wc)):
+            np.testing.assert_array_equal(got, want)
+            np.testing.assert_array_equal(alias[:k].cpu().numpy(), want)
