@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--shards", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--no-batch1", action="store_true", help="skip the secondary batch-1 (HBM-bound) measurement")
+    ap.add_argument("--no-k100", action="store_true", help="skip the top-100 sub-result (BASELINE configs[3] as written)")
+    ap.add_argument("--no-configs", action="store_true", help="skip the cfg1 / cfg2 / cfg5_search sub-results")
     ap.add_argument("--k", type=int, default=10)
     ap.add_argument("--cpu-sample-rows", type=int, default=400_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -344,27 +346,61 @@ def main():
         store.margin = keep
         line["roofline"]["margins"] = margins
         line["roofline"]["margin"] = keep
-    if not args.no_batch1 and args.batch != 1:
-        q1 = queries[:1].contiguous()
-        q1_host = q_host[:1]
-        f_dev = lambda: sharded.search_device(q1, args.k)
-        f_loc = lambda: store.search_device(q1, 0, args.k)
-        f_e2e = (lambda: store.search_nodes(q1_host[0].tolist(), limit=args.k)) if world == 1 else (lambda: sharded.search_host(q1_host, args.k))
+    def search_block(batch, k, steps):
+        """One (batch, k) search configuration over the same resident rows: device-timed value, e2e through the host API,
+        roofline of the dominant kernel."""
+        q = queries[:batch].contiguous()
+        qh = q_host[:batch]
+        is_batched = store._takes_batched_path(batch, k, n_local)
+        f_dev = lambda: sharded.search_device(q, k)
+        f_loc = lambda: store.search_device(q, 0, k)
+        if batch == 1 and world == 1:
+            f_e2e_block = lambda n_: [store.search_nodes(qh[0].tolist(), limit=k) for _ in range(n_)][-1]
+            api = "B200Store.search_nodes (List[float] -> List[str])"
+        else:
+            def f_e2e_block(n_):
+                pend = None
+                for i in range(n_):
+                    h = sharded.submit_host(qh, k, slot=i & 1)
+                    if pend is not None:
+                        pend.result()
+                    pend = h
+                return pend.result()
+            api = "ShardedSearch.submit_host(...).result(), one search kept in flight"
         for _ in range(3):
-            f_dev(); f_e2e()
-        n1 = max(args.steps, 10)
-        ms1, _ = timed(f_dev, n1)
-        ms1k, _ = timed(f_loc, n1)
-        ms1e, _ = timed(f_e2e, n1)
-        bytes1 = n_local * args.dim * 4
-        ach1 = bytes1 / (ms1k / n1 * 1e-3) / 1e9
-        line["batch1"] = {"value": 1e3 / (ms1 / n1), "unit": UNIT, "ms_per_step": ms1 / n1, "steps": n1,
-                          "e2e": {"value": 1e3 / (ms1e / n1), "unit": UNIT, "h2d_bytes_per_step": int(store._dim_p * 4),
-                                  "d2h_bytes_per_step": int(args.k * 16 + 4)},
-                          "roofline": {"bound": "hbm", "achieved": ach1, "peak": hbm_peak, "unit": "GB/s",
-                                       "frac": ach1 / hbm_peak, "traffic": traffic.get("scan_kernel_10M_b1"),
-                                       "kernel": "scan_kernel (lz_search_exact)", "algorithmic_bytes_per_launch": bytes1},
-                          "gpu_launches": int(n1 * (2 + (1 if world > 1 else 0)))}
+            f_dev()
+        f_e2e_block(2)
+        ms_d, _ = timed(f_dev, steps)
+        ms_k, _ = timed(f_loc, steps)
+        ms_e, _ = timed(f_e2e_block, steps, block=True)
+        out = {"batch": batch, "k": k, "value": batch * 1e3 / (ms_d / steps), "unit": UNIT, "ms_per_step": ms_d / steps, "steps": steps,
+               "e2e": {"value": batch * 1e3 / (ms_e / steps), "unit": UNIT, "h2d_bytes_per_step": int(batch * store._dim_p * 4),
+                       "d2h_bytes_per_step": int(batch * k * 16 + batch * 4), "api": api}}
+        if is_batched:
+            fl = 2.0 * batch * n_local * args.dim
+            ach = fl / (ms_k / steps * 1e-3) / 1e12
+            out["roofline"] = {"bound": "tensor", "achieved": ach, "peak": tc_peak, "unit": "TFLOP/s", "frac": ach / tc_peak,
+                               "traffic": None, "kernel": "gemm_topk_kernel (lz_search_batched)", "algorithmic_flops_per_launch": fl,
+                               "frac_of_burst": ach / tc_burst, "certified_fraction": float(store.last_certified.float().mean().item()),
+                               "margin": store.margin}
+            out["gpu_launches"] = int(steps * (7 + (1 if world > 1 else 0)))
+        else:
+            by = n_local * args.dim * 4 * ((batch + 3) // 4)
+            ach = by / (ms_k / steps * 1e-3) / 1e9
+            out["roofline"] = {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                               "traffic": traffic.get("scan_kernel_10M_b1") if (batch == 1 and k == 10) else None,
+                               "kernel": "scan_kernel (lz_search_exact)", "algorithmic_bytes_per_launch": by}
+            out["gpu_launches"] = int(steps * (2 + (1 if world > 1 else 0)))
+        return out
+
+    n_sub = max(args.steps, 10)
+    if not args.no_batch1 and args.batch != 1:
+        line["batch1"] = search_block(1, args.k, n_sub)
+    if not args.no_k100 and args.k != 100:
+        # BASELINE configs[3] as written: top-100, batch 1 and batch 1024, same rows
+        line["k100"] = {"workload": f"top-100 over the same {args.rows} x {args.dim} rows (BASELINE configs[3] as written)",
+                        f"batch{args.batch}": search_block(args.batch, 100, max(5, args.steps // 2)),
+                        "batch1": search_block(1, 100, n_sub)}
     if args.edges > 0:
         # north_star (3): decay + prune sweep over the edge table; edges are partitioned with their shards, so the
         # ranks sweep disjoint slices with no collective (total edges fixed: strong scaling like the search)
@@ -433,6 +469,160 @@ def main():
                                  "unit": "ms", "higher_is_better": False,
                                  "parts": parts, "gpu_launches": 5 * (7 + 3 + 1)}
         del new, cen, cen_sep
+    if not args.no_configs:
+        from lazzaro_b200.dist import TenantSearch
+        # ---- BASELINE configs[4], search half: 100k users x 1k memories over 8 GPUs = 12 500 tenants (12.5M x 768 rows)
+        # per GPU, WEAK scaling: every rank holds its own tenants, a query is routed by the host to the rank that owns
+        # its user and scans that user's 1000 rows only (the `.where(user_id = ...)` pre-filter, vector_store.py:136-139).
+        # No collective on the data path.  One step = a host batch of 4096 queries per rank.
+        users_per_rank, per_user, qb = 12_500, 1000, 4096
+        t_rows, _ = synth.clustered_rows_device(users_per_rank * per_user, args.dim, 1024, dev, seed=synth.SEED_DATA + 100 + rank)
+        tstore = B200Store(device=str(dev))
+        tstore.adopt_tenants(t_rows, per_user, first_user=rank * users_per_rank)
+        tsearch = TenantSearch(tstore, users_per_rank, rank, world)
+        rng = np.random.default_rng(4242)                       # the same global batch on every rank; each routes its share
+        g_users = rng.integers(0, users_per_rank * world, qb * world)
+        mine = tsearch.route(g_users)
+        local_users = g_users[mine] - rank * users_per_rank
+        tq = synth.queries_near_rows_device(t_rows, qb * world, seed=synth.SEED_QUERY + 9)[: mine.size].contiguous()
+        tq_host_all = np.zeros((qb * world, args.dim), np.float32)
+        tq_host_all[mine] = tq.cpu().numpy()
+        t_prep = tsearch.prepare(local_users)                       # per-query row spans and tags, resident like the queries
+        f_t = lambda: tsearch.search_device(tq, t_prep, args.k)
+        f_te = lambda: tsearch.search_host(tq_host_all, g_users, args.k)
+        for _ in range(3):
+            f_t(); f_te()
+        n_t = max(args.steps // 2, 5)
+        ms_t, out_t = timed(f_t, n_t)
+        ms_te, out_te = timed(f_te, n_t)
+        assert np.array_equal(out_te[1], out_t[0].cpu().numpy()) and int(out_t[2].min()) == args.k
+        own = (out_t[0] // per_user).cpu().numpy() == local_users[:, None]
+        assert own.all(), "a per-user search returned another tenant's row"
+        served = torch.tensor([float(mine.size)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(served)
+        t_bytes = mine.size * per_user * args.dim * 4
+        line["cfg5_search"] = {
+            "workload": f"per-user top-{args.k} search, {users_per_rank * world} users x {per_user} memories x {args.dim} "
+                        f"({users_per_rank} users = {users_per_rank * per_user} rows resident per GPU), {qb} queries per rank and step, "
+                        "routed to the owning rank by user (BASELINE configs[4], search half)",
+            "metric": "per-user-filtered search QPS", "value": float(served.item()) * 1e3 / (ms_t / n_t), "unit": UNIT,
+            "ms_per_step": ms_t / n_t, "steps": n_t, "scaling": "weak", "queries_per_step": int(served.item()),
+            "e2e": {"value": float(served.item()) * 1e3 / (ms_te / n_t), "unit": UNIT, "h2d_bytes_per_step": int(mine.size * args.dim * 4),
+                    "d2h_bytes_per_step": int(mine.size * (args.k * 8 + 4)), "api": "TenantSearch.search_host (numpy queries + user indices -> row ids)"},
+            "roofline": {"bound": "hbm", "achieved": t_bytes / (ms_t / n_t * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": t_bytes / (ms_t / n_t * 1e-3) / 1e9 / hbm_peak, "traffic": None, "kernel": "scan_kernel (lz_search_exact, one row span per query)",
+                         "algorithmic_bytes_per_launch": t_bytes},
+            "gpu_launches": int(n_t * 2)}
+        if rank == 0 and not args.no_cpu_baseline:
+            from oracle import flat_search
+            sample = t_rows[: 2000 * per_user].cpu().numpy()              # 2000 tenants
+            qs_c = tq_host_all[mine][:2000]
+            t0 = time.perf_counter()
+            for i in range(2000):                                          # one filtered flat search per query: the reference's call
+                flat_search.fast_topk_f32(sample[i * per_user:(i + 1) * per_user], qs_c[i:i + 1], args.k)
+            dt = time.perf_counter() - t0
+            line["cfg5_search"]["cpu_baseline"] = {"value": 2000 / dt, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                                   "sample": "2000 per-user searches (numpy sgemv + argpartition over the user's 1000 x 768 rows), one after another"}
+            del sample
+        del tstore, tsearch, t_rows, tq
+        torch.cuda.empty_cache()
+    if not args.no_configs and world == 1:
+        # ---- BASELINE configs[1]: 1M x 768 in 64 semantic shards, batch 256, top-10 — flat and two-level (nprobe 4), the
+        # two-level search once with queries spread over all 64 shards (every shard is touched: HBM-bound like the flat one)
+        # and once with the batch concentrated on 8 shards (a session's topics)
+        n2, S2, B2 = 1_000_000, 64, 256
+        r2, sh2 = synth.clustered_rows_device(n2, args.dim, S2, dev, seed=synth.SEED_DATA + 7)
+        st2 = B200Store(device=str(dev))
+        st2.adopt_rows(r2, id_prefix="node_")
+        off2 = torch.searchsorted(sh2.long().contiguous(), torch.arange(S2 + 1, device=dev)).cpu().numpy()
+        st2.set_shards(off2)
+        q2 = synth.queries_near_rows_device(r2, B2, seed=synth.SEED_QUERY + 2)
+        q2c = synth.queries_near_rows_device(r2[: int(off2[8])], B2, seed=synth.SEED_QUERY + 3)     # near shards 0..7 only
+        q2_host, q2c_host = q2.cpu().numpy(), q2c.cpu().numpy()
+        n_2 = max(args.steps, 10)
+        res2 = {}
+        for name, fn, fe in (("flat", lambda: st2.search_device(q2, 0, args.k), lambda: st2.search_batch(q2_host, limit=args.k)),
+                             ("two_level_nprobe4", lambda: st2.search_two_level_device(q2, args.k, 4), lambda: st2.search_two_level(q2_host, args.k, 4)),
+                             ("flat_concentrated", lambda: st2.search_device(q2c, 0, args.k), None),
+                             ("two_level_nprobe4_concentrated", lambda: st2.search_two_level_device(q2c, args.k, 4), None)):
+            for _ in range(3):
+                fn()
+            ms_2, o2 = timed(fn, n_2)
+            res2[name] = {"ms_per_step": ms_2 / n_2, "value": B2 * 1e3 / (ms_2 / n_2), "unit": UNIT, "ids": o2[0]}
+            if fe is not None:
+                fe()
+                ms_2e, _ = timed(fe, n_2)
+                res2[name]["e2e"] = {"value": B2 * 1e3 / (ms_2e / n_2), "unit": UNIT, "h2d_bytes_per_step": int(B2 * args.dim * 4),
+                                     "d2h_bytes_per_step": int(B2 * (args.k * 8 + 4)),
+                                     "api": "B200Store.search_batch / search_two_level (numpy queries -> id strings)"}
+        for name, base in (("two_level_nprobe4", "flat"), ("two_level_nprobe4_concentrated", "flat_concentrated")):
+            a_, b_ = res2[name]["ids"], res2[base]["ids"]
+            res2[name]["recall_at_%d" % args.k] = float((a_.unsqueeze(2) == b_.unsqueeze(1)).any(2).float().mean().item())
+        fl2 = 2.0 * B2 * n2 * args.dim
+        for name, v in res2.items():
+            v.pop("ids")
+            scanned = n2 if name.startswith("flat") else 4 * n2 // S2
+            tf = 2.0 * B2 * scanned * args.dim / (v["ms_per_step"] * 1e-3) / 1e12
+            v["roofline"] = {"bound": "tensor", "achieved": tf, "peak": tc_peak, "unit": "TFLOP/s", "frac": tf / tc_peak, "traffic": None,
+                             "kernel": "gemm_topk_kernel", "algorithmic_flops_per_launch": 2.0 * B2 * scanned * args.dim,
+                             "hbm_bound_alternative": {"achieved": n2 * args.dim * 2 / (v["ms_per_step"] * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                                       "note": "fp16 shadow bytes of all rows / time (batch 256 sits at the ridge: SURVEY §8d)"}}
+        line["cfg2"] = {"workload": f"{n2} x {args.dim} in {S2} semantic shards, batch {B2}, top-{args.k} (BASELINE configs[1])", **res2,
+                        "note": "nprobe < shards is an approximation of the flat search: reported with recall, never as parity; "
+                                "nprobe = shards equals the flat result bit for bit (tests/test_gpu_two_level.py)"}
+        if not args.no_cpu_baseline:
+            from oracle import flat_search
+            rs = r2[:200_000].cpu().numpy()
+            t0 = time.perf_counter()
+            flat_search.fast_topk_f32(rs, q2_host, args.k)
+            dt = time.perf_counter() - t0
+            line["cfg2"]["cpu_baseline"] = {"value": B2 / (dt * n2 / 200_000), "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
+                                            "sample": "numpy sgemm + argpartition flat search of the 256 queries over a 200k-row sample, scaled by 5 to 1M rows"}
+            del rs
+        del st2, r2, q2, q2c
+        torch.cuda.empty_cache()
+        # ---- BASELINE configs[0] (the reference's own scale): 1 user, 10k x 384, top-10 through the Store call
+        r1_np, _ = synth.clustered_rows(10_000, 384, 8, seed=synth.SEED_DATA + 1)
+        q1_np = synth.queries_near_rows(r1_np, 64, seed=synth.SEED_QUERY + 1)
+        st1 = B200Store(device=str(dev))
+        st1.add_rows(r1_np, id_prefix="node_")
+        q1_lists = [q.tolist() for q in q1_np]
+        for q in q1_lists[:8]:
+            st1.search_nodes(q, limit=10)
+        n_1 = 200
+        ms_1, _ = timed(lambda n_: [st1.search_nodes(q1_lists[i % 64], limit=10) for i in range(n_)][-1], n_1, block=True)
+        q1_dev = st1._to_device(q1_np[:1])
+        ms_1d, _ = timed(lambda: st1.search_device(q1_dev, 0, 10), n_1)
+        line["cfg1"] = {"workload": "1 user, 10k x 384 memories, top-10, one query per call (BASELINE configs[0], the reference's own scale)",
+                        "value": 1e3 / (ms_1d / n_1), "unit": UNIT, "ms_per_step": ms_1d / n_1, "steps": n_1,
+                        "e2e": {"value": 1e3 / (ms_1 / n_1), "unit": UNIT, "us_per_call": ms_1 / n_1 * 1e3, "h2d_bytes_per_step": 384 * 4,
+                                "d2h_bytes_per_step": 10 * 16 + 4, "api": "B200Store.search_nodes (List[float] -> List[str])"},
+                        "roofline": {"bound": "hbm", "achieved": 10_000 * 384 * 4 / (ms_1d / n_1 * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                     "frac": 10_000 * 384 * 4 / (ms_1d / n_1 * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                                     "kernel": "scan_kernel + merge_kernel", "algorithmic_bytes_per_launch": 10_000 * 384 * 4,
+                                     "note": "15 MB: launch-latency bound, not bandwidth bound"}}
+        if not args.no_cpu_baseline:
+            from oracle import flat_search, ref_loops
+            from oracle.flat_store import FlatStore
+            inv1 = (1.0 / np.linalg.norm(r1_np, axis=1)).astype(np.float32)
+            t0 = time.perf_counter()
+            for i in range(n_1):
+                flat_search.fast_topk_f32(r1_np, q1_np[i % 64:i % 64 + 1], 10, "cosine", inv1)
+            dt_f = (time.perf_counter() - t0) / n_1
+            fs = FlatStore(metric="cosine")
+            fs.add_nodes([{"id": f"node_{i}", "content": "", "embedding": r1_np[i]} for i in range(10_000)])
+            resident = {f"node_{i}": i for i in range(10_000)}
+            t0 = time.perf_counter()
+            for i in range(20):                                      # C1: search_memories over the injected float64 flat store
+                ref_loops.search_memories(fs, resident, q1_lists[i % 64], limit=10)
+            dt_r = (time.perf_counter() - t0) / 20
+            line["cfg1"]["cpu_baseline"] = {"value": 1.0 / dt_f, "unit": UNIT, "us_per_call": dt_f * 1e6, "cores": os.cpu_count(), "kind": "port",
+                                            "sample": "numpy float32 sgemv + argpartition over the 10k x 384 rows, one query per call",
+                                            "reference_shaped": {"value": 1.0 / dt_r, "unit": UNIT, "us_per_call": dt_r * 1e6, "cores": 1,
+                                                                 "sample": "search_memories restated (memory_system.py:1460-1472) over the oracle FlatStore: "
+                                                                           "float64 distances over the fp32 rows in numpy, ids -> resident nodes (BASELINE.md C1)"}}
+        del st1
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         if "consolidation" in line:
             # the reference's dedup is one flat scan per new memory (memory_system.py:719-742): numpy port on a bounded sample
@@ -447,6 +637,21 @@ def main():
                                                      "sample": "numpy sgemm + argmax dedup of 1000 x 50000 rows, scaled linearly to 10k x 1M (dedup part only)"}
         qps, desc, cores, _ = cpu_search_qps(args, 3, 1)
         line["cpu_baseline"] = {"value": qps, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+        if "consolidation" in line:
+            # the reference's own linking loop (memory_system.py:838-891 restated, oracle/ref_loops.py): per new
+            # memory a Python cosine against every existing node — 20 new x 10k existing, 768-d
+            from oracle import ref_loops
+            rng_ = np.random.default_rng(8)
+            ex = [ref_loops.Node(f"e{i}", v.tolist()) for i, v in enumerate(rng_.standard_normal((10_000, args.dim)))]
+            nw = [ref_loops.Node(f"x{i}", v.tolist()) for i, v in enumerate(rng_.standard_normal((20, args.dim)))]
+            t0 = time.perf_counter()
+            ref_loops.link_to_existing(nw, ex, {})
+            dt = time.perf_counter() - t0
+            line["consolidation"]["cpu_baseline"]["reference_shaped"] = {
+                "value": 20 * 10_000 / dt, "unit": "pairs/s", "cores": 1,
+                "sample": "the reference's per-pair Python cosine loop (memory_system.py:838-891 restated) on 20 new x 10k existing 768-d nodes; "
+                          "the same linking at 10k x 1M is 1e10 pairs", "seconds_for_10k_x_1M_extrapolated": 1e10 / (20 * 10_000 / dt)}
+            del ex, nw
         if "decay_prune" in line:
             from oracle import graph_ops
             es, ed, ew, ec = synth.edge_table(2_000_000, 1_000_000)
@@ -455,7 +660,20 @@ def main():
                 graph_ops.decay_prune_edges(es, ed, ew, ec, 0.99, 0.5)
             line["decay_prune"]["cpu_baseline"] = {"value": 2_000_000 * 3 / (time.perf_counter() - t0), "unit": "edges/s",
                                                    "cores": 1, "kind": "port",
-                                                   "sample": "numpy vectorised decay+mask+compress on 2M edges (the reference's per-object Python loop, memory_shard.py:64-84, measured ~2.7M edges/s in SURVEY §6)"}
+                                                   "sample": "numpy vectorised decay+mask+compress on 2M edges"}
+            # the reference's own per-object loop (memory_shard.py:64-84 restated) on 1M Edge objects
+            from oracle import ref_loops
+            es, ed, ew, _ = synth.edge_table(1_200_000, 1_000_000)
+            ed_ = ref_loops.make_edge_dict(es, ed, ew)
+            n_obj = len(ed_)
+            t0 = time.perf_counter()
+            ref_loops.decay_and_prune(ed_, {}, 0.01, 0.5)
+            dt = time.perf_counter() - t0
+            line["decay_prune"]["cpu_baseline"]["reference_shaped"] = {
+                "value": n_obj / dt, "unit": "edges/s", "cores": 1,
+                "sample": f"apply_temporal_decay + prune_weak_edges as the reference writes them (per-object Python loop over a dict of {n_obj} Edge objects); "
+                          "linear in the edge count"}
+            del ed_
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:

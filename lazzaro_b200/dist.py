@@ -204,3 +204,63 @@ def parity_check(n: int = 300_000, dim: int = 128, cases=PARITY_CASES, group=Non
         out.append({"batch": B, "k": k, "ok": bool(int(flag))})
     st.close()
     return out
+
+
+class TenantSearch:
+    """Multi-tenant search across the GPUs of one box (BASELINE configs[4]; SURVEY §8e "partition by user").
+
+    All of a user's rows live on ONE rank, so the per-user pre-filter of the reference (vector_store.py:136-139:
+    `.where(user_id = ...)` before the top-k) makes a query a single-GPU operation: the host routes it to the rank that
+    owns the user and that rank scans just the user's row span.  No collective is on the data path; throughput scales
+    with the number of ranks because the tenants (and their queries) do.  Users are dealt to ranks in contiguous blocks
+    of `users_per_rank` global user indices; this rank's store holds its block as local user indices 0..users_per_rank-1."""
+
+    def __init__(self, store, users_per_rank: int, rank: int = 0, world: int = 1):
+        self.store, self.users_per_rank, self.rank, self.world = store, int(users_per_rank), int(rank), int(world)
+        self._lo, self._hi = store.user_spans()
+
+    def owner(self, global_user: np.ndarray) -> np.ndarray:
+        """Rank that owns each global user index."""
+        return np.minimum(np.asarray(global_user, dtype=np.int64) // self.users_per_rank, self.world - 1)
+
+    def route(self, global_user: np.ndarray) -> np.ndarray:
+        """Positions (into the caller's batch) of the queries this rank must answer."""
+        return np.nonzero(self.owner(global_user) == self.rank)[0]
+
+    def prepare(self, local_user: np.ndarray):
+        """Device-resident per-query row spans and tags for a batch of local user indices (reusable across searches)."""
+        dev = self.store.device
+        lo_h, hi_h = self._lo[local_user], self._hi[local_user]
+        lo = torch.as_tensor(lo_h).to(dev)
+        hi = torch.as_tensor(hi_h).to(dev)
+        lo._lz_max_span = int((hi_h - lo_h).max()) if len(lo_h) else 0
+        return lo, hi, torch.as_tensor(np.asarray(local_user, dtype=np.int32)).to(dev)
+
+    def search_device(self, queries: torch.Tensor, local_user, k: int):
+        """queries float32 [b, dim_p] on this GPU, local_user int [b] (or what prepare() returned for it) ->
+        (row ids int64 [b,k], scores, counts), unsynchronised."""
+        lo, hi, tag = local_user if isinstance(local_user, tuple) else self.prepare(local_user)
+        return self.store.search_ranges_device(queries, lo, hi, tag, k)
+
+    def search_host(self, queries: np.ndarray, global_user: np.ndarray, k: int):
+        """The routed part of a host batch: (positions answered here, row ids int64 [m,k] as numpy, counts).  Every rank
+        calls this with the same batch; the union of the positions is the whole batch."""
+        st = self.store
+        mine = self.route(global_user)
+        if mine.size == 0:
+            return mine, np.empty((0, k), np.int64), np.empty(0, np.int32)
+        q = np.ascontiguousarray(queries[mine], dtype=np.float32)
+        with torch.cuda.device(st.device):
+            stage = st._pinned("tq", (q.shape[0], st._dim_p), torch.float32)
+            if st._dim_p != st.dim:
+                stage.zero_()
+            stage[:, :st.dim] = torch.from_numpy(q)
+            qd = stage.to(st.device, non_blocking=True)
+            local = (np.asarray(global_user, dtype=np.int64)[mine] - self.rank * self.users_per_rank)
+            ids, sc, cnt = self.search_device(qd, local, k)
+            h_ids = st._pinned("tids", tuple(ids.shape), torch.int64)
+            h_cnt = st._pinned("tcnt", tuple(cnt.shape), torch.int32)
+            h_ids.copy_(ids, non_blocking=True)
+            h_cnt.copy_(cnt, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+        return mine, h_ids.numpy().copy(), h_cnt.numpy().copy()

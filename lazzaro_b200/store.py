@@ -300,6 +300,38 @@ class B200Store:
             self._blocks.append((0, n, id_prefix, 0))
             self._version += 1
 
+    def adopt_tenants(self, rows: torch.Tensor, rows_per_user: int, first_user: int = 0, user_prefix: str = "user_"):
+        """Take ownership of a [n_users * rows_per_user, dim] float32 CUDA tensor holding equal-size tenants back to back
+        (store must be empty, dim % 8 == 0): user f"{user_prefix}{first_user + u}" owns rows [u*rows_per_user,
+        (u+1)*rows_per_user), ids are implicit f"{user}/{i}".  The multi-tenant benchmark layout (BASELINE configs[4]):
+        no per-row Python objects, one tag fill on the device."""
+        with self._lock:
+            assert self._n == 0 and rows.is_cuda and rows.dtype == torch.float32 and rows.is_contiguous()
+            assert rows.shape[1] % 8 == 0 and rows.shape[0] % rows_per_user == 0
+            n, n_users = rows.shape[0], rows.shape[0] // rows_per_user
+            self.dim = self._dim_p = int(rows.shape[1])
+            self.device = rows.device
+            self._rows = rows
+            self._gen += 1
+            self._graphs.clear()
+            self._norms = kernels.row_norms(rows, self._dim_p)
+            self._tags = (torch.arange(n, device=self.device, dtype=torch.int64) // rows_per_user).to(torch.int32)
+            self._row_user = np.repeat(np.arange(n_users, dtype=np.int32), rows_per_user)
+            self._n = n
+            for u in range(n_users):
+                name = f"{user_prefix}{first_user + u}"
+                self._users[name] = u
+                self._user_names.append(name)
+                self._span.append([u * rows_per_user, (u + 1) * rows_per_user])
+                self._live.append(rows_per_user)
+                self._blocks.append((u * rows_per_user, (u + 1) * rows_per_user, name + "/", 0))
+            self._version += 1
+
+    def user_spans(self):
+        """(lo int64 [n_users], hi int64 [n_users]) row span of every user, by user index (numpy, rebuilt on demand)."""
+        sp = np.asarray(self._span, dtype=np.int64).reshape(-1, 2)
+        return sp[:, 0].copy(), np.maximum(sp[:, 1], sp[:, 0])
+
     def get_nodes(self, user_id: str = "default") -> List[Dict[str, Any]]:
         with self._lock:
             u = self._user(user_id)
@@ -569,8 +601,11 @@ class B200Store:
     def search_ranges_device(self, queries: torch.Tensor, lo, hi, tag, k: int):
         """Exact search of query i over rows [lo[i], hi[i]) restricted to tag[i] (< 0: any live row)."""
         dev = self.device
-        as_dev = lambda a, dt: torch.as_tensor(np.asarray(a), dtype=dt).to(dev, non_blocking=True)
-        span = int(np.max(np.asarray(hi) - np.asarray(lo))) if len(lo) else 0
+        as_dev = lambda a, dt: a if isinstance(a, torch.Tensor) else torch.as_tensor(np.asarray(a), dtype=dt).to(dev, non_blocking=True)
+        if isinstance(lo, torch.Tensor):
+            span = int(getattr(lo, "_lz_max_span", 0)) or int((hi - lo).max().item())
+        else:
+            span = int(np.max(np.asarray(hi) - np.asarray(lo))) if len(lo) else 0
         n_chunks = kernels.default_chunks(max(span, 1), queries.shape[0], dev)
         return kernels.search_exact(self._rows, self._dim_p, self._norms, self._tags, queries, k, self._metric,
                                     row_range=(0, self._n), group_lo=as_dev(lo, torch.int64),

@@ -3,6 +3,10 @@ import os, sys, time
 sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..")))
 from lazzaro_b200 import _lib
 _lib.LIB_PATH = os.environ.get('LZ_LIB', _lib.LIB_PATH)
+if 'LZ_LIB' in os.environ:                     # an older build for A/B timing: bind only the symbols it has
+    import ctypes
+    _probe = ctypes.CDLL(_lib.LIB_PATH)
+    _lib.SIGNATURES = {k: v for k, v in _lib.SIGNATURES.items() if hasattr(_probe, k)}
 import torch
 from lazzaro_b200 import synth, kernels as K
 

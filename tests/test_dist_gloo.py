@@ -67,3 +67,19 @@ def test_partitioning_helpers():
     loads = [sum([5, 9, 1, 7, 3, 3][s] for s in o) for o in owned]
     assert abs(loads[0] - loads[1]) <= 2                 # greedy largest-first keeps the slabs even
     assert partition_shards([4, 4], 4)[2:] == [[], []]
+
+
+def test_tenant_routing_covers_every_query_once():
+    """TenantSearch.owner / route (configs[4]: users dealt to ranks in contiguous blocks): pure host bookkeeping."""
+    from lazzaro_b200.dist import TenantSearch
+
+    class _S:                                  # stands in for a store: only user_spans() is read at construction
+        def user_spans(self):
+            return np.arange(5) * 10, np.arange(1, 6) * 10
+
+    users = np.random.default_rng(0).integers(0, 20, 1000)
+    parts = [TenantSearch(_S(), 5, r, 4).route(users) for r in range(4)]
+    assert sorted(np.concatenate(parts).tolist()) == list(range(1000))
+    for r, idx in enumerate(parts):
+        assert (users[idx] // 5 == r).all()
+    assert TenantSearch(_S(), 5, 0, 4).owner(np.array([0, 4, 5, 19, 25])).tolist() == [0, 0, 1, 3, 3]

@@ -232,3 +232,36 @@ def test_graph_replay_survives_interleaved_shapes():
     st.add_nodes([{"id": f"x{i}", "content": "c", "embedding": rows[i].tolist()} for i in range(4000)], user_id="c")   # grows the columns
     assert len(st._graphs) < n_graphs or st._rows.shape[0] == 8192
     assert st.search_nodes(qs[0].tolist(), "a", 5) == want5[0]
+
+
+def test_tenant_search_routes_and_filters_by_user():
+    from oracle import flat_search
+    """configs[4]: equal-size tenants adopted in bulk; a routed batch returns, per query, the exact top-k of that
+    user's rows only (the reference's `.where(user_id = ...)` pre-filter, vector_store.py:136-139)."""
+    import torch
+    from lazzaro_b200 import synth
+    from lazzaro_b200.dist import TenantSearch
+    from lazzaro_b200.store import B200Store
+    n_users, per, dim = 40, 250, 64
+    rows_np, _ = synth.clustered_rows(n_users * per, dim, 8, seed=61)
+    world = 2
+    stores = []
+    for r in range(world):
+        st = B200Store()
+        st.adopt_tenants(torch.as_tensor(rows_np[r * 20 * per:(r + 1) * 20 * per]).cuda().contiguous(), per, first_user=r * 20)
+        stores.append(TenantSearch(st, 20, r, world))
+    users = np.random.default_rng(1).integers(0, n_users, 96)
+    qs = synth.queries_near_rows(rows_np, 96, seed=62)
+    got = {}
+    for ts in stores:
+        pos, ids, cnt = ts.search_host(qs, users, 7)
+        for p, row, c in zip(pos.tolist(), ids, cnt):
+            assert c == 7
+            got[p] = row + ts.rank * 20 * per                       # local row -> global row
+    assert sorted(got) == list(range(96))
+    for i in range(96):
+        u = users[i]
+        mask = np.zeros(n_users * per, bool); mask[u * per:(u + 1) * per] = True
+        want, _ = flat_search.flat_topk(rows_np, qs[i], 7, mask=mask)
+        np.testing.assert_array_equal(got[i], want)
+    assert stores[1].store.search_nodes(qs[0].tolist(), user_id="user_25", limit=3)[0].startswith("user_25/")

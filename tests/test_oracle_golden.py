@@ -245,3 +245,25 @@ def test_components_oracle_and_min_ancestor_form_match_reference():
         undirected = graph_ops.min_ancestor_labels(len(index), src, dst, np.where(walk > 0, 3, 0))
         order_dependent += int(len(set(undirected[:n_res].tolist())) != len([c for c in want]))
     assert order_dependent >= 2, "the fixture should include graphs where one-way edges change the components"
+
+
+def test_restated_reference_loops_match_reference(golden):
+    """oracle/ref_loops.py (the per-object Python loops bench.py times as the reference-shaped CPU baseline) against
+    what the reference's own loops produced: memory_shard.py:64-84 and memory_system.py:838-891."""
+    from oracle import ref_loops
+    g = golden
+    edges = ref_loops.make_edge_dict(g["dp_src"], g["dp_dst"], g["dp_w"])
+    nodes = {i: ref_loops.Node(i, [], float(s)) for i, s in enumerate(g["dp_sal"])}
+    pruned = ref_loops.decay_and_prune(edges, nodes, 0.01, 0.5)
+    assert pruned == int(g["dp_pruned"])
+    np.testing.assert_array_equal(np.array([[a, b] for a, b in edges], np.int32), g["dp_kept"])
+    np.testing.assert_array_equal(np.array([e.weight for e in edges.values()]), g["dp_kept_w"])
+    np.testing.assert_array_equal(np.array([n.salience for n in nodes.values()]), g["dp_sal_after"])
+    ref = _edges(g["ln_cross"])
+    rows, new = g["ln_rows"], g["ln_new"]
+    existing = [ref_loops.Node(f"e{i}", rows[i].astype(np.float64).tolist()) for i in range(rows.shape[0])]
+    fresh = [ref_loops.Node(f"x{i}", new[i].astype(np.float64).tolist()) for i in range(new.shape[0])]
+    made = {}
+    assert ref_loops.link_to_existing(fresh, existing, made) == len(ref)
+    assert [(a, b) for a, b, _, _ in ref] == list(made)
+    np.testing.assert_array_equal([w for _, _, w, _ in ref], [e.weight for e in made.values()])
