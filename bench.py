@@ -52,6 +52,8 @@ def parse():
     ap.add_argument("--shards", type=int, default=1024)
     ap.add_argument("--batch", type=int, default=1024)
     ap.add_argument("--no-batch1", action="store_true", help="skip the secondary batch-1 (HBM-bound) measurement")
+    ap.add_argument("--no-lanes", dest="lanes", action="store_false",
+                    help="time the K steps strictly one after another on one stream instead of on two alternating lanes")
     ap.add_argument("--no-k100", action="store_true", help="skip the top-100 sub-result (BASELINE configs[3] as written)")
     ap.add_argument("--no-configs", action="store_true", help="skip the cfg1 / cfg2 / cfg5_search sub-results")
     ap.add_argument("--k", type=int, default=10)
@@ -166,6 +168,8 @@ def workload(args):
                         f"{args.shards} semantic shards (BASELINE metric; configs[3] at k={args.k})",
             "rows": args.rows, "dim": args.dim, "batch": args.batch, "k": args.k,
             "l2_policy": "inputs (rows) are far larger than the 126 MB L2; no flush needed",
+            "issue": ("two lanes: step i+1's coarse pass overlaps step i's exact pass, all-gather and merge (ShardedSearch lanes)"
+                      if getattr(args, "lanes", False) and args.batch >= 8 else "one stream, one step after another"),
             "partitioning": f"rows split evenly over {args.gpus} GPU(s) by semantic shard; per-GPU top-k merged after an all-gather"}
 
 
@@ -229,6 +233,14 @@ def main():
     def step_device():
         return sharded.search_device(queries, args.k)
 
+    def steps_device_lanes(n_):
+        # K searches back to back on two lanes (two streams, two scratch sets): the exact pass + all-gather + merge of
+        # search i overlap the coarse pass of search i+1; every search is complete when the loop's join() returns
+        for i in range(n_):
+            out = sharded.search_device(queries, args.k, lane=i & 1)
+        sharded.join()
+        return out
+
     def step_e2e():
         if args.batch == 1 and world == 1:
             return store.search_nodes(q_host[0].tolist(), limit=args.k)       # the reference-shaped call
@@ -276,7 +288,11 @@ def main():
         step_e2e()
     e2e_block(2)
     with ClockSampler(local) as clocks:
-        ms_total, out = timed(step_device, args.steps)
+        if args.lanes and args.batch >= store.min_batch:
+            steps_device_lanes(4)
+            ms_total, out = timed(steps_device_lanes, args.steps, block=True)
+        else:
+            ms_total, out = timed(step_device, args.steps)
         # the dominant kernel alone (local scan + merge, no collective), for the roofline
         ms_kernel, _ = timed(lambda: store.search_device(queries, 0, args.k), args.steps)
         ms_e2e, out_e2e = timed(e2e_block, args.steps, block=True)

@@ -2031,7 +2031,11 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
     sp.cand = (const u64*)(s + L.cand); sp.cand_cnt = (const int32_t*)(s + L.cand_cnt);
     sp.cand_thr = (const float*)(s + L.cand_thr);
     sp.n_qtiles_pad = pl.n_qgroups * pl.cs; sp.n_slices = pl.n_slices; sp.kp = pl.kp; sp.cap = pl.cap; sp.k = k;
-    sp.cap_a = lz_next_pow2(2 * pl.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
+    sp.cap_a = lz_next_pow2(2 * pl.kp + 2 * kSelThreads);
+    // the rescoring loop pushes at most 128 rows between two compaction checks; for small k a 256-entry selector keeps the
+    // kernel's shared memory under what is left beside a resident GEMM CTA, so the exact pass of one search can run
+    // while the next search's coarse pass holds the SMs (ShardedSearch lanes)
+    sp.cap_b = k <= 16 ? lz_next_pow2(k + 128 + 32) : lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base; sp.sub = tiny_top1 ? 1 : kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;
@@ -2241,7 +2245,8 @@ extern "C" int lz_search_two_level(const void* shadow, const float* rows, int64_
     sp.tags = nullptr; sp.want_tag = -1; sp.row_lo = 0; sp.row_hi = n_rows_total;
     sp.cand = gp.cand; sp.cand_cnt = gp.cand_cnt; sp.cand_thr = gp.cand_thr;
     sp.n_qtiles_pad = 0; sp.n_slices = 0; sp.kp = L.kp; sp.cap = L.cap; sp.k = k;
-    sp.cap_a = lz_next_pow2(2 * L.kp + 2 * kSelThreads); sp.cap_b = lz_next_pow2(k + 2 * kSelThreads);
+    sp.cap_a = lz_next_pow2(2 * L.kp + 2 * kSelThreads);
+    sp.cap_b = k <= 16 ? lz_next_pow2(k + 128 + 32) : lz_next_pow2(k + 2 * kSelThreads);
     sp.id_base = id_base; sp.sub = kSub;
     sp.out_ids = out_ids; sp.out_scores = out_scores; sp.out_counts = out_counts; sp.certified = cert;
     sp.fb_list = fb_list; sp.fb_count = fb_count; sp.gthr = gthr; sp.metric = metric;

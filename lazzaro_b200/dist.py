@@ -52,23 +52,33 @@ class ShardedSearch:
         self._merge = merge or self._merge_cuda
         self._packed_merge = merge is None            # product path: lz_merge_topk_strided straight from the gathered block
         self._gather = self._part = self._cnt = None
+        self._lanes = {}                              # lane -> {"stream", "done", buffers}: searches kept in flight
 
     # -- the product path
-    def _local_cuda(self, queries: torch.Tensor, k: int, out=None):
-        ids, sc, cnt = self.store.search_device(queries, 0, k, id_base=self.row_offset, out=out)
+    def _local_cuda(self, queries: torch.Tensor, k: int, out=None, lane: int = 0):
+        ids, sc, cnt = self.store.search_device(queries, 0, k, id_base=self.row_offset, out=out, lane=lane)
         return ids, sc, cnt
 
     def _merge_cuda(self, ids: torch.Tensor, scores: torch.Tensor):
         from . import kernels
         return kernels.merge_topk(ids, scores, self.store._metric)
 
-    def search_device(self, queries: torch.Tensor, k: int):
+    def search_device(self, queries: torch.Tensor, k: int, lane: Optional[int] = None):
         """queries float32 [B, dim_p] on this rank's GPU (same batch on every rank) -> global
         (ids int64 [B,k], scores float64 [B,k], counts int32 [B]) on every rank.
+
+        lane = None: everything is enqueued on the current stream.  lane = 0 / 1 / ...: the search runs on that lane's
+        own stream with its own scratch and exchange buffers and returns at once; consecutive searches on DIFFERENT lanes
+        overlap on the GPU — the exact pass, all-gather and merge of one search run while the next search's coarse pass
+        (which holds every SM's shared memory but leaves room for the small exact-pass CTAs) is under way, which hides
+        the per-search fixed costs that do not shrink when the rows are split over more GPUs.  Results of a lane are
+        valid after join() (or after that lane's next call has been ordered behind them on its stream).
 
         The exchange is ONE all-gather per search: each rank's local search writes its ids and its scores' bits
         into one int64 block [2, B, k], the blocks are gathered into [world, 2, B, k], and the merge kernel reads
         the gathered block in place (lz_merge_topk_strided)."""
+        if lane is not None:
+            return self._search_on_lane(queries, k, int(lane))
         if self.world == 1:
             return self._local(queries, k)
         B, dev = queries.shape[0], queries.device
@@ -88,6 +98,37 @@ class ShardedSearch:
             from . import kernels
             return kernels.merge_topk_packed(self._gather, self.store._metric)
         return self._merge(self._gather[:, 0].contiguous(), self._gather[:, 1].contiguous().view(torch.float64))
+
+    def _search_on_lane(self, queries: torch.Tensor, k: int, lane: int):
+        dev = queries.device
+        L = self._lanes.get(lane)
+        if L is None:
+            L = self._lanes[lane] = {"stream": torch.cuda.Stream(device=dev), "done": None, "shape": None}
+        B = queries.shape[0]
+        ready = torch.cuda.Event()
+        ready.record()                                       # the queries (and anything before) on the caller's stream
+        with torch.cuda.stream(L["stream"]):
+            L["stream"].wait_event(ready)
+            if L["shape"] != (B, k):
+                L["part"] = torch.empty((2, B, k), dtype=torch.int64, device=dev)
+                L["gather"] = torch.empty((self.world, 2, B, k), dtype=torch.int64, device=dev)
+                L["cnt"] = torch.empty((B,), dtype=torch.int32, device=dev)
+                L["shape"] = (B, k)
+            part = L["part"]
+            out = self._local_cuda(queries, k, out=(part[0], part[1].view(torch.float64), L["cnt"]), lane=lane)
+            if self.world > 1:
+                self._all_gather(L["gather"], part)
+                from . import kernels
+                out = kernels.merge_topk_packed(L["gather"], self.store._metric)
+            L["done"] = torch.cuda.Event()
+            L["done"].record()
+        return out
+
+    def join(self):
+        """The current stream waits for every lane's last search."""
+        for L in self._lanes.values():
+            if L["done"] is not None:
+                torch.cuda.current_stream().wait_event(L["done"])
 
     def _all_gather(self, out: torch.Tensor, part: torch.Tensor):
         if dist.get_backend(self.group) == "gloo":           # CPU tests of the bookkeeping

@@ -119,7 +119,7 @@ class B200Store:
         # fp16 shadows by metric, built on first use: the store's own metric, and cosine on an l2 store when the
         # consolidation code asks for cosine neighbours (memory_system.py:858-867 ranks by cosine whatever the store does)
         self._shadows: Dict[int, _Shadow] = {}
-        self._bscratch: Optional[torch.Tensor] = None
+        self._bscratch: Dict[int, torch.Tensor] = {}      # tensor-core scratch per lane (searches in flight on different streams)
         self.last_certified: Optional[torch.Tensor] = None
         self._nodes_table = self                      # memory_system.py:1434-1439 reaches for this
         # search policy: "exact" (the parity mode: every row of the user is scored) or "two_level" (approximate:
@@ -508,12 +508,15 @@ class B200Store:
         return max(16, int(_lib.load().lz_search_exact_scratch_bytes(B, k, n_chunks)))
 
     def search_device(self, queries: torch.Tensor, user: int | str = 0, k: int = 10, id_base: int = 0,
-                      row_range=None, out=None, _own=None, metric: Optional[str] = None, margin: Optional[str] = None):
+                      row_range=None, out=None, _own=None, metric: Optional[str] = None, margin: Optional[str] = None,
+                      lane: int = 0):
         """Device-in / device-out search: queries float32 [B, dim_p] in HBM -> (ids, scores, counts)
         tensors, nothing synchronised.  Small batches: the exact fp64 scan over the user's row span; larger
         ones: the tensor-core path (same answer).
         `metric`  rank by "cosine" / "l2" instead of the store's own metric (a second fp16 shadow is built on first use)
         `margin`  certification margin of the tensor-core path for this call (default: the store's `margin`)
+        `lane`    which of the store's scratch buffers the tensor-core path uses: searches kept in flight on different
+                  streams must use different lanes
         `_own`    (internal) scratch / group tags owned by a captured CUDA graph instead of the store's shared ones."""
         u = self._user(user) if isinstance(user, str) else user
         lo, hi = self._span[u]
@@ -528,13 +531,13 @@ class B200Store:
         if batched:
             sh = self._shadow_for(mcode)
             need = int(_lib.load().lz_search_batched_scratch_bytes(hi - lo, B, k, self._dim_p))
-            if self._bscratch is None or self._bscratch.numel() < need:
-                self._bscratch = torch.empty(need, dtype=torch.uint8, device=self.device)
+            if lane not in self._bscratch or self._bscratch[lane].numel() < need:
+                self._bscratch[lane] = torch.empty(need, dtype=torch.uint8, device=self.device)
             det = sh.max_err if self._check_margin(margin or self.margin) == "worst_case" else None
             ids, sc, cnt, cert = kernels.search_batched(sh.t, self._rows, self._dim_p, self._norms, tags,
                                                         -1 if tags is None else u, queries, k, row_range=(lo, hi),
                                                         margin_sigmas=self.margin_sigmas, id_base=id_base,
-                                                        scratch=self._bscratch, n_rows_total=self._n,
+                                                        scratch=self._bscratch[lane], n_rows_total=self._n,
                                                         metric=mcode, max_row_norm=sh.max_norm, out=out,
                                                         det_row_err=det)
             self.last_certified = cert
@@ -557,6 +560,11 @@ class B200Store:
         if _own is not None:
             scratch = _own["scratch"]
             assert scratch.numel() >= need
+        elif lane != 0:
+            key = -lane                                    # exact-path scratch of the extra lanes lives beside the others
+            if key not in self._bscratch or self._bscratch[key].numel() < need:
+                self._bscratch[key] = torch.empty(need, dtype=torch.uint8, device=self.device)
+            scratch = self._bscratch[key]
         else:
             if self._scratch is None or self._scratch.numel() < need:
                 self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
@@ -803,7 +811,8 @@ class B200Store:
 
     def close(self):                                                  # vector_store.py:235-244
         with self._lock:
-            self._rows = self._norms = self._tags = self._scratch = self._bscratch = None
+            self._rows = self._norms = self._tags = self._scratch = None
+            self._bscratch.clear()
             self._shadows.clear()
             self._pin.clear()
             self._io.clear()

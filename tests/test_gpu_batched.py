@@ -149,3 +149,29 @@ def test_cfg4_size_10m_rows_properties():
     parts = [K.search_batched(shadow, rows, dim, norms, None, -1, qs, 10, row_range=r)[:2] for r in ((0, half), (half, n))]
     mids, msc, _ = K.merge_topk(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]), _lib.COSINE)
     assert torch.equal(mids, ids) and torch.equal(msc, sc)
+
+
+def test_searches_in_flight_on_two_lanes_give_the_same_answers():
+    """ShardedSearch lanes: consecutive searches on alternating lanes (own stream, own scratch) overlap on the GPU and
+    must return what the one-stream search returns — different query batches per step, so a scratch mix-up shows."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.dist import ShardedSearch
+    from lazzaro_b200.store import B200Store
+    rows_np, _ = synth.clustered_rows(60000, 128, 8, seed=5)
+    st = B200Store()
+    st.add_rows(rows_np)
+    ss = ShardedSearch(st, world=1)
+    batches = [torch.as_tensor(synth.queries_near_rows(rows_np, 96, seed=100 + i)).cuda() for i in range(6)]
+    want = [tuple(t.clone() for t in ss.search_device(q, 10)) for q in batches]
+    torch.cuda.synchronize()
+    got = []
+    for i, q in enumerate(batches):
+        out = ss.search_device(q, 10, lane=i & 1)
+        if i >= 1:                                       # a lane's buffers are reused two steps later: copy the previous result
+            pass
+        got.append(out)
+        if i % 2 == 1:
+            ss.join()
+            torch.cuda.current_stream().synchronize()
+            for j in (i - 1, i):
+                assert torch.equal(got[j][0], want[j][0]) and torch.equal(got[j][1], want[j][1]) and torch.equal(got[j][2], want[j][2])
