@@ -151,6 +151,21 @@ int lz_search_batched(const void* shadow, const float* rows, int64_t ld, int dim
                       int64_t* out_ids, double* out_scores, int32_t* out_counts, int32_t* out_certified,
                       void* stream);
 
+/* ONE query, ONE launch, no separate merge and no device->host copy: the call for a small store at the reference's own
+ * scale (10k rows), where launches and copies cost more than the scan.  Same answer as lz_search_exact for one query.
+ *   query      float32 [dim], 16-byte aligned, DEVICE-ACCESSIBLE — typically pinned host memory (cudaHostAlloc /
+ *              torch pin_memory: under unified addressing the host pointer is valid on the device), read in place
+ *   out_block  device-accessible, typically pinned host memory, k*16 + 8 bytes: [k int64 ids | k float64 scores |
+ *              int32 count | int32 flag]; the flag is set to `seq` by the kernel AFTER the answer is in place, so the
+ *              host may poll it instead of synchronising the stream (pass a different seq on every call)
+ *   scratch    device, >= lz_search_one_scratch_bytes(k); its first 256 bytes must be ZERO before the first call
+ *              (they hold the kernel's completion ticket, which it resets itself); one call at a time per scratch
+ *   tags / want_tag  as lz_search_exact with one group (want_tag < 0: any live row) */
+size_t lz_search_one_scratch_bytes(int k);
+int lz_search_one(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags, int want_tag,
+                  int64_t row_lo, int64_t row_hi, const float* query, int k, int metric, int64_t id_base,
+                  void* scratch, size_t scratch_bytes, void* out_block, int seq, void* stream);
+
 /* Exhaustive float64 top-k of query q over the UNION of n_ranges row ranges [range_lo[q*n_ranges + j],
  * range_hi[q*n_ranges + j]) (device int64 arrays; an empty range contributes nothing; ranges of one query must not
  * overlap) — the member scan of a two-level search whose probed shards differ per query, one pass, no merge of

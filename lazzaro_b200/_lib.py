@@ -32,6 +32,8 @@ SIGNATURES = {
     "lz_search_batched_scratch_bytes": (_sz, [_i64, _i32, _i32, _i32]),
     "lz_search_batched": (_i32, [_p, _p, _i64, _i32, _p, _p, _i32, _i64, _i64, _i64, _p, _i64, _i32, _i32, _f64,
                                  _i32, _f64, _f64, _i64, _p, _sz, _p, _p, _p, _p, _p]),
+    "lz_search_one_scratch_bytes": (_sz, [_i32]),
+    "lz_search_one": (_i32, [_p, _i64, _i32, _p, _p, _i32, _i64, _i64, _p, _i32, _i32, _i64, _p, _sz, _p, _i32, _p]),
     "lz_search_exact_ranges": (_i32, [_p, _i64, _i32, _p, _p, _p, _p, _i32, _i64, _p, _i64, _i32, _i32, _i32, _i32, _i64, _p, _sz,
                                       _p, _p, _p, _p]),
     "lz_search_two_level_scratch_bytes": (_sz, [_i32, _i32, _i32, _i32, _i32]),

@@ -50,6 +50,12 @@ struct ScanParams {
     u64* part_key; u32* part_id; int32_t* part_cnt;
     const int32_t* work_list;   // optional: indices of the queries to answer (group_size 1); others untouched
     const int32_t* work_count;  // device count of work_list entries
+    // fused single-query form (lz_search_one): at most 32 chunks; the LAST CTA to finish merges the chunk lists with one
+    // warp and writes the answer straight to `fused_out` (host-mapped memory), then the sequence number behind it
+    u32* fused_ticket;          // device counter, left at zero again by the merging CTA
+    unsigned char* fused_out;   // [k int64 ids | k float64 scores | int32 count | int32 flag]
+    int fused_seq; int metric; int64_t id_base;
+    int want_tag_all;           // tag wanted by every group when group_tag is null (-1: any live row)
     int n_ranges;               // > 1: group g scans the n_ranges ranges [group_lo[g*n_ranges + j], group_hi[...]) (the probed
                                 // shards of a two-level search); n_chunks is a multiple of n_ranges, chunk c works on range c / per
 };
@@ -97,7 +103,7 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
     int64_t lo = p.group_lo ? p.group_lo[ri] : p.row_lo;
     int64_t hi = p.group_hi ? p.group_hi[ri] : p.row_hi;
     if (hi < lo) hi = lo;
-    const int want_tag = p.group_tag ? p.group_tag[g] : -1;
+    const int want_tag = p.group_tag ? p.group_tag[g] : p.want_tag_all;
     const int64_t len = (hi - lo + per_range - 1) / per_range;
     const int64_t cta_lo = lo + (int64_t)(c % per_range) * len;
     const int64_t cta_hi = min(hi, cta_lo + len);
@@ -194,6 +200,52 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
         if (tid == 0) p.part_cnt[slot] = n;
     }
     __syncthreads();            // shared state is re-initialised by the next item
+    if (QB == 1 && p.fused_out != nullptr) {
+        // single query, <= 32 chunks: no second launch — the last CTA merges.  Lane l walks chunk l's sorted list; k rounds
+        // of a warp argmax under the (key desc, id asc) order give the global top-k.
+        __shared__ bool s_last;
+        if (tid == 0) {
+            __threadfence();
+            s_last = atomicAdd(p.fused_ticket, 1u) == (u32)p.n_chunks - 1u;
+        }
+        __syncthreads();
+        if (s_last && warp == 0) {
+            __threadfence();
+            const int cnt = lane < p.n_chunks ? __ldcg(p.part_cnt + lane) : 0;
+            int pos = 0;
+            int64_t* o_ids = reinterpret_cast<int64_t*>(p.fused_out);
+            double* o_sc = reinterpret_cast<double*>(p.fused_out + (size_t)p.k * 8);
+            int32_t* o_cnt = reinterpret_cast<int32_t*>(p.fused_out + (size_t)p.k * 16);
+            int found = 0;
+            for (int r = 0; r < p.k; ++r) {
+                u64 hk = pos < cnt ? __ldcg(p.part_key + (size_t)lane * p.k + pos) : 0ull;
+                u32 hi = pos < cnt ? __ldcg(p.part_id + (size_t)lane * p.k + pos) : 0xffffffffu;
+                u64 bk = hk; u32 bi = hi; int bl = lane;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) {
+                    const u64 ok = __shfl_xor_sync(0xffffffffu, bk, o);
+                    const u32 oi = __shfl_xor_sync(0xffffffffu, bi, o);
+                    const int ol = __shfl_xor_sync(0xffffffffu, bl, o);
+                    if (lz_better(ok, oi, bk, bi)) { bk = ok; bi = oi; bl = ol; }
+                }
+                if (bk == 0ull) break;                                        // every list exhausted (warp-uniform)
+                if (lane == bl) ++pos;
+                if (lane == 0) {
+                    const double v = lz_unord(bk);
+                    o_ids[r] = (int64_t)bi + p.id_base;
+                    o_sc[r] = p.metric == LZ_COSINE ? v : 0.0 - v;
+                }
+                ++found;
+            }
+            if (lane == 0) {
+                for (int r = found; r < p.k; ++r) { o_ids[r] = -1; o_sc[r] = __longlong_as_double(0x7ff8000000000000ll); }
+                *o_cnt = found;
+                *p.fused_ticket = 0u;                                         // ready for the next call
+                __threadfence_system();                                       // the answer is in host memory before the flag
+                *reinterpret_cast<volatile int32_t*>(p.fused_out + (size_t)p.k * 16 + 4) = p.fused_seq;
+            }
+        }
+    }
     }
 }
 
@@ -523,6 +575,8 @@ int lz_search_exact_impl(const float* rows, int64_t ld, int dim, const double* n
     p.queries = queries; p.q_ld = q_ld; p.n_queries = n_queries;
     p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows);
     p.work_list = work_list; p.work_count = work_count; p.n_ranges = n_ranges;
+    p.fused_ticket = nullptr; p.fused_out = nullptr; p.fused_seq = 0; p.metric = metric; p.id_base = id_base;
+    p.want_tag_all = -1;
     unsigned char* s = (unsigned char*)scratch;
     p.part_key = (u64*)s;
     p.part_id = (u32*)(s + slots * k * sizeof(u64));
@@ -557,6 +611,47 @@ extern "C" int lz_search_exact(const float* rows, int64_t ld, int dim, const dou
     return lz_search_exact_impl(rows, ld, dim, norms, tags, row_lo, row_hi, group_lo, group_hi, group_tag, queries,
                                 q_ld, n_queries, group_size, k, metric, n_chunks, id_base, scratch, scratch_bytes,
                                 out_ids, out_scores, out_counts, nullptr, nullptr, stream, 1);
+}
+
+extern "C" size_t lz_search_one_scratch_bytes(int k) {
+    return lz_search_exact_scratch_bytes(1, k, 32) + 256;
+}
+
+extern "C" int lz_search_one(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags, int want_tag,
+                             int64_t row_lo, int64_t row_hi, const float* query, int k, int metric, int64_t id_base,
+                             void* scratch, size_t scratch_bytes, void* out_block, int seq, void* stream) {
+    if (int rc = check_rows("lz_search_one", rows, ld, dim)) return rc;
+    LZ_REQUIRE(metric == LZ_COSINE || metric == LZ_L2, "lz_search_one: unknown metric %d", metric);
+    LZ_REQUIRE(metric == LZ_L2 || norms != nullptr, "lz_search_one: cosine needs norms");
+    LZ_REQUIRE(k >= 1 && k <= LZ_MAX_K, "lz_search_one: k=%d outside 1..%d", k, LZ_MAX_K);
+    LZ_REQUIRE(query && ((uintptr_t)query & 15) == 0 && out_block && scratch, "lz_search_one: NULL or misaligned pointer");
+    LZ_REQUIRE(0 <= row_lo && row_lo <= row_hi && row_hi <= 0xfffffffeLL, "lz_search_one: bad row range");
+    const size_t need = lz_search_one_scratch_bytes(k);
+    if (scratch_bytes < need) {
+        lz_set_error("lz_search_one: scratch has %zu bytes, needs %zu", scratch_bytes, need);
+        return LZ_ERR_SCRATCH;
+    }
+    const int sms = lz_sm_count();
+    if (sms <= 0) return LZ_ERR_DEVICE;
+    int64_t chunks = (row_hi - row_lo + 255) / 256;                       // at least ~256 rows per CTA, at most 32 CTAs
+    const int n_chunks = (int)(chunks < 1 ? 1 : (chunks > 32 ? 32 : chunks));
+    ScanParams p = {};
+    p.rows = rows; p.ld = ld; p.dim = dim; p.norms = norms; p.tags = tags;
+    p.row_lo = row_lo; p.row_hi = row_hi;
+    p.queries = query; p.q_ld = dim; p.n_queries = 1;
+    p.k = k; p.n_chunks = n_chunks; p.cap = lz_next_pow2(k + kChunkRows);
+    p.n_ranges = 1; p.metric = metric; p.id_base = id_base;
+    unsigned char* s = (unsigned char*)scratch;
+    p.fused_ticket = (u32*)s;                                              // zero before the first call (the caller clears the scratch once)
+    s += 256;
+    const size_t slots = 32;
+    p.part_key = (u64*)s;
+    p.part_id = (u32*)(s + slots * k * sizeof(u64));
+    p.part_cnt = (int32_t*)(s + (((slots * k * (sizeof(u64) + sizeof(u32))) + 15) & ~(size_t)15));
+    p.fused_out = (unsigned char*)out_block; p.fused_seq = seq;
+    p.group_tag = nullptr;
+    p.want_tag_all = tags != nullptr ? want_tag : -1;
+    return launch_scan<1>(p, metric, 1, (cudaStream_t)stream);
 }
 
 extern "C" int lz_search_exact_ranges(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,

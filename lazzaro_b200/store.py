@@ -103,6 +103,10 @@ class B200Store:
         self._graphs: Dict[tuple, object] = {}
         self._gtags: Dict[tuple, torch.Tensor] = {}
         self.use_graphs = True                 # CUDA-graph replay of the (launch-bound) exact path for host calls
+        self.use_fused_one = True              # single host queries: ONE launch reading the query from pinned host memory and
+                                               # writing the answer back to it (lz_search_one), the host polls a flag
+        self._one: Dict[int, dict] = {}        # per k: pinned query / answer block, device scratch, sequence number
+        self.fused_one_max_rows = 65_536       # beyond this a 32-CTA scan is slower than the full-grid scan + merge
         self._scratch: Optional[torch.Tensor] = None
         self._gen = 0                          # bumped whenever rows / norms / tags are reallocated or repacked
         if batched_search not in ("auto", "never", "always"):
@@ -445,6 +449,41 @@ class B200Store:
             io = self._io[key] = (q_pin, q_dev, o_dev, o_pin, views(o_dev), tuple(v.numpy() for v in views(o_pin)))
         return io
 
+    def _search_one_host(self, q: np.ndarray, u: int, k: int):
+        """One host query through lz_search_one: the kernel reads the query from pinned host memory, scans the user's row
+        span in at most 32 CTAs, the last CTA merges and writes ids / scores / count into pinned host memory followed by
+        a sequence flag that this thread polls — one launch, no copies enqueued, no stream synchronisation."""
+        st = self._one.get(k)
+        lib = _lib.load()
+        if st is None:
+            q_pin = torch.zeros(self._dim_p, dtype=torch.float32).pin_memory()
+            out = torch.zeros(k * 16 + 8, dtype=torch.uint8).pin_memory()
+            nbytes = int(lib.lz_search_one_scratch_bytes(k))
+            scratch = torch.zeros(nbytes, dtype=torch.uint8, device=self.device)      # zero: the completion ticket
+            o = out.numpy()
+            st = self._one[k] = {"q_pin": q_pin, "q": q_pin.numpy(), "out": out, "scratch": scratch, "nbytes": nbytes, "seq": 0,
+                                 "ids": o[:k * 8].view(np.int64), "sc": o[k * 8:k * 16].view(np.float64),
+                                 "cnt": o[k * 16:k * 16 + 4].view(np.int32), "flag": o[k * 16 + 4:].view(np.int32)}
+        st["q"][:self.dim] = q[0]
+        st["seq"] = seq = (st["seq"] % 0x7ffffff0) + 1
+        lo, hi = self._span[u]
+        single_user = len(self._user_names) == 1 and self._live[u] == self._n
+        with torch.cuda.device(self.device):
+            stream = torch.cuda.current_stream()
+            _lib.check(lib.lz_search_one(self._rows.data_ptr(), self._rows.stride(0), self._dim_p, self._norms.data_ptr(),
+                                         None if single_user else self._tags.data_ptr(), -1 if single_user else u, lo, hi,
+                                         st["q_pin"].data_ptr(), k, self._metric, 0, st["scratch"].data_ptr(), st["nbytes"],
+                                         st["out"].data_ptr(), seq, stream.cuda_stream), "lz_search_one")
+            flag = st["flag"]
+            for _ in range(200_000):                       # the answer usually lands within ~20 us
+                if flag[0] == seq:
+                    break
+            else:
+                stream.synchronize()
+                if flag[0] != seq:
+                    raise _lib.LazzaroB200Error("lz_search_one finished without publishing its answer")
+        return st["ids"][None, :], st["sc"][None, :], st["cnt"]
+
     def _search_host(self, q: np.ndarray, u: int, limit: int):
         """host queries [B, dim] -> (row ids int64 [B,k], scores float64 [B,k], counts int32 [B]) as numpy
         views of a pinned buffer (valid until the next search), one stream synchronisation at the end."""
@@ -452,6 +491,8 @@ class B200Store:
             raise ValueError(f"query has {q.shape[1]} dims, store has {self.dim}")
         k = self._check_limit(limit, u)
         B = q.shape[0]
+        if B == 1 and self.use_fused_one and self._span[u][1] - self._span[u][0] <= self.fused_one_max_rows:
+            return self._search_one_host(q, u, k)           # small spans: launches and copies cost more than the scan
         q_pin, q_dev, o_dev, o_pin, dev_views, host_views = self._io_buffers(B, k)
         with torch.cuda.device(self.device):
             q_pin[:, :self.dim] = torch.from_numpy(q)
@@ -813,6 +854,7 @@ class B200Store:
         with self._lock:
             self._rows = self._norms = self._tags = self._scratch = None
             self._bscratch.clear()
+            self._one.clear()
             self._shadows.clear()
             self._pin.clear()
             self._io.clear()

@@ -265,3 +265,34 @@ def test_tenant_search_routes_and_filters_by_user():
         want, _ = flat_search.flat_topk(rows_np, qs[i], 7, mask=mask)
         np.testing.assert_array_equal(got[i], want)
     assert stores[1].store.search_nodes(qs[0].tolist(), user_id="user_25", limit=3)[0].startswith("user_25/")
+
+
+def test_single_query_fused_path_equals_the_two_launch_path():
+    """lz_search_one (one launch, query and answer in pinned host memory, host polls a flag) against the regular exact
+    path and the oracle: several users, limits, deletions in between, both metrics, limit above the live row count."""
+    from oracle import flat_search
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    rows, _ = synth.clustered_rows(9000, 96, 6, seed=71)
+    qs = synth.queries_near_rows(rows, 10, seed=72)
+    for metric in ("cosine", "l2"):
+        st, ref = B200Store(metric=metric), FlatStore(metric=metric)
+        for s in (st, ref):
+            s.add_nodes([{"id": f"a{i}", "content": "", "embedding": rows[i].tolist()} for i in range(6000)], user_id="a")
+            s.add_nodes([{"id": f"b{i}", "content": "", "embedding": rows[6000 + i].tolist()} for i in range(3000)], user_id="b")
+        assert st.use_fused_one
+        for rounds in range(2):
+            for u in ("a", "b", "nobody"):
+                for q in qs:
+                    for limit in (1, 10, 64):
+                        got = st.search_nodes(q.tolist(), user_id=u, limit=limit)
+                        assert got == ref.search_nodes(q.tolist(), user_id=u, limit=limit)
+            st.use_fused_one = False
+            slow = [st.search_nodes(q.tolist(), user_id="a", limit=10) for q in qs]
+            st.use_fused_one = True
+            assert slow == [st.search_nodes(q.tolist(), user_id="a", limit=10) for q in qs]
+            for s in (st, ref):
+                s.delete_nodes([f"a{i}" for i in range(0, 6000, 3)], user_id="a")
+        few = B200Store(metric=metric)
+        few.add_nodes([{"id": f"n{i}", "content": "", "embedding": rows[i].tolist()} for i in range(3)])
+        assert few.search_nodes(qs[0].tolist(), limit=10) == [f"n{i}" for i in flat_search.flat_topk(rows[:3], qs[0], 3, metric)[0]]
