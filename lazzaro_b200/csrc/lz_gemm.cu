@@ -1232,10 +1232,40 @@ __global__ void __launch_bounds__(kSelThreads) assign_rescore_kernel(SelectParam
 // from HBM once, a candidate costs dim*4 bytes of shared-memory traffic.  When a block needs more distinct table rows
 // than fit, they are staged in rounds and a query is re-read in the rounds that hold some of its candidates.
 // Summation order per pair is the exact scan's, so scores are bit-identical to it.
-constexpr int kMultiQ = 1024;            // queries per CTA
+constexpr int kMultiQ = 512;             // queries per CTA
 constexpr int kMultiLive = 16;           // surviving candidates kept per query (more: the direct path)
 constexpr int kMultiThreads = 512;
 constexpr int kMultiTable = kBucketGroups * kSub;     // table rows the bitmap covers (2048)
+
+// float64 scores of N (1..4) cached table rows against one query held in registers: N independent accumulation chains,
+// each in the exact scan's summation order; lane-level partial sums are reduced across the warp.
+template <int NSEG, int METRIC, int N>
+__device__ __forceinline__ void assign_dots(const float* const (&xr)[4], const double (&qd)[NSEG][4], double (&acc)[4]) {
+#pragma unroll
+    for (int c = 0; c < N; ++c) acc[c] = 0.0;
+#pragma unroll
+    for (int sg = 0; sg < NSEG; ++sg) {
+        float4 x[N];
+#pragma unroll
+        for (int c = 0; c < N; ++c) x[c] = *reinterpret_cast<const float4*>(xr[c] + 128 * sg);
+#pragma unroll
+        for (int c = 0; c < N; ++c) {
+            if (METRIC == LZ_COSINE) {
+                acc[c] = fma((double)x[c].x, qd[sg][0], acc[c]); acc[c] = fma((double)x[c].y, qd[sg][1], acc[c]);
+                acc[c] = fma((double)x[c].z, qd[sg][2], acc[c]); acc[c] = fma((double)x[c].w, qd[sg][3], acc[c]);
+            } else {
+                const double d0 = (double)x[c].x - qd[sg][0], d1 = (double)x[c].y - qd[sg][1];
+                const double d2 = (double)x[c].z - qd[sg][2], d3 = (double)x[c].w - qd[sg][3];
+                acc[c] = fma(d0, d0, acc[c]); acc[c] = fma(d1, d1, acc[c]);
+                acc[c] = fma(d2, d2, acc[c]); acc[c] = fma(d3, d3, acc[c]);
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+        for (int c = 0; c < N; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+}
 
 template <int NSEG, int METRIC>
 __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParams p, int n_queries, int cache_rows) {
@@ -1248,6 +1278,8 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
     u32* s_bid = reinterpret_cast<u32*>(s_T + kMultiQ);                                 // [kMultiQ]
     unsigned short* s_list = reinterpret_cast<unsigned short*>(s_bid + kMultiQ);        // [kMultiQ][kMultiLive] table row - row_lo
     signed char* s_nlive = reinterpret_cast<signed char*>(s_list + (size_t)kMultiQ * kMultiLive);   // [kMultiQ], -1 = direct path
+    // per warp two staging buffers for query rows: the next query is fetched (cp.async) while the current one is scored
+    float* s_stage = reinterpret_cast<float*>(smem + ((size_t)cache_rows * (kStride * 4 + 8) + (size_t)kMultiQ * (8 + 4 + 4 + 2 * kMultiLive + 1) + 15) / 16 * 16);
     __shared__ u32 s_bits[kMultiTable / 32];
     __shared__ int s_pref[kMultiTable / 32 + 1];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1255,6 +1287,7 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
     const int q0 = blockIdx.x * kMultiQ;
     const int nq = min(kMultiQ, n_queries - q0);
     for (int i = tid; i < kMultiTable / 32; i += kMultiThreads) s_bits[i] = 0u;
+    for (int i = tid; i < kWarps * 2 * kStride; i += kMultiThreads) s_stage[i] = 0.f;     // the pads beyond dim stay zero
     __syncthreads();
     // A. one thread per query: best coarse candidate, the rows within 2 eps of it, the block's bitmap of needed rows
     for (int i = tid; i < nq; i += kMultiThreads) {
@@ -1323,10 +1356,48 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
             if (lane == 0) s_cnorm[slot] = METRIC == LZ_COSINE ? p.norms[p.row_lo + rel] : 0.0;
         }
         __syncthreads();
-        // every warp walks the block's queries; a query with candidates in this round is loaded once as float64
-        for (int i = warp; i < nq; i += kWarps) {
+        // every warp walks the block's queries; a query with candidates in this round is fetched once — asynchronously
+        // into the warp's staging buffer while the previous query is being scored — and held as float64 in registers
+        float* stage = s_stage + (size_t)warp * 2 * kStride;
+        const bool one_round = r0 == 0 && r1 == n_distinct;
+        auto has_work = [&](int i) -> bool {
             const int nl = s_nlive[i];
-            if (nl <= 0) continue;                                             // warp-uniform
+            if (nl <= 0) return false;
+            if (one_round) return true;
+            for (int j = 0; j < nl; ++j) {
+                const int rel = s_list[i * kMultiLive + j];
+                const int rank = s_pref[rel >> 5] + __popc(s_bits[rel >> 5] & ((1u << (rel & 31)) - 1u));
+                if (rank >= r0 && rank < r1) return true;
+            }
+            return false;
+        };
+        auto next_row = [&](int i) -> int {
+            i += kWarps;
+            while (i < nq && !has_work(i)) i += kWarps;
+            return i;
+        };
+        auto issue = [&](int i, int b) {
+            const float* qp = p.queries + (int64_t)(q0 + i) * p.q_ld;
+#pragma unroll
+            for (int sg = 0; sg < NSEG; ++sg) {
+                const int e = lane * 4 + 128 * sg;
+                if (e < p.dim)
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(stage + b * kStride + e)), "l"(qp + e) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
+        };
+        int cur = next_row(warp - kWarps), buf = 0;
+        if (cur < nq) issue(cur, 0);
+        while (cur < nq) {
+            const int i = cur;
+            const int nxt = next_row(cur);
+            if (nxt < nq) {
+                issue(nxt, buf ^ 1);
+                asm volatile("cp.async.wait_group 1;" ::: "memory");
+            } else {
+                asm volatile("cp.async.wait_group 0;" ::: "memory");
+            }
+            const int nl = s_nlive[i];
             int slots[kMultiLive];
             int n_here = 0;
 #pragma unroll
@@ -1337,16 +1408,15 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
                     if (rank >= r0 && rank < r1) slots[n_here++] = (rank - r0) | (rel << 16);
                 }
             }
-            if (n_here == 0) continue;
-            const float* qp = p.queries + (int64_t)(q0 + i) * p.q_ld;
             double qd[NSEG][4];
             double qs = 0.0;
 #pragma unroll
             for (int sg = 0; sg < NSEG; ++sg) {
-                const int e = lane * 4 + 128 * sg;
-                const float4 v = e < p.dim ? lz_ldg_stream(qp + e) : make_float4(0.f, 0.f, 0.f, 0.f);
+                const float4 v = *reinterpret_cast<const float4*>(stage + buf * kStride + lane * 4 + 128 * sg);   // pads stay zero
                 qd[sg][0] = v.x; qd[sg][1] = v.y; qd[sg][2] = v.z; qd[sg][3] = v.w;
             }
+            cur = nxt;
+            buf ^= 1;
 #pragma unroll
             for (int sg = 0; sg < NSEG; ++sg)
 #pragma unroll
@@ -1354,10 +1424,13 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
             const double qn = sqrt(lz_warp_sum(qs));
             u64 bkey = s_bkey[i];
             u32 bid = s_bid[i];
-            // four candidates at a time: four independent accumulation chains (each in the exact scan's order) keep the
-            // float64 pipe busy; a lone chain of dim/32 dependent DFMAs per pair left the warp waiting on its own latency
             constexpr int kAt = 4;
+            // (A float32 pre-pass over the candidates, keeping only those within 2e-5 of the best for the float64 pass, was
+            // tried: parity-green but slower, 4.62 vs 4.24 ms with ~10 candidates per row — the loop is bound by the
+            // shared-memory reads of the cached table rows, which a pre-pass repeats, not by the float64 arithmetic.)
+            // Up to four candidates at a time: independent accumulation chains, each in the exact scan's order
             for (int j0 = 0; j0 < n_here; j0 += kAt) {
+                const int n_valid = min(kAt, n_here - j0);
                 const float* xr[kAt];
                 int slot[kAt], rel[kAt];
 #pragma unroll
@@ -1368,33 +1441,13 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
                     xr[c] = s_rows + (size_t)slot[c] * kStride + lane * 4;
                 }
                 double acc[kAt];
-#pragma unroll
-                for (int c = 0; c < kAt; ++c) acc[c] = 0.0;
-#pragma unroll
-                for (int sg = 0; sg < NSEG; ++sg) {
-                    float4 x[kAt];
-#pragma unroll
-                    for (int c = 0; c < kAt; ++c) x[c] = *reinterpret_cast<const float4*>(xr[c] + 128 * sg);
-#pragma unroll
-                    for (int c = 0; c < kAt; ++c) {
-                        if (METRIC == LZ_COSINE) {
-                            acc[c] = fma((double)x[c].x, qd[sg][0], acc[c]); acc[c] = fma((double)x[c].y, qd[sg][1], acc[c]);
-                            acc[c] = fma((double)x[c].z, qd[sg][2], acc[c]); acc[c] = fma((double)x[c].w, qd[sg][3], acc[c]);
-                        } else {
-                            const double d0 = (double)x[c].x - qd[sg][0], d1 = (double)x[c].y - qd[sg][1];
-                            const double d2 = (double)x[c].z - qd[sg][2], d3 = (double)x[c].w - qd[sg][3];
-                            acc[c] = fma(d0, d0, acc[c]); acc[c] = fma(d1, d1, acc[c]);
-                            acc[c] = fma(d2, d2, acc[c]); acc[c] = fma(d3, d3, acc[c]);
-                        }
-                    }
-                }
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-                    for (int c = 0; c < kAt; ++c) acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], o);
+                if (n_valid == 4) assign_dots<NSEG, METRIC, 4>(xr, qd, acc);          // warp-uniform dispatch: no work on padding
+                else if (n_valid == 1) assign_dots<NSEG, METRIC, 1>(xr, qd, acc);
+                else if (n_valid == 2) assign_dots<NSEG, METRIC, 2>(xr, qd, acc);
+                else assign_dots<NSEG, METRIC, 3>(xr, qd, acc);
 #pragma unroll
                 for (int c = 0; c < kAt; ++c) {
-                    if (j0 + c >= n_here) break;                               // warp-uniform
+                    if (c >= n_valid) break;                                   // warp-uniform
                     double sc;
                     if (METRIC == LZ_COSINE) {
                         const double den = s_cnorm[slot[c]] * qn;
@@ -2044,9 +2097,10 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
         const size_t fixed = (size_t)kMultiQ * (8 + 4 + 4 + 2 * kMultiLive + 1) + 64;
         const int nseg0 = (dim + 127) / 128, nseg = nseg0 <= 2 ? 2 : nseg0 <= 4 ? 4 : nseg0 <= 6 ? 6 : 8;
         const size_t row_bytes = (size_t)nseg * 512 + 8;
-        int cache_rows = (int)((200 * 1024 - fixed) / row_bytes);
+        const size_t stage_bytes = (size_t)(kMultiThreads / 32) * 2 * nseg * 512 + 16;     // two query rows per warp
+        int cache_rows = (int)((200 * 1024 - fixed - stage_bytes) / row_bytes);
         if (cache_rows > 64) cache_rows = 64;
-        const size_t msmem = fixed + (size_t)cache_rows * row_bytes;
+        const size_t msmem = fixed + stage_bytes + (size_t)cache_rows * row_bytes;
         auto mk = metric == LZ_COSINE
                       ? (nseg == 2 ? assign_multi_kernel<2, LZ_COSINE> : nseg == 4 ? assign_multi_kernel<4, LZ_COSINE>
                          : nseg == 6 ? assign_multi_kernel<6, LZ_COSINE> : assign_multi_kernel<8, LZ_COSINE>)
