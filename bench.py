@@ -463,11 +463,15 @@ def main():
         cen_sep = graph[torch.randperm(n_g, device=dev, generator=torch.Generator(device=dev).manual_seed(9))[:kc]].contiguous()
         f_assign = lambda: consolidate.assign_to_centroids(graph, cen_sep)
         f_assign_co = lambda: consolidate.assign_to_centroids(graph, cen)
+        f_assign_res = lambda: consolidate.assign_store_rows(store, cen_sep, (0, n_g))      # the store's own shadow as the query side
+        f_assign_co_res = lambda: consolidate.assign_store_rows(store, cen, (0, n_g))
         f_update = lambda: consolidate.centroid_means(graph, seg_offsets=seg)
         parts = {}
         for name, fn, flops in (("dedup_10k_x_1M_top1", f_dedup, 2.0 * n_new * n_g * args.dim),
                                 ("assign_1M_x_1024_member_rows", f_assign, 2.0 * n_g * kc * args.dim),
                                 ("assign_1M_x_1024_coincident", f_assign_co, 2.0 * n_g * kc * args.dim),
+                                ("assign_1M_x_1024_member_rows_resident", f_assign_res, 2.0 * n_g * kc * args.dim),
+                                ("assign_1M_x_1024_coincident_resident", f_assign_co_res, 2.0 * n_g * kc * args.dim),
                                 ("centroid_update_1M", f_update, None)):
             for _ in range(2):
                 fn()
@@ -480,10 +484,12 @@ def main():
                 parts[name]["gbs"] = n_g * args.dim * 4 / (ms_c / 5 * 1e-3) / 1e9
                 parts[name]["frac_of_hbm_peak"] = parts[name]["gbs"] / hbm_peak
         line["consolidation"] = {"metric": "consolidation wall time: dedup 10k x 1M + shard reassignment (k=1024) + centroid update, 768-d",
-                                 "value": sum(v["ms"] for k_, v in parts.items() if k_ != "assign_1M_x_1024_coincident"),
-                                 "value_with_coincident_centroids": sum(v["ms"] for k_, v in parts.items() if k_ != "assign_1M_x_1024_member_rows"),
+                                 "value": sum(parts[k_]["ms"] for k_ in ("dedup_10k_x_1M_top1", "assign_1M_x_1024_member_rows_resident", "centroid_update_1M")),
+                                 "value_with_coincident_centroids": sum(parts[k_]["ms"] for k_ in ("dedup_10k_x_1M_top1", "assign_1M_x_1024_coincident_resident", "centroid_update_1M")),
+                                 "value_note": "dedup + reassignment of the graph's rows as they sit in the store (its fp16 shadow is the query side) + centroid update; "
+                                               "the parts without `_resident` convert the rows on every call (rows that are not in a store)",
                                  "unit": "ms", "higher_is_better": False,
-                                 "parts": parts, "gpu_launches": 5 * (7 + 3 + 1)}
+                                 "parts": parts, "gpu_launches": 5 * (7 + 4 * 5 + 1)}
         del new, cen, cen_sep
     if not args.no_configs:
         from lazzaro_b200.dist import TenantSearch
