@@ -221,6 +221,7 @@ struct GemmParams {
     const int4* items;        // [*n_items_dev] x = q-tile, y = first row, z = end row (of the shard slice)
     const int* n_items_dev;
     const int32_t* qmap;      // [perm rows] real query index of a permuted query row, -1 = padding
+    int debug_skip;           // profiling only (LZ_DEBUG_SKIP): 1 = the epilogue drains the accumulators without reading them
 };
 
 // What one CTA works on: a q-tile against rows tiles row_begin, row_begin + stride, ... (n_tiles of them); rows at or
@@ -511,6 +512,14 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 // query's neighbours.  TMEM loads are double-buffered in registers (load chunk c+1, scan c).
                 const uint32_t tacc = tmem_base + ((uint32_t)(quarter * 32) << 16) + acc * BN;
                 uint32_t va[32], vb[32];
+                if (p.debug_skip & 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty[acc]);
+                    acc ^= 1;
+                    if (acc == 0) acc_phase ^= 1;
+                    continue;
+                }
                 tmem_ld32(tacc, va);
 #pragma unroll 1
                 for (int c = 0; c < BN / 32; c += 2) {
@@ -2031,6 +2040,7 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
         g.row_lo = row_lo; g.row_hi = row_hi; g.kp = pl.kp; g.cap = pl.cap;
         g.tags = tags; g.want_tag = want_tag; g.gthr = gthr; g.top1_eps = tiny_top1 ? eps : nullptr;
         g.cand = (u64*)(s + L.cand); g.cand_cnt = (int32_t*)(s + L.cand_cnt); g.cand_thr = (float*)(s + L.cand_thr);
+        g.debug_skip = env_int("LZ_DEBUG_SKIP", 0);
         const size_t smem = kGemmSmem;
         auto kern = pl.kp == 32 ? gemm_topk_kernel<2> : pl.kp == 128 ? gemm_topk_kernel<8>
                     : pl.kp == 256 ? gemm_topk_kernel<16> : gemm_topk_kernel<32>;

@@ -60,7 +60,7 @@ struct ScanParams {
                                 // shards of a two-level search); n_chunks is a multiple of n_ranges, chunk c works on range c / per
 };
 
-template <int QB, int METRIC>
+template <int QB, int METRIC, bool FUSED = false>
 __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -200,7 +200,7 @@ __global__ void __launch_bounds__(kThreads, 2) scan_kernel(ScanParams p) {
         if (tid == 0) p.part_cnt[slot] = n;
     }
     __syncthreads();            // shared state is re-initialised by the next item
-    if (QB == 1 && p.fused_out != nullptr) {
+    if (FUSED) {
         // single query, <= 32 chunks: no second launch — the last CTA merges.  Lane l walks chunk l's sorted list; k rounds
         // of a warp argmax under the (key desc, id asc) order give the global top-k.
         __shared__ bool s_last;
@@ -480,10 +480,10 @@ size_t scan_smem_bytes(int qb, int dim, int cap) {
     return (size_t)qb * nseg * 1024 + (size_t)qb * cap * 12;
 }
 
-template <int QB>
+template <int QB, bool FUSED = false>
 int launch_scan(const ScanParams& p, int metric, int n_groups, cudaStream_t st) {
     const size_t smem = scan_smem_bytes(QB, p.dim, p.cap);
-    auto kern = metric == LZ_COSINE ? scan_kernel<QB, LZ_COSINE> : scan_kernel<QB, LZ_L2>;
+    auto kern = metric == LZ_COSINE ? scan_kernel<QB, LZ_COSINE, FUSED> : scan_kernel<QB, LZ_L2, FUSED>;
     LZ_REQUIRE(smem <= 220 * 1024, "lz_search_exact: k=%d dim=%d needs %zu B of shared memory", p.k, p.dim, smem);
     LZ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t grid = (int64_t)n_groups * p.n_chunks;
@@ -651,7 +651,7 @@ extern "C" int lz_search_one(const float* rows, int64_t ld, int dim, const doubl
     p.fused_out = (unsigned char*)out_block; p.fused_seq = seq;
     p.group_tag = nullptr;
     p.want_tag_all = tags != nullptr ? want_tag : -1;
-    return launch_scan<1>(p, metric, 1, (cudaStream_t)stream);
+    return launch_scan<1, true>(p, metric, 1, (cudaStream_t)stream);
 }
 
 extern "C" int lz_search_exact_ranges(const float* rows, int64_t ld, int dim, const double* norms, const int32_t* tags,
