@@ -1559,7 +1559,7 @@ struct GroupParams {
     int32_t* qmap;        // [max_ptiles * BM], pre-set to -1
     int64_t* range_lo;    // [n_queries * nprobe] the pair's row range (for the exact fallback)
     int64_t* range_hi;
-    int4* items; int* n_items; int max_items, max_ptiles, grid, max_nsl;
+    int4* items; int* n_items; int max_items, max_ptiles, grid, max_nsl, per_cta;
 };
 
 __global__ void __launch_bounds__(256) group_count_kernel(GroupParams g) {
@@ -1601,7 +1601,7 @@ __global__ void __launch_bounds__(1024) group_layout_kernel(GroupParams g) {
         long long w = 0;
         int mr = 0;
         for (int i = 0; i < 32; ++i) { w += s_red[i]; mr = max(mr, s_scan[0][i]); }
-        long long T = (w + 3ll * g.grid - 1) / (3ll * g.grid);               // ~3 items per CTA
+        long long T = (w + (long long)g.per_cta * g.grid - 1) / ((long long)g.per_cta * g.grid);   // ~per_cta items per CTA
         const long long t_min = (mr + g.max_nsl - 1) / g.max_nsl;            // at most max_nsl slices per q-tile
         if (T < t_min) T = t_min;
         if (T < 1) T = 1;
@@ -2259,6 +2259,8 @@ extern "C" int lz_search_two_level(const void* shadow, const float* rows, int64_
     g.range_lo = (int64_t*)(s + L.range_lo); g.range_hi = (int64_t*)(s + L.range_hi);
     g.items = (int4*)(s + L.items); g.n_items = (int*)(s + L.n_items);
     g.max_items = L.max_items; g.max_ptiles = L.max_ptiles; g.grid = L.grid; g.max_nsl = L.max_nsl;
+    g.per_cta = env_int("LZ_TL_ITEMS_PER_CTA", 3);
+    if (g.per_cta < 1 || g.per_cta > 3) g.per_cta = 3;                       // the item buffer is sized for 3
     const int pairs = n_queries * nprobe;
     LZ_CUDA(cudaMemsetAsync(g.cnt, 0, (size_t)n_shards * 4, st));
     LZ_CUDA(cudaMemsetAsync(g.qmap, 0xff, (size_t)L.max_ptiles * BM * 4, st));

@@ -187,15 +187,18 @@ class ShardedSearch:
                 ready = torch.cuda.Event()
                 ready.record()
             main.wait_event(ready)
-            ids, sc, cnt = self.search_device(qd, k)
+            # the search itself runs on the slot's lane (own stream, own scratch): with two slots alternating, the exact
+            # pass, exchange and read-back of one search overlap the coarse pass of the next
+            ids, sc, cnt = self.search_device(qd, k, lane=slot)
             h_ids = st._pinned(f"ids{slot}", (B, k), torch.int64)
             h_sc = st._pinned(f"sc{slot}", (B, k), torch.float64)
             h_cnt = st._pinned(f"cnt{slot}", (B,), torch.int32)
-            h_ids.copy_(ids, non_blocking=True)
-            h_sc.copy_(sc, non_blocking=True)
-            h_cnt.copy_(cnt, non_blocking=True)
-            done = torch.cuda.Event()
-            done.record()
+            with torch.cuda.stream(self._lanes[slot]["stream"]):
+                h_ids.copy_(ids, non_blocking=True)
+                h_sc.copy_(sc, non_blocking=True)
+                h_cnt.copy_(cnt, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record()
         return _PendingSearch(done, h_ids, h_sc, h_cnt)
 
 
