@@ -238,6 +238,17 @@ int lz_merge_topk_strided(const int64_t* in_ids, const double* in_scores, int64_
                           int n_queries, int k, int metric, int64_t* out_ids, double* out_scores,
                           int32_t* out_counts, void* stream);
 
+/* The exchange step of the multi-GPU search in one call: ncclAllGather of this rank's packed block, then the
+ * strided merge, both on `stream`.  No reference counterpart (the reference is a single process).
+ *   nccl_comm    an ncclComm_t (passed as void*) of `world` ranks, one per GPU, created by the NCCL library that is
+ *                loaded in this process (resolved with dlopen at first use; no NCCL is needed unless this is called)
+ *   local_block  int64 [2, n_queries, k]: this rank's ids (global row ids, -1 = empty) then its float64 scores' bits —
+ *                what lz_search_exact / lz_search_batched write when out_ids / out_scores point into one block
+ *   gathered     int64 [world, 2, n_queries, k] receive buffer
+ * Every rank ends with the same global top-k.  Each rank's kernels read that rank's own memory only. */
+int lz_allgather_merge(void* nccl_comm, int world, const int64_t* local_block, int64_t* gathered, int n_queries, int k,
+                       int metric, int64_t* out_ids, double* out_scores, int32_t* out_counts, void* stream);
+
 /* Exact float64 scores of explicit (query, row) pairs — the rescoring step after a coarse pass and
  * the pairwise cosine of memory_system.py:197-203.  pair_q int32 [n_pairs], pair_row int64
  * [n_pairs] (row < 0 gives NaN); out float64 [n_pairs]. */

@@ -43,6 +43,7 @@ SIGNATURES = {
     "lz_assign_nearest": (_i32, [_p, _p, _i64, _i32, _p, _i32, _f64, _p, _i64, _i64, _p, _p, _f64, _p, _sz, _p, _p, _p, _p, _p]),
     "lz_merge_topk": (_i32, [_p, _p, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_merge_topk_strided": (_i32, [_p, _p, _i64, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
+    "lz_allgather_merge": (_i32, [_p, _i32, _p, _p, _i32, _i32, _i32, _p, _p, _p, _p]),
     "lz_score_pairs": (_i32, [_p, _i64, _i32, _p, _p, _i64, _p, _p, _i64, _i32, _p, _p]),
     "lz_group_by_label_scratch_bytes": (_sz, [_i64, _i32]),
     "lz_group_by_label": (_i32, [_p, _i64, _i32, _p, _sz, _p, _p, _p]),

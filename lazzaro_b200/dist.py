@@ -308,3 +308,51 @@ class TenantSearch:
             h_cnt.copy_(cnt, non_blocking=True)
             torch.cuda.current_stream().synchronize()
         return mine, h_ids.numpy().copy(), h_cnt.numpy().copy()
+
+
+class NcclExchange:
+    """The exchange step through the C-ABI (lz_allgather_merge) instead of torch.distributed: what a non-Python binding of
+    include/lazzaro_b200.h would do.  Owns an ncclComm_t created with the NCCL library already loaded in this process
+    (the unique id travels through the initialised torch.distributed group, which is used for nothing else here)."""
+
+    def __init__(self, group=None):
+        import ctypes as C
+        self._C = C
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self._nccl = C.CDLL("libnccl.so.2")
+
+        class _Uid(C.Structure):
+            _fields_ = [("internal", C.c_char * 128)]
+        uid = _Uid()
+        if self.rank == 0:
+            rc = self._nccl.ncclGetUniqueId(C.byref(uid))
+            assert rc == 0, f"ncclGetUniqueId failed ({rc})"
+        box = [C.string_at(C.byref(uid), 128) if self.rank == 0 else None]      # all 128 bytes (the field access stops at a NUL)
+        dist.broadcast_object_list(box, src=0, group=group)
+        C.memmove(C.byref(uid), box[0], 128)
+        self.comm = C.c_void_p()
+        self._nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, _Uid, C.c_int]
+        rc = self._nccl.ncclCommInitRank(C.byref(self.comm), self.world, uid, self.rank)
+        assert rc == 0, f"ncclCommInitRank failed ({rc})"
+
+    def allgather_merge(self, part: torch.Tensor, metric: int):
+        """part int64 [2, B, k] (ids | score bits) on this GPU -> (ids, scores, counts) merged over all ranks."""
+        from . import _lib
+        from ._lib import check, ptr, stream_ptr
+        dev = part.device
+        _, B, k = part.shape
+        gathered = torch.empty((self.world, 2, B, k), dtype=torch.int64, device=dev)
+        ids = torch.empty((B, k), dtype=torch.int64, device=dev)
+        sc = torch.empty((B, k), dtype=torch.float64, device=dev)
+        cnt = torch.empty((B,), dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(_lib.load().lz_allgather_merge(self.comm, self.world, ptr(part), ptr(gathered), B, k, int(metric), ptr(ids), ptr(sc),
+                                                 ptr(cnt), stream_ptr(dev)), "lz_allgather_merge")
+        self._keep = gathered                          # alive until the stream has consumed it
+        return ids, sc, cnt
+
+    def close(self):
+        if self.comm:
+            self._nccl.ncclCommDestroy.argtypes = [self._C.c_void_p]
+            self._nccl.ncclCommDestroy(self.comm)
+            self.comm = None
