@@ -481,6 +481,7 @@ class B200Store:
             else:
                 stream.synchronize()
                 if flag[0] != seq:
+                    st["scratch"][:256].zero_()             # an aborted launch may have left the completion ticket half way
                     raise _lib.LazzaroB200Error("lz_search_one finished without publishing its answer")
         return st["ids"][None, :], st["sc"][None, :], st["cnt"]
 
