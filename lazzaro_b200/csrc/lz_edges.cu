@@ -7,14 +7,19 @@
 // look-back across tiles (tile order taken from an atomic ticket so a tile never waits on one that
 // has not started).  Survivors are staged in shared memory and written back coalesced.
 #include "lz_common.cuh"
+#include "lz_sm100.cuh"
 
+#include <cmath>
 #include <mutex>
+#include <stdlib.h>
 
 namespace {
 
 constexpr int kThreads = 256;
 constexpr int kItems = 8;                       // edges per thread (two 128-bit loads per array)
 constexpr int kTile = kThreads * kItems;        // 2048 edges per tile
+
+constexpr int kGroup = 64;                      // tiles per group of the two-pass form's offset sums
 
 constexpr u64 kFlagAgg = 1ull << 62;            // tile aggregate published
 constexpr u64 kFlagPrefix = 2ull << 62;         // inclusive prefix published
@@ -47,7 +52,10 @@ struct PruneParams {
     u32* ticket;       // zeroed before launch
     int64_t* out_kept;
     int n_tiles;
-    const int64_t* offsets;   // two-pass mode: exclusive prefix of the per-tile survivor counts
+    const int64_t* offsets;   // two-pass mode with the scan kernel: exclusive prefix of the per-tile survivor counts
+    const int32_t* counts;    // two-pass mode: survivors per tile ...
+    const u64* group_sum;     // ... and per group of kGroup tiles; a CTA sums what lies before it (offsets == nullptr)
+    float wstar; int use_wstar;   // factor > 0: keep <=> not (w < wstar), see prune_bound()
 };
 
 // CHAINED = true: single pass, tile order from an atomic ticket, offsets by decoupled look-back (safe in
@@ -59,6 +67,7 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
     __shared__ float s_w[kTile];
     __shared__ int s_cooc[kTile];
     __shared__ int s_warp[kThreads / 32];
+    __shared__ long long s_pre[kThreads / 32];
     __shared__ u32 s_tile;
     __shared__ long long s_prefix;
     __shared__ int s_total;
@@ -96,6 +105,14 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
             v_cooc[j] = in ? p.cooc[base + j] : 0;
         }
     }
+    // two-pass form without the scan kernel: what lies before this tile = the sums of the groups before its group +
+    // the counts of the tiles before it in its group (a handful of L2 loads per thread, in flight beside the columns)
+    long long before = 0;
+    if (!CHAINED && p.offsets == nullptr) {
+        const int g = tile / kGroup;
+        for (int i = tid; i < g; i += kThreads) before += (long long)p.group_sum[i];
+        if (tid < tile - g * kGroup) before += p.counts[g * kGroup + tid];
+    }
     // decay in float64, strict '<' prune in float64, store the float32 rounding
     unsigned keep = 0;
     int cnt = 0;
@@ -115,6 +132,11 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
         if (lane >= o) incl += t;
     }
     if (lane == 31) s_warp[warp] = incl;
+    if (!CHAINED && p.offsets == nullptr) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) before += __shfl_xor_sync(0xffffffffu, before, o);
+        if (lane == 0) s_pre[warp] = before;
+    }
     __syncthreads();
     if (warp == 0) {
         int ws = lane < kThreads / 32 ? s_warp[lane] : 0;
@@ -142,7 +164,17 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
     }
     __syncthreads();
     if (!CHAINED) {
-        if (tid == 0) s_prefix = p.offsets[tile];
+        if (tid == 0) {
+            if (p.offsets != nullptr) {
+                s_prefix = p.offsets[tile];
+            } else {
+                long long b = 0;
+#pragma unroll
+                for (int i = 0; i < kThreads / 32; ++i) b += s_pre[i];
+                s_prefix = b;
+                if (tile == p.n_tiles - 1) *p.out_kept = b + s_total;
+            }
+        }
     } else if (warp == 0) {
         const int total = s_total;
         // decoupled look-back: publish the aggregate, then walk predecessors 32 at a time
@@ -184,9 +216,317 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
     }
 }
 
+// ---- streamed single-pass form -------------------------------------------------------------------
+// One pass, every column read from HBM once, and no warp on the data path ever waits for another CTA.
+// A CTA is 16 compute warps plus three service warps and works through tiles whose numbers it draws from the
+// ticket, with a ring of `stages` tile buffers in shared memory and a small queue of tile records:
+//   count warp    runs `ahead` tiles in front of the data path: draws the next ticket, fetches that tile's weights
+//                 (8 KB bulk copy, L2 evict-last), counts the survivors and publishes the tile's aggregate
+//   offset warp   turns aggregates into output offsets.  Tiles form waves of kWave consecutive tickets;
+//                 offset(t) = wave_prefix[wave of t] + the aggregates of the tiles before t in its wave (at most
+//                 kWave/32 loads per lane, all issued at once); the CTA holding a wave's last tile publishes the next
+//                 wave's prefix.  Because the aggregates were published `ahead` tiles early, the offset is there
+//                 long before the data path asks for it
+//   loader warp   issues each tile's four column segments as plain bulk copies (cp.async.bulk global -> shared,
+//                 completion on the stage's mbarrier) as soon as a stage is free; the weights come out of the L2
+//   compute warps flags from shared memory, block scan, compaction in place in the stage buffer, coalesced
+//                 write-out at the tile's offset, stage handed back
+// Ticket order keeps it deadlock-free: a tile waits only for tiles with smaller tickets, and those are held by
+// CTAs that are running.  When outputs alias inputs (AHEAD = false) a tile's aggregate must not be published
+// before its columns are in shared memory (a later tile may overwrite them once it knows its offset), so there
+// the compute warps publish it after reading the stage and the count warp only draws tickets.
+constexpr int kMaxStages = 8;
+constexpr int kStreamThreads = 512;             // compute threads per CTA of the streamed form (4 edges each)
+constexpr int kStreamWarps = kStreamThreads / 32 + 3;
+constexpr int kWave = 256;                      // tiles per wave of the offset scheme
+constexpr int kQueue = 16;                      // tile records per CTA (>= ahead + 2)
+
+struct TileRec { int tile; int total; long long prefix; };
+
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(sm100::smem_u32(smem_dst)), "l"(gmem_src), "r"(bytes), "r"(sm100::smem_u32(bar)), "l"(policy) : "memory");
+}
+__device__ __forceinline__ uint64_t policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ uint64_t policy_evict_last() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
+__device__ __forceinline__ void named_bar(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ int ld_vol(const int* p) { return *reinterpret_cast<const volatile int*>(p); }
+__device__ __forceinline__ void st_vol(int* p, int v) { *reinterpret_cast<volatile int*>(p) = v; }
+__device__ __forceinline__ void wait_above(const int* counter, int n) {        // until *counter > n
+    while (ld_vol(counter) <= n) __nanosleep(20);
+    __threadfence_block();
+}
+
+// keep = not (float64(w) * factor < thr).  For factor > 0 that is monotone in w, so it equals not (w < wstar) for a
+// float32 bound found on the host; the float64 form stays for every other factor.
+__device__ __forceinline__ bool keep_edge(float w, const PruneParams& p) {
+    return p.use_wstar ? !(w < p.wstar) : !((double)w * p.factor < p.thr);
+}
+
+template <int THREADS, int ITEMS, bool AHEAD>
+__global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PruneParams p, int stages, int ahead) {
+    constexpr int TILE = THREADS * ITEMS;
+    constexpr int NW = THREADS / 32;
+    static_assert(TILE == kTile && NW <= 32 && ITEMS % 4 == 0, "tile geometry");
+    extern __shared__ __align__(128) unsigned char s_ring[];          // stages x [4 columns][TILE] words (+ TILE weights)
+    __shared__ uint64_t full[kMaxStages], empty[kMaxStages], cbar[2];
+    __shared__ TileRec queue[kQueue];
+    __shared__ int q_drawn, q_counted, q_offset, q_scattered;          // how many records each role has finished
+    __shared__ int s_tile[kMaxStages];
+    __shared__ int s_warp[2][NW];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        for (int s = 0; s < stages; ++s) { sm100::mbar_init(&full[s], 1); sm100::mbar_init(&empty[s], NW); }
+        sm100::mbar_init(&cbar[0], 1); sm100::mbar_init(&cbar[1], 1);
+        sm100::fence_mbar_init();
+        q_drawn = q_counted = q_offset = q_scattered = 0;
+    }
+    __syncthreads();
+
+    if (warp == NW) {
+        // ---------------- count warp ----------------
+        float* cw = reinterpret_cast<float*>(s_ring + (size_t)stages * 16 * TILE);      // two buffers of TILE weights
+        const uint64_t keep_in_l2 = policy_evict_last();
+        // draws the ticket of record n and starts the copy of that tile's weights; -1 past the last tile
+        auto fetch = [&](int n) -> int {
+            while (n - ld_vol(&q_scattered) >= ahead) __nanosleep(20);
+            int tile = 0;
+            if (lane == 0) tile = (int)atomicAdd(p.ticket, 1u);
+            tile = __shfl_sync(0xffffffffu, tile, 0);
+            if (tile >= p.n_tiles) return -1;
+            if (AHEAD && lane == 0 && (int64_t)(tile + 1) * TILE <= p.n) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                sm100::mbar_expect_tx(&cbar[n & 1], 4u * TILE);
+                bulk_load(cw + (n & 1) * TILE, p.w + (int64_t)tile * TILE, 4u * TILE, &cbar[n & 1], keep_in_l2);
+            }
+            return tile;
+        };
+        int tile = fetch(0);
+        for (int n = 0;; ++n) {
+            TileRec* e = &queue[n % kQueue];
+            if (lane == 0) {
+                e->tile = tile;
+                __threadfence_block();
+                st_vol(&q_drawn, n + 1);                                   // the loader may fetch the tile from here on
+                if (tile < 0 && AHEAD) st_vol(&q_counted, n + 1);          // aliased call: the compute warps pass the end mark on
+            }
+            if (tile < 0) break;
+            const int next = fetch(n + 1);                                 // in flight while this tile is counted
+            if (AHEAD) {
+                const int64_t base = (int64_t)tile * TILE;
+                int cnt = 0;
+                if (base + TILE <= p.n) {
+                    sm100::mbar_wait(&cbar[n & 1], (n >> 1) & 1);
+                    const float4* src = reinterpret_cast<const float4*>(cw + (n & 1) * TILE);
+#pragma unroll 4
+                    for (int r = 0; r < TILE / 128; ++r) {
+                        const float4 v = src[r * 32 + lane];
+                        cnt += keep_edge(v.x, p) + keep_edge(v.y, p) + keep_edge(v.z, p) + keep_edge(v.w, p);
+                    }
+                } else {
+                    for (int i = lane; base + i < p.n; i += 32) cnt += keep_edge(p.w[base + i], p);
+                }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+                if (lane == 0) {
+                    e->total = cnt;
+                    st_state(p.state + tile, kFlagAgg | (u64)cnt);
+                    __threadfence_block();
+                    st_vol(&q_counted, n + 1);
+                }
+            }
+            __syncwarp();
+            tile = next;
+        }
+        return;
+    }
+    if (warp == NW + 1) {
+        // ---------------- loader warp ----------------
+        const uint64_t stream_through = policy_evict_first();
+        for (int n = 0;; ++n) {
+            wait_above(&q_drawn, n);
+            const int tile = queue[n % kQueue].tile;
+            const int s = n % stages;
+            if (n >= stages) sm100::mbar_wait(&empty[s], ((n / stages) - 1) & 1);
+            int* buf = reinterpret_cast<int*>(s_ring) + (size_t)s * 4 * TILE;
+            const int64_t base = (int64_t)tile * TILE;
+            if (tile < 0) {
+                if (lane == 0) { s_tile[s] = -1; sm100::mbar_arrive(&full[s]); }
+                break;
+            }
+            if (base + TILE <= p.n) {
+                if (lane == 0) {
+                    s_tile[s] = tile;
+                    sm100::mbar_expect_tx(&full[s], 16u * TILE);
+                    bulk_load(buf + 2 * TILE, p.w + base, 4u * TILE, &full[s], stream_through);
+                    bulk_load(buf, p.src + base, 4u * TILE, &full[s], stream_through);
+                    bulk_load(buf + TILE, p.dst + base, 4u * TILE, &full[s], stream_through);
+                    bulk_load(buf + 3 * TILE, p.cooc + base, 4u * TILE, &full[s], stream_through);
+                }
+            } else {                                   // the ragged last tile: guarded loads by this warp
+                for (int i = lane; i < TILE; i += 32) {
+                    const bool in = base + i < p.n;
+                    buf[i] = in ? p.src[base + i] : 0;
+                    buf[TILE + i] = in ? p.dst[base + i] : 0;
+                    buf[2 * TILE + i] = in ? __float_as_int(p.w[base + i]) : 0;
+                    buf[3 * TILE + i] = in ? p.cooc[base + i] : 0;
+                }
+                __syncwarp();
+                if (lane == 0) { s_tile[s] = tile; sm100::mbar_arrive(&full[s]); }
+            }
+            __syncwarp();
+        }
+        return;
+    }
+    if (warp == NW + 2) {
+        // ---------------- offset warp ----------------
+        u64* wave_prefix = p.state + p.n_tiles;                       // [n_waves + 1]; wave 0 starts at 0
+        for (int n = 0;; ++n) {
+            wait_above(&q_counted, n);
+            TileRec* e = &queue[n % kQueue];
+            const int tile = e->tile;
+            if (tile < 0) break;
+            const int total = e->total;
+            long long sum;
+            if (p.offsets != nullptr) {                               // measurement mode: offsets precomputed
+                sum = p.offsets[tile];
+            } else {
+                const int w = tile / kWave, j = tile % kWave;
+                const u64* agg = p.state + (size_t)w * kWave;
+                u64 v[kWave / 32];
+                u64 wp = kFlagPrefix;
+#pragma unroll
+                for (int r = 0; r < kWave / 32; ++r) {
+                    const int idx = j - 1 - lane - 32 * r;
+                    v[r] = idx >= 0 ? ld_state(agg + idx) : kFlagAgg;
+                }
+                if (lane == 0 && w > 0) wp = ld_state(wave_prefix + w);
+                while (true) {
+                    bool pending = (wp >> 62) == 0;
+#pragma unroll
+                    for (int r = 0; r < kWave / 32; ++r) pending = pending || (v[r] >> 62) == 0;
+                    if (!__any_sync(0xffffffffu, pending)) break;
+                    __nanosleep(40);
+#pragma unroll
+                    for (int r = 0; r < kWave / 32; ++r)
+                        if ((v[r] >> 62) == 0) v[r] = ld_state(agg + (j - 1 - lane - 32 * r));
+                    if ((wp >> 62) == 0) wp = ld_state(wave_prefix + w);
+                }
+                sum = lane == 0 ? (long long)(wp & kValueMask) : 0;
+#pragma unroll
+                for (int r = 0; r < kWave / 32; ++r) sum += (long long)(v[r] & kValueMask);
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+                if (lane == 0 && j == kWave - 1) st_state(wave_prefix + w + 1, kFlagPrefix | (u64)(sum + total));
+            }
+            if (lane == 0) {
+                e->prefix = sum;
+                if (tile == p.n_tiles - 1) *p.out_kept = sum + total;
+                __threadfence_block();
+                st_vol(&q_offset, n + 1);
+            }
+            __syncwarp();
+        }
+        return;
+    }
+
+    // ---------------- compute warps ----------------
+    for (int it = 0;; ++it) {
+        const int s = it % stages, par = it & 1;
+        sm100::mbar_wait(&full[s], (it / stages) & 1);
+        const int tile = s_tile[s];
+        if (tile < 0) {
+            if (!AHEAD && tid == 0) st_vol(&q_counted, it + 1);
+            break;
+        }
+        int* buf = reinterpret_cast<int*>(s_ring) + (size_t)s * 4 * TILE;
+        const int64_t base = (int64_t)tile * TILE + (int64_t)tid * ITEMS;
+        int v_src[ITEMS], v_dst[ITEMS], v_cooc[ITEMS];
+        float v_w[ITEMS];
+#pragma unroll
+        for (int h = 0; h < ITEMS / 4; ++h) {
+            const int4 a = reinterpret_cast<const int4*>(buf)[tid * (ITEMS / 4) + h];
+            const int4 b = reinterpret_cast<const int4*>(buf + TILE)[tid * (ITEMS / 4) + h];
+            const int4 c = reinterpret_cast<const int4*>(buf + 2 * TILE)[tid * (ITEMS / 4) + h];
+            const int4 d = reinterpret_cast<const int4*>(buf + 3 * TILE)[tid * (ITEMS / 4) + h];
+            v_src[4 * h] = a.x; v_src[4 * h + 1] = a.y; v_src[4 * h + 2] = a.z; v_src[4 * h + 3] = a.w;
+            v_dst[4 * h] = b.x; v_dst[4 * h + 1] = b.y; v_dst[4 * h + 2] = b.z; v_dst[4 * h + 3] = b.w;
+            v_w[4 * h] = __int_as_float(c.x); v_w[4 * h + 1] = __int_as_float(c.y);
+            v_w[4 * h + 2] = __int_as_float(c.z); v_w[4 * h + 3] = __int_as_float(c.w);
+            v_cooc[4 * h] = d.x; v_cooc[4 * h + 1] = d.y; v_cooc[4 * h + 2] = d.z; v_cooc[4 * h + 3] = d.w;
+        }
+        unsigned keep = 0;
+        int cnt = 0;
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            const bool k = (base + j < p.n) && keep_edge(v_w[j], p);
+            v_w[j] = (float)((double)v_w[j] * p.factor);
+            keep |= (unsigned)k << j;
+            cnt += k;
+        }
+        int incl = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_warp[par][warp] = incl;
+        named_bar(1, THREADS);                         // every thread has read its items out of the stage by now
+        // every warp scans the warp totals for itself
+        const int ws = lane < NW ? s_warp[par][lane] : 0;
+        int wi = ws;
+#pragma unroll
+        for (int o = 1; o < NW; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, wi, o);
+            if (lane >= o) wi += t;
+        }
+        const int total = __shfl_sync(0xffffffffu, wi, NW - 1);
+        if (!AHEAD && warp == 0 && lane == 0) {        // aliased call: the aggregate goes out only now, with the columns on chip
+            TileRec* e = &queue[it % kQueue];
+            e->total = total;
+            st_state(p.state + tile, kFlagAgg | (u64)total);
+            __threadfence_block();
+            st_vol(&q_counted, it + 1);
+        }
+        int off = __shfl_sync(0xffffffffu, wi - ws, warp) + incl - cnt;
+#pragma unroll
+        for (int j = 0; j < ITEMS; ++j) {
+            if (keep >> j & 1) {
+                buf[off] = v_src[j]; buf[TILE + off] = v_dst[j];
+                buf[2 * TILE + off] = __float_as_int(v_w[j]); buf[3 * TILE + off] = v_cooc[j];
+                ++off;
+            }
+        }
+        named_bar(1, THREADS);                         // compaction complete
+        wait_above(&q_offset, it);
+        const int64_t out0 = queue[it % kQueue].prefix;
+        for (int i = tid; i < total; i += THREADS) {
+            p.o_src[out0 + i] = buf[i];
+            p.o_dst[out0 + i] = buf[TILE + i];
+            p.o_w[out0 + i] = __int_as_float(buf[2 * TILE + i]);
+            p.o_cooc[out0 + i] = buf[3 * TILE + i];
+        }
+        __syncwarp();
+        if (lane == 0) {
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the next writer of this stage is a bulk copy
+            sm100::mbar_arrive(&empty[s]);
+            if (warp == 0) st_vol(&q_scattered, it + 1);
+        }
+    }
+}
+
 // First pass of the two-pass form: survivors per tile (reads the weights only, 4 B per edge).
 __global__ void __launch_bounds__(kThreads) count_kernel(const float* __restrict__ w, int64_t n, double factor, double thr,
-                                                         int32_t* __restrict__ counts) {
+                                                         int32_t* __restrict__ counts, u64* __restrict__ group_sum) {
     __shared__ int s_warp[kThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t base = (int64_t)blockIdx.x * kTile + (int64_t)tid * kItems;
@@ -213,6 +553,7 @@ __global__ void __launch_bounds__(kThreads) count_kernel(const float* __restrict
 #pragma unroll
         for (int i = 0; i < kThreads / 32; ++i) t += s_warp[i];
         counts[blockIdx.x] = t;
+        if (group_sum != nullptr) atomicAdd((unsigned long long*)(group_sum + blockIdx.x / kGroup), (unsigned long long)t);
     }
 }
 
@@ -289,13 +630,81 @@ int elementwise_blocks(int64_t n) {
     return (int)(blocks < cap ? (blocks < 1 ? 1 : blocks) : cap);
 }
 
+// Streamed form: ring depth, run-ahead and CTAs per SM fixed at first use (LZ_PRUNE_STAGES / LZ_PRUNE_AHEAD / LZ_PRUNE_CTAS
+// override them for measurements).  Scratch: ticket word, one aggregate word per tile, one prefix word per wave; this
+// call zeroes them.
+struct StreamCfg { int stages = 3, ahead = 6, ctas_per_sm = 0; bool ready = false; };
+StreamCfg g_stream_cfg;
+std::mutex g_stream_mu;
+
+size_t stream_state_words(int64_t tiles) { return (size_t)(1 + tiles + tiles / kWave + 2); }
+
+// The smallest float32 w with not (float64(w) * factor < thr), for factor > 0 (the product is monotone in w then).
+bool prune_bound(double factor, double thr, float* out) {
+    if (!(factor > 0.0) || !std::isfinite(factor) || !std::isfinite(thr)) return false;
+    auto pruned = [&](float w) { return (double)w * factor < thr; };
+    float c = (float)(thr / factor);
+    if (!std::isfinite(c)) return false;
+    for (int i = 0; i < 8 && pruned(c); ++i) c = nextafterf(c, INFINITY);
+    for (int i = 0; i < 8; ++i) {
+        const float d = nextafterf(c, -INFINITY);
+        if (pruned(d)) break;
+        c = d;
+    }
+    if (pruned(c) || !pruned(nextafterf(c, -INFINITY))) return false;
+    *out = c;
+    return true;
+}
+
+int launch_stream(PruneParams p, void* scratch, bool aliased, cudaStream_t st) {
+    StreamCfg c;
+    constexpr int kItemsS = kTile / kStreamThreads;
+    {
+        std::lock_guard<std::mutex> lock(g_stream_mu);
+        if (!g_stream_cfg.ready) {
+            if (const char* e = getenv("LZ_PRUNE_STAGES")) g_stream_cfg.stages = max(2, min(kMaxStages, atoi(e)));
+            if (const char* e = getenv("LZ_PRUNE_AHEAD")) g_stream_cfg.ahead = max(2, min(kQueue - 2, atoi(e)));
+            const size_t smem = (size_t)g_stream_cfg.stages * 16 * kTile + 8 * kTile;
+            LZ_CUDA(cudaFuncSetAttribute(prune_stream_kernel<kStreamThreads, kItemsS, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            LZ_CUDA(cudaFuncSetAttribute(prune_stream_kernel<kStreamThreads, kItemsS, false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            LZ_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&g_stream_cfg.ctas_per_sm,
+                                                                  prune_stream_kernel<kStreamThreads, kItemsS, true>,
+                                                                  kStreamThreads + 96, smem));
+            LZ_REQUIRE(g_stream_cfg.ctas_per_sm >= 1, "lz_edge_decay_prune: streamed kernel does not fit (%d stages)",
+                       g_stream_cfg.stages);
+            if (const char* e = getenv("LZ_PRUNE_CTAS")) g_stream_cfg.ctas_per_sm = max(1, min(g_stream_cfg.ctas_per_sm, atoi(e)));
+            if (getenv("LZ_PRUNE_VERBOSE"))
+                fprintf(stderr, "[lz] streamed prune: %d stages, ahead %d, %d CTAs per SM\n", g_stream_cfg.stages, g_stream_cfg.ahead,
+                        g_stream_cfg.ctas_per_sm);
+            g_stream_cfg.ready = true;
+        }
+        c = g_stream_cfg;
+    }
+    const int64_t tiles = (p.n + kTile - 1) / kTile;
+    LZ_CUDA(cudaMemsetAsync(scratch, 0, stream_state_words(tiles) * 8, st));
+    p.ticket = (u32*)scratch;
+    p.state = (u64*)scratch + 1;
+    p.n_tiles = (int)tiles;
+    p.use_wstar = prune_bound(p.factor, p.thr, &p.wstar) ? 1 : 0;
+    const int sms = lz_sm_count() > 0 ? lz_sm_count() : 148;
+    const unsigned grid = (unsigned)min(tiles, (int64_t)sms * c.ctas_per_sm);
+    const size_t smem = (size_t)c.stages * 16 * kTile + 8 * kTile;
+    if (aliased) prune_stream_kernel<kStreamThreads, kItemsS, false><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.stages);
+    else prune_stream_kernel<kStreamThreads, kItemsS, true><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.ahead);
+    LZ_CUDA(cudaGetLastError());
+    return LZ_OK;
+}
+
 }  // namespace
 
 extern "C" size_t lz_edge_decay_prune_scratch_bytes(int64_t n) {
     if (n <= 0) return 256;
     const int64_t tiles = (n + kTile - 1) / kTile;
-    // chained form: ticket + one look-back word per tile; two-pass form: int64 offsets + int32 counts
-    return (size_t)(((tiles + 1) * 8 + tiles * 4 + 255) & ~255ll);
+    // single-pass forms: ticket + one word per tile (+ one per wave of 256 tiles in the streamed form); two-pass form:
+    // int64 offsets + int32 counts
+    return (size_t)(((tiles + tiles / 256 + 4) * 8 + tiles * 4 + 255) & ~255ll);
 }
 
 extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* weight, const int32_t* cooc,
@@ -326,7 +735,7 @@ extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const
     p.n = n; p.factor = factor; p.thr = threshold;
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
-    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr;
+    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr; p.counts = nullptr; p.group_sum = nullptr; p.wstar = 0.f; p.use_wstar = 0;
     // Do any outputs overlap any inputs?  In place, a tile may only be overwritten after it has been read,
     // which the single-pass chained kernel guarantees; out of place the tiles are independent and the
     // two-pass form (count, scan, scatter) runs without any CTA waiting on another.
@@ -336,15 +745,38 @@ extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const
     for (int i = 0; i < 4; ++i)
         for (int j = 0; j < 4; ++j)
             aliased = aliased || (out[j] < in[i] + (uintptr_t)n * 4 && in[i] < out[j] + (uintptr_t)n * 4);
-    if (aliased) {
+    static const int form = [] { const char* e = getenv("LZ_PRUNE_FORM"); return e ? atoi(e) : 0; }();   // 1: streamed, 2: chained, 3: two-pass with the scan kernel
+    if (form == 4) {                                      // measurement only: streamed data path with offsets from a first call
+        static bool primed = false;
+        const size_t words = stream_state_words(tiles);
+        int64_t* offsets = (int64_t*)scratch + words;
+        int32_t* counts = (int32_t*)(offsets + tiles + 1);
+        if (!primed) {
+            count_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(weight, n, factor, threshold, counts, nullptr);
+            tile_scan_kernel<<<1, 1024, 0, st>>>(counts, (int)tiles, offsets, out_kept);
+            primed = true;
+        }
+        p.offsets = offsets;
+        if (int rc = launch_stream(p, scratch, aliased, st)) return rc;
+    } else if (form == 1 || (form == 0 && false)) {
+        if (int rc = launch_stream(p, scratch, aliased, st)) return rc;
+    } else if (aliased || form == 2) {
         LZ_CUDA(cudaMemsetAsync(scratch, 0, (size_t)(tiles + 1) * 8, st));
         decay_prune_kernel<true><<<(unsigned)tiles, kThreads, 0, st>>>(p);
     } else {
-        int64_t* offsets = (int64_t*)scratch;
         int32_t* counts = (int32_t*)((unsigned char*)scratch + (size_t)(tiles + 1) * 8);
-        count_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(weight, n, factor, threshold, counts);
-        tile_scan_kernel<<<1, 1024, 0, st>>>(counts, (int)tiles, offsets, out_kept);
-        p.offsets = offsets;
+        p.counts = counts;
+        if (form == 3 || tiles > (1ll << 20)) {          // with the scan kernel (very large tables: too many groups to sum per CTA)
+            int64_t* offsets = (int64_t*)scratch;
+            count_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(weight, n, factor, threshold, counts, nullptr);
+            tile_scan_kernel<<<1, 1024, 0, st>>>(counts, (int)tiles, offsets, out_kept);
+            p.offsets = offsets;
+        } else {
+            u64* group_sum = (u64*)scratch;
+            LZ_CUDA(cudaMemsetAsync(group_sum, 0, (size_t)(tiles / kGroup + 1) * 8, st));
+            count_kernel<<<(unsigned)tiles, kThreads, 0, st>>>(weight, n, factor, threshold, counts, group_sum);
+            p.group_sum = group_sum;
+        }
         decay_prune_kernel<false><<<(unsigned)tiles, kThreads, 0, st>>>(p);
     }
     LZ_CUDA(cudaGetLastError());
@@ -441,7 +873,7 @@ extern "C" int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* ds
     p.n = n; p.factor = factor; p.thr = threshold;
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
-    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr;
+    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr; p.counts = nullptr; p.group_sum = nullptr; p.wstar = 0.f; p.use_wstar = 0;
     decay_prune_kernel<true><<<(unsigned)tiles, kThreads, 0, st>>>(p);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
