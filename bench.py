@@ -255,20 +255,26 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def host_pipeline(qh, k, steps, depth=2):
+        # K searches through the host API with `depth` kept in flight (staging slots i % (depth + 1), two lanes): every
+        # step's inputs come from host memory and every step's result is read back to the host inside the timed region
+        pend, out = [], None
+        for i in range(steps):
+            pend.append(sharded.submit_host(qh, k, slot=i % (depth + 1)))
+            if len(pend) > depth:
+                out = pend.pop(0).result()
+        while pend:
+            out = pend.pop(0).result()
+        return out
+
     def e2e_block(steps):
-        # K steps through the host API with one search kept in flight: step i+1's staging + H2D copy overlap step
+        # K steps through the host API with two searches kept in flight: step i+1's staging + H2D copy overlap step
         # i's search; every step's inputs come from host memory and every step's result is read back to the host
         if args.batch == 1 and world == 1:
             for _ in range(steps):
                 out = step_e2e()
             return out
-        pend = out = None
-        for i in range(steps):
-            h = sharded.submit_host(q_host, args.k, slot=i & 1)
-            if pend is not None:
-                out = pend.result()
-            pend = h
-        return pend.result()
+        return host_pipeline(q_host, args.k, steps)
 
     def timed(fn, steps, block=False):
         barrier()
@@ -377,15 +383,8 @@ def main():
             f_e2e_block = lambda n_: [store.search_nodes(qh[0].tolist(), limit=k) for _ in range(n_)][-1]
             api = "B200Store.search_nodes (List[float] -> List[str])"
         else:
-            def f_e2e_block(n_):
-                pend = None
-                for i in range(n_):
-                    h = sharded.submit_host(qh, k, slot=i & 1)
-                    if pend is not None:
-                        pend.result()
-                    pend = h
-                return pend.result()
-            api = "ShardedSearch.submit_host(...).result(), one search kept in flight"
+            f_e2e_block = lambda n_: host_pipeline(qh, k, n_)
+            api = "ShardedSearch.submit_host(...).result(), two searches kept in flight"
         # warm-up: 3 steps, then as many more as fill 0.25 s of this block's own work, so that the SM clock has settled
         # after the previous (tensor-core, power-capped) block before anything here is timed; the count is agreed over the
         # ranks (the sharded search has a collective in it, so every rank must make the same number of calls)
@@ -448,10 +447,11 @@ def main():
         ach_e = ebytes / (ms_e / n_e * 1e-3) / 1e9
         line["decay_prune"] = {"metric": "decay+prune edges/s over %d edges (factor 0.99, threshold 0.5)" % args.edges,
                                "value": ne * world / (ms_e / n_e * 1e-3), "unit": "edges/s", "ms_per_step": ms_e / n_e,
-                               "kept_fraction": kf, "gpu_launches": int(n_e * 3),
+                               "kept_fraction": kf, "gpu_launches": int(n_e),
                                "roofline": {"bound": "hbm", "achieved": ach_e, "peak": hbm_peak, "unit": "GB/s",
-                                            "frac": ach_e / hbm_peak, "traffic": None,
-                                            "kernel": "count_kernel + tile_scan_kernel + decay_prune_kernel (lz_edge_decay_prune)",
+                                            "frac": ach_e / hbm_peak,
+                                            "traffic": traffic.get("prune_stream_kernel_50M") if (ne == 50_000_000) else None,
+                                            "kernel": "prune_stream_kernel (lz_edge_decay_prune; one launch + one memset of the tile words)",
                                             "algorithmic_bytes_per_launch": ebytes}}
     if world == 1 and not args.no_consolidation and n_local >= 1_000_000 and args.dim == 768:
         # north_star (2) / BASELINE configs[2]: a 10k-node episodic buffer deduplicated against a 1M-node graph (top-1 +

@@ -1,11 +1,10 @@
 // K7: biological decay + threshold prune over the edge table (struct of arrays), one pass.
 //
 // Stands behind MemoryShard.apply_temporal_decay / prune_weak_edges (core/memory_shard.py:64-84).
-// HBM-bound integer/float streaming: 16 B read per edge (src, dst, weight, co_occurrence as four
-// 128-bit loads per 8 edges and thread) + 16 B written per surviving edge.  Survivors are compacted
-// stably in a single pass: per-thread flags -> warp ballot/shuffle scan -> block scan -> decoupled
-// look-back across tiles (tile order taken from an atomic ticket so a tile never waits on one that
-// has not started).  Survivors are staged in shared memory and written back coalesced.
+// HBM-bound integer/float streaming: 16 B read per edge (src, dst, weight, co_occurrence) + 16 B written per
+// surviving edge.  Survivors are compacted stably in a single pass by the streamed kernel below (bulk copies into
+// a shared-memory ring, survivor counts published ahead of the data path, coalesced write-out); the earlier forms
+// (chained look-back, count + scatter in two passes) stay selectable with LZ_PRUNE_FORM for comparison.
 #include "lz_common.cuh"
 #include "lz_sm100.cuh"
 
@@ -656,6 +655,17 @@ bool prune_bound(double factor, double thr, float* out) {
     return true;
 }
 
+// Do any output columns overlap any input columns?
+bool columns_alias(const PruneParams& p) {
+    const uintptr_t in[4] = {(uintptr_t)p.src, (uintptr_t)p.dst, (uintptr_t)p.w, (uintptr_t)p.cooc};
+    const uintptr_t out[4] = {(uintptr_t)p.o_src, (uintptr_t)p.o_dst, (uintptr_t)p.o_w, (uintptr_t)p.o_cooc};
+    bool aliased = false;
+    for (int i = 0; i < 4; ++i)
+        for (int j = 0; j < 4; ++j)
+            aliased = aliased || (out[j] < in[i] + (uintptr_t)p.n * 4 && in[i] < out[j] + (uintptr_t)p.n * 4);
+    return aliased;
+}
+
 int launch_stream(PruneParams p, void* scratch, bool aliased, cudaStream_t st) {
     StreamCfg c;
     constexpr int kItemsS = kTile / kStreamThreads;
@@ -736,16 +746,13 @@ extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
     p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr; p.counts = nullptr; p.group_sum = nullptr; p.wstar = 0.f; p.use_wstar = 0;
-    // Do any outputs overlap any inputs?  In place, a tile may only be overwritten after it has been read,
-    // which the single-pass chained kernel guarantees; out of place the tiles are independent and the
-    // two-pass form (count, scan, scatter) runs without any CTA waiting on another.
-    const uintptr_t in[4] = {(uintptr_t)src, (uintptr_t)dst, (uintptr_t)weight, (uintptr_t)cooc};
-    const uintptr_t out[4] = {(uintptr_t)out_src, (uintptr_t)out_dst, (uintptr_t)out_weight, (uintptr_t)out_cooc};
-    bool aliased = false;
-    for (int i = 0; i < 4; ++i)
-        for (int j = 0; j < 4; ++j)
-            aliased = aliased || (out[j] < in[i] + (uintptr_t)n * 4 && in[i] < out[j] + (uintptr_t)n * 4);
-    static const int form = [] { const char* e = getenv("LZ_PRUNE_FORM"); return e ? atoi(e) : 0; }();   // 1: streamed, 2: chained, 3: two-pass with the scan kernel
+    // Do any outputs overlap any inputs?  In place, a tile may only be overwritten after it has been read: the
+    // streamed kernel then publishes a tile's aggregate only once its columns are in shared memory; out of place the
+    // aggregates are counted ahead of the data path.
+    const bool aliased = columns_alias(p);
+    static const int form = [] { const char* e = getenv("LZ_PRUNE_FORM"); return e ? atoi(e) : 0; }();
+    // default: the streamed single-pass kernel.  For comparisons: 2 chained look-back, 3 two-pass with the scan kernel,
+    // 5 two-pass with group sums, 4 streamed data path alone (offsets from a first call; scripts/run_edges_form4.py)
     if (form == 4) {                                      // measurement only: streamed data path with offsets from a first call
         static bool primed = false;
         const size_t words = stream_state_words(tiles);
@@ -758,7 +765,7 @@ extern "C" int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const
         }
         p.offsets = offsets;
         if (int rc = launch_stream(p, scratch, aliased, st)) return rc;
-    } else if (form == 1 || (form == 0 && false)) {
+    } else if (form <= 1) {
         if (int rc = launch_stream(p, scratch, aliased, st)) return rc;
     } else if (aliased || form == 2) {
         LZ_CUDA(cudaMemsetAsync(scratch, 0, (size_t)(tiles + 1) * 8, st));
@@ -818,7 +825,7 @@ constexpr int64_t kNoAllocMaxEdges = LZ_NOALLOC_MAX_EDGES;                 // 2^
 constexpr int64_t kNoAllocMaxTiles = kNoAllocMaxEdges / kTile;             // 32768 tiles
 }  // namespace
 
-static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + 1];   // 256 KiB + 8 B
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocMaxTiles / kWave + 4];   // ~257 KiB
 
 namespace {
 std::mutex g_noalloc_mu;
@@ -864,19 +871,13 @@ extern "C" int lz_edge_decay_prune_noalloc(const int32_t* src, const int32_t* ds
                "lz_edge_decay_prune_noalloc: edge arrays must be 16-byte aligned");
     void* scratch = nullptr;
     if (int rc = noalloc_scratch(&scratch)) return rc;
-    const int64_t tiles = (n + kTile - 1) / kTile;
-    // the array still holds the previous call's ticket and look-back words: start them from zero
-    LZ_CUDA(cudaMemsetAsync(scratch, 0, (size_t)(tiles + 1) * sizeof(u64), st));
+    // the array still holds the previous call's ticket and aggregate words: launch_stream starts them from zero
     PruneParams p;
     p.src = src; p.dst = dst; p.w = weight; p.cooc = cooc;
     p.o_src = out_src; p.o_dst = out_dst; p.o_w = out_weight; p.o_cooc = out_cooc;
     p.n = n; p.factor = factor; p.thr = threshold;
-    p.ticket = (u32*)scratch;
-    p.state = (u64*)scratch + 1;
-    p.out_kept = out_kept; p.n_tiles = (int)tiles; p.offsets = nullptr; p.counts = nullptr; p.group_sum = nullptr; p.wstar = 0.f; p.use_wstar = 0;
-    decay_prune_kernel<true><<<(unsigned)tiles, kThreads, 0, st>>>(p);
-    LZ_CUDA(cudaGetLastError());
-    return LZ_OK;
+    p.out_kept = out_kept; p.offsets = nullptr; p.counts = nullptr; p.group_sum = nullptr; p.wstar = 0.f; p.use_wstar = 0;
+    return launch_stream(p, scratch, columns_alias(p), st);
 }
 
 // ---- connected components over the edge table --------------------------------------

@@ -1395,17 +1395,16 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
             }
             asm volatile("cp.async.commit_group;" ::: "memory");
         };
+        // two queries in flight per warp: a staging buffer is handed to the query after next as soon as the current
+        // one sits in registers, so 6 KB per warp (96 KB per SM) are on their way while a query is being scored
+        auto skip_issue = [&]() { asm volatile("cp.async.commit_group;" ::: "memory"); };
         int cur = next_row(warp - kWarps), buf = 0;
-        if (cur < nq) issue(cur, 0);
+        int nxt = cur < nq ? next_row(cur) : nq;
+        if (cur < nq) issue(cur, 0); else skip_issue();
+        if (nxt < nq) issue(nxt, 1); else skip_issue();
         while (cur < nq) {
             const int i = cur;
-            const int nxt = next_row(cur);
-            if (nxt < nq) {
-                issue(nxt, buf ^ 1);
-                asm volatile("cp.async.wait_group 1;" ::: "memory");
-            } else {
-                asm volatile("cp.async.wait_group 0;" ::: "memory");
-            }
+            asm volatile("cp.async.wait_group 1;" ::: "memory");             // the older of the two has landed
             const int nl = s_nlive[i];
             int slots[kMultiLive];
             int n_here = 0;
@@ -1424,8 +1423,14 @@ __global__ void __launch_bounds__(kMultiThreads) assign_multi_kernel(SelectParam
                 const float4 v = *reinterpret_cast<const float4*>(stage + buf * kStride + lane * 4 + 128 * sg);   // pads stay zero
                 qd[sg][0] = v.x; qd[sg][1] = v.y; qd[sg][2] = v.z; qd[sg][3] = v.w;
             }
-            cur = nxt;
-            buf ^= 1;
+            __syncwarp();                                                      // every lane has its part of the query
+            {
+                const int after = nxt < nq ? next_row(nxt) : nq;
+                if (after < nq) issue(after, buf); else skip_issue();
+                cur = nxt;
+                nxt = after;
+                buf ^= 1;
+            }
 #pragma unroll
             for (int sg = 0; sg < NSEG; ++sg)
 #pragma unroll

@@ -161,9 +161,10 @@ class ShardedSearch:
     # -- pipelined host interface: the next batch's staging + H2D copy overlap the current batch's search
     def submit_host(self, queries: np.ndarray, k: int, slot: int = 0) -> "_PendingSearch":
         """Starts a search of host queries without waiting for it: stage into pinned memory, H2D on a copy
-        stream, the search and the D2H of the result on the current stream.  `slot` (0 or 1) picks one of two
-        sets of staging buffers — resubmit a slot only after its previous result() was taken.  Same answer as
-        search_host; a loop that keeps one search in flight hides the copies and the host work behind it."""
+        stream, the search and the D2H of the result on the slot's lane.  `slot` (0..3) picks a set of staging
+        buffers — resubmit a slot only after its previous result() was taken; slots alternate between the two lanes.
+        Same answer as search_host; a loop that keeps one or two searches in flight hides the copies and the host
+        work behind them (two absorb the jitter of the other ranks' hosts when the search has a collective in it)."""
         st = self.store
         q = np.ascontiguousarray(queries, dtype=np.float32)
         B = q.shape[0]
@@ -189,11 +190,12 @@ class ShardedSearch:
             main.wait_event(ready)
             # the search itself runs on the slot's lane (own stream, own scratch): with two slots alternating, the exact
             # pass, exchange and read-back of one search overlap the coarse pass of the next
-            ids, sc, cnt = self.search_device(qd, k, lane=slot)
+            lane = slot & 1
+            ids, sc, cnt = self.search_device(qd, k, lane=lane)
             h_ids = st._pinned(f"ids{slot}", (B, k), torch.int64)
             h_sc = st._pinned(f"sc{slot}", (B, k), torch.float64)
             h_cnt = st._pinned(f"cnt{slot}", (B,), torch.int32)
-            with torch.cuda.stream(self._lanes[slot]["stream"]):
+            with torch.cuda.stream(self._lanes[lane]["stream"]):
                 h_ids.copy_(ids, non_blocking=True)
                 h_sc.copy_(sc, non_blocking=True)
                 h_cnt.copy_(cnt, non_blocking=True)

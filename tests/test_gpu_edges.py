@@ -60,6 +60,37 @@ def test_decay_prune_sizes_and_extremes(n, thr):
     np.testing.assert_array_equal(ww, ew); np.testing.assert_array_equal(c, ec)
 
 
+@pytest.mark.parametrize("factor,thr", [(0.99, 0.5), (1.0, 0.5), (0.5, 0.3), (1e-3, 1e-4), (3.0, 0.7), (0.99, 0.0),
+                                        (0.99, -0.25), (-1.0, 0.5), (0.0, 0.5), (0.99, 1e-40), (1.0 / 3.0, 1.0 / 3.0)])
+@pytest.mark.parametrize("in_place", [False, True])
+def test_prune_decision_on_the_boundary(factor, thr, in_place):
+    """Weights packed into the few float32 values either side of the point where float64(w) * factor crosses the threshold
+    (memory_shard.py:79-84 compares in float64): the kept set must be the oracle's, whatever form the kernels decide in."""
+    from lazzaro_b200.graph import EdgeTable
+    centre = np.float32(thr / factor) if factor != 0 else np.float32(thr)
+    band = [centre]
+    for _ in range(40):
+        band.append(np.nextafter(band[-1], np.float32(np.inf), dtype=np.float32))
+    lo = centre
+    for _ in range(40):
+        lo = np.nextafter(lo, np.float32(-np.inf), dtype=np.float32)
+        band.append(lo)
+    band = np.array(band + [0.0, -0.0, 1e-45, -1e-45, 1.0, -1.0, 3.4e38, -3.4e38], np.float32)
+    rng = np.random.default_rng(5)
+    n = 70_001
+    w = band[rng.integers(0, band.size, n)]
+    src = rng.integers(0, 1000, n).astype(np.int32); dst = rng.integers(0, 1000, n).astype(np.int32)
+    cooc = np.arange(n, dtype=np.int32)
+    t = EdgeTable(device="cuda", capacity=n, in_place=in_place)
+    t.append(src, dst, w, cooc)
+    pruned = t.decay_prune(factor, thr)
+    es, ed, ew, ec, ep = graph_ops.decay_prune_edges(src, dst, w, cooc, factor, thr)
+    s, d, ww, c = t.to_numpy()
+    assert pruned == ep
+    np.testing.assert_array_equal(c, ec); np.testing.assert_array_equal(s, es)
+    np.testing.assert_array_equal(ww.view(np.int32), ew.view(np.int32))
+
+
 def test_in_place_and_out_of_place_tables_agree():
     from lazzaro_b200 import synth
     from lazzaro_b200.graph import EdgeTable
