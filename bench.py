@@ -74,19 +74,23 @@ def peaks():
 
 
 class ClockSampler:
-    """Samples nvidia-smi SM clocks / throttle reasons while the timed region runs."""
+    """Samples nvidia-smi SM clocks / throttle reasons while the timed region runs.  One sampler per job: rank 0 polls the
+    GPUs of all ranks (every rank polling for itself puts N nvidia-smi processes on the driver's locks, which showed up as
+    host-side launch stalls in the 8-GPU end-to-end number); the other ranks sample nothing."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+    def __init__(self, indices, period_ms: int = 20):
+        self.indices, self.period, self.rows, self.proc, self.t0 = list(indices), period_ms, [], None, None
 
     def __enter__(self):
+        if not self.indices:
+            return self
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-i", str(self.index), "-lms", "20"], stdout=subprocess.PIPE,
-                                         stderr=subprocess.DEVNULL, text=True)
+                                          "-i", ",".join(str(i) for i in self.indices), "-lms", str(self.period)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except OSError:
@@ -95,7 +99,16 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def wait_first(self, timeout: float = 10.0):
+        """nvidia-smi takes a second or more to come up on a multi-GPU box: do not start the timed region before it reports."""
+        t_end = time.time() + timeout
+        while self.proc and not self.rows and time.time() < t_end:
+            time.sleep(0.02)
+
+    def mark(self):
+        self.t0 = time.time()                        # samples from here on are "under load"
 
     def __exit__(self, *a):
         if self.proc:
@@ -106,7 +119,8 @@ class ClockSampler:
     def summary(self):
         sm, mx, reasons = [], 0, set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.t0 is None or t >= self.t0] or [r for _, r in self.rows]
+        for r in rows:
             try:
                 sm.append(float(r[0])); mx = max(mx, float(r[1]))
                 for n, v in zip(names, r[3:7]):
@@ -116,7 +130,7 @@ class ClockSampler:
                 pass
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "gpus_sampled": len(self.indices)}
 
 
 def cpu_search_qps(args, steps, warmup):
@@ -296,7 +310,12 @@ def main():
         step_device()
         step_e2e()
     e2e_block(2)
-    with ClockSampler(local) as clocks:
+    vis = [v for v in os.environ.get("CUDA_VISIBLE_DEVICES", "").split(",") if v.strip().isdigit()]
+    job_gpus = ([int(v) for v in vis][:world] if len(vis) >= world else list(range(world))) if rank == 0 else []
+    with ClockSampler(job_gpus, 20 if world == 1 else 50) as clocks:
+        clocks.wait_first()
+        barrier()
+        clocks.mark()
         if args.lanes and args.batch >= store.min_batch:
             steps_device_lanes(4)
             ms_total, out = timed(steps_device_lanes, args.steps, block=True)
@@ -636,10 +655,17 @@ def main():
             from oracle import flat_search, ref_loops
             from oracle.flat_store import FlatStore
             inv1 = (1.0 / np.linalg.norm(r1_np, axis=1)).astype(np.float32)
+            names1 = [f"node_{i}" for i in range(10_000)]
             t0 = time.perf_counter()
-            for i in range(n_1):
-                flat_search.fast_topk_f32(r1_np, q1_np[i % 64:i % 64 + 1], 10, "cosine", inv1)
+            for i in range(n_1):                                     # the same call shape as search_nodes: List[float] in, List[str] out
+                qq = np.asarray(q1_lists[i % 64], dtype=np.float32).reshape(1, -1)
+                got = flat_search.fast_topk_f32(r1_np, qq, 10, "cosine", inv1)
+                [names1[r] for r in np.asarray(got[0]).reshape(-1).tolist()]
             dt_f = (time.perf_counter() - t0) / n_1
+            t0 = time.perf_counter()
+            for i in range(n_1):                                     # the arithmetic alone: float32 array in, row indices out
+                flat_search.fast_topk_f32(r1_np, q1_np[i % 64:i % 64 + 1], 10, "cosine", inv1)
+            dt_a = (time.perf_counter() - t0) / n_1
             fs = FlatStore(metric="cosine")
             fs.add_nodes([{"id": f"node_{i}", "content": "", "embedding": r1_np[i]} for i in range(10_000)])
             resident = {f"node_{i}": i for i in range(10_000)}
@@ -648,7 +674,8 @@ def main():
                 ref_loops.search_memories(fs, resident, q1_lists[i % 64], limit=10)
             dt_r = (time.perf_counter() - t0) / 20
             line["cfg1"]["cpu_baseline"] = {"value": 1.0 / dt_f, "unit": UNIT, "us_per_call": dt_f * 1e6, "cores": os.cpu_count(), "kind": "port",
-                                            "sample": "numpy float32 sgemv + argpartition over the 10k x 384 rows, one query per call",
+                                            "sample": "numpy float32 sgemv + argpartition over the 10k x 384 rows, one query per call, List[float] in and id strings out like "
+                                                      "search_nodes (the arithmetic alone, array in / indices out: %.1f us)" % (dt_a * 1e6),
                                             "reference_shaped": {"value": 1.0 / dt_r, "unit": UNIT, "us_per_call": dt_r * 1e6, "cores": 1,
                                                                  "sample": "search_memories restated (memory_system.py:1460-1472) over the oracle FlatStore: "
                                                                            "float64 distances over the fp32 rows in numpy, ids -> resident nodes (BASELINE.md C1)"}}

@@ -162,7 +162,8 @@ class ShardedSearch:
     def submit_host(self, queries: np.ndarray, k: int, slot: int = 0) -> "_PendingSearch":
         """Starts a search of host queries without waiting for it: stage into pinned memory, H2D on a copy
         stream, the search and the D2H of the result on the slot's lane.  `slot` (0..3) picks a set of staging
-        buffers — resubmit a slot only after its previous result() was taken; slots alternate between the two lanes.
+        buffers — resubmit a slot only after its previous result() was taken; consecutive submissions alternate between
+        the two lanes.
         Same answer as search_host; a loop that keeps one or two searches in flight hides the copies and the host
         work behind them (two absorb the jitter of the other ranks' hosts when the search has a collective in it)."""
         st = self.store
@@ -190,7 +191,7 @@ class ShardedSearch:
             main.wait_event(ready)
             # the search itself runs on the slot's lane (own stream, own scratch): with two slots alternating, the exact
             # pass, exchange and read-back of one search overlap the coarse pass of the next
-            lane = slot & 1
+            lane = self._host_seq = (getattr(self, "_host_seq", 1) + 1) & 1      # lanes alternate by submission order
             ids, sc, cnt = self.search_device(qd, k, lane=lane)
             h_ids = st._pinned(f"ids{slot}", (B, k), torch.int64)
             h_sc = st._pinned(f"sc{slot}", (B, k), torch.float64)

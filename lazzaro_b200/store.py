@@ -468,12 +468,19 @@ class B200Store:
         st["seq"] = seq = (st["seq"] % 0x7ffffff0) + 1
         lo, hi = self._span[u]
         single_user = len(self._user_names) == 1 and self._live[u] == self._n
-        with torch.cuda.device(self.device):
+        key = (self._gen, u, lo, hi, single_user)
+        if st.get("key") != key:                            # the call's fixed arguments, rebuilt when the layout changes
+            st["key"] = key
+            st["args"] = (self._rows.data_ptr(), self._rows.stride(0), self._dim_p, self._norms.data_ptr(),
+                          None if single_user else self._tags.data_ptr(), -1 if single_user else u, lo, hi,
+                          st["q_pin"].data_ptr(), k, self._metric, 0, st["scratch"].data_ptr(), st["nbytes"], st["out"].data_ptr())
+        idx = self.device.index
+        guard = torch.cuda.device(self.device) if torch.cuda.current_device() != idx else None
+        if guard is not None:
+            guard.__enter__()
+        try:
             stream = torch.cuda.current_stream()
-            _lib.check(lib.lz_search_one(self._rows.data_ptr(), self._rows.stride(0), self._dim_p, self._norms.data_ptr(),
-                                         None if single_user else self._tags.data_ptr(), -1 if single_user else u, lo, hi,
-                                         st["q_pin"].data_ptr(), k, self._metric, 0, st["scratch"].data_ptr(), st["nbytes"],
-                                         st["out"].data_ptr(), seq, stream.cuda_stream), "lz_search_one")
+            _lib.check(lib.lz_search_one(*st["args"], seq, stream.cuda_stream), "lz_search_one")
             flag = st["flag"]
             for _ in range(200_000):                       # the answer usually lands within ~20 us
                 if flag[0] == seq:
@@ -483,6 +490,9 @@ class B200Store:
                 if flag[0] != seq:
                     st["scratch"][:256].zero_()             # an aborted launch may have left the completion ticket half way
                     raise _lib.LazzaroB200Error("lz_search_one finished without publishing its answer")
+        finally:
+            if guard is not None:
+                guard.__exit__(None, None, None)
         return st["ids"][None, :], st["sc"][None, :], st["cnt"]
 
     def _search_host(self, q: np.ndarray, u: int, limit: int):
