@@ -105,6 +105,49 @@ def test_in_place_and_out_of_place_tables_agree():
             np.testing.assert_array_equal(x, y)
 
 
+def test_two_sweeps_on_two_streams_at_once():
+    """Two tables swept concurrently on two streams, each with its own scratch: the streamed kernel's CTAs take their tiles
+    from a ticket, so two grids sharing the SMs cannot wait on each other; both results equal the oracle's."""
+    from lazzaro_b200 import kernels, synth, _lib
+    lib = _lib.load()
+    jobs = []
+    for seed, n, thr in ((3, 4_000_037, 0.5), (4, 3_500_011, 0.2)):
+        cols = synth.edge_table(n, 7000, seed=seed)
+        ins = [torch.as_tensor(a).cuda() for a in cols]
+        outs = [torch.empty_like(a) for a in ins]
+        scratch = torch.empty(int(lib.lz_edge_decay_prune_scratch_bytes(n)), dtype=torch.uint8, device="cuda")
+        kept = torch.zeros(1, dtype=torch.int64, device="cuda")
+        jobs.append((cols, ins, outs, scratch, kept, n, thr, torch.cuda.Stream()))
+    torch.cuda.synchronize()
+    for _ in range(5):                                     # several rounds: the two grids interleave differently each time
+        for cols, ins, outs, scratch, kept, n, thr, stream in jobs:
+            with torch.cuda.stream(stream):
+                kernels.edge_decay_prune(*ins, n, 0.99, thr, out=tuple(outs), scratch=scratch, kept=kept)
+    torch.cuda.synchronize()
+    for cols, ins, outs, scratch, kept, n, thr, stream in jobs:
+        es, ed, ew, ec, ep = graph_ops.decay_prune_edges(*cols, 0.99, thr)
+        k = int(kept.item())
+        assert k == n - ep
+        np.testing.assert_array_equal(outs[0][:k].cpu().numpy(), es)
+        np.testing.assert_array_equal(outs[2][:k].cpu().numpy(), ew)
+        np.testing.assert_array_equal(outs[3][:k].cpu().numpy(), ec)
+
+
+def test_in_place_keeps_everything():
+    """threshold below every weight, in place: every tile writes exactly onto its own input range, the case where a tile's
+    output reaches furthest into its predecessors' columns."""
+    from lazzaro_b200 import synth
+    from lazzaro_b200.graph import EdgeTable
+    n = 2_222_222
+    cols = synth.edge_table(n, 9000, seed=12)
+    t = EdgeTable(device="cuda", capacity=n, in_place=True)
+    t.append(*cols)
+    for _ in range(3):
+        assert t.decay_prune(1.0, -1.0) == 0
+    for x, y in zip(t.to_numpy(), cols):
+        np.testing.assert_array_equal(x, np.asarray(y))
+
+
 def test_out_of_place_and_idempotence():
     from lazzaro_b200 import kernels, synth
     n = 300_000
