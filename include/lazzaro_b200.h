@@ -286,6 +286,7 @@ size_t lz_edge_decay_prune_scratch_bytes(int64_t n);
  * (memory_shard.py:69-70 with factor = (1-decay_rate)^sweeps), drop edges with double(w)*factor <
  * threshold (strict, memory_shard.py:81), and compact the survivors stably (their order is kept,
  * as dict order is in the reference).  Outputs may alias the inputs (in-place compaction).
+ * One pass over the table: every column is read from HBM once (one kernel launch + one memset).
  *   src,dst,cooc int32 [n]; weight float32 [n]; out_* same types, capacity >= n
  *   out_kept     int64 [1] device: number of surviving edges (pruned = n - kept)
  *   scratch      >= lz_edge_decay_prune_scratch_bytes(n); cleared by the call itself
@@ -301,14 +302,15 @@ int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* wei
  * Such callers are, for example, a service that filled HBM with the row store at start-up, where a
  * late cudaMalloc may fail and would in any case synchronise the device under the searches in
  * flight, or a plain-C / cgo / JNI binding that owns the edge columns but has no device allocator
- * to ask for scratch.  The look-back words live in an array inside the library image instead
- * (256 KiB + 8 B of global memory on every GPU that loads the library, kept until the process exits),
+ * to ask for scratch.  The per-tile words live in an array inside the library image instead
+ * (about 257 KiB of global memory on every GPU that loads the library, kept until the process exits),
  * so this call takes inputs and outputs only and never calls cudaMalloc, cudaFree or any allocating
  * routine.
  *   limit      n <= LZ_NOALLOC_MAX_EDGES (2^26 = 67,108,864 edges); a larger n is rejected with
  *              LZ_ERR_ARG and a message — use lz_edge_decay_prune with your own scratch for those.
  *   first call the first call on each device looks the array's address up (with that device
- *              current) and caches it; make that first call outside of any stream capture.
+ *              current) and caches it, and the first sweep of a process sets the kernel's
+ *              shared-memory attribute; make that first call outside of any stream capture.
  *   sharing    every call on a device uses the same array and finds the previous call's contents
  *              in it; the call zeroes the words it needs on `stream` before the kernel, so calls
  *              issued one after another on one stream are fine, but two calls that can overlap on
