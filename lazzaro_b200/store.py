@@ -202,6 +202,17 @@ class B200Store:
                 return f"{prefix}{first + row - lo}"
         return str(row)
 
+    def _ids_of(self, ids: np.ndarray, counts: np.ndarray) -> List[List[str]]:
+        """Id strings of a [B, k] block of row indices (first counts[b] entries of each line).  The bulk layout —
+        one adopted block of rows, no per-row id overrides — formats without the per-row lookups of _id_of."""
+        lists = np.asarray(ids).tolist()
+        cnt = np.asarray(counts).tolist()
+        if not self._row_id and len(self._blocks) == 1:
+            lo, hi, prefix, first = self._blocks[0]
+            off = first - lo
+            return [[f"{prefix}{r + off}" if lo <= r < hi else str(r) for r in row[:c]] for row, c in zip(lists, cnt)]
+        return [[self._id_of(r) for r in row[:c]] for row, c in zip(lists, cnt)]
+
     @property
     def n_rows(self) -> int:
         return self._n
@@ -417,7 +428,7 @@ class B200Store:
                 empty = [[] for _ in range(q.shape[0])]
                 return (empty, empty) if return_scores else empty
             ids, scores, counts = self._search_host(q, u, limit)
-            out = [[self._id_of(r) for r in ids[b, :counts[b]].tolist()] for b in range(q.shape[0])]
+            out = self._ids_of(ids, counts)
             if return_scores:
                 return out, [scores[b, :counts[b]].tolist() for b in range(q.shape[0])]
             return out
@@ -734,7 +745,7 @@ class B200Store:
             if return_rows:
                 return ids, sc, cnt
             ids, cnt = ids.cpu().numpy(), cnt.cpu().numpy()
-            return [[self._id_of(int(r)) for r in ids[b, :cnt[b]]] for b in range(B)]
+            return self._ids_of(ids, cnt)
 
     def delete_nodes(self, node_ids: List[str], user_id: str = "default"):
         with self._lock:

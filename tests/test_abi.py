@@ -71,3 +71,18 @@ def test_no_cpu_fallback():
     from lazzaro_b200 import kernels
     with pytest.raises(_lib.LazzaroB200Error):
         kernels.row_norms(torch.zeros(4, 8))
+
+
+def test_bulk_id_formatting_matches_per_row_lookup():
+    """B200Store._ids_of (the batch searches' id strings) against _id_of row by row: one adopted block, explicit
+    id overrides, several blocks, short counts, rows outside every block."""
+    import numpy as np
+    from lazzaro_b200.store import B200Store
+    st = B200Store.__new__(B200Store)                       # host-side bookkeeping only: no device needed
+    ids = np.array([[3, 999, -1, 1000], [0, 1, 2, 7]], np.int64)
+    for row_id, blocks in (({}, [(0, 1000, "node_", 5)]), ({1: "x", 999: "y"}, [(0, 1000, "node_", 5)]),
+                           ({}, [(0, 10, "a", 0), (10, 2000, "b", 3)]), ({}, [])):
+        st._row_id, st._blocks = dict(row_id), list(blocks)
+        for cnt in (np.array([4, 4]), np.array([2, 0]), np.array([0, 3])):
+            want = [[st._id_of(int(r)) for r in ids[b, :cnt[b]]] for b in range(2)]
+            assert st._ids_of(ids, cnt) == want
