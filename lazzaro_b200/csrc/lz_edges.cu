@@ -222,10 +222,11 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
 //   count warp    runs `ahead` tiles in front of the data path: draws the next ticket, fetches that tile's weights
 //                 (8 KB bulk copy, L2 evict-last), counts the survivors and publishes the tile's aggregate
 //   offset warp   turns aggregates into output offsets.  Tiles form waves of kWave consecutive tickets;
-//                 offset(t) = wave_prefix[wave of t] + the aggregates of the tiles before t in its wave (at most
-//                 kWave/32 loads per lane, all issued at once); the CTA holding a wave's last tile publishes the next
-//                 wave's prefix.  Because the aggregates were published `ahead` tiles early, the offset is there
-//                 long before the data path asks for it
+//                 offset(t) = what lies before t's wave + the aggregates of the tiles before t in its wave (at most
+//                 kWave/32 loads per lane, all issued at once).  The CTA holding a wave's last tile publishes the
+//                 wave's total as soon as it knows it and the inclusive prefix once it has its own offset; "what lies
+//                 before the wave" is a 32-wide look-back over those wave words, so no offset waits on a chain of
+//                 CTAs — only on counts, and those were published `ahead` tiles early
 //   loader warp   issues each tile's four column segments as plain bulk copies (cp.async.bulk global -> shared,
 //                 completion on the stage's mbarrier) as soon as a stage is free; the weights come out of the L2
 //   compute warps flags from shared memory, block scan, compaction in place in the stage buffer, coalesced
@@ -388,7 +389,7 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
     }
     if (warp == NW + 2) {
         // ---------------- offset warp ----------------
-        u64* wave_prefix = p.state + p.n_tiles;                       // [n_waves + 1]; wave 0 starts at 0
+        u64* wave_word = p.state + p.n_tiles;      // [n_waves]: a wave's total, later its inclusive prefix (flagged)
         for (int n = 0;; ++n) {
             wait_above(&q_counted, n);
             TileRec* e = &queue[n % kQueue];
@@ -402,15 +403,14 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
                 const int w = tile / kWave, j = tile % kWave;
                 const u64* agg = p.state + (size_t)w * kWave;
                 u64 v[kWave / 32];
-                u64 wp = kFlagPrefix;
 #pragma unroll
                 for (int r = 0; r < kWave / 32; ++r) {
                     const int idx = j - 1 - lane - 32 * r;
                     v[r] = idx >= 0 ? ld_state(agg + idx) : kFlagAgg;
                 }
-                if (lane == 0 && w > 0) wp = ld_state(wave_prefix + w);
+                u64 ws = w - 1 - lane >= 0 ? ld_state(wave_word + (w - 1 - lane)) : kFlagPrefix;   // in flight with the above
                 while (true) {
-                    bool pending = (wp >> 62) == 0;
+                    bool pending = false;
 #pragma unroll
                     for (int r = 0; r < kWave / 32; ++r) pending = pending || (v[r] >> 62) == 0;
                     if (!__any_sync(0xffffffffu, pending)) break;
@@ -418,14 +418,38 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
 #pragma unroll
                     for (int r = 0; r < kWave / 32; ++r)
                         if ((v[r] >> 62) == 0) v[r] = ld_state(agg + (j - 1 - lane - 32 * r));
-                    if ((wp >> 62) == 0) wp = ld_state(wave_prefix + w);
                 }
-                sum = lane == 0 ? (long long)(wp & kValueMask) : 0;
+                sum = 0;
 #pragma unroll
                 for (int r = 0; r < kWave / 32; ++r) sum += (long long)(v[r] & kValueMask);
 #pragma unroll
                 for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-                if (lane == 0 && j == kWave - 1) st_state(wave_prefix + w + 1, kFlagPrefix | (u64)(sum + total));
+                // the wave's last tile knows the wave's total now: publish it before its own offset is known, so that
+                // later waves never wait on a chain of CTAs, only on counts (which run ahead)
+                const bool closes_wave = j == kWave - 1;
+                if (closes_wave && lane == 0) st_state(wave_word + w, kFlagAgg | (u64)(sum + total));
+                // look-back over the wave words: totals back to the nearest published inclusive prefix
+                long long before = 0;
+                for (int look = w - 1;; look -= 32) {
+                    unsigned pref, empty;
+                    int first;
+                    while (true) {
+                        pref = __ballot_sync(0xffffffffu, (ws >> 62) == 2);
+                        first = pref ? __ffs(pref) - 1 : 31;
+                        empty = __ballot_sync(0xffffffffu, (ws >> 62) == 0) & (0xffffffffu >> (31 - first));
+                        if (!empty) break;
+                        __nanosleep(40);
+                        if ((ws >> 62) == 0) ws = ld_state(wave_word + (look - lane));
+                    }
+                    long long t = lane <= first ? (long long)(ws & kValueMask) : 0;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+                    before += t;
+                    if (pref) break;
+                    ws = look - 32 - lane >= 0 ? ld_state(wave_word + (look - 32 - lane)) : kFlagPrefix;
+                }
+                if (closes_wave && lane == 0) st_state(wave_word + w, kFlagPrefix | (u64)(before + sum + total));
+                sum += before;
             }
             if (lane == 0) {
                 e->prefix = sum;
