@@ -1840,6 +1840,7 @@ int make_plan(int64_t n_rows, int n_queries, int k, Plan* pl) {
     pl->n_slices = (pl->n_tiles + pl->tiles_per_slice - 1) / pl->tiles_per_slice;
     if (pl->n_slices < 1) pl->n_slices = 1;
     pl->kp = k <= 3 ? 32 : (k <= 16 ? 128 : (k <= 48 ? 256 : 512));
+    if (const int kp_env = env_int("LZ_KP", 0)) { if (kp_env >= k && (kp_env == 128 || kp_env == 256 || kp_env == 512)) pl->kp = kp_env; }   // measurements
     // a table this small (centroids) has at most 2*128 candidate groups per query: keep them all and never
     // compact — compaction per item would otherwise dominate when the query side is the large one
     if (n_rows <= 2 * 128 * kSub && pl->kp < 128) pl->kp = 128;
