@@ -489,9 +489,11 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
         }
         unsigned keep = 0;
         int cnt = 0;
+        // only the table's last tile can be ragged
+        const int n_valid = (int)min((int64_t)ITEMS, p.n - base);
 #pragma unroll
         for (int j = 0; j < ITEMS; ++j) {
-            const bool k = (base + j < p.n) && keep_edge(v_w[j], p);
+            const bool k = j < n_valid && keep_edge(v_w[j], p);
             v_w[j] = (float)((double)v_w[j] * p.factor);
             keep |= (unsigned)k << j;
             cnt += k;

@@ -4,6 +4,7 @@ import os, sys
 sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..")))
 import torch
 from lazzaro_b200 import kernels as K, _lib
+_lib.LIB_PATH = os.environ.get('LZ_LIB', _lib.LIB_PATH)       # an older build for same-box A/B timing
 lib = _lib.load()
 dev = "cuda"
 
