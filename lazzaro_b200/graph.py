@@ -107,8 +107,9 @@ class EdgeTable:
             need = int(lib.lz_edge_decay_prune_scratch_bytes(n0))
             if self._scratch is None or self._scratch.numel() < need:
                 self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
-            # out of place into a second set of columns (then swap): the kernels then run the two-pass form
-            # with no CTA waiting on another; `in_place=True` at construction keeps one copy of the table
+            # out of place into a second set of columns (then swap): the streamed kernel then counts survivors ahead of
+            # its data path (0.85 of the HBM copy peak); `in_place=True` at construction keeps one copy of the table and
+            # publishes each tile's count only once its columns are on chip (slower, 0.6-0.65)
             if self._in_place:
                 out = None
             else:

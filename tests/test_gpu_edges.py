@@ -96,8 +96,8 @@ def test_in_place_and_out_of_place_tables_agree():
     from lazzaro_b200.graph import EdgeTable
     n = 777_777
     cols = synth.edge_table(n, 9000, seed=8)
-    a = EdgeTable.from_arrays(*cols, device="cuda")                  # two-pass, ping-pong columns
-    b = EdgeTable(device="cuda", capacity=n, in_place=True)          # single-pass chained scan, in place
+    a = EdgeTable.from_arrays(*cols, device="cuda")                  # ping-pong columns: counts ahead of the data path
+    b = EdgeTable(device="cuda", capacity=n, in_place=True)          # in place: counts published with the columns on chip
     b.append(*cols)
     for factor, thr in ((0.99, 0.3), (0.97, 0.3), (1.0, 0.5)):
         assert a.decay_prune(factor, thr) == b.decay_prune(factor, thr)

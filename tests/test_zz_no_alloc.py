@@ -3,7 +3,7 @@
 Some users of the library cannot allocate device memory at the moment the sweep runs — a service
 that handed all of HBM to the row store at start-up (a late cudaMalloc may fail, and it would
 synchronise the device under the searches in flight), or a bare C-ABI binding that has no device
-allocator of its own.  For them the sweep's look-back words live in an array inside the library.
+allocator of its own.  For them the sweep's per-tile words live in an array inside the library.
 This test drives that entry point through the C-ABI and requires bit-identical output to
 lz_edge_decay_prune (our edge tests compare exactly, so this one does too), on two calls in a row:
 the second call finds the first call's words still in the shared array and must not be disturbed
