@@ -222,6 +222,8 @@ struct GemmParams {
     const int* n_items_dev;
     const int32_t* qmap;      // [perm rows] real query index of a permuted query row, -1 = padding
     int debug_skip;           // profiling only (LZ_DEBUG_SKIP): 1 = the epilogue drains the accumulators without reading them
+    int raw_items;            // sampling pass of the grouped search: items are short enough never to overflow a candidate
+                              // buffer; leave the buffers as pushed (no compaction to kp at the end of an item)
 };
 
 // What one CTA works on: a q-tile against rows tiles row_begin, row_begin + stride, ... (n_tiles of them); rows at or
@@ -544,7 +546,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 acc ^= 1;
                 if (acc == 0) acc_phase ^= 1;
             }
-            const unsigned need = __ballot_sync(0xffffffffu, count > p.kp);
+            const unsigned need = p.raw_items ? 0u : __ballot_sync(0xffffffffu, count > p.kp);
             if (need) warp_select<EPL>(need, buf, count, thr, p.kp, lane);
             p.cand_cnt[slot0] = count;
             p.cand_thr[slot0] = thr;
@@ -1565,6 +1567,8 @@ struct GroupParams {
     int64_t* range_lo;    // [n_queries * nprobe] the pair's row range (for the exact fallback)
     int64_t* range_hi;
     int4* items; int* n_items; int max_items, max_ptiles, grid, max_nsl, per_cta;
+    int4* sample_items;   // [max_ptiles] one per permuted q-tile: the first sample_tiles rows tiles of its shard
+    int* n_sample; int sample_tiles;
 };
 
 __global__ void __launch_bounds__(256) group_count_kernel(GroupParams g) {
@@ -1637,6 +1641,10 @@ __global__ void __launch_bounds__(1024) group_layout_kernel(GroupParams g) {
         g.qt_base[s] = q_run;
         g.item_base[s] = i_run;
         const int64_t lo = g.shard_off[s], hi = g.shard_off[s + 1];
+        for (int qt = 0; qt < g.n_qt[s]; ++qt) {
+            if (q_run + qt < g.max_ptiles)
+                g.sample_items[q_run + qt] = make_int4(q_run + qt, (int)lo, (int)min(hi, lo + (int64_t)g.sample_tiles * BN), s);
+        }
         for (int qt = 0; qt < g.n_qt[s]; ++qt)
             for (int sl = 0; sl < g.nsl[s]; ++sl) {
                 const int item = i_run + qt * g.nsl[s] + sl;
@@ -1648,7 +1656,10 @@ __global__ void __launch_bounds__(1024) group_layout_kernel(GroupParams g) {
         i_run += g.n_qt[s] * g.nsl[s];
         g.cnt[s] = 0;                                                       // becomes the scatter cursor
     }
-    if (tid == 1023) *g.n_items = min(i_run, g.max_items);                  // the last thread holds the totals
+    if (tid == 1023) {                                                      // the last thread holds the totals
+        *g.n_items = min(i_run, g.max_items);
+        *g.n_sample = min(q_run, g.max_ptiles);
+    }
 }
 
 __global__ void __launch_bounds__(256) group_scatter_kernel(GroupParams g) {
@@ -1723,6 +1734,61 @@ __global__ void __launch_bounds__(256) seed_threshold_warp_kernel(SelectParams p
         if (c >= p.kp) prefix = cand;
     }
     if (lane == 0) gthr[q] = prefix;                                         // the kp-th largest sampled key
+}
+
+// Seeding for the grouped (two-level) search.  Its items are short — a q-tile against a few thousand rows of one shard —
+// so without a starting threshold every lane accepts everything, overflows its buffer once per item and compacts it
+// again at the end (32 warp-wide selections per warp and item: the member GEMM then runs at 40 % of the flat one's
+// speed), and the exact pass receives kp groups per item.  A sampling pass over the first sample_tiles rows tiles of
+// every (q-tile, shard) leaves its candidates as pushed (slot = the permuted query row); here a warp gathers a real
+// query's sampled keys over its probed shards and bisects for the kp-th largest, exactly as the flat seeding does.  The
+// kp-th best of a subset of the probed rows cannot exceed the kp-th best of all of them, so the seed is a valid bound.
+__global__ void __launch_bounds__(256) seed_threshold_grouped_kernel(const u64* __restrict__ cand, const int32_t* __restrict__ cand_cnt,
+                                                                     int cap, int kp, const int32_t* __restrict__ pair_row, int nprobe,
+                                                                     int sample_tiles, u32* gthr, int n_queries) {
+    constexpr int kMine = 64;                                                // keys per lane: 2048 sampled groups per query at most
+    const int lane = threadIdx.x & 31;
+    const int q = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (q >= n_queries) return;
+    const int per = sample_tiles * (BN / kSub);                              // keys a sampled slot can hold
+    const int np = min(nprobe, (kMine * 32) / per);
+    u32 key[kMine];
+#pragma unroll
+    for (int i = 0; i < kMine; ++i) {
+        const int flat = i * 32 + lane;
+        const int j = flat / per, e = flat - j * per;
+        u32 kv = 0u;
+        if (j < np) {
+            const int row = pair_row[(size_t)q * nprobe + j];
+            if (row >= 0 && e < cand_cnt[row]) kv = (u32)(cand[(size_t)row * cap + e] >> 32);
+        }
+        key[i] = kv;
+    }
+    u32 mx = 0u, mn = 0xffffffffu;
+    int live = 0;
+#pragma unroll
+    for (int i = 0; i < kMine; ++i) {
+        mx = max(mx, key[i]);
+        mn = min(mn, key[i] != 0u ? key[i] : 0xffffffffu);
+        live += key[i] != 0u;
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    live = __reduce_add_sync(0xffffffffu, live);
+    if (live < kp) return;                                                   // too few sampled groups to rank: no seed
+    const u32 diff = mx ^ mn;
+    const int top = diff ? 31 - __clz(diff) : -1;
+    u32 prefix = top >= 0 ? (mx & ~((2u << top) - 1u)) : mx;
+#pragma unroll 1
+    for (int bit = top; bit >= 0; --bit) {
+        const u32 c0 = prefix | (1u << bit);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < kMine; ++i) c += key[i] >= c0;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (c >= kp) prefix = c0;
+    }
+    if (lane == 0) atomicMax(gthr + q, prefix);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -2147,7 +2213,7 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
 // ---- two-level search (north_star (1); the reference's level 1 is core/memory_system.py:464-470) ---------------------
 namespace {
 struct TwoLevelLayout {
-    size_t l1, probe_ids, probe_sc, probe_cnt, shard_i32, pair_row, qmap, range_lo, range_hi, items, n_items,
+    size_t l1, probe_ids, probe_sc, probe_cnt, shard_i32, pair_row, qmap, range_lo, range_hi, items, n_items, sample_items, n_sample,
            q16, qperm, eps, gtag, gthr, fb_list, fb_count, cand, cand_cnt, cand_thr, certified, fallback, total;
     int max_ptiles, max_items, kp, cap, grid, fb_cps, max_nsl;
     size_t l1_bytes, fb_bytes;
@@ -2182,6 +2248,8 @@ int two_level_layout(int n_shards, int n_queries, int k, int nprobe, int dim, Tw
     L->range_hi = take((size_t)pairs * 8);
     L->items = take((size_t)L->max_items * 16);
     L->n_items = take(4);
+    L->sample_items = take((size_t)L->max_ptiles * 16);
+    L->n_sample = take(4);
     L->q16 = take((size_t)n_queries * (dim + 8) * 2);
     L->qperm = take((size_t)L->max_ptiles * BM * (dim + 8) * 2);
     L->eps = take((size_t)n_queries * 8);
@@ -2267,6 +2335,19 @@ extern "C" int lz_search_two_level(const void* shadow, const float* rows, int64_
     g.max_items = L.max_items; g.max_ptiles = L.max_ptiles; g.grid = L.grid; g.max_nsl = L.max_nsl;
     g.per_cta = env_int("LZ_TL_ITEMS_PER_CTA", 3);
     if (g.per_cta < 1 || g.per_cta > 3) g.per_cta = 3;                       // the item buffer is sized for 3
+    // sampling pass for the threshold seeds: up to 64 rows tiles per query over its probed shards, never more per item
+    // than a candidate buffer holds without compaction; skipped when the shards are hardly larger than the sample
+    g.sample_items = (int4*)(s + L.sample_items); g.n_sample = (int*)(s + L.n_sample);
+    g.sample_tiles = 64 / nprobe < 1 ? 1 : 64 / nprobe;
+    if (g.sample_tiles > L.cap / (BN / kSub) - 1) g.sample_tiles = L.cap / (BN / kSub) - 1;
+    // Measured: 1M x 768 / 64 shards / batch 256 (16 pairs per shard): the two extra launches cost 64 us and pay from nprobe 4
+    // on — 0.598 -> 0.572 ms at 4, 0.664 -> 0.553 at 16, 0.914 -> 0.763 at 64; at nprobe 1-2 they cost more than they save.
+    // 10M x 768 / 1024 shards / batch 1024 (4 pairs per shard, every q-tile nearly empty): 3.13 -> 3.60 ms at nprobe 4 — the
+    // sample costs a fifth of the member pass and spares few lanes a compaction.  Hence: from nprobe 4 on and only when the
+    // q-tiles are reasonably filled.  LZ_TL_SEED=0/2: never/always.
+    const int seed_mode = env_int("LZ_TL_SEED", 1);
+    const bool seeded = seed_mode != 0 && g.sample_tiles >= 1 && n_rows_total / n_shards >= (int64_t)4 * g.sample_tiles * BN &&
+                        (seed_mode == 2 || (nprobe >= 4 && (int64_t)n_queries * nprobe >= (int64_t)8 * n_shards));
     const int pairs = n_queries * nprobe;
     LZ_CUDA(cudaMemsetAsync(g.cnt, 0, (size_t)n_shards * 4, st));
     LZ_CUDA(cudaMemsetAsync(g.qmap, 0xff, (size_t)L.max_ptiles * BM * 4, st));
@@ -2310,6 +2391,16 @@ extern "C" int lz_search_two_level(const void* shadow, const float* rows, int64_
     attr[0].val.clusterDim.x = 1; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+    if (seeded) {
+        // the same kernel over the sample items (slot = permuted query row), candidates left as pushed; then one warp per
+        // real query turns its sampled keys into the starting threshold of every item that scans for it
+        GemmParams gs = gp;
+        gs.items = g.sample_items; gs.n_items_dev = g.n_sample; gs.raw_items = 1;
+        LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, gs));
+        seed_threshold_grouped_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(gp.cand, gp.cand_cnt, L.cap, L.kp, g.pair_row, nprobe,
+                                                                           g.sample_tiles, gthr, n_queries);
+        LZ_CUDA(cudaGetLastError());
+    }
     LZ_CUDA(cudaLaunchKernelEx(&cfg, kern, tq, tx, gp));
 
     SelectParams sp = {};
