@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
     constexpr int TILE = THREADS * ITEMS;
     constexpr int NW = THREADS / 32;
     static_assert(TILE == kTile && NW <= 32 && ITEMS % 4 == 0, "tile geometry");
-    extern __shared__ __align__(128) unsigned char s_ring[];          // stages x [4 columns][TILE] words (+ TILE weights)
+    extern __shared__ __align__(128) unsigned char s_ring[];          // stages x [4 columns][TILE] words + 2 x TILE weights of the count warp
     __shared__ uint64_t full[kMaxStages], empty[kMaxStages], cbar[2];
     __shared__ TileRec queue[kQueue];
     __shared__ int q_drawn, q_counted, q_offset, q_scattered;          // how many records each role has finished
