@@ -265,6 +265,19 @@ def test_tenant_search_routes_and_filters_by_user():
         want, _ = flat_search.flat_topk(rows_np, qs[i], 7, mask=mask)
         np.testing.assert_array_equal(got[i], want)
     assert stores[1].store.search_nodes(qs[0].tolist(), user_id="user_25", limit=3)[0].startswith("user_25/")
+    # the pipelined host form: three batches in flight over three staging slots give the answers of search_host
+    batches = [(synth.queries_near_rows(rows_np, 64, seed=70 + b), np.random.default_rng(b).integers(0, n_users, 64)) for b in range(5)]
+    ts = stores[0]
+    want_b = [ts.search_host(q, u, 5) for q, u in batches]
+    pend = [ts.submit_host(q, u, 5, slot=b % 3) for b, (q, u) in enumerate(batches[:3])]
+    got_b = [h.result() for h in pend]
+    pend = [ts.submit_host(q, u, 5, slot=b % 3) for b, (q, u) in enumerate(batches[3:])]
+    got_b += [h.result() for h in pend]
+    for w, g in zip(want_b, got_b):
+        for a, b_ in zip(w, g):
+            np.testing.assert_array_equal(a, b_)
+    none_here = ts.submit_host(batches[0][0], np.full(64, n_users - 1), 5).result()      # every query belongs to the other rank
+    assert none_here[0].size == 0 and none_here[1].shape == (0, 5)
 
 
 def test_single_query_fused_path_equals_the_two_launch_path():
