@@ -210,6 +210,9 @@ def main():
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        # torchrun pins OMP_NUM_THREADS=1; the host side of the host-API legs (staging copies, the tenants' gather) may use
+        # this rank's share of the host cores
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // world))
     _lib.load()
 
     # ---- rows of this rank: whole semantic shards, generated in HBM ---------------------------------
