@@ -148,6 +148,34 @@ def test_in_place_keeps_everything():
         np.testing.assert_array_equal(x, np.asarray(y))
 
 
+def test_prune_many_random_tables():
+    """150 random tables (sizes around tile, wave and CTA-count multiples, every kept fraction, in place and out of place, a
+    dirty scratch buffer) against the same arithmetic in torch float64 on the device: counts, order and bits."""
+    from lazzaro_b200 import kernels, _lib
+    lib = _lib.load()
+    rng = np.random.default_rng(2024)
+    specials = [2048 * 256, 2048 * 256 + 1, 2048 * 296, 2048 * 296 * 3 + 5, 2048 * 512 - 1, 2048 * 257]
+    for case in range(150):
+        n = int(specials[case % len(specials)] + rng.integers(-3, 4)) if case % 5 == 0 else int(rng.integers(1, 3_000_000))
+        factor = float(rng.choice([0.99, 1.0, 0.5, 0.97]))
+        thr = float(rng.choice([0.0, 0.1, 0.5, 0.9, 0.999, 2.0]))
+        g = torch.Generator(device="cuda"); g.manual_seed(case)
+        cols = [torch.randint(0, 1 << 20, (n,), generator=g, device="cuda", dtype=torch.int32),
+                torch.randint(0, 1 << 20, (n,), generator=g, device="cuda", dtype=torch.int32),
+                torch.rand(n, generator=g, device="cuda"), torch.arange(n, device="cuda", dtype=torch.int32)]
+        w64 = cols[2].double() * factor
+        keep = ~(w64 < thr)
+        want = [cols[0][keep], cols[1][keep], w64.float()[keep], cols[3][keep]]
+        in_place = case % 3 == 0
+        outs = cols if in_place else [torch.full_like(c, -7) for c in cols]
+        scratch = torch.randint(0, 255, (int(lib.lz_edge_decay_prune_scratch_bytes(n)),), device="cuda", dtype=torch.uint8)
+        kept, _ = kernels.edge_decay_prune(*cols, n, factor, thr, out=None if in_place else tuple(outs), scratch=scratch)
+        m = int(kept.item())
+        assert m == int(keep.sum()), (case, n, factor, thr, in_place)
+        for o, w in zip(outs, want):
+            assert torch.equal(o[:m], w), (case, n, factor, thr, in_place)
+
+
 def test_out_of_place_and_idempotence():
     from lazzaro_b200 import kernels, synth
     n = 300_000
