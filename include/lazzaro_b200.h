@@ -303,7 +303,7 @@ int lz_edge_decay_prune(const int32_t* src, const int32_t* dst, const float* wei
  * late cudaMalloc may fail and would in any case synchronise the device under the searches in
  * flight, or a plain-C / cgo / JNI binding that owns the edge columns but has no device allocator
  * to ask for scratch.  The per-tile words live in an array inside the library image instead
- * (about 257 KiB of global memory on every GPU that loads the library, kept until the process exits),
+ * (about 385 KiB of global memory on every GPU that loads the library, kept until the process exits),
  * so this call takes inputs and outputs only and never calls cudaMalloc, cudaFree or any allocating
  * routine.
  *   limit      n <= LZ_NOALLOC_MAX_EDGES (2^26 = 67,108,864 edges); a larger n is rejected with

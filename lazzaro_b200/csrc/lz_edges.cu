@@ -55,6 +55,8 @@ struct PruneParams {
     const int32_t* counts;    // two-pass mode: survivors per tile ...
     const u64* group_sum;     // ... and per group of kGroup tiles; a CTA sums what lies before it (offsets == nullptr)
     float wstar; int use_wstar;   // factor > 0: keep <=> not (w < wstar), see prune_bound()
+    int32_t* loaded;              // streamed form, outputs aliasing inputs: [n_tiles] set once a tile's columns are on chip
+    int check_loaded;
 };
 
 // CHAINED = true: single pass, tile order from an atomic ticket, offsets by decoupled look-back (safe in
@@ -232,9 +234,12 @@ __global__ void __launch_bounds__(kThreads) decay_prune_kernel(PruneParams p) {
 //   compute warps flags from shared memory, block scan, compaction in place in the stage buffer, coalesced
 //                 write-out at the tile's offset, stage handed back
 // Ticket order keeps it deadlock-free: a tile waits only for tiles with smaller tickets, and those are held by
-// CTAs that are running.  When outputs alias inputs (AHEAD = false) a tile's aggregate must not be published
-// before its columns are in shared memory (a later tile may overwrite them once it knows its offset), so there
-// the compute warps publish it after reading the stage and the count warp only draws tickets.
+// CTAs that are running.  When outputs alias inputs, a tile's survivors land in the input ranges of at most two tiles
+// (itself or earlier ones); the compute warps flag a tile once its columns are in shared memory and the offset warp
+// releases an offset only when those two tiles are flagged (the count warp has read a tile's weights before its
+// aggregate is public, and nobody writes before they have seen every earlier aggregate).  AHEAD = false is the
+// earlier in-place form: the compute warps publish the aggregate after reading the stage, the count warp only draws
+// tickets (LZ_PRUNE_INPLACE_OLD=1).
 constexpr int kMaxStages = 8;
 constexpr int kStreamThreads = 512;             // compute threads per CTA of the streamed form (4 edges each)
 constexpr int kStreamWarps = kStreamThreads / 32 + 3;
@@ -451,6 +456,18 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
                 if (closes_wave && lane == 0) st_state(wave_word + w, kFlagPrefix | (u64)(before + sum + total));
                 sum += before;
             }
+            if (AHEAD && p.check_loaded && total > 0 && lane < 2) {
+                // in place: the survivors land in the input ranges of at most two tiles (both <= this one); those must
+                // be on chip in whichever CTA holds them before anything is written over them
+                const long long t_in = (lane == 0 ? sum : sum + total - 1) / TILE;
+                unsigned f = 0;
+                while (true) {
+                    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(f) : "l"(p.loaded + t_in) : "memory");
+                    if (f != 0u) break;
+                    __nanosleep(40);
+                }
+            }
+            __syncwarp();
             if (lane == 0) {
                 e->prefix = sum;
                 if (tile == p.n_tiles - 1) *p.out_kept = sum + total;
@@ -472,6 +489,10 @@ __global__ void __launch_bounds__(THREADS + 96, 2) prune_stream_kernel(PrunePara
             break;
         }
         int* buf = reinterpret_cast<int*>(s_ring) + (size_t)s * 4 * TILE;
+        // in place: from here on nobody needs this tile's columns in global memory any more (the count warp read the
+        // weights before it published the aggregate, and nobody writes before they have seen that)
+        if (AHEAD && p.check_loaded && tid == 0)
+            asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p.loaded + tile), "r"(1u) : "memory");
         const int64_t base = (int64_t)tile * TILE + (int64_t)tid * ITEMS;
         int v_src[ITEMS], v_dst[ITEMS], v_cooc[ITEMS];
         float v_w[ITEMS];
@@ -719,16 +740,25 @@ int launch_stream(PruneParams p, void* scratch, bool aliased, cudaStream_t st) {
         c = g_stream_cfg;
     }
     const int64_t tiles = (p.n + kTile - 1) / kTile;
-    LZ_CUDA(cudaMemsetAsync(scratch, 0, stream_state_words(tiles) * 8, st));
+    static const bool old_in_place = [] { const char* e = getenv("LZ_PRUNE_INPLACE_OLD"); return e && atoi(e) != 0; }();
+    const bool ahead_in_place = aliased && !old_in_place;
+    LZ_CUDA(cudaMemsetAsync(scratch, 0, stream_state_words(tiles) * 8 + (ahead_in_place ? (size_t)tiles * 4 : 0), st));
     p.ticket = (u32*)scratch;
     p.state = (u64*)scratch + 1;
+    p.loaded = (int32_t*)((u64*)scratch + stream_state_words(tiles));
+    p.check_loaded = ahead_in_place ? 1 : 0;
     p.n_tiles = (int)tiles;
     p.use_wstar = prune_bound(p.factor, p.thr, &p.wstar) ? 1 : 0;
     const int sms = lz_sm_count() > 0 ? lz_sm_count() : 148;
     const unsigned grid = (unsigned)min(tiles, (int64_t)sms * c.ctas_per_sm);
     const size_t smem = (size_t)c.stages * 16 * kTile + 8 * kTile;
-    if (aliased) prune_stream_kernel<kStreamThreads, kItemsS, false><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.stages);
-    else prune_stream_kernel<kStreamThreads, kItemsS, true><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.ahead);
+    // in place the counts run ahead too; what a tile must wait for before it writes is that the (at most two) tiles whose
+    // input ranges its survivors land in are on chip (LZ_PRUNE_INPLACE_OLD=1: the earlier form, counts published by the
+    // compute warps once the columns are on chip)
+    if (aliased && old_in_place)
+        prune_stream_kernel<kStreamThreads, kItemsS, false><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.stages);
+    else
+        prune_stream_kernel<kStreamThreads, kItemsS, true><<<grid, kStreamThreads + 96, smem, st>>>(p, c.stages, c.ahead);
     LZ_CUDA(cudaGetLastError());
     return LZ_OK;
 }
@@ -851,7 +881,7 @@ constexpr int64_t kNoAllocMaxEdges = LZ_NOALLOC_MAX_EDGES;                 // 2^
 constexpr int64_t kNoAllocMaxTiles = kNoAllocMaxEdges / kTile;             // 32768 tiles
 }  // namespace
 
-static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocMaxTiles / kWave + 4];   // ~257 KiB
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocMaxTiles + kNoAllocMaxTiles / kWave + 4 + kNoAllocMaxTiles / 2];   // ~385 KiB
 
 namespace {
 std::mutex g_noalloc_mu;

@@ -108,8 +108,8 @@ class EdgeTable:
             if self._scratch is None or self._scratch.numel() < need:
                 self._scratch = torch.empty(need, dtype=torch.uint8, device=self.device)
             # out of place into a second set of columns (then swap): the streamed kernel then counts survivors ahead of
-            # its data path (0.85 of the HBM copy peak); `in_place=True` at construction keeps one copy of the table and
-            # publishes each tile's count only once its columns are on chip (slower, 0.6-0.65)
+            # its data path (0.85 of the HBM copy peak); `in_place=True` at construction keeps one copy of the table: a tile
+            # then also waits until the (at most two) tiles its survivors land on are on chip (0.73 of the copy peak)
             if self._in_place:
                 out = None
             else:
