@@ -414,10 +414,21 @@ def main():
         for _ in range(min(2000, int(250.0 / max(ms_w / 3, 1e-3)))):
             f_dev(); f_loc()
         f_e2e_block(2)
-        ms_d, _ = timed(f_dev, steps)
+        if is_batched and args.lanes:
+            # like the headline: K searches on two lanes, complete when the loop's join() returns
+            def f_dev_lanes(n_):
+                for i in range(n_):
+                    o = sharded.search_device(q, k, lane=i & 1)
+                sharded.join()
+                return o
+            f_dev_lanes(2)
+            ms_d, _ = timed(f_dev_lanes, steps, block=True)
+        else:
+            ms_d, _ = timed(f_dev, steps)
         ms_k, _ = timed(f_loc, steps)
         ms_e, _ = timed(f_e2e_block, steps, block=True)
         out = {"batch": batch, "k": k, "value": batch * 1e3 / (ms_d / steps), "unit": UNIT, "ms_per_step": ms_d / steps, "steps": steps,
+               "issue": "two lanes" if (is_batched and args.lanes) else "one stream",
                "e2e": {"value": batch * 1e3 / (ms_e / steps), "unit": UNIT, "h2d_bytes_per_step": int(batch * store._dim_p * 4),
                        "d2h_bytes_per_step": int(batch * k * 16 + batch * 4), "api": api}}
         if is_batched:
