@@ -1,3 +1,4 @@
+"""Batch-1024 search time and certified fraction under the two certification margins, alternating: python scripts/run_margin2.py [rows]"""
 import os, sys
 sys.path.insert(0, os.path.abspath(os.path.join(os.path.dirname(__file__), "..")))
 import torch
