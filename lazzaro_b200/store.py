@@ -113,7 +113,10 @@ class B200Store:
             raise ValueError("batched_search must be 'auto', 'never' or 'always'")
         self.batched_search = batched_search
         self.min_batch = 8                    # 'auto': query batches this large go to the tensor-core path
-        self.min_rows_small_batch = 500_000   # ... and batches of 2-7 too when the scan is this long (measured: 3.5 vs 5-7 ms at 10M rows)
+        self.min_rows_small_batch = 500_000   # ... and smaller batches too when the scan is this long: the coarse pass reads
+                                              # the fp16 shadow, half the bytes of the float32 rows (10M x 768: one query
+                                              # 3.3 ms against 4.7 ms for the exact scan, 2-7 queries 3.4 against 5-9 ms)
+        self.shadow_for_single_queries = True # False: single queries always take the exact scan (no shadow needed for them)
         self.margin_sigmas = 4.0
         # certification margin of the tensor-core path: "worst_case" = deterministic bound from the measured bf16
         # rounding-error norms of rows and query (valid for any data; the default, because north_star asks for
@@ -559,7 +562,8 @@ class B200Store:
     def _takes_batched_path(self, B: int, k: int, span: int) -> bool:
         return (k <= _lib.BATCHED_MAX_K and
                 (self.batched_search == "always" or
-                 (self.batched_search == "auto" and (B >= self.min_batch or (B >= 2 and span >= self.min_rows_small_batch)))))
+                 (self.batched_search == "auto" and
+                  (B >= self.min_batch or (span >= self.min_rows_small_batch and (B >= 2 or self.shadow_for_single_queries))))))
 
     def _exact_groups(self, B: int):
         gs = 4 if B >= 4 else (2 if B >= 2 else 1)
