@@ -1927,7 +1927,7 @@ ScratchLayout layout(const Plan& pl, int n_queries, int k, int dim, bool with_q1
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t at = off; off = (off + bytes + 255) & ~(size_t)255; return at; };
     const size_t items = (size_t)pl.n_qgroups * pl.cs * (pl.n_slices > 64 ? pl.n_slices : 64);
-    L.q16 = take(with_q16 ? (size_t)n_queries * (dim + 8) * 2 : 0);
+    L.q16 = take(with_q16 ? (size_t)((n_queries + BM - 1) / BM * BM) * (dim + 8) * 2 : 0);      // whole q-tiles (zero rows behind the queries)
     L.eps = take((size_t)n_queries * 8);
     L.gtag = take((size_t)n_queries * 4);
     L.gthr = take((size_t)n_queries * 4);
@@ -2074,6 +2074,7 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
     }
     unsigned char* s = (unsigned char*)scratch;
     __half* q16 = (__half*)(s + L.q16);
+    int q_rows = n_queries;                        // rows of the query-side tensor map
     double* eps = (double*)(s + L.eps);
     int32_t* cert = out_certified ? out_certified : (int32_t*)(s + L.certified);
 
@@ -2091,6 +2092,12 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
         queries_to_shadow_kernel<<<(n_queries + 7) / 8, 256, 0, st>>>(queries, n_queries, dim, q_ld, q16, eps, gtag, gthr,
                                                                     fb_count, want_tag, margin_sigmas, metric, max_row_norm,
                                                                     det_row_err);
+        // the last q-tile is filled up with zero rows in memory, so that no TMA box of the query side reaches out of bounds
+        q_rows = (n_queries + BM - 1) / BM * BM;
+        if (q_rows > n_queries && env_int("LZ_QPAD", 1))
+            LZ_CUDA(cudaMemsetAsync(q16 + (size_t)n_queries * dim_s, 0, (size_t)(q_rows - n_queries) * dim_s * 2, st));
+        else
+            q_rows = n_queries;
     }
     LZ_CUDA(cudaGetLastError());
 
@@ -2103,7 +2110,7 @@ int search_batched_core(const void* shadow, const float* rows, int64_t ld, int d
     // epilogue compacts more often, which stalls the MMA pipeline.  The top-1 tiny-table mode is the one user.)
     if (row_hi > row_lo) {
         CUtensorMap tq, tx;
-        if (int rc = make_tmap(&tq, q16, n_queries, dim_s, BM)) return rc;
+        if (int rc = make_tmap(&tq, q16, q_rows, dim_s, BM)) return rc;
         if (int rc = make_tmap(&tx, shadow, n_rows_total, dim_s, BN / pl.cs)) return rc;
         GemmParams g = {};
         g.n_queries = n_queries; g.n_qtiles = pl.n_qtiles; g.n_slices = pl.n_slices;
