@@ -362,12 +362,14 @@ def main():
                                 "rescoring + fallback launches, no collective) inside the timed loop of back-to-back steps, so peak is "
                                 "the measured SUSTAINED bf16 figure (power-capped loop); frac_of_burst is against the burst figure"}
             ach = by / (ms_per_search * 1e-3) / 1e9
-            return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak, "traffic": None,
+            return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                    "traffic": traffic.get("gemm_topk_kernel_10M_b%d" % batch) if k == 10 else None,
                     "kernel": "gemm_topk_kernel (lz_search_batched), memory-bound regime", "peak_source": peak_src,
                     "algorithmic_bytes_per_launch": by, "certified_fraction": cert, "margin": store.margin,
                     "note": "small batches on a large span go through the fp16 shadow: the coarse pass reads rows*dim*2 bytes, half of "
                             "what the exact float32 scan must read, and the answer is the same (fp64 rescoring + certification); "
-                            "achieved uses the device time of the whole local search"}
+                            "achieved uses the device time of the whole local search; peak is the measured COPY bandwidth (read + "
+                            "write), which a read-only stream can exceed by a few per cent"}
         by = float(n_local) * args.dim * 4 * ((batch + 3) // 4)
         ach = by / (ms_per_search * 1e-3) / 1e9
         return {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
