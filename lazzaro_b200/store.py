@@ -117,6 +117,7 @@ class B200Store:
                                               # the fp16 shadow, half the bytes of the float32 rows (10M x 768: one query
                                               # 3.3 ms against 4.7 ms for the exact scan, 2-7 queries 3.4 against 5-9 ms)
         self.shadow_for_single_queries = True # False: single queries always take the exact scan (no shadow needed for them)
+        self._shadow_oom = False              # the shadow did not fit beside the rows: small batches stay on the exact scan
         self.margin_sigmas = 4.0
         # certification margin of the tensor-core path: "worst_case" = deterministic bound from the measured bf16
         # rounding-error norms of rows and query (valid for any data; the default, because north_star asks for
@@ -563,7 +564,8 @@ class B200Store:
         return (k <= _lib.BATCHED_MAX_K and
                 (self.batched_search == "always" or
                  (self.batched_search == "auto" and
-                  (B >= self.min_batch or (span >= self.min_rows_small_batch and (B >= 2 or self.shadow_for_single_queries))))))
+                  (B >= self.min_batch or (span >= self.min_rows_small_batch and not self._shadow_oom and
+                                           (B >= 2 or self.shadow_for_single_queries))))))
 
     def _exact_groups(self, B: int):
         gs = 4 if B >= 4 else (2 if B >= 2 else 1)
@@ -595,6 +597,15 @@ class B200Store:
         B = queries.shape[0]
         mcode = self._metric if metric is None else _lib.METRICS[metric]
         batched = self._takes_batched_path(B, k, hi - lo)
+        if batched and B < self.min_batch and self.batched_search == "auto":
+            # for small batches the shadow is an accelerator, not a requirement: when it does not fit beside the rows
+            # (+50 % of their bytes) they keep the exact scan — on the GPU, same answer
+            try:
+                self._shadow_for(mcode)
+            except torch.cuda.OutOfMemoryError:
+                self._shadows.pop(mcode, None)
+                self._shadow_oom = True
+                batched = False
         if batched:
             sh = self._shadow_for(mcode)
             need = int(_lib.load().lz_search_batched_scratch_bytes(hi - lo, B, k, self._dim_p))

@@ -309,3 +309,30 @@ def test_single_query_fused_path_equals_the_two_launch_path():
         few = B200Store(metric=metric)
         few.add_nodes([{"id": f"n{i}", "content": "", "embedding": rows[i].tolist()} for i in range(3)])
         assert few.search_nodes(qs[0].tolist(), limit=10) == [f"n{i}" for i in flat_search.flat_topk(rows[:3], qs[0], 3, metric)[0]]
+
+
+def test_small_batches_keep_the_exact_scan_when_the_shadow_does_not_fit(monkeypatch):
+    """A span large enough for single queries to take the fp16 shadow, and a shadow allocation that fails: the search
+    still answers (exact scan on the GPU, same ids as with the shadow) and stops asking for the shadow."""
+    import torch
+    from oracle import flat_search
+    from lazzaro_b200 import store as store_mod, synth
+    from lazzaro_b200.store import B200Store
+    n, dim = 520_000, 32
+    rows_np, _ = synth.clustered_rows(n, dim, 16, seed=77)
+    qs = synth.queries_near_rows(rows_np, 3, seed=78)
+    a = B200Store(); a.adopt_rows(torch.as_tensor(rows_np).cuda(), id_prefix="n")
+    with_shadow = [a.search_nodes(q.tolist(), limit=5) for q in qs]
+    assert a._shadows and not a._shadow_oom                                  # the shadow path was taken
+    b = B200Store(); b.adopt_rows(torch.as_tensor(rows_np).cuda(), id_prefix="n")
+
+    def no_room(self, st):
+        raise torch.cuda.OutOfMemoryError("no room for the shadow (simulated)")
+    monkeypatch.setattr(store_mod._Shadow, "ensure", no_room)
+    without = [b.search_nodes(q.tolist(), limit=5) for q in qs]
+    assert b._shadow_oom and not b._shadows
+    assert without == with_shadow
+    want, _ = flat_search.flat_topk(rows_np, qs[0], 5)
+    assert without[0] == [f"n{r}" for r in want.tolist()]
+    with pytest.raises(torch.cuda.OutOfMemoryError):                          # a real batch needs the shadow: the error stands
+        b.search_batch(np.repeat(qs, 4, axis=0), limit=5)
