@@ -336,3 +336,40 @@ def test_small_batches_keep_the_exact_scan_when_the_shadow_does_not_fit(monkeypa
     assert without[0] == [f"n{r}" for r in want.tolist()]
     with pytest.raises(torch.cuda.OutOfMemoryError):                          # a real batch needs the shadow: the error stands
         b.search_batch(np.repeat(qs, 4, axis=0), limit=5)
+
+
+def test_single_queries_on_a_large_span_follow_adds_and_deletes():
+    """Single queries over 520k rows take the fp16 shadow; rows added and deleted afterwards must show up / disappear exactly
+    as with the exact scan (the shadow is extended for appended rows, tombstones are filtered in the exact pass)."""
+    import torch
+    from oracle import flat_search
+    from lazzaro_b200 import synth
+    from lazzaro_b200.store import B200Store
+    n, dim = 520_000, 32
+    rows_np, _ = synth.clustered_rows(n, dim, 16, seed=91)
+    qs = synth.queries_near_rows(rows_np, 4, seed=92)
+    st = B200Store(); st.adopt_rows(torch.as_tensor(rows_np).cuda(), id_prefix="n")
+    ex = B200Store(); ex.adopt_rows(torch.as_tensor(rows_np).cuda(), id_prefix="n")
+    ex.shadow_for_single_queries = False                                    # the same operations through the exact scan
+    user = st._user_names[0]
+
+    def same():
+        for q in qs:
+            a, b = st.search_nodes(q.tolist(), user, 8), ex.search_nodes(q.tolist(), user, 8)
+            assert a == b and len(a) == 8
+        return st.search_nodes(qs[0].tolist(), user, 8)
+
+    first = same()
+    assert st._shadows and not ex._shadows
+    want, _ = flat_search.flat_topk(rows_np, qs[0], 8)
+    assert first == [f"n{r}" for r in want.tolist()]
+    near = [{"id": f"new{i}", "content": "", "embedding": (qs[0] * (1.0 + 1e-3 * i)).tolist()} for i in range(5)]   # collinear with query 0
+    for s_ in (st, ex):
+        s_.add_nodes(near, user_id=user)
+    after_add = same()
+    assert set(after_add[:5]) == {f"new{i}" for i in range(5)}
+    for s_ in (st, ex):
+        s_.delete_nodes(["new0", "new3", first[0]], user_id=user)
+    after_del = same()
+    assert "new0" not in after_del and "new3" not in after_del and first[0] not in after_del
+    assert {"new1", "new2", "new4"} <= set(after_del)
