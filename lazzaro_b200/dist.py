@@ -236,7 +236,11 @@ def parity_check(n: int = 300_000, dim: int = 128, cases=PARITY_CASES, group=Non
     ss = ShardedSearch(st, row_offset=lo, world=world, group=group)
     norms = K.row_norms(rows)
     out = []
-    for B, k in cases:
+    # every case as the store would route it at this size, then the small-batch cases once more through the fp16 shadow
+    # (what single queries and batches below 8 take on spans of 500k rows or more): same bits either way
+    runs = [(B, k, None) for B, k in cases] + [(B, k, 1) for B, k in cases if B < st.min_batch and k <= _lib.BATCHED_MAX_K]
+    for B, k, small_rows in runs:
+        st.min_rows_small_batch = small_rows if small_rows is not None else 500_000
         q = synth.queries_near_rows_device(rows, B, seed=synth.SEED_QUERY + B)
         ids, sc, cnt = ss.search_device(q, k)
         want_ids, want_sc, want_cnt = K.search_exact(rows, dim, norms, None, q, k, _lib.COSINE)
@@ -248,7 +252,8 @@ def parity_check(n: int = 300_000, dim: int = 128, cases=PARITY_CASES, group=Non
             good = good and bool((owners > 0).all())
         flag = torch.tensor([int(good)], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
-        out.append({"batch": B, "k": k, "ok": bool(int(flag))})
+        out.append({"batch": B, "k": k, "path": "shadow" if (small_rows is not None or B >= st.min_batch) else "exact scan",
+                    "ok": bool(int(flag))})
     st.close()
     return out
 

@@ -17,7 +17,7 @@ dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 res = parity_check()
 if rank == 0:
     for r in res:
-        print(f"B={r['batch']} k={r['k']}:", "OK" if r["ok"] else "MISMATCH", flush=True)
+        print(f"B={r['batch']} k={r['k']} ({r.get('path', '-')}):", "OK" if r["ok"] else "MISMATCH", flush=True)
 dist.barrier()
 dist.destroy_process_group()
 sys.exit(0 if all(r["ok"] for r in res) else 1)
